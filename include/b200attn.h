@@ -1,0 +1,206 @@
+/*
+ * b200attn.h — C-ABI of the B200-native paged decode-attention path.
+ *
+ * This is the drop-in boundary: a shared library with plain
+ * pointers and sizes, no torch types.  Every entry point enqueues work on the
+ * given CUDA stream and returns immediately: no host synchronisation, no
+ * allocation, CUDA-graph capture safe.  All memory is owned by the caller.
+ *
+ * Reference interfaces each entry replaces (paths relative to the reference
+ * tree, microsoft/ltp-sglang):
+ *
+ *   b200attn_kv_store   python/sglang/srt/mem_cache/memory_pool.py:369-407
+ *                       (MHATokenToKVPool.set_kv_buffer: optional div_ by
+ *                       k/v scale, cast to the pool dtype, index_put by loc)
+ *   b200attn_plan       python/sglang/srt/layers/attention/triton_backend.py:160-221
+ *                       (cumsum -> kv_indptr, create_flashinfer_kv_indices_triton
+ *                       layers/attention/utils.py:10-46, get_num_kv_splits :124-158)
+ *   b200attn_decode     python/sglang/srt/layers/attention/triton_ops/decode_attention.py:677-728
+ *                       (decode_attention_fwd: split-KV stage 1 :240-488 + stage 2
+ *                       LSE merge :491-596), and the math of
+ *                       torch_native_backend.py:112-180
+ *   b200attn_merge_states  sgl-kernel/csrc/attention/merge_attn_states.cu:31-204
+ *                       (merge_state_v2: 2-way (o, lse) merge)
+ *
+ * Error convention: 0 on success, a negative B200ATTN_E_* code otherwise.
+ * Nothing is launched when an error is returned.  Launch failures reported by
+ * cudaGetLastError() right after a launch map to B200ATTN_E_CUDA.
+ */
+#ifndef B200ATTN_H_
+#define B200ATTN_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define B200ATTN_ABI_VERSION 1
+
+/* cudaStream_t without pulling in the CUDA headers. */
+typedef void* b200attn_stream_t;
+
+enum {
+  B200ATTN_OK = 0,
+  B200ATTN_E_INVALID = -1,     /* null pointer, negative size, bad enum */
+  B200ATTN_E_UNSUPPORTED = -2, /* shape / dtype combination has no kernel */
+  B200ATTN_E_ALIGN = -3,       /* pointer or stride breaks an alignment rule */
+  B200ATTN_E_CUDA = -4,        /* the CUDA runtime reported a launch error */
+  B200ATTN_E_WORKSPACE = -5    /* plan / workspace buffer too small */
+};
+
+/* Element types. */
+enum {
+  B200ATTN_BF16 = 0,
+  B200ATTN_F16 = 1,
+  B200ATTN_FP8_E4M3 = 2 /* torch.float8_e4m3fn, stored as raw bytes (uint8 pool) */
+};
+
+/* Width of the seq_lens / req_pool_indices arrays (int64 eager, int32 under
+ * CUDA graphs: cuda_graph_runner.py:302-305). */
+enum { B200ATTN_I32 = 0, B200ATTN_I64 = 1 };
+
+/* How kv_store divides by the per-tensor scale before the fp8 cast. */
+enum {
+  B200ATTN_SCALE_NONE = 0,      /* set_kv_buffer called without k_scale/v_scale */
+  B200ATTN_SCALE_TRUE_DIV = 1,  /* x / s in fp32, rounded to the source dtype
+                                   (torch CPU div_, or CUDA div_ by a 0-dim tensor) */
+  B200ATTN_SCALE_RECIP_MUL = 2  /* x * (1.0f / s): what torch's CUDA div_ computes
+                                   when the divisor is a Python float */
+};
+
+/* ------------------------------------------------------------------ */
+/* K1: KV store                                                        */
+/* ------------------------------------------------------------------ */
+typedef struct {
+  /* new K / V of this step: [n_tokens, num_kv_heads, head_dim], last dim
+   * contiguous, strides in ELEMENTS (views into the fused qkv buffer). */
+  void* k;
+  void* v;
+  int64_t k_stride_token, k_stride_head;
+  int64_t v_stride_token, v_stride_head;
+  const int64_t* loc;          /* [n_tokens] pool slot per token (out_cache_loc) */
+  /* pool of one layer: [slots, num_kv_heads, head_dim], contiguous rows. */
+  void* k_pool;
+  void* v_pool;
+  int64_t k_pool_stride_slot;  /* elements (of the pool dtype) between slots */
+  int64_t v_pool_stride_slot;
+  int64_t pool_slots;          /* rows in the pool; a loc outside [0, slots) is skipped */
+  int32_t n_tokens;
+  int32_t num_kv_heads;
+  int32_t head_dim;            /* K head dim */
+  int32_t v_head_dim;          /* V head dim */
+  int32_t src_dtype;           /* B200ATTN_BF16 | B200ATTN_F16 */
+  int32_t pool_dtype;          /* same as src, or B200ATTN_FP8_E4M3 */
+  int32_t scale_mode;          /* B200ATTN_SCALE_*; ignored unless pool is fp8 */
+  int32_t mutate_src;          /* 1: write x/scale back into k/v (div_ is in place) */
+  float k_scale, v_scale;      /* host scales (used when *_scale_ptr is NULL) */
+  const float* k_scale_ptr;    /* optional device 0-dim fp32 scale (layer.k_scale) */
+  const float* v_scale_ptr;
+} b200attn_kv_store_args;
+
+int b200attn_kv_store(const b200attn_kv_store_args* args, b200attn_stream_t stream);
+
+/* ------------------------------------------------------------------ */
+/* K0: plan (once per forward; shared by all layers)                   */
+/* ------------------------------------------------------------------ */
+typedef struct {
+  /* request -> slot map: int32 [max_reqs, stride] (ReqToTokenPool.req_to_token) */
+  const int32_t* req_to_token;
+  int64_t req_to_token_stride; /* elements between rows */
+  const void* req_pool_indices; /* [batch] int32|int64 */
+  const void* seq_lens;         /* [batch] int32|int64, includes the token being decoded */
+  int32_t index_dtype;          /* B200ATTN_I32 | B200ATTN_I64 (both arrays) */
+  int32_t batch;
+  /* shape key of the decode calls that will use this plan */
+  int32_t num_q_heads;
+  int32_t num_kv_heads;
+  int32_t head_dim;
+  int32_t kv_dtype;             /* pool dtype */
+  /* CSR input mode (speculative decode hands kv_indptr/kv_indices in):
+   * when csr_indptr != NULL, req_to_token/req_pool_indices/seq_lens are ignored,
+   * request b reads csr_indices[csr_indptr[b] .. csr_indptr[b+1]). */
+  const int32_t* csr_indptr;
+  /* outputs */
+  int32_t* kv_indptr;           /* optional [batch+1] int32 (bit-exact with torch.cumsum) */
+  int32_t* kv_indices;          /* optional [sum(seq_lens)] int32 (bit-exact with
+                                   create_flashinfer_kv_indices_triton) */
+  void* plan;                   /* opaque, b200attn_plan_bytes(batch) bytes, 16B aligned */
+  size_t plan_bytes;
+  int32_t max_ctas;             /* 0 = one per SM; tests use small values to force splits */
+  int32_t min_chunks_per_cta;   /* 0 = library default */
+} b200attn_plan_args;
+
+size_t b200attn_plan_bytes(int32_t batch);
+int b200attn_plan(const b200attn_plan_args* args, b200attn_stream_t stream);
+
+/* ------------------------------------------------------------------ */
+/* K2 + K3: split-KV decode and LSE merge (once per layer)             */
+/* ------------------------------------------------------------------ */
+typedef struct {
+  const void* q;               /* [batch, num_q_heads, head_dim], strides in elements */
+  int64_t q_stride_batch, q_stride_head;
+  const void* k_pool;          /* [slots, num_kv_heads, head_dim] */
+  const void* v_pool;
+  int64_t k_pool_stride_slot;  /* elements */
+  int64_t v_pool_stride_slot;
+  void* o;                     /* [batch, num_q_heads, v_head_dim], q dtype */
+  int64_t o_stride_batch, o_stride_head;
+  float* lse;                  /* optional [batch, num_q_heads]: ln sum exp(scaled logits) */
+  const void* plan;            /* written by b200attn_plan on the same stream */
+  const int32_t* indices;      /* req_to_token base, or csr kv_indices in CSR mode */
+  float* ws_o;                 /* workspace, b200attn_workspace_bytes() */
+  size_t ws_bytes;
+  int32_t batch;
+  int32_t num_q_heads;
+  int32_t num_kv_heads;
+  int32_t head_dim;
+  int32_t v_head_dim;
+  int32_t q_dtype;             /* B200ATTN_BF16 | B200ATTN_F16 */
+  int32_t kv_dtype;            /* q_dtype or B200ATTN_FP8_E4M3 */
+  float sm_scale;              /* layer.scaling */
+  float logit_cap;             /* 0 disables; cap * tanh(x / cap) otherwise */
+  float k_scale;               /* fp8 dequant: K = fp8 * k_scale (1.0 for 16-bit pools) */
+  float v_scale;
+} b200attn_decode_args;
+
+/* Bytes of split-KV workspace (partial o + lse) for up to `batch` requests. */
+size_t b200attn_workspace_bytes(int32_t batch, int32_t num_q_heads, int32_t num_kv_heads,
+                                int32_t head_dim, int32_t v_head_dim, int32_t kv_dtype);
+int b200attn_decode(const b200attn_decode_args* args, b200attn_stream_t stream);
+
+/* ------------------------------------------------------------------ */
+/* 2-way state merge (merge_state_v2 semantics)                        */
+/* ------------------------------------------------------------------ */
+typedef struct {
+  const void* o_a;             /* [tokens, heads, head_dim] contiguous */
+  const float* lse_a;          /* [tokens, heads] */
+  const void* o_b;
+  const float* lse_b;
+  void* o_out;                 /* [tokens, heads, head_dim] */
+  float* lse_out;              /* optional */
+  int32_t tokens, heads, head_dim;
+  int32_t dtype;               /* B200ATTN_BF16 | B200ATTN_F16 */
+} b200attn_merge_states_args;
+
+int b200attn_merge_states(const b200attn_merge_states_args* args, b200attn_stream_t stream);
+
+/* ------------------------------------------------------------------ */
+/* misc                                                                */
+/* ------------------------------------------------------------------ */
+int b200attn_abi_version(void);
+const char* b200attn_strerror(int code);
+/* Kernels launched by this library in this process (all devices); bench.py
+ * reports the delta over the timed region as "gpu_launches". */
+uint64_t b200attn_launch_count(void);
+/* Decode geometry the library picks for a shape (for tests / DESIGN.md):
+ * out[0]=heads per CTA, out[1]=token slices, out[2]=tokens per chunk,
+ * out[3]=pipeline stages, out[4]=dynamic smem bytes, out[5]=head groups. */
+int b200attn_decode_geometry(int32_t num_q_heads, int32_t num_kv_heads, int32_t head_dim,
+                             int32_t kv_dtype, int32_t out[6]);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* B200ATTN_H_ */

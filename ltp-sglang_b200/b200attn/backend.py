@@ -1,0 +1,255 @@
+"""``B200AttnBackend``: the sm_100a paged decode-attention backend.
+
+Drop-in for the reference's ``AttentionBackend`` plug-in surface
+(python/sglang/srt/layers/attention/base_attn_backend.py:14-117); host logic
+mirrors ``TritonAttnBackend`` (layers/attention/triton_backend.py:41-732):
+
+* ``init_forward_metadata``      one ``plan`` launch per forward (kv_indptr scan,
+  optional kv_indices, split plan) instead of cumsum + Triton index kernel +
+  Triton split heuristic (:160-221);
+* ``forward_decode``             ``kv_store`` + ``decode`` (2 + 1 launches)
+  instead of 2-6 ATen launches + 2 Triton launches (:687-732);
+* CUDA-graph hooks               all buffers are allocated once in ``__init__``,
+  so capture / replay only re-run the plan (:338-627);
+* ``forward_extend``             delegates to a prefill backend, the way
+  ``HybridAttnBackend`` does (layers/attention/hybrid_attn_backend.py:88-100).
+
+Registration in sglang is one ``elif`` in
+``ModelRunner._get_attention_backend_from_str`` (model_runner.py:1374-1460) and
+one choice string (server_args.py:1263-1279); see INTEGRATION.md.
+"""
+from __future__ import annotations
+
+from dataclasses import dataclass
+from typing import Any, Optional
+
+import torch
+
+from . import capi, ops
+from .interfaces import AttentionBackend
+
+
+def store_kv(k_pool: torch.Tensor, v_pool: torch.Tensor, loc: torch.Tensor, cache_k: torch.Tensor,
+             cache_v: torch.Tensor, k_scale=None, v_scale=None) -> None:
+    """``set_kv_buffer`` semantics (memory_pool.py:369-407) on raw layer pools.
+
+    Scales apply only when the pool dtype differs from the source dtype (fp8).
+    A Python float divides the way torch's CUDA ``div_`` does for a CPU scalar
+    (multiply by the fp32 reciprocal); a 0-dim tensor (``layer.k_scale``) is a
+    true fp32 division.  ``cache_k`` / ``cache_v`` are updated in place like
+    ``div_`` does.
+    """
+    if loc.dtype != torch.int64:
+        loc = loc.to(torch.int64)
+    fp8 = k_pool.dtype in (torch.uint8, torch.float8_e4m3fn)
+    ks = vs = kt = vt = None
+    mode = capi.SCALE_NONE
+    if fp8 and (k_scale is not None or v_scale is not None):
+        tensors = isinstance(k_scale, torch.Tensor) or isinstance(v_scale, torch.Tensor)
+        mode = capi.SCALE_TRUE_DIV if tensors else capi.SCALE_RECIP_MUL
+        if tensors:
+            kt = _scale_tensor(k_scale, cache_k.device)
+            vt = _scale_tensor(v_scale, cache_v.device)
+        else:
+            ks = 1.0 if k_scale is None else float(k_scale)
+            vs = 1.0 if v_scale is None else float(v_scale)
+    torch.ops.b200attn.kv_store(cache_k, cache_v, loc, k_pool, v_pool, ks, vs, kt, vt, mode)
+
+
+def _scale_tensor(s, device) -> torch.Tensor:
+    if s is None:
+        return torch.ones((), dtype=torch.float32, device=device)
+    if isinstance(s, torch.Tensor):
+        if s.dtype != torch.float32 or s.device != device:
+            s = s.to(device=device, dtype=torch.float32)
+        return s
+    return torch.full((), float(s), dtype=torch.float32, device=device)
+
+
+@dataclass
+class ForwardMetadata:
+    batch: int
+    indices: torch.Tensor            # req_to_token, or kv_indices in CSR mode
+    kv_indptr: Optional[torch.Tensor]
+    kv_indices: Optional[torch.Tensor]
+
+
+class B200AttnBackend(AttentionBackend):
+    def __init__(self, model_runner: Any, prefill_backend: Optional[AttentionBackend] = None,
+                 materialize_kv_indices: bool = False, max_ctas: int = 0, min_chunks: int = 0,
+                 return_lse: bool = False):
+        super().__init__()
+        capi.lib()  # fail here, loudly, if the CUDA library has not been built
+        self.device = torch.device(model_runner.device)
+        if self.device.type != "cuda":
+            raise RuntimeError("B200AttnBackend needs a CUDA device (sm_100a); there is no CPU path")
+        self.prefill_backend = prefill_backend
+        self.req_to_token = model_runner.req_to_token_pool.req_to_token
+        self.max_bs = model_runner.req_to_token_pool.size
+        self.token_to_kv_pool = model_runner.token_to_kv_pool
+
+        mc = model_runner.model_config
+        try:  # inside sglang the attention TP size is process-global state
+            from sglang.srt.layers.dp_attention import get_attention_tp_size
+
+            tp = int(get_attention_tp_size())
+        except Exception:
+            tp = int(getattr(model_runner, "attention_tp_size", 1) or 1)
+        self.num_head = mc.num_attention_heads // tp
+        self.num_kv_head = mc.get_num_kv_heads(tp)
+        k0 = self.token_to_kv_pool.get_key_buffer(0)
+        v0 = self.token_to_kv_pool.get_value_buffer(0)
+        self.head_dim = k0.shape[-1]
+        self.v_head_dim = v0.shape[-1]
+        self.kv_dtype = ops.dtype_code(k0.dtype)
+        if getattr(model_runner, "sliding_window_size", None):
+            raise NotImplementedError("B200AttnBackend: sliding-window attention is not supported yet")
+        if getattr(mc, "is_encoder_decoder", False):
+            raise NotImplementedError("B200AttnBackend: cross attention is not supported yet")
+        if self.head_dim != self.v_head_dim:
+            raise NotImplementedError("B200AttnBackend: qk_head_dim != v_head_dim is not supported yet")
+        # raises B200AttnError(E_UNSUPPORTED) for shapes without a kernel
+        self.geometry = capi.decode_geometry(self.num_head, self.num_kv_head, self.head_dim, self.kv_dtype)
+
+        self.materialize_kv_indices = materialize_kv_indices
+        self.max_ctas = max_ctas
+        self.min_chunks = min_chunks
+        self.return_lse = return_lse
+        self.max_context_len = getattr(mc, "context_len", self.req_to_token.shape[1])
+
+        dev = self.device
+        self.plan_buf = torch.zeros(ops.plan_bytes(self.max_bs), dtype=torch.uint8, device=dev)
+        ws = ops.workspace_bytes(self.max_bs, self.num_head, self.num_kv_head, self.head_dim,
+                                 self.v_head_dim, self.kv_dtype)
+        self.workspace = torch.empty(ws // 4, dtype=torch.float32, device=dev)
+        self.kv_indptr = torch.zeros(self.max_bs + 1, dtype=torch.int32, device=dev)
+        self.lse = torch.empty(self.max_bs * self.num_head, dtype=torch.float32, device=dev) if return_lse else None
+        self.cuda_graph_kv_indices: Optional[torch.Tensor] = None
+        self.forward_metadata: Optional[ForwardMetadata] = None
+
+    # ------------------------------------------------------------------ #
+    # metadata
+    # ------------------------------------------------------------------ #
+    def _plan(self, bs: int, req_pool_indices: torch.Tensor, seq_lens: torch.Tensor,
+              seq_lens_sum: Optional[int], spec_info: Any, graph: bool) -> None:
+        if bs > self.max_bs:
+            raise ValueError(f"batch {bs} exceeds req_to_token_pool.size {self.max_bs}")
+        if spec_info is not None:
+            kv_indptr, kv_indices = spec_info.kv_indptr, spec_info.kv_indices
+            torch.ops.b200attn.plan_csr(kv_indptr, self.plan_buf, self.num_head, self.num_kv_head,
+                                        self.head_dim, self.kv_dtype, self.max_ctas, self.min_chunks)
+            self.forward_metadata = ForwardMetadata(kv_indptr.numel() - 1, kv_indices, kv_indptr, kv_indices)
+            return
+        kv_indices = None
+        if self.materialize_kv_indices:
+            if graph:
+                kv_indices = self.cuda_graph_kv_indices
+            else:
+                if seq_lens_sum is None:
+                    seq_lens_sum = int(seq_lens[:bs].sum().item())
+                kv_indices = torch.empty(seq_lens_sum, dtype=torch.int32, device=self.device)
+        torch.ops.b200attn.plan(self.req_to_token, req_pool_indices[:bs], seq_lens[:bs], self.plan_buf,
+                                self.kv_indptr, kv_indices, self.num_head, self.num_kv_head,
+                                self.head_dim, self.kv_dtype, self.max_ctas, self.min_chunks)
+        self.forward_metadata = ForwardMetadata(bs, self.req_to_token, self.kv_indptr[: bs + 1], kv_indices)
+
+    def init_forward_metadata(self, forward_batch):
+        mode = forward_batch.forward_mode
+        if mode.is_decode_or_idle():
+            if forward_batch.batch_size == 0:
+                self.forward_metadata = ForwardMetadata(0, self.req_to_token, self.kv_indptr[:1], None)
+                return
+            self._plan(forward_batch.batch_size, forward_batch.req_pool_indices, forward_batch.seq_lens,
+                       forward_batch.seq_lens_sum, forward_batch.spec_info, graph=False)
+        else:
+            self._prefill().init_forward_metadata(forward_batch)
+
+    def init_cuda_graph_state(self, max_bs: int, max_num_tokens: int):
+        if self.materialize_kv_indices:
+            self.cuda_graph_kv_indices = torch.zeros(max_num_tokens * self.max_context_len,
+                                                     dtype=torch.int32, device=self.device)
+        if self.prefill_backend is not None and hasattr(self.prefill_backend, "init_cuda_graph_state"):
+            try:
+                self.prefill_backend.init_cuda_graph_state(max_bs, max_num_tokens)
+            except NotImplementedError:
+                pass
+
+    def init_forward_metadata_capture_cuda_graph(self, bs, num_tokens, req_pool_indices, seq_lens,
+                                                 encoder_lens, forward_mode, spec_info):
+        assert encoder_lens is None, "cross attention is not supported"
+        if not forward_mode.is_decode_or_idle():
+            return self._prefill().init_forward_metadata_capture_cuda_graph(
+                bs, num_tokens, req_pool_indices, seq_lens, encoder_lens, forward_mode, spec_info)
+        self._plan(bs, req_pool_indices, seq_lens, None, spec_info, graph=True)
+
+    def init_forward_metadata_replay_cuda_graph(self, bs, req_pool_indices, seq_lens, seq_lens_sum,
+                                                encoder_lens, forward_mode, spec_info, seq_lens_cpu):
+        if not forward_mode.is_decode_or_idle():
+            return self._prefill().init_forward_metadata_replay_cuda_graph(
+                bs, req_pool_indices, seq_lens, seq_lens_sum, encoder_lens, forward_mode, spec_info,
+                seq_lens_cpu)
+        self._plan(bs, req_pool_indices, seq_lens, seq_lens_sum, spec_info, graph=True)
+
+    def get_cuda_graph_seq_len_fill_value(self):
+        return 1
+
+    # ------------------------------------------------------------------ #
+    # forward
+    # ------------------------------------------------------------------ #
+    def forward_decode(self, q, k, v, layer, forward_batch, save_kv_cache: bool = True):
+        if getattr(layer, "is_cross_attention", False):
+            raise NotImplementedError("B200AttnBackend: cross attention is not supported")
+        sw = getattr(layer, "sliding_window_size", -1)
+        if sw is not None and sw > -1:
+            raise NotImplementedError("B200AttnBackend: sliding-window layers are not supported")
+        if layer.qk_head_dim != layer.v_head_dim:
+            raise NotImplementedError("B200AttnBackend: qk_head_dim != v_head_dim is not supported")
+
+        q = q.reshape(-1, layer.tp_q_head_num * layer.qk_head_dim)
+        o = torch.empty_like(q)
+        pool = forward_batch.token_to_kv_pool
+        start = getattr(pool, "start_layer", 0) or 0
+        k_pool = pool.k_buffer[layer.layer_id - start]
+        v_pool = pool.v_buffer[layer.layer_id - start]
+        if save_kv_cache and k is not None:
+            store_kv(k_pool, v_pool, forward_batch.out_cache_loc,
+                     k.view(-1, layer.tp_k_head_num, layer.qk_head_dim),
+                     v.view(-1, layer.tp_v_head_num, layer.v_head_dim),
+                     getattr(layer, "k_scale", None), getattr(layer, "v_scale", None))
+        md = self.forward_metadata
+        bs = q.shape[0]
+        if bs == 0:
+            return o
+        if md is None or md.batch != bs:
+            raise RuntimeError("B200AttnBackend.forward_decode: init_forward_metadata was not run for this batch")
+        k_scale = getattr(layer, "k_scale_float", None)
+        v_scale = getattr(layer, "v_scale_float", None)
+        fp8 = self.kv_dtype == capi.FP8_E4M3
+        torch.ops.b200attn.decode(
+            q.view(bs, layer.tp_q_head_num, layer.qk_head_dim), k_pool, v_pool,
+            o.view(bs, layer.tp_q_head_num, layer.v_head_dim),
+            self.lse[: bs * self.num_head] if self.lse is not None else None,
+            self.plan_buf, md.indices, self.workspace, float(layer.scaling),
+            float(getattr(layer, "logit_cap", 0.0) or 0.0),
+            float(k_scale) if (fp8 and k_scale is not None) else 1.0,
+            float(v_scale) if (fp8 and v_scale is not None) else 1.0)
+        return o
+
+    def last_lse(self, bs: int) -> torch.Tensor:
+        """ln sum exp(scaled logits) of the most recent forward_decode, ``[bs, heads]``."""
+        if self.lse is None:
+            raise RuntimeError("construct the backend with return_lse=True")
+        return self.lse[: bs * self.num_head].view(bs, self.num_head)
+
+    def forward_extend(self, q, k, v, layer, forward_batch, save_kv_cache: bool = True):
+        return self._prefill().forward_extend(q, k, v, layer, forward_batch, save_kv_cache=save_kv_cache)
+
+    def _prefill(self) -> AttentionBackend:
+        if self.prefill_backend is None:
+            raise NotImplementedError(
+                "B200AttnBackend implements decode; construct it with prefill_backend=<an extend-capable "
+                "backend> (or use --prefill-attention-backend) for EXTEND / MIXED / speculative modes")
+        return self.prefill_backend
+
+    def support_triton(self):
+        return True

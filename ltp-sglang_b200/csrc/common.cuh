@@ -1,0 +1,244 @@
+// Shared host/device definitions of the b200attn library: decode geometry,
+// the plan buffer layout, and small PTX wrappers (mbarrier, bulk copy,
+// ldmatrix, mma).  sm_100a only.
+#pragma once
+
+#include <cuda_bf16.h>
+#include <cuda_fp16.h>
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include "b200attn.h"
+
+namespace b200attn {
+
+// ---------------------------------------------------------------------------
+// Decode geometry.  One persistent CTA per SM: 8 consumer warps + 1 producer
+// warp.  A CTA serves `hc` kv heads of one "virtual request" (request x head
+// group); consumer warp w = (head w % hc, token slice w / hc).  A chunk is
+// 16 * ts tokens; each token row of the chunk (hc heads, contiguous in the
+// pool) is moved HBM -> smem by one bulk async copy (UBLKCP) into a row padded
+// by 16 B so ldmatrix over 8 consecutive tokens is bank-conflict free.
+// ---------------------------------------------------------------------------
+constexpr int kConsumerWarps = 8;
+constexpr int kThreads = (kConsumerWarps + 1) * 32;
+constexpr int kRowPad = 16;           // bytes
+constexpr int kBarrierBytes = 256;    // mbarrier area at the start of smem
+constexpr int kMaxStages = 8;
+constexpr int kMaxSmem = 227 * 1024;
+constexpr int kMaxCtas = 1024;
+constexpr int kMaxRowBytes = 2048;    // per token row per tensor staged by one CTA
+
+struct Geometry {
+  int hc;            // kv heads per CTA
+  int ts;            // token slices (consumer warps per head)
+  int ng;            // head groups = num_kv_heads / hc
+  int group;         // q heads per kv head
+  int chunk_tokens;  // 16 * ts
+  int row_bytes;     // hc * head_dim * elem
+  int row_stride;    // row_bytes + pad
+  int stage_bytes;   // K + V
+  int stages;
+  int smem_bytes;
+};
+
+__host__ __device__ inline int elem_bytes(int dtype) { return dtype == B200ATTN_FP8_E4M3 ? 1 : 2; }
+
+// Returns false when the shape has no kernel.
+inline bool make_geometry(int hq, int hkv, int d, int kv_dtype, Geometry* g) {
+  if (hq <= 0 || hkv <= 0 || hq % hkv != 0) return false;
+  if (d != 64 && d != 128 && d != 256) return false;
+  int group = hq / hkv;
+  if (group > 16) return false;
+  int e = elem_bytes(kv_dtype);
+  int hc = 8;
+  while (hc > 1 && (hkv % hc != 0 || hc * d * e > kMaxRowBytes)) hc >>= 1;
+  if (hc * d * e > kMaxRowBytes) return false;
+  g->hc = hc;
+  g->ts = kConsumerWarps / hc;
+  g->ng = hkv / hc;
+  g->group = group;
+  g->chunk_tokens = 16 * g->ts;
+  g->row_bytes = hc * d * e;
+  g->row_stride = g->row_bytes + kRowPad;
+  g->stage_bytes = 2 * g->chunk_tokens * g->row_stride;
+  int stages = (kMaxSmem - kBarrierBytes) / g->stage_bytes;
+  if (stages > kMaxStages) stages = kMaxStages;
+  if (stages < 2) return false;
+  g->stages = stages;
+  g->smem_bytes = kBarrierBytes + stages * g->stage_bytes;
+  return true;
+}
+
+// ---------------------------------------------------------------------------
+// Plan buffer layout (device memory, written by plan_kernel, read by the
+// decode and merge kernels).  All offsets are derived from `batch`.
+// ---------------------------------------------------------------------------
+struct PlanHeader {
+  int32_t magic;
+  int32_t batch;
+  int32_t ng;              // head groups
+  int32_t chunk_tokens;
+  int32_t total_chunks;    // ng * sum_b ceil(S_b / chunk_tokens)
+  int32_t chunks_per_cta;
+  int32_t n_cta;           // CTAs that own at least the slot (c * chunks_per_cta < total)
+  int32_t csr_mode;
+  int32_t total_tokens;    // sum_b S_b
+  int32_t pad[7];
+};
+static_assert(sizeof(PlanHeader) == 64, "PlanHeader is 64 bytes");
+constexpr int32_t kPlanMagic = 0x42323030;  // "B200"
+
+struct PlanView {
+  PlanHeader* hdr;
+  int32_t* seq_len;       // [batch]
+  int32_t* chunk_prefix;  // [batch + 1] exclusive prefix of ceil(S_b / T)
+  int64_t* row_off;       // [batch] element offset of request b's index row
+  int32_t* cta_start;     // [kMaxCtas] first virtual request of CTA c
+};
+
+__host__ __device__ inline size_t align_up(size_t x, size_t a) { return (x + a - 1) / a * a; }
+
+__host__ __device__ inline size_t plan_bytes_for(int batch) {
+  size_t n = sizeof(PlanHeader);
+  n += align_up((size_t)batch * 4, 16);        // seq_len
+  n += align_up((size_t)(batch + 1) * 4, 16);  // chunk_prefix
+  n += align_up((size_t)batch * 8, 16);        // row_off
+  n += (size_t)kMaxCtas * 4;                   // cta_start
+  return n;
+}
+
+__host__ __device__ inline PlanView plan_view(void* base, int batch) {
+  PlanView v;
+  char* p = reinterpret_cast<char*>(base);
+  v.hdr = reinterpret_cast<PlanHeader*>(p);
+  p += sizeof(PlanHeader);
+  v.seq_len = reinterpret_cast<int32_t*>(p);
+  p += align_up((size_t)batch * 4, 16);
+  v.chunk_prefix = reinterpret_cast<int32_t*>(p);
+  p += align_up((size_t)(batch + 1) * 4, 16);
+  v.row_off = reinterpret_cast<int64_t*>(p);
+  p += align_up((size_t)batch * 8, 16);
+  v.cta_start = reinterpret_cast<int32_t*>(p);
+  return v;
+}
+
+// Workspace: partial outputs.  Piece (virtual request v, CTA c) has id v + c
+// (unique because both only grow along the chunk sequence); each piece holds
+// ts slices of [hq_per_vreq, dv] fp32 plus [hq_per_vreq] lse.
+inline size_t workspace_floats(int batch, int hq, int dv, const Geometry& g, int n_cta,
+                               size_t* lse_off) {
+  size_t pieces = (size_t)batch * g.ng + n_cta;
+  size_t rows = pieces * g.ts * (size_t)(hq / g.ng);
+  if (lse_off) *lse_off = rows * dv;
+  return rows * dv + rows;
+}
+
+int sm_count();        // SMs of the current device (148 when there is no device)
+void count_launch();   // bumps the process-wide launch counter
+
+#ifdef __CUDACC__
+// ---------------------------------------------------------------------------
+// PTX wrappers
+// ---------------------------------------------------------------------------
+__device__ __forceinline__ uint32_t smem_u32(const void* p) {
+  return static_cast<uint32_t>(__cvta_generic_to_shared(p));
+}
+
+__device__ __forceinline__ void mbar_init(uint32_t bar, uint32_t count) {
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(bar), "r"(count) : "memory");
+}
+
+__device__ __forceinline__ void mbar_arrive(uint32_t bar) {
+  asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(bar) : "memory");
+}
+
+__device__ __forceinline__ void mbar_arrive_expect_tx(uint32_t bar, uint32_t bytes) {
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes)
+               : "memory");
+}
+
+__device__ __forceinline__ bool mbar_try_wait(uint32_t bar, uint32_t parity) {
+  uint32_t ok;
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t"
+      "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+      "selp.u32 %0, 1, 0, p;\n\t}"
+      : "=r"(ok)
+      : "r"(bar), "r"(parity)
+      : "memory");
+  return ok != 0;
+}
+
+__device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
+  while (!mbar_try_wait(bar, parity)) {
+  }
+}
+
+// 1-D bulk async copy global -> shared (TMA engine, SASS UBLKCP); completion is
+// signalled on an mbarrier as a transaction byte count.  16 B granularity.
+__device__ __forceinline__ void bulk_g2s(uint32_t dst, const void* src, uint32_t bytes,
+                                         uint32_t bar) {
+  asm volatile(
+      "cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::
+          "r"(dst),
+      "l"(src), "r"(bytes), "r"(bar)
+      : "memory");
+}
+
+__device__ __forceinline__ void fence_proxy_async() {
+  asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+}
+
+__device__ __forceinline__ void fence_barrier_init() {
+  asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+}
+
+__device__ __forceinline__ void ldsm_x4(uint32_t addr, uint32_t (&r)[4]) {
+  asm volatile("ldmatrix.sync.aligned.m8n8.x4.shared.b16 {%0,%1,%2,%3}, [%4];"
+               : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3])
+               : "r"(addr));
+}
+
+__device__ __forceinline__ void ldsm_x4_trans(uint32_t addr, uint32_t (&r)[4]) {
+  asm volatile("ldmatrix.sync.aligned.m8n8.x4.trans.shared.b16 {%0,%1,%2,%3}, [%4];"
+               : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3])
+               : "r"(addr));
+}
+
+// D(16x8, f32) += A(16x16) * B(16x8).  HALF selects f16 vs bf16 operands.
+template <bool HALF>
+__device__ __forceinline__ void mma16816(float (&d)[4], uint32_t a0, uint32_t a1, uint32_t a2,
+                                         uint32_t a3, uint32_t b0, uint32_t b1) {
+  if constexpr (HALF) {
+    asm volatile(
+        "mma.sync.aligned.m16n8k16.row.col.f32.f16.f16.f32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, "
+        "{%8,%9}, {%0,%1,%2,%3};"
+        : "+f"(d[0]), "+f"(d[1]), "+f"(d[2]), "+f"(d[3])
+        : "r"(a0), "r"(a1), "r"(a2), "r"(a3), "r"(b0), "r"(b1));
+  } else {
+    asm volatile(
+        "mma.sync.aligned.m16n8k16.row.col.f32.bf16.bf16.f32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, "
+        "{%8,%9}, {%0,%1,%2,%3};"
+        : "+f"(d[0]), "+f"(d[1]), "+f"(d[2]), "+f"(d[3])
+        : "r"(a0), "r"(a1), "r"(a2), "r"(a3), "r"(b0), "r"(b1));
+  }
+}
+
+// Two e4m3 bytes (low 16 bits of x) -> f16x2, exact.
+__device__ __forceinline__ uint32_t e4m3x2_to_f16x2(uint32_t x) {
+  uint32_t r;
+  asm("{\n\t.reg .b16 t;\n\tcvt.u16.u32 t, %1;\n\tcvt.rn.f16x2.e4m3x2 %0, t;\n\t}"
+      : "=r"(r)
+      : "r"(x));
+  return r;
+}
+
+__device__ __forceinline__ float fast_exp2(float x) {
+  float y;
+  asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+  return y;
+}
+#endif  // __CUDACC__
+
+}  // namespace b200attn

@@ -1,0 +1,522 @@
+// K2: split-KV GQA decode, persistent, warp-specialised (sm_100a).
+//
+// Replaces the reference's Triton stage-1 kernels
+// (python/sglang/srt/layers/attention/triton_ops/decode_attention.py:44-169
+// MHA, :240-401 grouped) and computes the math of the torch_native oracle
+// (layers/attention/torch_native_backend.py:112-180).
+//
+// Layout of one CTA (288 threads, 1 CTA / SM, grid = SM count):
+//   warp 8      producer: reads slot indices (req_to_token row or kv_indices)
+//               one chunk ahead, and issues one bulk async copy (TMA engine,
+//               SASS UBLKCP) per token row for K and for V into a ring of smem
+//               stages; completion is counted in bytes on a "full" mbarrier.
+//   warps 0..7  consumers: warp (h, slice) owns kv head h of the CTA's head
+//               group and 16 tokens of every chunk.  All `group` q heads that
+//               share the kv head ride in the M dimension of one
+//               mma.sync.m16n8k16 tile, so every K/V byte is read from HBM and
+//               from smem once.  Online softmax in registers (quad shuffles),
+//               P stays in registers as the A operand of P.V.
+// The chunk sequence of the whole batch is cut into equal per-CTA ranges by
+// plan_kernel; a CTA therefore streams its share of the KV bytes with a single
+// pipeline fill, whatever the mix of request lengths.  A range that ends
+// inside a request leaves a normalised partial (o, lse) in the workspace for
+// merge_kernel; a request that fits one range is written straight to `o`.
+#pragma once
+
+#include <math_constants.h>
+
+#include "common.cuh"
+
+namespace b200attn {
+
+struct DecodeParams {
+  const void* q;
+  int64_t q_sb, q_sh;            // elements
+  const uint8_t* k_pool;
+  const uint8_t* v_pool;
+  int64_t k_slot_bytes, v_slot_bytes;
+  void* o;
+  int64_t o_sb, o_sh;            // elements
+  float* lse;                    // optional [batch, hq]
+  const void* plan;
+  const int32_t* indices;
+  float* ws_o;
+  float* ws_lse;
+  int32_t batch, hq;
+  int32_t hc, ts, ng, group;
+  int32_t row_bytes, row_stride, stage_bytes, stages, chunk_tokens;
+  float scale_log2;              // sm_scale * k_scale * log2(e)
+  float sm_scale_k;              // sm_scale * k_scale
+  float logit_cap;
+  float v_scale;
+};
+
+constexpr float kLog2e = 1.4426950408889634f;
+constexpr float kLn2 = 0.6931471805599453f;
+
+template <bool HALF>
+__device__ __forceinline__ uint32_t pack2(float lo, float hi) {
+  if constexpr (HALF) {
+    __half2 h = __floats2half2_rn(lo, hi);
+    return *reinterpret_cast<uint32_t*>(&h);
+  } else {
+    __nv_bfloat162 h = __floats2bfloat162_rn(lo, hi);
+    return *reinterpret_cast<uint32_t*>(&h);
+  }
+}
+
+__device__ __forceinline__ float q_to_f32(__nv_bfloat16 x) { return __bfloat162float(x); }
+__device__ __forceinline__ float q_to_f32(__half x) { return __half2float(x); }
+__device__ __forceinline__ void store_q(__nv_bfloat16* p, float x) { *p = __float2bfloat16_rn(x); }
+__device__ __forceinline__ void store_q(__half* p, float x) { *p = __float2half_rn(x); }
+
+// S-tile MMA with the Q fragment: q = {a0, a2} (+ {a1, a3} for 16 valid rows).
+template <bool HALF, bool ROWS16, int QR>
+__device__ __forceinline__ void mma_q(float (&d)[4], const uint32_t (&q)[QR], uint32_t b0,
+                                      uint32_t b1) {
+  if constexpr (ROWS16) {
+    mma16816<HALF>(d, q[0], q[2], q[1], q[3], b0, b1);
+  } else {
+    mma16816<HALF>(d, q[0], 0u, q[1], 0u, b0, b1);
+  }
+}
+
+// Walks the (virtual request, local chunk range) pieces of one CTA's range.
+struct PieceWalk {
+  int v, g, g1, ng;
+  __device__ __forceinline__ bool next(const PlanView& pv, int& b, int& hg, int& lc0, int& lc1,
+                                       int& nchunks, int& vreq) {
+    while (g < g1) {
+      b = v / ng;
+      hg = v - b * ng;
+      const int cp0 = pv.chunk_prefix[b];
+      const int n = pv.chunk_prefix[b + 1] - cp0;
+      const int vstart = ng * cp0 + hg * n;
+      const int vend = vstart + n;
+      if (vend <= g) {
+        ++v;
+        continue;
+      }
+      lc0 = g - vstart;
+      lc1 = (vend < g1 ? vend : g1) - vstart;
+      nchunks = n;
+      vreq = v;
+      g = vstart + lc1;
+      ++v;
+      return true;
+    }
+    return false;
+  }
+};
+
+template <typename QT, bool FP8, int D, bool ROWS16>
+__global__ void __launch_bounds__(kThreads, 1) decode_kernel(const DecodeParams p) {
+  constexpr bool HALF = FP8 || std::is_same<QT, __half>::value;
+  constexpr int KSTEPS = D / 16;       // k16 steps of Q.K^T
+  constexpr int NTILES = D / 8;        // n8 tiles of P.V
+  constexpr int QR = ROWS16 ? 4 : 2;   // A-fragment registers per k-step actually loaded
+  constexpr int EB = FP8 ? 1 : 2;      // KV element bytes
+
+  extern __shared__ __align__(128) uint8_t smem[];
+  const PlanView pv = plan_view(const_cast<void*>(p.plan), p.batch);
+  const int cta = blockIdx.x;
+  const int per = pv.hdr->chunks_per_cta;
+  const int total = pv.hdr->total_chunks;
+  if (static_cast<int64_t>(cta) * per >= total) return;
+  const int g0 = cta * per;
+  const int g1 = g0 + per < total ? g0 + per : total;
+
+  const uint32_t bar_full = smem_u32(smem);
+  const uint32_t bar_empty = bar_full + kMaxStages * 8;
+  const uint32_t stage0 = bar_full + kBarrierBytes;
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+
+  if (threadIdx.x == 0) {
+    for (int s = 0; s < p.stages; ++s) {
+      mbar_init(bar_full + s * 8, 1);
+      mbar_init(bar_empty + s * 8, kConsumerWarps);
+    }
+    fence_barrier_init();
+  }
+  __syncthreads();
+
+  const int T = p.chunk_tokens;
+  const uint32_t v_off = T * p.row_stride;  // V rows follow the K rows of a stage
+  PieceWalk walk{pv.cta_start[cta], g0, g1, p.ng};
+  int b, hg, lc0, lc1, nchunks, vreq;
+  int stage = 0;
+  uint32_t phase = 0;
+
+  if (warp == kConsumerWarps) {
+    // ------------------------------ producer ------------------------------
+    while (walk.next(pv, b, hg, lc0, lc1, nchunks, vreq)) {
+      const int S = pv.seq_len[b];
+      const int32_t* idx = p.indices + pv.row_off[b];
+      const uint8_t* kb = p.k_pool + static_cast<int64_t>(hg) * p.row_bytes;
+      const uint8_t* vb = p.v_pool + static_cast<int64_t>(hg) * p.row_bytes;
+      int32_t nxt[4];
+#pragma unroll
+      for (int r = 0; r < 4; ++r) {
+        const int t = lc0 * T + lane + 32 * r;
+        nxt[r] = (lane + 32 * r < T && t < S) ? idx[t] : 0;
+      }
+      for (int lc = lc0; lc < lc1; ++lc) {
+        int32_t cur[4];
+#pragma unroll
+        for (int r = 0; r < 4; ++r) cur[r] = nxt[r];
+        if (lc + 1 < lc1) {  // index prefetch, one chunk ahead of the copies
+#pragma unroll
+          for (int r = 0; r < 4; ++r) {
+            const int t = (lc + 1) * T + lane + 32 * r;
+            nxt[r] = (lane + 32 * r < T && t < S) ? idx[t] : 0;
+          }
+        }
+        const int t0 = lc * T;
+        const int nvalid = S - t0 < T ? S - t0 : T;
+        mbar_wait(bar_empty + stage * 8, phase ^ 1);
+        const uint32_t full = bar_full + stage * 8;
+        if (lane == 0) mbar_arrive_expect_tx(full, static_cast<uint32_t>(nvalid) * 2u * p.row_bytes);
+        __syncwarp();
+        const uint32_t kdst = stage0 + stage * p.stage_bytes;
+#pragma unroll
+        for (int r = 0; r < 4; ++r) {
+          const int i = lane + 32 * r;
+          if (i < nvalid) {
+            const int64_t slot = cur[r];
+            bulk_g2s(kdst + i * p.row_stride, kb + slot * p.k_slot_bytes, p.row_bytes, full);
+            bulk_g2s(kdst + v_off + i * p.row_stride, vb + slot * p.v_slot_bytes, p.row_bytes, full);
+          }
+        }
+        if (++stage == p.stages) {
+          stage = 0;
+          phase ^= 1;
+        }
+      }
+    }
+    return;
+  }
+
+  // -------------------------------- consumers --------------------------------
+  const int h = warp % p.hc;
+  const int tsi = warp / p.hc;
+  const int gq = lane >> 2, jq = lane & 3;     // MMA fragment coordinates
+  const int mat = lane >> 3, mr = lane & 7;    // ldmatrix: matrix id, row
+  const bool cap = p.logit_cap > 0.f;
+  const float c = cap ? kLog2e : p.scale_log2;
+  const float cap_pre = cap ? p.sm_scale_k / p.logit_cap : 0.f;
+
+  // lane-constant parts of the ldmatrix addresses (bytes inside a stage)
+  uint32_t k_lane, v_lane;
+  if constexpr (!FP8) {
+    k_lane = (tsi * 16 + mr) * p.row_stride + h * D * 2 + mat * 16;
+    v_lane = (tsi * 16 + (mat & 1) * 8 + mr) * p.row_stride + h * D * 2 + (mat >> 1) * 16;
+  } else {
+    k_lane = (tsi * 16 + mr) * p.row_stride + h * D + mat * 16;
+    v_lane = (tsi * 16 + (mat & 1) * 8 + mr) * p.row_stride + h * D + (mat >> 1) * 16;
+  }
+  v_lane += v_off;
+
+  while (walk.next(pv, b, hg, lc0, lc1, nchunks, vreq)) {
+    const int S = pv.seq_len[b];
+    const int hq0 = (hg * p.hc + h) * p.group;
+    const bool row0 = gq < p.group;
+    const bool row1 = ROWS16 && (gq + 8 < p.group);
+
+    // ---- Q fragments (A operand), loaded once per piece ----
+    uint32_t qf[KSTEPS][QR];
+    {
+      const QT* q0 = reinterpret_cast<const QT*>(p.q) + b * p.q_sb + (hq0 + gq) * p.q_sh;
+      const QT* q1 = q0 + 8 * p.q_sh;
+#pragma unroll
+      for (int kk = 0; kk < KSTEPS; ++kk) {
+        if constexpr (!FP8) {
+          const int d0 = kk * 16 + 2 * jq;
+          qf[kk][0] = row0 ? *reinterpret_cast<const uint32_t*>(q0 + d0) : 0u;
+          qf[kk][1] = row0 ? *reinterpret_cast<const uint32_t*>(q0 + d0 + 8) : 0u;
+          if constexpr (ROWS16) {
+            qf[kk][2] = row1 ? *reinterpret_cast<const uint32_t*>(q1 + d0) : 0u;
+            qf[kk][3] = row1 ? *reinterpret_cast<const uint32_t*>(q1 + d0 + 8) : 0u;
+          }
+        } else {
+          // fp8 K: MMA k-slot (2j, 2j+1, 2j+8, 2j+9) of step kk <-> d = 16kk + 4j + (0..3)
+          const int d0 = kk * 16 + 4 * jq;
+          float f[4] = {0.f, 0.f, 0.f, 0.f};
+          if (row0) {
+#pragma unroll
+            for (int e = 0; e < 4; ++e) f[e] = fminf(fmaxf(q_to_f32(q0[d0 + e]), -65504.f), 65504.f);
+          }
+          qf[kk][0] = pack2<true>(f[0], f[1]);
+          qf[kk][1] = pack2<true>(f[2], f[3]);
+          if constexpr (ROWS16) {
+            float f1[4] = {0.f, 0.f, 0.f, 0.f};
+            if (row1) {
+#pragma unroll
+              for (int e = 0; e < 4; ++e) f1[e] = fminf(fmaxf(q_to_f32(q1[d0 + e]), -65504.f), 65504.f);
+            }
+            qf[kk][2] = pack2<true>(f1[0], f1[1]);
+            qf[kk][3] = pack2<true>(f1[2], f1[3]);
+          }
+        }
+      }
+    }
+
+    float o[NTILES][QR];
+#pragma unroll
+    for (int n = 0; n < NTILES; ++n)
+#pragma unroll
+      for (int e = 0; e < QR; ++e) o[n][e] = 0.f;
+    float m0 = -CUDART_INF_F, m1 = -CUDART_INF_F, l0 = 0.f, l1 = 0.f;
+
+    for (int lc = lc0; lc < lc1; ++lc) {
+      mbar_wait(bar_full + stage * 8, phase);
+      const uint32_t sbase = stage0 + stage * p.stage_bytes;
+
+      // ---- S = Q.K^T for 16 tokens (two n8 tiles) ----
+      float s[2][4];
+#pragma unroll
+      for (int nt = 0; nt < 2; ++nt) {
+        s[nt][0] = s[nt][1] = s[nt][2] = s[nt][3] = 0.f;
+        const uint32_t ka = sbase + k_lane + nt * 8 * p.row_stride;
+        if constexpr (!FP8) {
+#pragma unroll
+          for (int k2 = 0; k2 < KSTEPS / 2; ++k2) {
+            uint32_t kf[4];
+            ldsm_x4(ka + k2 * 64, kf);
+            mma_q<HALF, ROWS16, QR>(s[nt], qf[2 * k2], kf[0], kf[1]);
+            mma_q<HALF, ROWS16, QR>(s[nt], qf[2 * k2 + 1], kf[2], kf[3]);
+          }
+        } else {
+#pragma unroll
+          for (int k4 = 0; k4 < KSTEPS / 4; ++k4) {
+            uint32_t kf[4];
+            ldsm_x4(ka + k4 * 64, kf);
+#pragma unroll
+            for (int mm = 0; mm < 4; ++mm) {
+              const int kk = 4 * k4 + mm;
+              const uint32_t b0 = e4m3x2_to_f16x2(kf[mm]);
+              const uint32_t b1 = e4m3x2_to_f16x2(kf[mm] >> 16);
+              mma_q<true, ROWS16, QR>(s[nt], qf[kk], b0, b1);
+            }
+          }
+        }
+      }
+
+      // ---- logit cap, tail mask ----
+      if (cap) {
+#pragma unroll
+        for (int nt = 0; nt < 2; ++nt)
+#pragma unroll
+          for (int e = 0; e < 4; ++e) s[nt][e] = p.logit_cap * tanhf(s[nt][e] * cap_pre);
+      }
+      const int tok0 = lc * T + tsi * 16 + 2 * jq;  // token of s[0][0]
+      const bool tail = (lc + 1) * T > S;
+      if (tail) {
+#pragma unroll
+        for (int nt = 0; nt < 2; ++nt)
+#pragma unroll
+          for (int e = 0; e < 4; ++e)
+            if (tok0 + nt * 8 + (e & 1) >= S) s[nt][e] = -CUDART_INF_F;
+      }
+
+      // ---- online softmax (rows gq and, for wide groups, gq + 8) ----
+      float mx0 = fmaxf(fmaxf(s[0][0], s[0][1]), fmaxf(s[1][0], s[1][1]));
+      mx0 = fmaxf(mx0, __shfl_xor_sync(0xffffffffu, mx0, 1));
+      mx0 = fmaxf(mx0, __shfl_xor_sync(0xffffffffu, mx0, 2));
+      const float mn0 = fmaxf(m0, mx0);
+      const float mr0 = mn0 == -CUDART_INF_F ? 0.f : mn0;
+      const float corr0 = fast_exp2((m0 - mr0) * c);
+      m0 = mn0;
+      const float mc0 = mr0 * c;
+      float pr[2][4];
+      pr[0][0] = fast_exp2(fmaf(s[0][0], c, -mc0));
+      pr[0][1] = fast_exp2(fmaf(s[0][1], c, -mc0));
+      pr[1][0] = fast_exp2(fmaf(s[1][0], c, -mc0));
+      pr[1][1] = fast_exp2(fmaf(s[1][1], c, -mc0));
+      l0 = fmaf(l0, corr0, (pr[0][0] + pr[0][1]) + (pr[1][0] + pr[1][1]));
+      float corr1 = 1.f;
+      if constexpr (ROWS16) {
+        float mx1 = fmaxf(fmaxf(s[0][2], s[0][3]), fmaxf(s[1][2], s[1][3]));
+        mx1 = fmaxf(mx1, __shfl_xor_sync(0xffffffffu, mx1, 1));
+        mx1 = fmaxf(mx1, __shfl_xor_sync(0xffffffffu, mx1, 2));
+        const float mn1 = fmaxf(m1, mx1);
+        const float mr1 = mn1 == -CUDART_INF_F ? 0.f : mn1;
+        corr1 = fast_exp2((m1 - mr1) * c);
+        m1 = mn1;
+        const float mc1 = mr1 * c;
+        pr[0][2] = fast_exp2(fmaf(s[0][2], c, -mc1));
+        pr[0][3] = fast_exp2(fmaf(s[0][3], c, -mc1));
+        pr[1][2] = fast_exp2(fmaf(s[1][2], c, -mc1));
+        pr[1][3] = fast_exp2(fmaf(s[1][3], c, -mc1));
+        l1 = fmaf(l1, corr1, (pr[0][2] + pr[0][3]) + (pr[1][2] + pr[1][3]));
+      }
+      if (__any_sync(0xffffffffu, corr0 != 1.f || corr1 != 1.f)) {
+#pragma unroll
+        for (int n = 0; n < NTILES; ++n) {
+          o[n][0] *= corr0;
+          o[n][1] *= corr0;
+          if constexpr (ROWS16) {
+            o[n][2] *= corr1;
+            o[n][3] *= corr1;
+          }
+        }
+      }
+
+      // ---- P (A operand) ----
+      const uint32_t pa0 = pack2<HALF>(pr[0][0], pr[0][1]);
+      const uint32_t pa2 = pack2<HALF>(pr[1][0], pr[1][1]);
+      uint32_t pa1 = 0u, pa3 = 0u;
+      if constexpr (ROWS16) {
+        pa1 = pack2<HALF>(pr[0][2], pr[0][3]);
+        pa3 = pack2<HALF>(pr[1][2], pr[1][3]);
+      }
+      // V fragments of masked tail tokens are zeroed: the smem rows behind them
+      // hold stale bytes of another request (0 * inf would poison this one).
+      uint32_t vm0 = 0xffffffffu, vm1 = 0xffffffffu;
+      if (tail) {
+        vm0 = (tok0 < S ? 0x0000ffffu : 0u) | (tok0 + 1 < S ? 0xffff0000u : 0u);
+        vm1 = (tok0 + 8 < S ? 0x0000ffffu : 0u) | (tok0 + 9 < S ? 0xffff0000u : 0u);
+      }
+
+      // ---- O += P.V ----
+      const uint32_t va = sbase + v_lane;
+      if constexpr (!FP8) {
+#pragma unroll
+        for (int n2 = 0; n2 < NTILES / 2; ++n2) {
+          uint32_t vf[4];
+          ldsm_x4_trans(va + n2 * 32, vf);
+          if constexpr (ROWS16) {
+            mma16816<HALF>(o[2 * n2], pa0, pa1, pa2, pa3, vf[0] & vm0, vf[1] & vm1);
+            mma16816<HALF>(o[2 * n2 + 1], pa0, pa1, pa2, pa3, vf[2] & vm0, vf[3] & vm1);
+          } else {
+            float d0[4] = {o[2 * n2][0], o[2 * n2][1], 0.f, 0.f};
+            mma16816<HALF>(d0, pa0, 0u, pa2, 0u, vf[0] & vm0, vf[1] & vm1);
+            o[2 * n2][0] = d0[0];
+            o[2 * n2][1] = d0[1];
+            float d1[4] = {o[2 * n2 + 1][0], o[2 * n2 + 1][1], 0.f, 0.f};
+            mma16816<HALF>(d1, pa0, 0u, pa2, 0u, vf[2] & vm0, vf[3] & vm1);
+            o[2 * n2 + 1][0] = d1[0];
+            o[2 * n2 + 1][1] = d1[1];
+          }
+        }
+      } else {
+        // fp8 V: one x4.trans covers 32 d; a b16 transpose leaves each register
+        // with {tok 2j: d, d+1 | tok 2j+1: d, d+1}; PRMT regroups by d parity.
+#pragma unroll
+        for (int n4 = 0; n4 < NTILES / 4; ++n4) {
+          uint32_t vf[4];
+          ldsm_x4_trans(va + n4 * 32, vf);
+#pragma unroll
+          for (int gg = 0; gg < 2; ++gg) {
+#pragma unroll
+            for (int par = 0; par < 2; ++par) {
+              const uint32_t sel = par ? 0x4431u : 0x4420u;
+              const uint32_t b0 = e4m3x2_to_f16x2(__byte_perm(vf[2 * gg], 0u, sel)) & vm0;
+              const uint32_t b1 = e4m3x2_to_f16x2(__byte_perm(vf[2 * gg + 1], 0u, sel)) & vm1;
+              const int n = n4 * 4 + gg * 2 + par;
+              if constexpr (ROWS16) {
+                mma16816<true>(o[n], pa0, pa1, pa2, pa3, b0, b1);
+              } else {
+                float d0[4] = {o[n][0], o[n][1], 0.f, 0.f};
+                mma16816<true>(d0, pa0, 0u, pa2, 0u, b0, b1);
+                o[n][0] = d0[0];
+                o[n][1] = d0[1];
+              }
+            }
+          }
+        }
+      }
+
+      __syncwarp();
+      if (lane == 0) mbar_arrive(bar_empty + stage * 8);
+      if (++stage == p.stages) {
+        stage = 0;
+        phase ^= 1;
+      }
+    }
+
+    // ---- epilogue: normalise, write final o or a partial ----
+    l0 += __shfl_xor_sync(0xffffffffu, l0, 1);
+    l0 += __shfl_xor_sync(0xffffffffu, l0, 2);
+    const float inv0 = l0 > 0.f ? p.v_scale / l0 : 0.f;
+    const float lse0 = l0 > 0.f ? m0 * c * kLn2 + logf(l0) : -CUDART_INF_F;
+    float inv1 = 0.f, lse1 = -CUDART_INF_F;
+    if constexpr (ROWS16) {
+      l1 += __shfl_xor_sync(0xffffffffu, l1, 1);
+      l1 += __shfl_xor_sync(0xffffffffu, l1, 2);
+      inv1 = l1 > 0.f ? p.v_scale / l1 : 0.f;
+      lse1 = l1 > 0.f ? m1 * c * kLn2 + logf(l1) : -CUDART_INF_F;
+    }
+    const bool whole = p.ts == 1 && lc0 == 0 && lc1 == nchunks;
+    // column (head-dim index) of accumulator element e (0/1) of tile n
+    auto col_of = [&](int n, int e) -> int {
+      if constexpr (!FP8) return n * 8 + 2 * jq + e;
+      return (n >> 1) * 16 + 4 * jq + 2 * e + (n & 1);
+    };
+    if (whole) {
+      QT* o0 = reinterpret_cast<QT*>(p.o) + b * p.o_sb + (hq0 + gq) * p.o_sh;
+      if (row0) {
+#pragma unroll
+        for (int n = 0; n < NTILES; ++n) {
+          store_q(o0 + col_of(n, 0), o[n][0] * inv0);
+          store_q(o0 + col_of(n, 1), o[n][1] * inv0);
+        }
+        if (p.lse && jq == 0) p.lse[static_cast<int64_t>(b) * p.hq + hq0 + gq] = lse0;
+      }
+      if constexpr (ROWS16) {
+        if (row1) {
+          QT* o1 = o0 + 8 * p.o_sh;
+#pragma unroll
+          for (int n = 0; n < NTILES; ++n) {
+            store_q(o1 + col_of(n, 0), o[n][2] * inv1);
+            store_q(o1 + col_of(n, 1), o[n][3] * inv1);
+          }
+          if (p.lse && jq == 0) p.lse[static_cast<int64_t>(b) * p.hq + hq0 + gq + 8] = lse1;
+        }
+      }
+    } else {
+      const int hqv = p.hc * p.group;
+      const int64_t row = (static_cast<int64_t>(vreq + cta) * p.ts + tsi) * hqv + h * p.group + gq;
+      if (row0) {
+        float* w = p.ws_o + row * D;
+#pragma unroll
+        for (int n = 0; n < NTILES; ++n) {
+          w[col_of(n, 0)] = o[n][0] * inv0;
+          w[col_of(n, 1)] = o[n][1] * inv0;
+        }
+        if (jq == 0) p.ws_lse[row] = lse0;
+      }
+      if constexpr (ROWS16) {
+        if (row1) {
+          float* w = p.ws_o + (row + 8) * D;
+#pragma unroll
+          for (int n = 0; n < NTILES; ++n) {
+            w[col_of(n, 0)] = o[n][2] * inv1;
+            w[col_of(n, 1)] = o[n][3] * inv1;
+          }
+          if (jq == 0) p.ws_lse[row + 8] = lse1;
+        }
+      }
+    }
+  }
+}
+
+template <typename QT, bool FP8>
+cudaError_t launch_decode(const DecodeParams& p, int head_dim, bool rows16, int grid, int smem,
+                          cudaStream_t stream);
+
+#define B200ATTN_DEFINE_LAUNCH(QT, FP8)                                                          \
+  template <>                                                                                    \
+  cudaError_t launch_decode<QT, FP8>(const DecodeParams& p, int head_dim, bool rows16, int grid, \
+                                     int smem, cudaStream_t stream) {                            \
+    void (*fn)(const DecodeParams) = nullptr;                                                    \
+    if (head_dim == 64) fn = rows16 ? decode_kernel<QT, FP8, 64, true> : decode_kernel<QT, FP8, 64, false>;        \
+    else if (head_dim == 128) fn = rows16 ? decode_kernel<QT, FP8, 128, true> : decode_kernel<QT, FP8, 128, false>; \
+    else if (head_dim == 256) fn = rows16 ? decode_kernel<QT, FP8, 256, true> : decode_kernel<QT, FP8, 256, false>; \
+    if (!fn) return cudaErrorInvalidValue;                                                       \
+    cudaError_t e = cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, smem); \
+    if (e != cudaSuccess) return e;                                                              \
+    fn<<<grid, kThreads, smem, stream>>>(p);                                                     \
+    return cudaGetLastError();                                                                   \
+  }
+
+}  // namespace b200attn

@@ -1,0 +1,139 @@
+// K3: LSE merge of the split-KV partials (stage 2), and the stand-alone 2-way
+// state merge.
+//
+// Reference: _fwd_kernel_stage2,
+// python/sglang/srt/layers/attention/triton_ops/decode_attention.py:491-552
+// (online merge: m' = max(m, lse_i), acc = acc e^{m-m'} + e^{lse_i-m'} o_i);
+// merge_state_v2, sgl-kernel/csrc/attention/merge_attn_states.cu:31-106.
+#include <math_constants.h>
+
+#include "merge.cuh"
+
+namespace b200attn {
+
+// One warp per (request, q head).  Pieces of virtual request v live at
+// workspace rows ((v + c) * ts + slice) * hqv + head_in_vreq, for every CTA c
+// whose chunk range intersects the request.
+template <typename QT>
+__global__ void __launch_bounds__(128) merge_kernel(const MergeParams p) {
+  const PlanView pv = plan_view(const_cast<void*>(p.plan), p.batch);
+  const int warp_global = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+  const int lane = threadIdx.x & 31;
+  if (warp_global >= p.batch * p.hq) return;
+  const int b = warp_global / p.hq;
+  const int hq = warp_global - b * p.hq;
+  const int hqv = p.hq / p.ng;
+  const int hg = hq / hqv;
+  const int hl = hq - hg * hqv;
+  const int v = b * p.ng + hg;
+  const int cp0 = pv.chunk_prefix[b];
+  const int n = pv.chunk_prefix[b + 1] - cp0;
+  QT* out = reinterpret_cast<QT*>(p.o) + b * p.o_sb + hq * p.o_sh;
+  if (n == 0) {  // empty request: defined output, no pieces were written
+    for (int d = lane; d < p.dv; d += 32) out[d] = QT(0.f);
+    if (p.lse && lane == 0) p.lse[static_cast<int64_t>(b) * p.hq + hq] = -CUDART_INF_F;
+    return;
+  }
+  const int per = pv.hdr->chunks_per_cta;
+  const int vstart = p.ng * cp0 + hg * n;
+  const int c_first = vstart / per;
+  const int c_last = (vstart + n - 1) / per;
+  if (p.ts == 1 && c_first == c_last) return;  // decode_kernel wrote o directly
+
+  const int np = (c_last - c_first + 1) * p.ts;
+  const int64_t row0 = (static_cast<int64_t>(v + c_first) * p.ts) * hqv + hl;
+  // rows of consecutive partials are hqv apart
+  float mx = -CUDART_INF_F;
+  for (int i = lane; i < np; i += 32) mx = fmaxf(mx, p.ws_lse[row0 + static_cast<int64_t>(i) * hqv]);
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, o));
+  if (mx == -CUDART_INF_F) {
+    for (int d = lane; d < p.dv; d += 32) out[d] = QT(0.f);
+    if (p.lse && lane == 0) p.lse[static_cast<int64_t>(b) * p.hq + hq] = -CUDART_INF_F;
+    return;
+  }
+  float sum = 0.f;
+  for (int i = 0; i < np; ++i) sum += __expf(p.ws_lse[row0 + static_cast<int64_t>(i) * hqv] - mx);
+  const float inv = 1.f / sum;
+  for (int d = lane; d < p.dv; d += 32) {
+    float acc = 0.f;
+    for (int i = 0; i < np; ++i) {
+      const int64_t row = row0 + static_cast<int64_t>(i) * hqv;
+      const float w = __expf(p.ws_lse[row] - mx);
+      acc = fmaf(w, p.ws_o[row * p.dv + d], acc);
+    }
+    out[d] = QT(acc * inv);
+  }
+  if (p.lse && lane == 0) p.lse[static_cast<int64_t>(b) * p.hq + hq] = mx + logf(sum);
+}
+
+template __global__ void merge_kernel<__nv_bfloat16>(const MergeParams);
+template __global__ void merge_kernel<__half>(const MergeParams);
+
+cudaError_t launch_merge(const MergeParams& p, bool half, cudaStream_t stream) {
+  const int warps = p.batch * p.hq;
+  const int blocks = (warps + 3) / 4;
+  if (half) merge_kernel<__half><<<blocks, 128, 0, stream>>>(p);
+  else merge_kernel<__nv_bfloat16><<<blocks, 128, 0, stream>>>(p);
+  return cudaGetLastError();
+}
+
+// 2-way merge; one thread per 8-element pack.  +inf lse counts as -inf
+// (merge_attn_states.cu:68-69).
+template <typename QT>
+__global__ void __launch_bounds__(128) merge_states_kernel(const QT* __restrict__ oa,
+                                                          const float* __restrict__ la,
+                                                          const QT* __restrict__ ob,
+                                                          const float* __restrict__ lb,
+                                                          QT* __restrict__ out,
+                                                          float* __restrict__ lout, int tokens,
+                                                          int heads, int dim) {
+  const int packs = dim / 8;
+  const int64_t i = blockIdx.x * static_cast<int64_t>(blockDim.x) + threadIdx.x;
+  if (i >= static_cast<int64_t>(tokens) * heads * packs) return;
+  const int64_t th = i / packs;
+  const int pk = static_cast<int>(i - th * packs);
+  float a = la[th], b = lb[th];
+  if (isinf(a)) a = -CUDART_INF_F;
+  if (isinf(b)) b = -CUDART_INF_F;
+  const float mx = fmaxf(a, b);
+  const float ea = expf(a - mx), eb = expf(b - mx);
+  const float se = ea + eb;
+  const float wa = ea / se, wb = eb / se;
+  const int64_t off = th * dim + pk * 8;
+  QT xa[8], xb[8], y[8];
+  *reinterpret_cast<uint4*>(xa) = *reinterpret_cast<const uint4*>(oa + off);
+  *reinterpret_cast<uint4*>(xb) = *reinterpret_cast<const uint4*>(ob + off);
+#pragma unroll
+  for (int e = 0; e < 8; ++e) y[e] = QT(float(xa[e]) * wa + float(xb[e]) * wb);
+  *reinterpret_cast<uint4*>(out + off) = *reinterpret_cast<const uint4*>(y);
+  if (lout && pk == 0) lout[th] = logf(se) + mx;
+}
+
+}  // namespace b200attn
+
+using namespace b200attn;
+
+extern "C" __attribute__((visibility("default"))) int b200attn_merge_states(const b200attn_merge_states_args* a, b200attn_stream_t s_) {
+  if (!a || !a->o_a || !a->o_b || !a->lse_a || !a->lse_b || !a->o_out) return B200ATTN_E_INVALID;
+  if (a->tokens < 0 || a->heads <= 0 || a->head_dim <= 0) return B200ATTN_E_INVALID;
+  if (a->head_dim % 8 != 0) return B200ATTN_E_UNSUPPORTED;
+  if (a->dtype != B200ATTN_BF16 && a->dtype != B200ATTN_F16) return B200ATTN_E_UNSUPPORTED;
+  if ((reinterpret_cast<uintptr_t>(a->o_a) | reinterpret_cast<uintptr_t>(a->o_b) |
+       reinterpret_cast<uintptr_t>(a->o_out)) & 15)
+    return B200ATTN_E_ALIGN;
+  if (a->tokens == 0) return B200ATTN_OK;
+  const int64_t n = static_cast<int64_t>(a->tokens) * a->heads * (a->head_dim / 8);
+  const unsigned blocks = static_cast<unsigned>((n + 127) / 128);
+  cudaStream_t s = static_cast<cudaStream_t>(s_);
+  if (a->dtype == B200ATTN_BF16)
+    merge_states_kernel<__nv_bfloat16><<<blocks, 128, 0, s>>>(
+        static_cast<const __nv_bfloat16*>(a->o_a), a->lse_a, static_cast<const __nv_bfloat16*>(a->o_b),
+        a->lse_b, static_cast<__nv_bfloat16*>(a->o_out), a->lse_out, a->tokens, a->heads, a->head_dim);
+  else
+    merge_states_kernel<__half><<<blocks, 128, 0, s>>>(
+        static_cast<const __half*>(a->o_a), a->lse_a, static_cast<const __half*>(a->o_b), a->lse_b,
+        static_cast<__half*>(a->o_out), a->lse_out, a->tokens, a->heads, a->head_dim);
+  count_launch();
+  return cudaGetLastError() == cudaSuccess ? B200ATTN_OK : B200ATTN_E_CUDA;
+}

@@ -1,0 +1,222 @@
+// K0: plan.  One launch per forward (all layers share it): scans seq_lens into
+// kv_indptr (bit-exact with torch.cumsum, triton_backend.py:172), optionally
+// flattens req_to_token rows into kv_indices (bit-exact with
+// create_flashinfer_kv_indices_triton, layers/attention/utils.py:10-46), and
+// cuts the chunk sequence of the whole batch into equal per-CTA ranges for the
+// persistent decode kernel.  This replaces the reference's per-request split
+// heuristic (get_num_kv_splits_triton, triton_backend.py:875-924): any split
+// plan gives the same math, so the plan is built for 148 SMs instead.
+// Everything runs on the device: no host sync, CUDA-graph safe.
+#include "common.cuh"
+
+namespace b200attn {
+
+struct PlanParams {
+  const int32_t* req_to_token;
+  int64_t r2t_stride;
+  const void* req_pool_indices;
+  const void* seq_lens;
+  const int32_t* csr_indptr;
+  int32_t* kv_indptr;
+  void* plan;
+  int32_t idx64;
+  int32_t batch;
+  int32_t ng;
+  int32_t chunk_tokens;
+  int32_t max_ctas;
+  int32_t min_chunks;
+};
+
+constexpr int kPlanThreads = 1024;
+
+__device__ __forceinline__ int64_t load_idx(const void* p, int i, int idx64) {
+  return idx64 ? reinterpret_cast<const int64_t*>(p)[i]
+               : static_cast<int64_t>(reinterpret_cast<const int32_t*>(p)[i]);
+}
+
+// Block-wide inclusive scan of one int per thread (1024 threads).
+__device__ __forceinline__ int block_scan_incl(int v, int* warp_sums) {
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+#pragma unroll
+  for (int o = 1; o < 32; o <<= 1) {
+    int t = __shfl_up_sync(0xffffffffu, v, o);
+    if (lane >= o) v += t;
+  }
+  if (lane == 31) warp_sums[warp] = v;
+  __syncthreads();
+  if (warp == 0) {
+    int w = warp_sums[lane];
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+      int t = __shfl_up_sync(0xffffffffu, w, o);
+      if (lane >= o) w += t;
+    }
+    warp_sums[lane] = w;
+  }
+  __syncthreads();
+  if (warp > 0) v += warp_sums[warp - 1];
+  __syncthreads();
+  return v;
+}
+
+__global__ void __launch_bounds__(kPlanThreads) plan_kernel(PlanParams p) {
+  __shared__ int warp_sums[32];
+  __shared__ int carry_tok, carry_chunk;
+  PlanView pv = plan_view(p.plan, p.batch);
+  const int tid = threadIdx.x;
+  if (tid == 0) {
+    carry_tok = 0;
+    carry_chunk = 0;
+    pv.chunk_prefix[0] = 0;
+    if (p.kv_indptr) p.kv_indptr[0] = 0;
+  }
+  __syncthreads();
+
+  const int T = p.chunk_tokens;
+  for (int base = 0; base < p.batch; base += kPlanThreads) {
+    const int b = base + tid;
+    int s = 0;
+    int64_t row = 0;
+    if (b < p.batch) {
+      if (p.csr_indptr) {
+        const int lo = p.csr_indptr[b];
+        s = p.csr_indptr[b + 1] - lo;
+        row = lo;
+      } else {
+        int64_t sl = load_idx(p.seq_lens, b, p.idx64);
+        s = sl < 0 ? 0 : static_cast<int>(sl);
+        row = load_idx(p.req_pool_indices, b, p.idx64) * p.r2t_stride;
+      }
+      if (s < 0) s = 0;
+    }
+    const int nch = (s + T - 1) / T;
+    const int tok_incl = block_scan_incl(s, warp_sums);
+    const int ch_incl = block_scan_incl(nch, warp_sums);
+    if (b < p.batch) {
+      pv.seq_len[b] = s;
+      pv.row_off[b] = row;
+      pv.chunk_prefix[b + 1] = carry_chunk + ch_incl;
+      if (p.kv_indptr) p.kv_indptr[b + 1] = carry_tok + tok_incl;
+    }
+    __syncthreads();
+    if (tid == kPlanThreads - 1) {
+      carry_tok += tok_incl;
+      carry_chunk += ch_incl;
+    }
+    __syncthreads();
+  }
+
+  // chunk_prefix[] was written by this block: make it visible to all threads.
+  __threadfence_block();
+  __syncthreads();
+
+  const int total = carry_chunk * p.ng;
+  int per = (total + p.max_ctas - 1) / p.max_ctas;
+  if (per < p.min_chunks) per = p.min_chunks;
+  if (per < 1) per = 1;
+  const int n_cta = (total + per - 1) / per;
+  if (tid == 0) {
+    PlanHeader h;
+    h.magic = kPlanMagic;
+    h.batch = p.batch;
+    h.ng = p.ng;
+    h.chunk_tokens = T;
+    h.total_chunks = total;
+    h.chunks_per_cta = per;
+    h.n_cta = n_cta;
+    h.csr_mode = p.csr_indptr != nullptr;
+    h.total_tokens = carry_tok;
+#pragma unroll
+    for (int i = 0; i < 7; ++i) h.pad[i] = 0;
+    *pv.hdr = h;
+  }
+
+  // First virtual request (b * ng + hg) of every CTA: the one whose chunk
+  // range contains chunk c * per.  Virtual request (b, hg) starts at
+  // ng * prefix[b] + hg * n_b.
+  for (int c = tid; c < p.max_ctas; c += kPlanThreads) {
+    int start = p.batch * p.ng;
+    const int64_t g0 = static_cast<int64_t>(c) * per;
+    if (g0 < total) {
+      int lo = 0, hi = p.batch;  // largest b with ng * prefix[b] <= g0
+      while (hi - lo > 1) {
+        const int mid = (lo + hi) >> 1;
+        if (static_cast<int64_t>(pv.chunk_prefix[mid]) * p.ng <= g0) lo = mid; else hi = mid;
+      }
+      const int nb = pv.chunk_prefix[lo + 1] - pv.chunk_prefix[lo];
+      const int hg = nb > 0 ? static_cast<int>((g0 - static_cast<int64_t>(pv.chunk_prefix[lo]) * p.ng) / nb) : 0;
+      start = lo * p.ng + hg;
+    }
+    pv.cta_start[c] = start;
+  }
+}
+
+// kv_indices[kv_indptr[b] + j] = req_to_token[req_pool_indices[b], j]
+__global__ void __launch_bounds__(256) kv_indices_kernel(const int32_t* __restrict__ r2t,
+                                                        const void* plan_base, int batch,
+                                                        const int32_t* __restrict__ kv_indptr,
+                                                        int32_t* __restrict__ out) {
+  PlanView pv = plan_view(const_cast<void*>(plan_base), batch);
+  for (int b = blockIdx.x; b < batch; b += gridDim.x) {
+    const int s = pv.seq_len[b];
+    const int32_t* row = r2t + pv.row_off[b];
+    int32_t* dst = out + kv_indptr[b];
+    for (int j = threadIdx.x; j < s; j += blockDim.x) dst[j] = row[j];
+  }
+}
+
+}  // namespace b200attn
+
+using namespace b200attn;
+
+extern "C" __attribute__((visibility("default"))) size_t b200attn_plan_bytes(int32_t batch) {
+  if (batch < 0) return 0;
+  return plan_bytes_for(batch);
+}
+
+extern "C" __attribute__((visibility("default"))) int b200attn_plan(const b200attn_plan_args* a, b200attn_stream_t stream_) {
+  if (!a || !a->plan || a->batch < 0) return B200ATTN_E_INVALID;
+  if (a->batch == 0) return B200ATTN_OK;
+  const bool csr = a->csr_indptr != nullptr;
+  if (!csr && (!a->req_to_token || !a->req_pool_indices || !a->seq_lens)) return B200ATTN_E_INVALID;
+  if (a->index_dtype != B200ATTN_I32 && a->index_dtype != B200ATTN_I64) return B200ATTN_E_INVALID;
+  if (a->kv_indices && (csr || !a->kv_indptr)) return B200ATTN_E_INVALID;
+  if (reinterpret_cast<uintptr_t>(a->plan) % 16 != 0) return B200ATTN_E_ALIGN;
+  if (a->plan_bytes < plan_bytes_for(a->batch)) return B200ATTN_E_WORKSPACE;
+  Geometry g;
+  if (!make_geometry(a->num_q_heads, a->num_kv_heads, a->head_dim, a->kv_dtype, &g))
+    return B200ATTN_E_UNSUPPORTED;
+
+  PlanParams p;
+  p.req_to_token = a->req_to_token;
+  p.r2t_stride = a->req_to_token_stride;
+  p.req_pool_indices = a->req_pool_indices;
+  p.seq_lens = a->seq_lens;
+  p.csr_indptr = a->csr_indptr;
+  p.kv_indptr = a->kv_indptr;
+  p.plan = a->plan;
+  p.idx64 = a->index_dtype == B200ATTN_I64;
+  p.batch = a->batch;
+  p.ng = g.ng;
+  p.chunk_tokens = g.chunk_tokens;
+  int n = sm_count();
+  if (a->max_ctas > 0 && a->max_ctas < n) n = a->max_ctas;
+  if (n > kMaxCtas) n = kMaxCtas;
+  p.max_ctas = n;
+  // Default floor: >= 64 tokens per piece so the partial write-out stays small
+  // next to the KV bytes a piece streams.
+  p.min_chunks = a->min_chunks_per_cta > 0 ? a->min_chunks_per_cta : (64 + g.chunk_tokens - 1) / g.chunk_tokens;
+
+  cudaStream_t stream = static_cast<cudaStream_t>(stream_);
+  plan_kernel<<<1, kPlanThreads, 0, stream>>>(p);
+  count_launch();
+  if (cudaGetLastError() != cudaSuccess) return B200ATTN_E_CUDA;
+  if (a->kv_indices) {
+    int blocks = a->batch < sm_count() * 8 ? a->batch : sm_count() * 8;
+    kv_indices_kernel<<<blocks, 256, 0, stream>>>(a->req_to_token, a->plan, a->batch, a->kv_indptr,
+                                                  a->kv_indices);
+    count_launch();
+    if (cudaGetLastError() != cudaSuccess) return B200ATTN_E_CUDA;
+  }
+  return B200ATTN_OK;
+}

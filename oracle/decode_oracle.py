@@ -1,0 +1,268 @@
+"""CPU oracle for the paged decode-attention path.  TEST INFRASTRUCTURE ONLY.
+
+A plain numpy / torch-CPU restatement of what the reference computes on this
+path.  Only ``tests/``, ``__graft_entry__.smoke()`` and ``bench.py``'s
+``cpu_baseline`` / ``--impl reference`` leg may import this module; the product
+(``ltp-sglang_b200/``) never does.
+
+Parity status: PINNED.  ``tests/golden/*.npz`` were produced by running the
+reference's own Python (``TorchNativeAttnBackend.forward_decode`` +
+``MHATokenToKVPool.set_kv_buffer``, imported from the read-only reference tree
+by ``tests/golden/make_golden.py``) and ``tests/test_oracle.py`` checks every
+function below against them; the fp8 cast is additionally checked against
+torch's own ``.to(float8_e4m3fn)`` on all 65536 bf16 bit patterns.
+
+What each function follows (paths relative to the reference tree):
+
+* ``kv_store``            python/sglang/srt/mem_cache/memory_pool.py:369-407
+* ``kv_indices``          python/sglang/srt/layers/attention/utils.py:10-46 and
+                          test/srt/test_create_kvindices.py:43-49 (the Python gather
+                          the reference's own test uses as ground truth)
+* ``decode_attention``    python/sglang/srt/layers/attention/torch_native_backend.py:112-180
+                          (per-request gather + softmax(scale q.K^T) V), in float64,
+                          plus lse = ln sum exp(scale q.K^T) as defined by
+                          triton_ops/decode_attention.py:385-401
+* ``torch_native_decode`` the same loop through torch SDPA in the model dtype (what the
+                          reference backend literally executes; used as the timed CPU port)
+* ``merge_states``        sgl-kernel/csrc/attention/merge_attn_states.cu:31-106
+"""
+from __future__ import annotations
+
+from typing import Optional, Tuple
+
+import numpy as np
+import torch
+
+# --------------------------------------------------------------------------- #
+# bit-level casts
+# --------------------------------------------------------------------------- #
+
+
+def f32_to_bf16_bits(x: np.ndarray) -> np.ndarray:
+    """float32 -> bfloat16 bits, round-to-nearest-even (NaN -> 0x7FC0 like torch CPU)."""
+    x = np.ascontiguousarray(x, dtype=np.float32)
+    b = x.view(np.uint32)
+    nan = np.isnan(x)
+    rounded = ((b + (np.uint32(0x7FFF) + ((b >> np.uint32(16)) & np.uint32(1)))) >> np.uint32(16)).astype(np.uint16)
+    return np.where(nan, np.uint16(0x7FC0), rounded)
+
+
+def bf16_bits_to_f32(b: np.ndarray) -> np.ndarray:
+    return (np.ascontiguousarray(b, dtype=np.uint16).astype(np.uint32) << np.uint32(16)).view(np.float32)
+
+
+def f32_to_e4m3fn_bits(x: np.ndarray) -> np.ndarray:
+    """float32 -> float8_e4m3fn bits the way torch casts: RNE, NOT saturating.
+
+    |x| >= 480 and NaN -> 0x7F | sign; (464, 480) rounds up into 0x7F; [448, 464] -> 0x7E;
+    subnormals kept (2^-9 -> 0x01, 2^-10 ties to even -> 0x00).  SURVEY.md Appendix A.7.
+    """
+    x = np.ascontiguousarray(x, dtype=np.float32)
+    bits = x.view(np.uint32).copy()
+    sign = bits & np.uint32(0x80000000)
+    bits ^= sign
+    out = np.zeros(bits.shape, dtype=np.uint8)
+
+    over = bits >= np.uint32(1087 << 20)
+    sub = (~over) & (bits < np.uint32(121 << 23))
+    norm = ~(over | sub)
+
+    out[over] = 0x7F
+    magic = np.uint32(141 << 23)
+    if sub.any():
+        a = bits[sub].view(np.float32) + np.array([magic], dtype=np.uint32).view(np.float32)[0]
+        out[sub] = (a.astype(np.float32).view(np.uint32) - magic).astype(np.uint8)
+    if norm.any():
+        nb = bits[norm].astype(np.uint64)
+        odd = (nb >> 20) & 1
+        nb = (nb + np.uint64(((7 - 127) << 23) & 0xFFFFFFFF) + np.uint64(0x7FFFF) + odd) & np.uint64(0xFFFFFFFF)
+        out[norm] = (nb >> 20).astype(np.uint8)
+    return out | (sign >> np.uint32(24)).astype(np.uint8)
+
+
+_E4M3_TABLE: Optional[np.ndarray] = None
+
+
+def e4m3fn_bits_to_f32(b: np.ndarray) -> np.ndarray:
+    """float8_e4m3fn bits -> float32 (exact; 0x7F / 0xFF are NaN)."""
+    global _E4M3_TABLE
+    if _E4M3_TABLE is None:
+        t = np.zeros(256, dtype=np.float32)
+        for i in range(256):
+            s = -1.0 if i & 0x80 else 1.0
+            e = (i >> 3) & 0xF
+            m = i & 7
+            if e == 0xF and m == 7:
+                v = np.nan
+            elif e == 0:
+                v = s * (m / 8.0) * 2.0 ** -6
+            else:
+                v = s * (1.0 + m / 8.0) * 2.0 ** (e - 7)
+            t[i] = v
+        _E4M3_TABLE = t
+    return _E4M3_TABLE[np.ascontiguousarray(b, dtype=np.uint8)]
+
+
+def _to_f32(t: torch.Tensor) -> np.ndarray:
+    return t.detach().to(torch.float32).cpu().numpy()
+
+
+# --------------------------------------------------------------------------- #
+# KV store
+# --------------------------------------------------------------------------- #
+SCALE_NONE, SCALE_TRUE_DIV, SCALE_RECIP_MUL = 0, 1, 2
+
+
+def _round_to(x32: np.ndarray, dtype: torch.dtype) -> np.ndarray:
+    """Round float32 values to the source dtype and return them as float32."""
+    if dtype == torch.bfloat16:
+        return bf16_bits_to_f32(f32_to_bf16_bits(x32))
+    if dtype == torch.float16:
+        return x32.astype(np.float16).astype(np.float32)
+    raise TypeError(dtype)
+
+
+def kv_store(k_pool: torch.Tensor, v_pool: torch.Tensor, loc: torch.Tensor, cache_k: torch.Tensor,
+             cache_v: torch.Tensor, k_scale: Optional[float] = None, v_scale: Optional[float] = None,
+             scale_mode: int = SCALE_TRUE_DIV) -> None:
+    """In-place ``set_kv_buffer`` on CPU tensors.
+
+    ``k_pool``/``v_pool``: one layer's ``[slots, heads, dim]`` pool, either the source dtype or
+    ``uint8`` (fp8-e4m3 bytes).  With an fp8 pool and a scale: ``x <- round_src(x / s)`` is
+    written back into ``cache_k``/``cache_v`` (``div_`` is in place, memory_pool.py:385-389),
+    then cast.  ``scale_mode`` picks true division (torch CPU; CUDA with a tensor divisor) or
+    multiplication by the fp32 reciprocal (torch CUDA with a Python-float divisor).
+    """
+    loc_np = loc.detach().cpu().numpy().astype(np.int64)
+    for pool, cache, scale in ((k_pool, cache_k, k_scale), (v_pool, cache_v, v_scale)):
+        if pool.dtype == torch.uint8:
+            x = _to_f32(cache)
+            if scale is not None and scale_mode != SCALE_NONE:
+                s = np.float32(scale)
+                if scale_mode == SCALE_RECIP_MUL:
+                    x = x * (np.float32(1.0) / s)
+                else:
+                    x = x / s
+                x = _round_to(x.astype(np.float32), cache.dtype)
+                cache.copy_(torch.from_numpy(x).to(cache.dtype))
+            bits = f32_to_e4m3fn_bits(x)
+            pool_np = pool.numpy()
+            pool_np[loc_np] = bits  # last write wins for duplicate slots, like index_put
+        else:
+            assert pool.dtype == cache.dtype
+            pool[torch.from_numpy(loc_np)] = cache
+
+
+# --------------------------------------------------------------------------- #
+# page indexing
+# --------------------------------------------------------------------------- #
+def kv_indices(req_to_token: torch.Tensor, req_pool_indices: torch.Tensor,
+               seq_lens: torch.Tensor) -> Tuple[np.ndarray, np.ndarray]:
+    """(kv_indptr[B+1], kv_indices[sum S]) as int32 numpy arrays."""
+    r2t = req_to_token.detach().cpu().numpy()
+    rpi = req_pool_indices.detach().cpu().numpy().astype(np.int64)
+    sl = seq_lens.detach().cpu().numpy().astype(np.int64)
+    indptr = np.zeros(len(sl) + 1, dtype=np.int32)
+    indptr[1:] = np.cumsum(sl).astype(np.int32)
+    parts = [r2t[rpi[i], : sl[i]] for i in range(len(sl))]
+    flat = np.concatenate(parts).astype(np.int32) if parts else np.zeros(0, dtype=np.int32)
+    return indptr, flat
+
+
+# --------------------------------------------------------------------------- #
+# decode attention (float64 SDPA + lse)
+# --------------------------------------------------------------------------- #
+def pool_to_f32(pool: torch.Tensor) -> np.ndarray:
+    if pool.dtype in (torch.uint8, torch.float8_e4m3fn):
+        return e4m3fn_bits_to_f32(pool.view(torch.uint8).cpu().numpy())
+    return _to_f32(pool)
+
+
+def decode_attention(q: torch.Tensor, k_pool: torch.Tensor, v_pool: torch.Tensor,
+                     req_to_token: torch.Tensor, req_pool_indices: torch.Tensor, seq_lens: torch.Tensor,
+                     sm_scale: float, logit_cap: float = 0.0, k_scale: float = 1.0,
+                     v_scale: float = 1.0) -> Tuple[np.ndarray, np.ndarray]:
+    """Returns (out [B, Hq, Dv] float32, lse [B, Hq] float32), computed in float64.
+
+    Request b attends to slots ``req_to_token[req_pool_indices[b], :seq_lens[b]]``
+    (torch_native_backend.py:160-163); q head h uses kv head ``h // (Hq / Hkv)`` (SDPA
+    ``enable_gqa``).  fp8 pools are dequantised as ``fp8 * scale``
+    (layers/quantization/kv_cache.py:21-23).  ``logit_cap``: ``cap * tanh(x / cap)`` after the
+    scale (triton_ops/decode_attention.py:349-352).
+    """
+    qf = _to_f32(q).astype(np.float64)
+    B, Hq, D = qf.shape
+    kf = pool_to_f32(k_pool)
+    vf = pool_to_f32(v_pool)
+    Hkv, Dv = kf.shape[1], vf.shape[2]
+    G = Hq // Hkv
+    r2t = req_to_token.detach().cpu().numpy()
+    rpi = req_pool_indices.detach().cpu().numpy().astype(np.int64)
+    sl = seq_lens.detach().cpu().numpy().astype(np.int64)
+    out = np.zeros((B, Hq, Dv), dtype=np.float32)
+    lse = np.full((B, Hq), -np.inf, dtype=np.float32)
+    for b in range(B):
+        S = int(sl[b])
+        if S == 0:
+            continue
+        slots = r2t[rpi[b], :S].astype(np.int64)
+        K = kf[slots].astype(np.float64) * k_scale  # [S, Hkv, D]
+        V = vf[slots].astype(np.float64) * v_scale
+        qg = qf[b].reshape(Hkv, G, D)
+        logits = np.einsum("hgd,shd->hgs", qg, K) * sm_scale
+        if logit_cap > 0:
+            logits = logit_cap * np.tanh(logits / logit_cap)
+        m = logits.max(axis=-1, keepdims=True)
+        p = np.exp(logits - m)
+        l = p.sum(axis=-1, keepdims=True)
+        o = np.einsum("hgs,shd->hgd", p / l, V)
+        out[b] = o.reshape(Hq, Dv).astype(np.float32)
+        lse[b] = (m + np.log(l)).reshape(Hq).astype(np.float32)
+    return out, lse
+
+
+def torch_native_decode(q: torch.Tensor, k_pool: torch.Tensor, v_pool: torch.Tensor,
+                        req_to_token: torch.Tensor, req_pool_indices: torch.Tensor,
+                        seq_lens: torch.Tensor, sm_scale: float) -> torch.Tensor:
+    """What the reference's torch_native backend executes for decode: one SDPA per request on
+    gathered K/V, in the model dtype (torch_native_backend.py:147-178).  Returns [B, Hq, Dv]."""
+    B, Hq, _ = q.shape
+    Hkv = k_pool.shape[1]
+    out = torch.empty((B, Hq, v_pool.shape[2]), dtype=q.dtype)
+    qh = q.movedim(0, 1)  # [Hq, B, D]
+    for b in range(B):
+        S = int(seq_lens[b])
+        slots = req_to_token[int(req_pool_indices[b]), :S].to(torch.int64)
+        K = k_pool[slots].movedim(0, 1)
+        V = v_pool[slots].movedim(0, 1)
+        o = torch.nn.functional.scaled_dot_product_attention(
+            qh[:, b : b + 1, :].unsqueeze(0), K.unsqueeze(0), V.unsqueeze(0),
+            enable_gqa=Hq != Hkv, scale=sm_scale, is_causal=False)
+        out[b] = o.squeeze(0).movedim(1, 0)[0]
+    return out
+
+
+# --------------------------------------------------------------------------- #
+# state merge
+# --------------------------------------------------------------------------- #
+def merge_states(o_a: np.ndarray, lse_a: np.ndarray, o_b: np.ndarray,
+                 lse_b: np.ndarray) -> Tuple[np.ndarray, np.ndarray]:
+    """2-way (o, lse) merge; +inf lse is treated as -inf (merge_attn_states.cu:68-69)."""
+    a = np.where(np.isinf(lse_a), -np.inf, lse_a).astype(np.float64)
+    b = np.where(np.isinf(lse_b), -np.inf, lse_b).astype(np.float64)
+    m = np.maximum(a, b)
+    with np.errstate(invalid="ignore"):
+        ea, eb = np.exp(a - m), np.exp(b - m)
+    s = ea + eb
+    out = o_a.astype(np.float64) * (ea / s)[..., None] + o_b.astype(np.float64) * (eb / s)[..., None]
+    return out.astype(np.float32), (np.log(s) + m).astype(np.float32)
+
+
+def merge_n(o: np.ndarray, lse: np.ndarray) -> Tuple[np.ndarray, np.ndarray]:
+    """N-way merge over axis 0 (stage-2 semantics, triton_ops/decode_attention.py:529-552)."""
+    l = lse.astype(np.float64)
+    m = l.max(axis=0)
+    w = np.exp(l - m)
+    s = w.sum(axis=0)
+    out = (o.astype(np.float64) * w[..., None]).sum(axis=0) / s[..., None]
+    return out.astype(np.float32), (m + np.log(s)).astype(np.float32)

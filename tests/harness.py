@@ -1,0 +1,108 @@
+"""Shared test/bench harness: a mock ModelRunner around a synthetic workload, the way the
+reference's LTP numerical tests fabricate one
+(python/sglang/test/numerical_tests/modules/sglang/test_attention.py:164-326)."""
+from __future__ import annotations
+
+import os
+import types
+
+import numpy as np
+import torch
+
+import synth
+
+GOLDEN_DIR = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
+
+_TORCH_KV = {"bf16": torch.bfloat16, "f16": torch.float16, "fp8_e4m3": torch.float8_e4m3fn}
+
+
+def make_runner(w: synth.Workload, device, tp_size: int = 1):
+    """Mock model_runner exposing what attention backends read (triton_backend.py:62-122)."""
+    import b200attn
+
+    c = w.cfg
+    r2t = b200attn.ReqToTokenPool(w.req_to_token.shape[0], w.req_to_token.shape[1], device)
+    r2t.req_to_token.copy_(w.req_to_token)
+    pool = b200attn.MHATokenToKVPool(w.pool_size, c.page_size, _TORCH_KV[c.kv_dtype], c.num_kv_heads,
+                                     c.head_dim, layer_num=1, device=device)
+    assert pool.k_buffer[0].shape == w.k_pool.shape, (pool.k_buffer[0].shape, w.k_pool.shape)
+    # adopt the workload's pool storage (no copy: full-size pools are GiBs)
+    pool.k_buffer[0] = w.k_pool
+    pool.v_buffer[0] = w.v_pool
+    mc = types.SimpleNamespace(num_attention_heads=c.num_q_heads * tp_size,
+                               get_num_kv_heads=lambda tp: c.num_kv_heads,
+                               context_len=w.req_to_token.shape[1] - 4, is_encoder_decoder=False)
+    return types.SimpleNamespace(device=str(device), req_to_token_pool=r2t, token_to_kv_pool=pool,
+                                 model_config=mc, sliding_window_size=None, attention_tp_size=tp_size)
+
+
+def make_layer(w: synth.Workload, logit_cap: float = 0.0, with_scales: bool = True):
+    import b200attn
+
+    c = w.cfg
+    layer = b200attn.AttnLayer(c.num_q_heads, c.head_dim, w.sm_scale, c.num_kv_heads, layer_id=0,
+                               logit_cap=logit_cap)
+    if c.kv_dtype == "fp8_e4m3" and with_scales:
+        dev = w.k_pool.device
+        layer.k_scale = torch.tensor(c.k_scale, dtype=torch.float32, device=dev)
+        layer.v_scale = torch.tensor(c.v_scale, dtype=torch.float32, device=dev)
+        layer.k_scale_float, layer.v_scale_float = c.k_scale, c.v_scale
+    return layer
+
+
+def make_batch(w: synth.Workload, runner, backend, index_dtype=torch.int64):
+    import b200attn
+
+    return b200attn.ForwardBatch(
+        forward_mode=b200attn.ForwardMode.DECODE, batch_size=w.cfg.batch,
+        req_pool_indices=w.req_pool_indices.to(index_dtype), seq_lens=w.seq_lens.to(index_dtype),
+        out_cache_loc=w.out_cache_loc, seq_lens_sum=w.seq_lens_sum,
+        req_to_token_pool=runner.req_to_token_pool, token_to_kv_pool=runner.token_to_kv_pool,
+        attn_backend=backend)
+
+
+def run_decode(backend, runner, w: synth.Workload, layer=None, save_kv_cache=True,
+               index_dtype=torch.int64):
+    """init_forward_metadata + RadixAttention-style layer call; returns [B, Hq * D]."""
+    layer = layer or make_layer(w)
+    fb = make_batch(w, runner, backend, index_dtype)
+    backend.init_forward_metadata(fb)
+    return layer(w.q, w.k, w.v, fb, save_kv_cache=save_kv_cache)
+
+
+def oracle_step(w_cpu: synth.Workload, logit_cap: float = 0.0, save_kv: bool = True,
+                scale_mode=None):
+    """kv_store + decode_attention on the CPU oracle; returns (out, lse, k_pool, v_pool, k, v)."""
+    from oracle import decode_oracle as oracle
+
+    c = w_cpu.cfg
+    kp, vp = w_cpu.k_pool.clone(), w_cpu.v_pool.clone()
+    k = w_cpu.k.reshape(c.batch, c.num_kv_heads, c.head_dim).clone()
+    v = w_cpu.v.reshape(c.batch, c.num_kv_heads, c.head_dim).clone()
+    fp8 = c.kv_dtype == "fp8_e4m3"
+    if save_kv:
+        oracle.kv_store(kp, vp, w_cpu.out_cache_loc, k, v, c.k_scale if fp8 else None,
+                        c.v_scale if fp8 else None,
+                        oracle.SCALE_TRUE_DIV if scale_mode is None else scale_mode)
+    out, lse = oracle.decode_attention(
+        w_cpu.q.reshape(c.batch, c.num_q_heads, c.head_dim), kp, vp, w_cpu.req_to_token,
+        w_cpu.req_pool_indices, w_cpu.seq_lens, w_cpu.sm_scale, logit_cap,
+        c.k_scale if fp8 else 1.0, c.v_scale if fp8 else 1.0)
+    return out, lse, kp, vp, k, v
+
+
+def assert_close_out(got: np.ndarray, ref: np.ndarray, atol=2e-2, rtol=1e-2, what="attention output"):
+    """BASELINE.json tolerance: max-abs 2e-2 / rel 1e-2 against the fp32+ oracle."""
+    err = np.abs(got.astype(np.float64) - ref.astype(np.float64))
+    bound = atol + rtol * np.abs(ref)
+    worst = float((err - bound).max())
+    assert worst <= 0, f"{what}: max abs err {err.max():.4e} exceeds atol {atol} + rtol {rtol}"
+    return float(err.max())
+
+
+def canon_e4m3_nan(b: np.ndarray) -> np.ndarray:
+    """float8_e4m3fn has two NaN encodings (0x7F, 0xFF).  Which one a NaN *input* lands on after
+    ``div_`` depends on the platform's bf16 rounding of NaN (torch's AVX512 path writes 0xFFFF,
+    its scalar path 0x7FC0, CUDA 0x7FFF), so NaN bytes are compared up to sign."""
+    b = np.asarray(b, dtype=np.uint8)
+    return np.where((b & 0x7F) == 0x7F, np.uint8(0x7F), b)

@@ -1,0 +1,167 @@
+"""CPU tests: the oracle against the golden vectors produced by the reference itself
+(tests/golden/make_golden.py), and against the reference's live code where the read-only tree is
+mounted.  These pin the oracle; the GPU tests then compare the CUDA path with the oracle."""
+from __future__ import annotations
+
+import os
+import types
+
+import numpy as np
+import pytest
+import torch
+
+import synth
+from oracle import decode_oracle as oracle
+from oracle import ref_loader
+from tests.golden.make_golden import CASES, KAT, digest
+from tests.harness import GOLDEN_DIR, assert_close_out, canon_e4m3_nan, oracle_step
+
+
+def _from_bits(a: np.ndarray, dt: torch.dtype) -> torch.Tensor:
+    return torch.from_numpy(a.view(np.int16).copy()).view(dt)
+
+
+@pytest.mark.parametrize("name", sorted(CASES))
+def test_decode_oracle_vs_reference_golden(name):
+    cfg = CASES[name]
+    g = np.load(os.path.join(GOLDEN_DIR, name + ".npz"))
+    w = synth.make_workload(cfg, "cpu")
+    assert digest(w) == g["digest"].tobytes().decode(), "synthetic inputs drifted: regenerate goldens"
+    fp8 = cfg.kv_dtype == "fp8_e4m3"
+    if fp8:  # golden: dequantised copy, scales 1, no store (see make_golden.py)
+        out, lse = oracle.decode_attention(w.q.reshape(cfg.batch, cfg.num_q_heads, cfg.head_dim), w.k_pool,
+                                           w.v_pool, w.req_to_token, w.req_pool_indices, w.seq_lens,
+                                           w.sm_scale)
+    else:
+        out, lse, kp, vp, _, _ = oracle_step(w)
+        loc = w.out_cache_loc
+        dt = w.k_pool.dtype
+        assert torch.equal(kp[loc], _from_bits(g["k_rows_after"], dt))
+        assert torch.equal(vp[loc], _from_bits(g["v_rows_after"], dt))
+    ref_dt = torch.float16 if cfg.q_dtype == "f16" else torch.bfloat16
+    ref = _from_bits(g["out_bits"], ref_dt).float().numpy()
+    # the reference output is a bf16/f16-rounded SDPA; the oracle is float64
+    assert_close_out(out, ref, atol=4e-3, rtol=8e-3, what=f"{name}: oracle vs reference")
+    indptr, indices = oracle.kv_indices(w.req_to_token, w.req_pool_indices, w.seq_lens)
+    assert np.array_equal(indptr, g["kv_indptr"]) and np.array_equal(indices, g["kv_indices"])
+    # lse consistency: lse = ln sum exp(scaled logits) => exp(logit - lse) sums to 1 (spot check)
+    assert np.isfinite(lse).all()
+
+
+def test_torch_native_port_matches_golden():
+    """The timed CPU port (per-request SDPA in the model dtype) reproduces the reference bit for bit
+    on the non-fp8 goldens: it is the same arithmetic, restated."""
+    for name, cfg in CASES.items():
+        if cfg.kv_dtype == "fp8_e4m3":
+            continue
+        g = np.load(os.path.join(GOLDEN_DIR, name + ".npz"))
+        w = synth.make_workload(cfg, "cpu")
+        _, _, kp, vp, _, _ = oracle_step(w)
+        out = oracle.torch_native_decode(w.q.reshape(cfg.batch, cfg.num_q_heads, cfg.head_dim), kp, vp,
+                                         w.req_to_token, w.req_pool_indices, w.seq_lens, w.sm_scale)
+        ref_dt = torch.float16 if cfg.q_dtype == "f16" else torch.bfloat16
+        assert torch.equal(out, _from_bits(g["out_bits"], ref_dt)), name
+
+
+def test_fp8_cast_table_exhaustive():
+    table = np.load(os.path.join(GOLDEN_DIR, "g6_cast_table_bf16_e4m3fn.npz"))["table"]
+    allbf = np.arange(65536, dtype=np.uint32).astype(np.uint16)
+    got = oracle.f32_to_e4m3fn_bits(oracle.bf16_bits_to_f32(allbf))
+    assert np.array_equal(got, table)
+    # and against torch in this process (not only the stored table)
+    t = torch.from_numpy(allbf.view(np.int16)).view(torch.bfloat16).to(torch.float8_e4m3fn).view(torch.uint8)
+    assert np.array_equal(got, t.numpy())
+
+
+def test_fp8_cast_f32_inputs_and_kat():
+    x = np.array(KAT + [-v for v in KAT], dtype=np.float32)
+    want = torch.from_numpy(x).to(torch.float8_e4m3fn).view(torch.uint8).numpy()
+    assert np.array_equal(oracle.f32_to_e4m3fn_bits(x), want)
+    rng = np.random.default_rng(0)
+    y = (rng.standard_normal(200000) * np.exp(rng.uniform(-12, 7, 200000))).astype(np.float32)
+    want = torch.from_numpy(y).to(torch.float8_e4m3fn).view(torch.uint8).numpy()
+    assert np.array_equal(oracle.f32_to_e4m3fn_bits(y), want)
+    # survey table (Appendix A.7)
+    tab = [(448.0, 0x7E), (456.0, 0x7E), (464.0, 0x7E), (472.0, 0x7F), (480.0, 0x7F), (1e4, 0x7F),
+           (-1e4, 0xFF), (2.0 ** -9, 0x01), (2.0 ** -10, 0x00), (0.0, 0x00), (-0.0, 0x80)]
+    for k, v in tab:
+        assert int(oracle.f32_to_e4m3fn_bits(np.array([k], dtype=np.float32))[0]) == v, k
+
+
+def test_e4m3_decode_table():
+    b = np.arange(256, dtype=np.uint8)
+    want = torch.from_numpy(b).view(torch.float8_e4m3fn).float().numpy()
+    got = oracle.e4m3fn_bits_to_f32(b)
+    assert np.array_equal(np.isnan(got), np.isnan(want))
+    assert np.array_equal(got[~np.isnan(got)], want[~np.isnan(want)])
+
+
+def test_bf16_rounding():
+    rng = np.random.default_rng(1)
+    x = (rng.standard_normal(100000) * np.exp(rng.uniform(-20, 20, 100000))).astype(np.float32)
+    want = torch.from_numpy(x).to(torch.bfloat16).view(torch.int16).numpy().view(np.uint16)
+    assert np.array_equal(oracle.f32_to_bf16_bits(x), want)
+
+
+@pytest.mark.parametrize("dname", ["bf16", "f16"])
+@pytest.mark.parametrize("tag", ["none", "one", "half_two", "odd"])
+def test_fp8_store_oracle_vs_reference_golden(dname, tag):
+    g = np.load(os.path.join(GOLDEN_DIR, f"g6_fp8_store_{dname}_{tag}.npz"))
+    dt = torch.bfloat16 if dname == "bf16" else torch.float16
+    k, v = _from_bits(g["k_in"], dt), _from_bits(g["v_in"], dt)
+    loc = torch.from_numpy(g["loc"])
+    kp = torch.zeros(g["k_pool"].shape, dtype=torch.uint8)
+    vp = torch.zeros(g["v_pool"].shape, dtype=torch.uint8)
+    ks, vs = float(g["k_scale"]), float(g["v_scale"])
+    oracle.kv_store(kp, vp, loc, k, v, None if ks < 0 else ks, None if vs < 0 else vs, oracle.SCALE_TRUE_DIV)
+    assert np.array_equal(canon_e4m3_nan(kp.numpy()), canon_e4m3_nan(g["k_pool"]))
+    assert np.array_equal(canon_e4m3_nan(vp.numpy()), canon_e4m3_nan(g["v_pool"]))
+    for got, want in ((k, g["k_after"]), (v, g["v_after"])):
+        wf = _from_bits(want, dt).float().numpy()
+        gf = got.float().numpy()
+        nan = np.isnan(wf)
+        assert np.array_equal(gf[~nan], wf[~nan]) and np.isnan(gf[nan]).all()
+
+
+def test_merge_oracle_vs_reference_golden():
+    for dname, dt in (("bf16", torch.bfloat16), ("f16", torch.float16)):
+        g = np.load(os.path.join(GOLDEN_DIR, f"g8_merge_{dname}.npz"))
+        oa = _from_bits(g["o_a"], dt).float().numpy()
+        ob = _from_bits(g["o_b"], dt).float().numpy()
+        out, lse = oracle.merge_states(oa, g["lse_a"], ob, g["lse_b"])
+        assert np.abs(out - g["out"]).max() <= 1e-2  # reference output is rounded to bf16/f16
+        fin = np.isfinite(g["lse"])
+        assert np.abs(lse[fin] - g["lse"][fin]).max() <= 1e-5
+
+
+def test_merge_n_equals_full_softmax():
+    """Splitting a request into pieces and merging (stage-2 semantics) is exact."""
+    cfg = synth.Config("m", 2, 0, 8, 2, 64, ragged=(90, 200), seed=3)
+    w = synth.make_workload(cfg, "cpu")
+    full, full_lse, kp, vp, _, _ = oracle_step(w, save_kv=False)
+    outs, lses = [], []
+    cuts = [0, 17, 64, 10 ** 9]
+    q = w.q.reshape(cfg.batch, cfg.num_q_heads, cfg.head_dim)
+    for a, b in zip(cuts[:-1], cuts[1:]):
+        r2t = w.req_to_token[:, a:].contiguous()
+        sl = torch.clamp(torch.clamp(w.seq_lens, max=b) - a, min=0)
+        o, l = oracle.decode_attention(q, kp, vp, r2t, w.req_pool_indices, sl, w.sm_scale)
+        outs.append(o)
+        lses.append(l)
+    out, lse = oracle.merge_n(np.stack(outs), np.stack(lses))
+    assert np.abs(out - full).max() <= 1e-6 and np.abs(lse - full_lse).max() <= 1e-5
+
+
+@pytest.mark.skipif(not ref_loader.available(), reason="reference tree not mounted (GPU box)")
+def test_oracle_vs_live_reference():
+    """Where the reference tree is mounted, run its set_kv_buffer + torch_native forward_decode live
+    on a fresh seed (not one of the stored goldens)."""
+    from tests.golden.make_golden import run_reference_decode
+
+    ref = ref_loader.load()
+    cfg = synth.Config("live", 4, 0, 16, 4, 128, page_size=4, ragged=(5, 333), share_groups=2, seed=77)
+    w = synth.make_workload(cfg, "cpu")
+    out_ref, pool = run_reference_decode(ref, w, w.k_pool, w.v_pool, torch.bfloat16)
+    out, _, kp, vp, _, _ = oracle_step(w)
+    assert torch.equal(pool.k_buffer[0], kp) and torch.equal(pool.v_buffer[0], vp)
+    assert_close_out(out, out_ref.float().numpy().reshape(out.shape), atol=4e-3, rtol=8e-3)
