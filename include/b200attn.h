@@ -64,8 +64,10 @@ enum { B200ATTN_I32 = 0, B200ATTN_I64 = 1 };
 /* How kv_store divides by the per-tensor scale before the fp8 cast. */
 enum {
   B200ATTN_SCALE_NONE = 0,      /* set_kv_buffer called without k_scale/v_scale */
-  B200ATTN_SCALE_TRUE_DIV = 1,  /* x / s in fp32, rounded to the source dtype
-                                   (torch CPU div_, or CUDA div_ by a 0-dim tensor) */
+  B200ATTN_SCALE_TRUE_DIV = 1,  /* x / s in fp32, rounded to the source dtype (torch CPU div_;
+                                   CUDA div_ by a 0-dim CUDA tensor, where torch first casts
+                                   the divisor to the source dtype: a *_scale_ptr scale is
+                                   therefore rounded to src_dtype before use) */
   B200ATTN_SCALE_RECIP_MUL = 2  /* x * (1.0f / s): what torch's CUDA div_ computes
                                    when the divisor is a Python float */
 };
@@ -163,6 +165,9 @@ typedef struct {
   float logit_cap;             /* 0 disables; cap * tanh(x / cap) otherwise */
   float k_scale;               /* fp8 dequant: K = fp8 * k_scale (1.0 for 16-bit pools) */
   float v_scale;
+  int32_t phases;              /* 0 = split-KV kernel + merge; 1 = split-KV kernel only (K2);
+                                  2 = merge only (K3).  1 and 2 exist so each kernel can be
+                                  timed and profiled alone; 1 followed by 2 equals 0. */
 } b200attn_decode_args;
 
 /* Bytes of split-KV workspace (partial o + lse) for up to `batch` requests. */

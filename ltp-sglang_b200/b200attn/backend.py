@@ -30,14 +30,16 @@ from .interfaces import AttentionBackend
 
 
 def store_kv(k_pool: torch.Tensor, v_pool: torch.Tensor, loc: torch.Tensor, cache_k: torch.Tensor,
-             cache_v: torch.Tensor, k_scale=None, v_scale=None) -> None:
+             cache_v: torch.Tensor, k_scale=None, v_scale=None, scale_mode: Optional[int] = None) -> None:
     """``set_kv_buffer`` semantics (memory_pool.py:369-407) on raw layer pools.
 
     Scales apply only when the pool dtype differs from the source dtype (fp8).
-    A Python float divides the way torch's CUDA ``div_`` does for a CPU scalar
-    (multiply by the fp32 reciprocal); a 0-dim tensor (``layer.k_scale``) is a
-    true fp32 division.  ``cache_k`` / ``cache_v`` are updated in place like
-    ``div_`` does.
+    The arithmetic follows what the reference's ``cache_k.div_(k_scale)`` does on
+    CUDA: a Python float multiplies by the fp32 reciprocal (torch's CPU-scalar
+    fast path); a 0-dim CUDA tensor (``layer.k_scale``) is first cast to the
+    source dtype, then divides in fp32.  ``scale_mode`` overrides the choice
+    (``capi.SCALE_TRUE_DIV`` with floats reproduces torch's CPU result).
+    ``cache_k`` / ``cache_v`` are updated in place like ``div_`` does.
     """
     if loc.dtype != torch.int64:
         loc = loc.to(torch.int64)
@@ -47,6 +49,8 @@ def store_kv(k_pool: torch.Tensor, v_pool: torch.Tensor, loc: torch.Tensor, cach
     if fp8 and (k_scale is not None or v_scale is not None):
         tensors = isinstance(k_scale, torch.Tensor) or isinstance(v_scale, torch.Tensor)
         mode = capi.SCALE_TRUE_DIV if tensors else capi.SCALE_RECIP_MUL
+        if scale_mode is not None:
+            mode = scale_mode
         if tensors:
             kt = _scale_tensor(k_scale, cache_k.device)
             vt = _scale_tensor(v_scale, cache_v.device)

@@ -101,6 +101,7 @@ class DecodeArgs(C.Structure):
         ("logit_cap", C.c_float),
         ("k_scale", C.c_float),
         ("v_scale", C.c_float),
+        ("phases", C.c_int32),
     ]
 
 

@@ -133,7 +133,8 @@ def _plan_csr(csr_indptr, plan_buf, num_q_heads, num_kv_heads, head_dim, kv_dtyp
         capi.check("b200attn_plan", capi.lib().b200attn_plan(C.byref(a), _stream(plan_buf)))
 
 
-def _decode(q, k_pool, v_pool, o, lse, plan_buf, indices, workspace, sm_scale, logit_cap, k_scale, v_scale):
+def _decode(q, k_pool, v_pool, o, lse, plan_buf, indices, workspace, sm_scale, logit_cap, k_scale, v_scale,
+            phases=0):
     _cuda(q, k_pool, v_pool, o, lse, plan_buf, indices, workspace)
     if q.dim() != 3 or o.dim() != 3 or k_pool.dim() != 3 or v_pool.dim() != 3:
         raise ValueError("decode: q/o must be [batch, heads, dim]; pools [slots, kv_heads, dim]")
@@ -168,6 +169,7 @@ def _decode(q, k_pool, v_pool, o, lse, plan_buf, indices, workspace, sm_scale, l
     a.q_dtype = dtype_code(q.dtype)
     a.kv_dtype = dtype_code(k_pool.dtype)
     a.sm_scale, a.logit_cap, a.k_scale, a.v_scale = sm_scale, logit_cap, k_scale, v_scale
+    a.phases = phases
     with torch.cuda.device(q.device):
         capi.check("b200attn_decode", capi.lib().b200attn_decode(C.byref(a), _stream(q)))
 
@@ -210,7 +212,7 @@ _LIB.define(
 _LIB.define(
     "decode(Tensor q, Tensor k_pool, Tensor v_pool, Tensor(a!) o, Tensor(b!)? lse, Tensor plan_buf, "
     "Tensor indices, Tensor(c!) workspace, float sm_scale, float logit_cap, float k_scale, "
-    "float v_scale) -> ()"
+    "float v_scale, int phases=0) -> ()"
 )
 _LIB.define(
     "merge_states(Tensor o_a, Tensor lse_a, Tensor o_b, Tensor lse_b, Tensor(a!) o_out, "

@@ -84,6 +84,7 @@ extern "C" __attribute__((visibility("default"))) int b200attn_decode(const b200
   if (!a) return B200ATTN_E_INVALID;
   if (a->batch < 0) return B200ATTN_E_INVALID;
   if (a->batch == 0) return B200ATTN_OK;
+  if (a->phases < 0 || a->phases > 2) return B200ATTN_E_INVALID;
   if (!a->q || !a->k_pool || !a->v_pool || !a->o || !a->plan || !a->indices || !a->ws_o)
     return B200ATTN_E_INVALID;
   if (a->q_dtype != B200ATTN_BF16 && a->q_dtype != B200ATTN_F16) return B200ATTN_E_UNSUPPORTED;
@@ -146,8 +147,10 @@ extern "C" __attribute__((visibility("default"))) int b200attn_decode(const b200
   cudaStream_t stream = static_cast<cudaStream_t>(stream_);
   const bool rows16 = g.group > 8;
   const bool half = a->q_dtype == B200ATTN_F16;
-  cudaError_t err;
-  if (half) {
+  cudaError_t err = cudaSuccess;
+  if (a->phases == 2) {
+    // merge only
+  } else if (half) {
     err = fp8 ? launch_decode<__half, true>(p, a->head_dim, rows16, n_sm, g.smem_bytes, stream)
               : launch_decode<__half, false>(p, a->head_dim, rows16, n_sm, g.smem_bytes, stream);
   } else {
@@ -155,7 +158,8 @@ extern "C" __attribute__((visibility("default"))) int b200attn_decode(const b200
               : launch_decode<__nv_bfloat16, false>(p, a->head_dim, rows16, n_sm, g.smem_bytes, stream);
   }
   if (err != cudaSuccess) return B200ATTN_E_CUDA;
-  count_launch();
+  if (a->phases != 2) count_launch();
+  if (a->phases == 1) return B200ATTN_OK;
 
   MergeParams m;
   m.plan = a->plan;

@@ -114,7 +114,9 @@ __global__ void __launch_bounds__(256) kv_store_kernel(StoreParams p) {
 
     if constexpr (FP8) {
       if (p.scale_mode != B200ATTN_SCALE_NONE) {
-        const float s = p.scale_ptr[which] ? *p.scale_ptr[which] : p.scale[which];
+        // A device scale is a 0-dim CUDA tensor: torch casts it to the common dtype (the
+        // source dtype) before dividing, so the divisor is rounded first.
+        const float s = p.scale_ptr[which] ? to_f32<T>(from_f32<T>(*p.scale_ptr[which])) : p.scale[which];
         if (p.scale_mode == B200ATTN_SCALE_RECIP_MUL) {
           const float inv = __fdiv_rn(1.0f, s);
 #pragma unroll

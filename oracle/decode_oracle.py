@@ -124,7 +124,7 @@ def _round_to(x32: np.ndarray, dtype: torch.dtype) -> np.ndarray:
 
 def kv_store(k_pool: torch.Tensor, v_pool: torch.Tensor, loc: torch.Tensor, cache_k: torch.Tensor,
              cache_v: torch.Tensor, k_scale: Optional[float] = None, v_scale: Optional[float] = None,
-             scale_mode: int = SCALE_TRUE_DIV) -> None:
+             scale_mode: int = SCALE_TRUE_DIV, scale_is_cuda_tensor: bool = False) -> None:
     """In-place ``set_kv_buffer`` on CPU tensors.
 
     ``k_pool``/``v_pool``: one layer's ``[slots, heads, dim]`` pool, either the source dtype or
@@ -132,6 +132,8 @@ def kv_store(k_pool: torch.Tensor, v_pool: torch.Tensor, loc: torch.Tensor, cach
     written back into ``cache_k``/``cache_v`` (``div_`` is in place, memory_pool.py:385-389),
     then cast.  ``scale_mode`` picks true division (torch CPU; CUDA with a tensor divisor) or
     multiplication by the fp32 reciprocal (torch CUDA with a Python-float divisor).
+    ``scale_is_cuda_tensor``: the divisor is a 0-dim CUDA tensor, which torch casts to the source
+    dtype before dividing.
     """
     loc_np = loc.detach().cpu().numpy().astype(np.int64)
     for pool, cache, scale in ((k_pool, cache_k, k_scale), (v_pool, cache_v, v_scale)):
@@ -139,6 +141,8 @@ def kv_store(k_pool: torch.Tensor, v_pool: torch.Tensor, loc: torch.Tensor, cach
             x = _to_f32(cache)
             if scale is not None and scale_mode != SCALE_NONE:
                 s = np.float32(scale)
+                if scale_is_cuda_tensor:
+                    s = _round_to(np.array([s], dtype=np.float32), cache.dtype)[0]
                 if scale_mode == SCALE_RECIP_MUL:
                     x = x * (np.float32(1.0) / s)
                 else:

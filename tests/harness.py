@@ -71,7 +71,7 @@ def run_decode(backend, runner, w: synth.Workload, layer=None, save_kv_cache=Tru
 
 
 def oracle_step(w_cpu: synth.Workload, logit_cap: float = 0.0, save_kv: bool = True,
-                scale_mode=None):
+                scale_mode=None, scale_is_cuda_tensor: bool = True):
     """kv_store + decode_attention on the CPU oracle; returns (out, lse, k_pool, v_pool, k, v)."""
     from oracle import decode_oracle as oracle
 
@@ -83,7 +83,8 @@ def oracle_step(w_cpu: synth.Workload, logit_cap: float = 0.0, save_kv: bool = T
     if save_kv:
         oracle.kv_store(kp, vp, w_cpu.out_cache_loc, k, v, c.k_scale if fp8 else None,
                         c.v_scale if fp8 else None,
-                        oracle.SCALE_TRUE_DIV if scale_mode is None else scale_mode)
+                        oracle.SCALE_TRUE_DIV if scale_mode is None else scale_mode,
+                        scale_is_cuda_tensor)
     out, lse = oracle.decode_attention(
         w_cpu.q.reshape(c.batch, c.num_q_heads, c.head_dim), kp, vp, w_cpu.req_to_token,
         w_cpu.req_pool_indices, w_cpu.seq_lens, w_cpu.sm_scale, logit_cap,

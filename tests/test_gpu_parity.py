@@ -136,8 +136,8 @@ def test_golden_fp8_store(dname, tag):
     if ks < 0:
         b200attn.store_kv(kp, vp, loc, k, v)
     else:
-        # tensor scales select true division, which is what the CPU reference computed
-        b200attn.store_kv(kp, vp, loc, k, v, torch.tensor(ks, device=DEV), torch.tensor(vs, device=DEV))
+        # the CPU reference divided by an unrounded fp32 scalar: host floats + true division
+        b200attn.store_kv(kp, vp, loc, k, v, ks, vs, scale_mode=capi.SCALE_TRUE_DIV)
     torch.cuda.synchronize()
     assert np.array_equal(canon_e4m3_nan(kp.cpu().numpy()), canon_e4m3_nan(g["k_pool"]))
     assert np.array_equal(canon_e4m3_nan(vp.cpu().numpy()), canon_e4m3_nan(g["v_pool"]))
