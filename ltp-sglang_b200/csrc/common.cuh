@@ -47,7 +47,7 @@ __host__ __device__ inline int elem_bytes(int dtype) { return dtype == B200ATTN_
 // Returns false when the shape has no kernel.
 inline bool make_geometry(int hq, int hkv, int d, int kv_dtype, Geometry* g) {
   if (hq <= 0 || hkv <= 0 || hq % hkv != 0) return false;
-  if (d != 64 && d != 128 && d != 256) return false;
+  if (d != 64 && d != 128) return false;  // instantiated head dims
   int group = hq / hkv;
   if (group > 16) return false;
   int e = elem_bytes(kv_dtype);

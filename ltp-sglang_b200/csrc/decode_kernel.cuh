@@ -511,7 +511,6 @@ cudaError_t launch_decode(const DecodeParams& p, int head_dim, bool rows16, int 
     void (*fn)(const DecodeParams) = nullptr;                                                    \
     if (head_dim == 64) fn = rows16 ? decode_kernel<QT, FP8, 64, true> : decode_kernel<QT, FP8, 64, false>;        \
     else if (head_dim == 128) fn = rows16 ? decode_kernel<QT, FP8, 128, true> : decode_kernel<QT, FP8, 128, false>; \
-    else if (head_dim == 256) fn = rows16 ? decode_kernel<QT, FP8, 256, true> : decode_kernel<QT, FP8, 256, false>; \
     if (!fn) return cudaErrorInvalidValue;                                                       \
     cudaError_t e = cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, smem); \
     if (e != cudaSuccess) return e;                                                              \
