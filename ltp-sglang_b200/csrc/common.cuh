@@ -13,15 +13,19 @@
 namespace b200attn {
 
 // ---------------------------------------------------------------------------
-// Decode geometry.  One persistent CTA per SM: 8 consumer warps + 1 producer
-// warp.  A CTA serves `hc` kv heads of one "virtual request" (request x head
+// Decode geometry.  One persistent CTA per SM: 8 consumer warps + 4 producer
+// warps.  A CTA serves `hc` kv heads of one "virtual request" (request x head
 // group); consumer warp w = (head w % hc, token slice w / hc).  A chunk is
 // 16 * ts tokens; each token row of the chunk (hc heads, contiguous in the
 // pool) is moved HBM -> smem by one bulk async copy (UBLKCP) into a row padded
 // by 16 B so ldmatrix over 8 consecutive tokens is bank-conflict free.
 // ---------------------------------------------------------------------------
 constexpr int kConsumerWarps = 8;
-constexpr int kThreads = (kConsumerWarps + 1) * 32;
+// Bulk copies take uniform-register operands, so a warp issues its lanes' copies one by one
+// (~45 clk each, ncu r01): four producer warps (K/V x even/odd tokens) keep the issue rate
+// above what HBM can deliver.  384 threads cost no registers over 288 (same allocation step).
+constexpr int kProducerWarps = 4;
+constexpr int kThreads = (kConsumerWarps + kProducerWarps) * 32;
 constexpr int kRowPad = 16;           // bytes
 constexpr int kBarrierBytes = 256;    // mbarrier area at the start of smem
 constexpr int kMaxStages = 8;

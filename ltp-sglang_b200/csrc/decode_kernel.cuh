@@ -5,9 +5,9 @@
 // MHA, :240-401 grouped) and computes the math of the torch_native oracle
 // (layers/attention/torch_native_backend.py:112-180).
 //
-// Layout of one CTA (288 threads, 1 CTA / SM, grid = SM count):
-//   warp 8      producer: reads slot indices (req_to_token row or kv_indices)
-//               one chunk ahead, and issues one bulk async copy (TMA engine,
+// Layout of one CTA (384 threads, 1 CTA / SM, grid = SM count):
+//   warps 8..11 producers: read slot indices (req_to_token row or kv_indices)
+//               one chunk ahead, and issue one bulk async copy (TMA engine,
 //               SASS UBLKCP) per token row for K and for V into a ring of smem
 //               stages; completion is counted in bytes on a "full" mbarrier.
 //   warps 0..7  consumers: warp (h, slice) owns kv head h of the CTA's head
@@ -133,7 +133,7 @@ __global__ void __launch_bounds__(kThreads, 1) decode_kernel(const DecodeParams 
 
   if (threadIdx.x == 0) {
     for (int s = 0; s < p.stages; ++s) {
-      mbar_init(bar_full + s * 8, 1);
+      mbar_init(bar_full + s * 8, kProducerWarps);
       mbar_init(bar_empty + s * 8, kConsumerWarps);
     }
     fence_barrier_init();
@@ -147,45 +147,50 @@ __global__ void __launch_bounds__(kThreads, 1) decode_kernel(const DecodeParams 
   int stage = 0;
   uint32_t phase = 0;
 
-  if (warp == kConsumerWarps) {
-    // ------------------------------ producer ------------------------------
+  if (warp >= kConsumerWarps) {
+    // ------------------------------ producers ------------------------------
+    // warp pw: tensor = pw & 1 (K / V), tokens of parity pw >> 1.  Lane l, round r owns chunk
+    // token 2 * (l + 32 r) + parity.
+    const int pw = warp - kConsumerWarps;
+    const int which = pw & 1;
+    const int par = pw >> 1;
+    const uint8_t* pool = which ? p.v_pool : p.k_pool;
+    const int64_t slot_bytes = which ? p.v_slot_bytes : p.k_slot_bytes;
     while (walk.next(pv, b, hg, lc0, lc1, nchunks, vreq)) {
       const int S = pv.seq_len[b];
       const int32_t* idx = p.indices + pv.row_off[b];
-      const uint8_t* kb = p.k_pool + static_cast<int64_t>(hg) * p.row_bytes;
-      const uint8_t* vb = p.v_pool + static_cast<int64_t>(hg) * p.row_bytes;
-      int32_t nxt[4];
+      const uint8_t* base = pool + static_cast<int64_t>(hg) * p.row_bytes;
+      int32_t nxt[2];
 #pragma unroll
-      for (int r = 0; r < 4; ++r) {
-        const int t = lc0 * T + lane + 32 * r;
-        nxt[r] = (lane + 32 * r < T && t < S) ? idx[t] : 0;
+      for (int r = 0; r < 2; ++r) {
+        const int i = 2 * (lane + 32 * r) + par;
+        const int t = lc0 * T + i;
+        nxt[r] = (i < T && t < S) ? idx[t] : 0;
       }
       for (int lc = lc0; lc < lc1; ++lc) {
-        int32_t cur[4];
-#pragma unroll
-        for (int r = 0; r < 4; ++r) cur[r] = nxt[r];
+        int32_t cur[2] = {nxt[0], nxt[1]};
         if (lc + 1 < lc1) {  // index prefetch, one chunk ahead of the copies
 #pragma unroll
-          for (int r = 0; r < 4; ++r) {
-            const int t = (lc + 1) * T + lane + 32 * r;
-            nxt[r] = (lane + 32 * r < T && t < S) ? idx[t] : 0;
+          for (int r = 0; r < 2; ++r) {
+            const int i = 2 * (lane + 32 * r) + par;
+            const int t = (lc + 1) * T + i;
+            nxt[r] = (i < T && t < S) ? idx[t] : 0;
           }
         }
         const int t0 = lc * T;
         const int nvalid = S - t0 < T ? S - t0 : T;
+        const int mine = (nvalid - par + 1) >> 1;  // valid tokens of this warp's parity
         mbar_wait(bar_empty + stage * 8, phase ^ 1);
         const uint32_t full = bar_full + stage * 8;
-        if (lane == 0) mbar_arrive_expect_tx(full, static_cast<uint32_t>(nvalid) * 2u * p.row_bytes);
+        if (lane == 0) mbar_arrive_expect_tx(full, static_cast<uint32_t>(mine) * p.row_bytes);
         __syncwarp();
-        const uint32_t kdst = stage0 + stage * p.stage_bytes;
+        const uint32_t dst = stage0 + stage * p.stage_bytes + (which ? v_off : 0u);
 #pragma unroll
-        for (int r = 0; r < 4; ++r) {
-          const int i = lane + 32 * r;
-          if (i < nvalid) {
-            const int64_t slot = cur[r];
-            bulk_g2s(kdst + i * p.row_stride, kb + slot * p.k_slot_bytes, p.row_bytes, full);
-            bulk_g2s(kdst + v_off + i * p.row_stride, vb + slot * p.v_slot_bytes, p.row_bytes, full);
-          }
+        for (int r = 0; r < 2; ++r) {
+          const int i = 2 * (lane + 32 * r) + par;
+          if (i < nvalid)
+            bulk_g2s(dst + i * p.row_stride, base + static_cast<int64_t>(cur[r]) * slot_bytes,
+                     p.row_bytes, full);
         }
         if (++stage == p.stages) {
           stage = 0;
