@@ -197,6 +197,25 @@ def make_workload(cfg: Config, device="cpu", max_reqs: Optional[int] = None, sla
         sm_scale=float(D) ** -0.5, unique_tokens=unique)
 
 
+def shard_workload(w: Workload, rank: int, tp_size: int) -> Workload:
+    """Rank ``rank``'s head slice of a global workload under KV-head tensor parallelism: kv heads
+    ``[rank * Hkv / tp, (rank + 1) * Hkv / tp)`` with the ``Hq / Hkv`` q heads attached to each
+    (models/llama.py:119-132; pool sized per rank, model_runner.py:1251-1263).  Request tables,
+    ``seq_lens`` and ``out_cache_loc`` are shared by all ranks (same scheduler decisions)."""
+    c = w.cfg
+    rc = shard(c, tp_size)
+    Hq, Hkv, D = c.num_q_heads, c.num_kv_heads, c.head_dim
+    hq, hkv = rc.num_q_heads, rc.num_kv_heads
+    q = w.q.reshape(c.batch, Hq, D)[:, rank * hq:(rank + 1) * hq]
+    k = w.k.reshape(c.batch, Hkv, D)[:, rank * hkv:(rank + 1) * hkv]
+    v = w.v.reshape(c.batch, Hkv, D)[:, rank * hkv:(rank + 1) * hkv]
+    qkv = torch.cat([q.reshape(c.batch, -1), k.reshape(c.batch, -1), v.reshape(c.batch, -1)], dim=-1).contiguous()
+    q, k, v = qkv.split([hq * D, hkv * D, hkv * D], dim=-1)
+    return replace(w, cfg=rc, qkv=qkv, q=q, k=k, v=v,
+                   k_pool=w.k_pool[:, rank * hkv:(rank + 1) * hkv].contiguous(),
+                   v_pool=w.v_pool[:, rank * hkv:(rank + 1) * hkv].contiguous())
+
+
 def small(name: str, **kw) -> Config:
     """A reduced copy of a named config for oracle-speed tests."""
     return replace(CONFIGS[name], **kw)
