@@ -247,10 +247,17 @@ class Rank:
         return float(t.item())
 
     def flush_l2(self):
-        """Writes a buffer twice the size of L2 so the next step starts from HBM."""
+        """Writes a buffer twice the size of L2, then reads a second one of the same size, so the
+        next step starts from HBM with an L2 full of CLEAN lines.  (A write-only flush leaves
+        126 MB of dirty lines whose write-back lands inside the next timed step: ~20 us of HBM
+        time, as much as a small config's whole step.)"""
+        torch = self.torch
         if self.flush_buf is None:
-            self.flush_buf = self.torch.empty(2 * L2_BYTES, dtype=self.torch.uint8, device=self.dev)
+            self.flush_buf = torch.empty(2 * L2_BYTES, dtype=torch.uint8, device=self.dev)
+            self.flush_src = torch.zeros(2 * L2_BYTES // 8, dtype=torch.int64, device=self.dev)
+            self.flush_sink = torch.zeros((), dtype=torch.int64, device=self.dev)
         self.flush_buf.zero_()
+        torch.sum(self.flush_src, out=self.flush_sink)
 
     def timed(self, fn, steps: int, flush: bool) -> float:
         """ms per step by CUDA events on the current stream.  With `flush` every step is timed on
@@ -298,7 +305,7 @@ def measure(R: Rank, args, gcfg, scaling: str, with_clocks: bool = True) -> dict
     # (one 0.5-3 MB device copy inside the timed region) instead of letting k drift to inf.
     qkv0 = w.qkv.clone()
     refresh = fp8
-    l2_note = ("L2 flushed (252 MB memset) before every timed step; each step timed by its own event pair"
+    l2_note = ("L2 flushed (252 MB memset, then a 252 MB read so no dirty lines remain) before every timed step; each step timed by its own event pair"
                if flush else "per-GPU KV working set (%d MB) far larger than the 126 MB L2; no flush" % (kv_bytes >> 20))
 
     # ---------------- device-resident timing: `value` ----------------

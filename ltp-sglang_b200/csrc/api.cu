@@ -1,6 +1,7 @@
 // C-ABI entry points that are not tied to one kernel file: the decode call
 // (K2 + K3), geometry / workspace queries, error strings, launch counter.
 #include <atomic>
+#include <cstdlib>
 
 #include "decode_kernel.cuh"
 #include "merge.cuh"
@@ -26,6 +27,16 @@ int sm_count() {
   }
   cache[dev].store(n, std::memory_order_relaxed);
   return n;
+}
+
+// Rows up to this many bytes are staged with 16-byte cp.async instead of one bulk copy per row.
+// B200ATTN_CPASYNC_MAX_ROW overrides the default (a tuning aid; read once).
+static int cp_async_max_row() {
+  static const int v = [] {
+    const char* e = getenv("B200ATTN_CPASYNC_MAX_ROW");
+    return e ? atoi(e) : 256;
+  }();
+  return v;
 }
 
 template <>
@@ -139,6 +150,9 @@ extern "C" __attribute__((visibility("default"))) int b200attn_decode(const b200
   p.stage_bytes = g.stage_bytes;
   p.stages = g.stages;
   p.chunk_tokens = g.chunk_tokens;
+  p.cp_async = g.row_bytes <= cp_async_max_row();
+  p.unit_shift = 0;
+  while ((16 << p.unit_shift) < g.row_bytes) ++p.unit_shift;
   p.sm_scale_k = a->sm_scale * a->k_scale;
   p.scale_log2 = p.sm_scale_k * kLog2e;
   p.logit_cap = a->logit_cap;

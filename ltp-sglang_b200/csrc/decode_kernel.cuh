@@ -45,6 +45,8 @@ struct DecodeParams {
   int32_t batch, hq;
   int32_t hc, ts, ng, group;
   int32_t row_bytes, row_stride, stage_bytes, stages, chunk_tokens;
+  int32_t cp_async;              // 1: producers use 16-byte cp.async (small rows), 0: one bulk copy per row
+  int32_t unit_shift;            // log2(row_bytes / 16)
   float scale_log2;              // sm_scale * k_scale * log2(e)
   float sm_scale_k;              // sm_scale * k_scale
   float logit_cap;
@@ -133,7 +135,7 @@ __global__ void __launch_bounds__(kThreads, 1) decode_kernel(const DecodeParams 
 
   if (threadIdx.x == 0) {
     for (int s = 0; s < p.stages; ++s) {
-      mbar_init(bar_full + s * 8, kProducerWarps);
+      mbar_init(bar_full + s * 8, p.cp_async ? kProducerWarps * 32 : kProducerWarps);
       mbar_init(bar_empty + s * 8, kConsumerWarps);
     }
     fence_barrier_init();
@@ -156,6 +158,63 @@ __global__ void __launch_bounds__(kThreads, 1) decode_kernel(const DecodeParams 
     const int par = pw >> 1;
     const uint8_t* pool = which ? p.v_pool : p.k_pool;
     const int64_t slot_bytes = which ? p.v_slot_bytes : p.k_slot_bytes;
+    if (p.cp_async) {
+      // Small rows (<= 256 B): a bulk copy is issued per row at ~20 clk / row / SM whatever its
+      // size (4.2 TB/s at 256 B, 2.0 TB/s at 128 B, profiles/ r01 tp-sim), so rows are moved as
+      // 16-byte cp.async units instead: one warp instruction carries 512 B (6.1 / 4.2 TB/s).
+      // From 512 B up the bulk copy wins (its issue costs the SM nothing).  Warp (tensor, half)
+      // owns tokens [half * T/2, (half + 1) * T/2) of every chunk; lane l holds the slot ids of
+      // tokens l and l + 32 of that range (one chunk ahead) and hands them out by shuffle.
+      const int ush = p.unit_shift;
+      const int umask = (1 << ush) - 1;
+      const int Tw = T >> 1;
+      const int n_instr = (Tw << ush) >> 5;  // multiple of 8: a tensor-chunk is >= 8 KB
+      const int tbase = par * Tw;
+      while (walk.next(pv, b, hg, lc0, lc1, nchunks, vreq)) {
+        const int S = pv.seq_len[b];
+        const int32_t* idx = p.indices + pv.row_off[b];
+        const uint8_t* base = pool + static_cast<int64_t>(hg) * p.row_bytes;
+        int32_t nxt[2];
+#pragma unroll
+        for (int r = 0; r < 2; ++r) {
+          const int i = lane + 32 * r;
+          const int t = lc0 * T + tbase + i;
+          nxt[r] = (i < Tw && t < S) ? idx[t] : 0;
+        }
+        for (int lc = lc0; lc < lc1; ++lc) {
+          const int32_t cur0 = nxt[0], cur1 = nxt[1];
+          if (lc + 1 < lc1) {
+#pragma unroll
+            for (int r = 0; r < 2; ++r) {
+              const int i = lane + 32 * r;
+              const int t = (lc + 1) * T + tbase + i;
+              nxt[r] = (i < Tw && t < S) ? idx[t] : 0;
+            }
+          }
+          const int nvalid = S - lc * T - tbase;  // valid tokens of this warp's range (may be <= 0)
+          mbar_wait(bar_empty + stage * 8, phase ^ 1);
+          const uint32_t full = bar_full + stage * 8;
+          const uint32_t dst = stage0 + stage * p.stage_bytes + (which ? v_off : 0u) + tbase * p.row_stride;
+#pragma unroll 8
+          for (int i = 0; i < n_instr; ++i) {
+            const int u = i * 32 + lane;
+            const int tl = u >> ush;
+            const int col = (u & umask) << 4;
+            const int32_t s0 = __shfl_sync(0xffffffffu, cur0, tl & 31);
+            const int32_t s1 = __shfl_sync(0xffffffffu, cur1, tl & 31);
+            const int32_t slot = tl < 32 ? s0 : s1;
+            if (tl < nvalid)
+              cp_async16(dst + tl * p.row_stride + col, base + static_cast<int64_t>(slot) * slot_bytes + col);
+          }
+          cp_async_mbar_arrive_noinc(full);
+          if (++stage == p.stages) {
+            stage = 0;
+            phase ^= 1;
+          }
+        }
+      }
+      return;
+    }
     while (walk.next(pv, b, hg, lc0, lc1, nchunks, vreq)) {
       const int S = pv.seq_len[b];
       const int32_t* idx = p.indices + pv.row_off[b];
