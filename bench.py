@@ -246,6 +246,26 @@ class Rank:
             self.dist.all_reduce(t, op=self.dist.ReduceOp.MAX)
         return float(t.item())
 
+    def shutdown(self):
+        """Leaves the process group without ever hanging the launcher: everything this rank had to
+        report is printed by now, so if NCCL teardown stalls (seen with CUDA graphs that captured a
+        collective still alive) a watchdog ends the process with exit code 0 after 20 s."""
+        sys.stdout.flush()
+        if self.world <= 1:
+            return
+        import gc
+
+        def _bail():
+            time.sleep(20)
+            os._exit(0)
+
+        threading.Thread(target=_bail, daemon=True).start()
+        gc.collect()
+        if self.cuda:
+            self.torch.cuda.synchronize()
+        self.dist.barrier()
+        self.dist.destroy_process_group()
+
     def flush_l2(self):
         """Writes a buffer twice the size of L2, then reads a second one of the same size, so the
         next step starts from HBM with an L2 full of CLEAN lines.  (A write-only flush leaves
@@ -576,9 +596,7 @@ def main():
             line["cpu_baseline"] = {"value": tps, "unit": UNIT, "cores": info["cores"], "kind": info["kind"],
                                     "sample": info["sample"], "ms_per_step": cms, "gb_per_s": info["gb_per_s"]}
         print(json.dumps(line), flush=True)
-    if world > 1:
-        R.dist.barrier()
-        R.dist.destroy_process_group()
+    R.shutdown()
 
 
 def _measured_peak():

@@ -19,6 +19,9 @@
  *                       (decode_attention_fwd: split-KV stage 1 :240-488 + stage 2
  *                       LSE merge :491-596), and the math of
  *                       torch_native_backend.py:112-180
+ *   b200attn_rope_kv_store  python/sglang/srt/layers/rotary_embedding.py:218-236 +
+ *                       sgl-kernel/csrc/elementwise/rope.cu:22-89 (RoPE in place) fused with
+ *                       set_kv_buffer (memory_pool.py:369-407); call site models/llama.py:186-189
  *   b200attn_merge_states  sgl-kernel/csrc/attention/merge_attn_states.cu:31-204
  *                       (merge_state_v2: 2-way (o, lse) merge)
  *
@@ -103,6 +106,38 @@ typedef struct {
 } b200attn_kv_store_args;
 
 int b200attn_kv_store(const b200attn_kv_store_args* args, b200attn_stream_t stream);
+
+/* ------------------------------------------------------------------ */
+/* K4: fused RoPE + KV store (producer side of K1)                     */
+/* ------------------------------------------------------------------ */
+/* Replaces, in one launch, the two steps LlamaAttention.forward runs between the qkv
+ * projection and attention (python/sglang/srt/models/llama.py:186-189):
+ *   q, k = rotary_emb(positions, q, k)      layers/rotary_embedding.py:218-236 (forward_cuda)
+ *                                           -> sgl-kernel/csrc/elementwise/rope.cu:22-89
+ *                                           (apply_rope_pos_ids_cos_sin_cache, in place)
+ *   set_kv_buffer(layer, loc, k, v, ...)    mem_cache/memory_pool.py:369-407
+ * q and k are rotated IN PLACE (fp32 math on the fp32 cos|sin cache, one rounding to the
+ * source dtype: the arithmetic of the reference's CUDA path); the rotated k and v are then
+ * stored exactly as b200attn_kv_store would store them. */
+typedef struct {
+  void* q;                      /* [n_tokens, num_q_heads, head_dim], strides in elements */
+  int64_t q_stride_token, q_stride_head;
+  int32_t num_q_heads;
+  int32_t rotary_dim;           /* leading dims of each head that rotate; even, <= head_dim,
+                                   multiple of 16 for neox / of 8 for interleaved layout */
+  int32_t is_neox;              /* 1: pairs (i, i + rotary_dim/2); 0: pairs (2i, 2i + 1) */
+  int32_t pos_dtype;            /* B200ATTN_I32 | B200ATTN_I64 */
+  const void* positions;        /* [n_tokens] */
+  const float* cos_sin_cache;   /* [max_position, rotary_dim] fp32: cos | sin halves */
+  int64_t cache_stride;         /* elements between cache rows */
+  int64_t max_position;         /* rows in the cache; positions are clamped into range */
+  int32_t save_kv;              /* 1: scatter rotated k and v into the pool; 0: RoPE only */
+  int32_t pad_;
+  b200attn_kv_store_args kv;    /* k (rotated in place), v, loc, pools, scales: as for
+                                   b200attn_kv_store; head_dim must equal v_head_dim here */
+} b200attn_rope_kv_store_args;
+
+int b200attn_rope_kv_store(const b200attn_rope_kv_store_args* args, b200attn_stream_t stream);
 
 /* ------------------------------------------------------------------ */
 /* K0: plan (once per forward; shared by all layers)                   */

@@ -8,7 +8,7 @@ from . import capi
 capi.lib()
 
 from . import ops  # noqa: E402  (registers torch.ops.b200attn.*)
-from .backend import B200AttnBackend, ForwardMetadata, store_kv  # noqa: E402
+from .backend import B200AttnBackend, ForwardMetadata, rope_store_kv, store_kv  # noqa: E402
 from .interfaces import (  # noqa: E402
     AttentionBackend,
     AttnLayer,
@@ -24,6 +24,7 @@ __all__ = [
     "B200AttnBackend",
     "ForwardMetadata",
     "store_kv",
+    "rope_store_kv",
     "AttentionBackend",
     "AttnLayer",
     "ForwardBatch",

@@ -60,6 +60,39 @@ def store_kv(k_pool: torch.Tensor, v_pool: torch.Tensor, loc: torch.Tensor, cach
     torch.ops.b200attn.kv_store(cache_k, cache_v, loc, k_pool, v_pool, ks, vs, kt, vt, mode)
 
 
+def rope_store_kv(q: torch.Tensor, k: torch.Tensor, v: Optional[torch.Tensor], positions: torch.Tensor,
+                  cos_sin_cache: torch.Tensor, is_neox: bool = True, loc: Optional[torch.Tensor] = None,
+                  k_pool: Optional[torch.Tensor] = None, v_pool: Optional[torch.Tensor] = None,
+                  k_scale=None, v_scale=None, scale_mode: Optional[int] = None) -> None:
+    """One launch for ``rotary_emb(positions, q, k)`` + ``set_kv_buffer(layer, loc, k, v, ...)``
+    (models/llama.py:186-189; layers/rotary_embedding.py:218-236; memory_pool.py:369-407).
+
+    ``q`` / ``k`` ``[tokens, heads, head_dim]`` are rotated in place (views of the fused qkv buffer are
+    fine); with ``loc`` and the layer's pools the rotated k and v are stored with ``store_kv``
+    semantics, and attention is then called with ``save_kv_cache=False``.  ``cos_sin_cache`` is the
+    fp32 ``RotaryEmbedding.cos_sin_cache``; its width is the rotary dim.
+    """
+    ks = vs = kt = vt = None
+    mode = capi.SCALE_NONE
+    if loc is not None:
+        if loc.dtype != torch.int64:
+            loc = loc.to(torch.int64)
+        fp8 = k_pool.dtype in (torch.uint8, torch.float8_e4m3fn)
+        if fp8 and (k_scale is not None or v_scale is not None):
+            tensors = isinstance(k_scale, torch.Tensor) or isinstance(v_scale, torch.Tensor)
+            mode = capi.SCALE_TRUE_DIV if tensors else capi.SCALE_RECIP_MUL
+            if scale_mode is not None:
+                mode = scale_mode
+            if tensors:
+                kt = _scale_tensor(k_scale, k.device)
+                vt = _scale_tensor(v_scale, k.device)
+            else:
+                ks = 1.0 if k_scale is None else float(k_scale)
+                vs = 1.0 if v_scale is None else float(v_scale)
+    torch.ops.b200attn.rope_kv_store(q, k, v, positions, cos_sin_cache, bool(is_neox), loc, k_pool, v_pool,
+                                     ks, vs, kt, vt, mode)
+
+
 def _scale_tensor(s, device) -> torch.Tensor:
     if s is None:
         return torch.ones((), dtype=torch.float32, device=device)

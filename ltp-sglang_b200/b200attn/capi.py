@@ -51,6 +51,25 @@ class KvStoreArgs(C.Structure):
     ]
 
 
+class RopeKvStoreArgs(C.Structure):
+    _fields_ = [
+        ("q", C.c_void_p),
+        ("q_stride_token", C.c_int64),
+        ("q_stride_head", C.c_int64),
+        ("num_q_heads", C.c_int32),
+        ("rotary_dim", C.c_int32),
+        ("is_neox", C.c_int32),
+        ("pos_dtype", C.c_int32),
+        ("positions", C.c_void_p),
+        ("cos_sin_cache", C.c_void_p),
+        ("cache_stride", C.c_int64),
+        ("max_position", C.c_int64),
+        ("save_kv", C.c_int32),
+        ("pad_", C.c_int32),
+        ("kv", KvStoreArgs),
+    ]
+
+
 class PlanArgs(C.Structure):
     _fields_ = [
         ("req_to_token", C.c_void_p),
@@ -123,6 +142,7 @@ class MergeStatesArgs(C.Structure):
 # name -> (restype, argtypes); every symbol include/b200attn.h declares.
 SYMBOLS = {
     "b200attn_kv_store": (C.c_int, [C.POINTER(KvStoreArgs), C.c_void_p]),
+    "b200attn_rope_kv_store": (C.c_int, [C.POINTER(RopeKvStoreArgs), C.c_void_p]),
     "b200attn_plan_bytes": (C.c_size_t, [C.c_int32]),
     "b200attn_plan": (C.c_int, [C.POINTER(PlanArgs), C.c_void_p]),
     "b200attn_workspace_bytes": (

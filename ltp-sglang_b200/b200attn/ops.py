@@ -83,6 +83,72 @@ def _kv_store(k, v, loc, k_pool, v_pool, k_scale, v_scale, k_scale_t, v_scale_t,
         capi.check("b200attn_kv_store", capi.lib().b200attn_kv_store(C.byref(a), _stream(k)))
 
 
+def _fill_store_args(a, k, v, loc, k_pool, v_pool, k_scale, v_scale, k_scale_t, v_scale_t, scale_mode):
+    a.k, a.v = k.data_ptr(), v.data_ptr()
+    a.k_stride_token, a.k_stride_head = k.stride(0), k.stride(1)
+    a.v_stride_token, a.v_stride_head = v.stride(0), v.stride(1)
+    a.loc = loc.data_ptr()
+    a.k_pool, a.v_pool = k_pool.data_ptr(), v_pool.data_ptr()
+    a.k_pool_stride_slot, a.v_pool_stride_slot = k_pool.stride(0), v_pool.stride(0)
+    a.pool_slots = k_pool.shape[0]
+    a.n_tokens, a.num_kv_heads = k.shape[0], k.shape[1]
+    a.head_dim, a.v_head_dim = k.shape[2], v.shape[2]
+    a.src_dtype = dtype_code(k.dtype)
+    a.pool_dtype = dtype_code(k_pool.dtype)
+    a.scale_mode = scale_mode
+    a.mutate_src = 1
+    a.k_scale = 1.0 if k_scale is None else k_scale
+    a.v_scale = 1.0 if v_scale is None else v_scale
+    a.k_scale_ptr, a.v_scale_ptr = _ptr(k_scale_t), _ptr(v_scale_t)
+
+
+def _rope_kv_store(q, k, v, positions, cos_sin_cache, is_neox, loc, k_pool, v_pool, k_scale, v_scale,
+                   k_scale_t, v_scale_t, scale_mode):
+    """RoPE on q and k in place (+ the KV store when ``loc`` / pools are given)."""
+    save = loc is not None
+    _cuda(q, k, v, positions, cos_sin_cache, loc, k_pool, v_pool, k_scale_t, v_scale_t)
+    if q.dim() != 3 or k.dim() != 3 or q.stride(2) != 1 or k.stride(2) != 1:
+        raise ValueError("rope_kv_store: q / k must be [tokens, heads, dim] with a contiguous last dim")
+    if q.shape[0] != k.shape[0] or q.shape[2] != k.shape[2] or q.dtype != k.dtype:
+        raise ValueError("rope_kv_store: q and k disagree on tokens, head_dim or dtype")
+    if cos_sin_cache.dtype != torch.float32 or cos_sin_cache.dim() != 2 or cos_sin_cache.stride(1) != 1:
+        raise ValueError("rope_kv_store: cos_sin_cache should be float32 [max_position, rotary_dim]")
+    if positions.dtype not in _IDX or not positions.is_contiguous() or positions.numel() != q.shape[0]:
+        raise TypeError("rope_kv_store: positions must be contiguous int32/int64 [tokens]")
+    a = capi.RopeKvStoreArgs()
+    a.q = q.data_ptr()
+    a.q_stride_token, a.q_stride_head = q.stride(0), q.stride(1)
+    a.num_q_heads = q.shape[1]
+    a.rotary_dim = cos_sin_cache.shape[1]
+    a.is_neox = 1 if is_neox else 0
+    a.pos_dtype = _IDX[positions.dtype]
+    a.positions = positions.data_ptr()
+    a.cos_sin_cache = cos_sin_cache.data_ptr()
+    a.cache_stride = cos_sin_cache.stride(0)
+    a.max_position = cos_sin_cache.shape[0]
+    a.save_kv = 1 if save else 0
+    if save:
+        if v is None or k_pool is None or v_pool is None:
+            raise ValueError("rope_kv_store: v, k_pool and v_pool are needed to store")
+        if v.dim() != 3 or v.stride(2) != 1 or v.shape != k.shape:
+            raise ValueError("rope_kv_store: v must match k ([tokens, kv_heads, dim])")
+        if loc.dtype != torch.int64 or not loc.is_contiguous() or loc.numel() != k.shape[0]:
+            raise TypeError("rope_kv_store: loc must be a contiguous int64 [tokens] tensor (out_cache_loc)")
+        if not k_pool.is_contiguous() or not v_pool.is_contiguous() or k_pool.dim() != 3:
+            raise ValueError("rope_kv_store: pools must be contiguous [slots, kv_heads, dim]")
+        if k.shape[1] != k_pool.shape[1] or k.shape[2] != k_pool.shape[2] or v.shape[2] != v_pool.shape[2]:
+            raise ValueError("rope_kv_store: k/v shape does not match the pool")
+        _fill_store_args(a.kv, k, v, loc, k_pool, v_pool, k_scale, v_scale, k_scale_t, v_scale_t, scale_mode)
+    else:
+        a.kv.k = k.data_ptr()
+        a.kv.k_stride_token, a.kv.k_stride_head = k.stride(0), k.stride(1)
+        a.kv.n_tokens, a.kv.num_kv_heads = k.shape[0], k.shape[1]
+        a.kv.head_dim = a.kv.v_head_dim = k.shape[2]
+        a.kv.src_dtype = a.kv.pool_dtype = dtype_code(k.dtype)
+    with torch.cuda.device(q.device):
+        capi.check("b200attn_rope_kv_store", capi.lib().b200attn_rope_kv_store(C.byref(a), _stream(q)))
+
+
 def _plan(req_to_token, req_pool_indices, seq_lens, plan_buf, kv_indptr, kv_indices,
           num_q_heads, num_kv_heads, head_dim, kv_dtype, max_ctas, min_chunks):
     _cuda(req_to_token, req_pool_indices, seq_lens, plan_buf, kv_indptr, kv_indices)
@@ -201,6 +267,11 @@ _LIB.define(
     "float? k_scale, float? v_scale, Tensor? k_scale_t, Tensor? v_scale_t, int scale_mode) -> ()"
 )
 _LIB.define(
+    "rope_kv_store(Tensor(a!) q, Tensor(b!) k, Tensor(c!)? v, Tensor positions, Tensor cos_sin_cache, "
+    "bool is_neox, Tensor? loc, Tensor(d!)? k_pool, Tensor(e!)? v_pool, float? k_scale, float? v_scale, "
+    "Tensor? k_scale_t, Tensor? v_scale_t, int scale_mode) -> ()"
+)
+_LIB.define(
     "plan(Tensor req_to_token, Tensor req_pool_indices, Tensor seq_lens, Tensor(a!) plan_buf, "
     "Tensor(b!)? kv_indptr, Tensor(c!)? kv_indices, int num_q_heads, int num_kv_heads, int head_dim, "
     "int kv_dtype, int max_ctas, int min_chunks) -> ()"
@@ -219,6 +290,7 @@ _LIB.define(
     "Tensor(b!)? lse_out) -> ()"
 )
 _LIB.impl("kv_store", _kv_store, "CUDA")
+_LIB.impl("rope_kv_store", _rope_kv_store, "CUDA")
 _LIB.impl("plan", _plan, "CUDA")
 _LIB.impl("plan_csr", _plan_csr, "CUDA")
 _LIB.impl("decode", _decode, "CUDA")

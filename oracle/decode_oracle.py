@@ -25,6 +25,11 @@ What each function follows (paths relative to the reference tree):
 * ``torch_native_decode`` the same loop through torch SDPA in the model dtype (what the
                           reference backend literally executes; used as the timed CPU port)
 * ``merge_states``        sgl-kernel/csrc/attention/merge_attn_states.cu:31-106
+* ``cos_sin_cache`` / ``rope``  python/sglang/srt/layers/rotary_embedding.py:113-166
+                          (``_compute_cos_sin_cache`` and ``forward_native`` with
+                          ``_apply_rotary_emb`` :49-75), in float64 on the fp32 cache: the
+                          arithmetic of the reference's CUDA path
+                          (sgl-kernel/csrc/elementwise/rope.cu:22-89 keeps the cache in fp32)
 """
 from __future__ import annotations
 
@@ -270,3 +275,41 @@ def merge_n(o: np.ndarray, lse: np.ndarray) -> Tuple[np.ndarray, np.ndarray]:
     s = w.sum(axis=0)
     out = (o.astype(np.float64) * w[..., None]).sum(axis=0) / s[..., None]
     return out.astype(np.float32), (m + np.log(s)).astype(np.float32)
+
+
+# --------------------------------------------------------------------------- #
+# rotary embedding
+# --------------------------------------------------------------------------- #
+def cos_sin_cache(rotary_dim: int, max_position: int, base: float = 10000.0) -> torch.Tensor:
+    """fp32 [max_position, rotary_dim] cache, cos | sin halves (rotary_embedding.py:113-136)."""
+    inv_freq = 1.0 / (base ** (torch.arange(0, rotary_dim, 2, dtype=torch.float) / rotary_dim))
+    t = torch.arange(max_position, dtype=torch.float)
+    freqs = torch.einsum("i,j -> ij", t, inv_freq)
+    return torch.cat((freqs.cos(), freqs.sin()), dim=-1)
+
+
+def rope(positions: torch.Tensor, x: torch.Tensor, cache: torch.Tensor, is_neox: bool = True) -> np.ndarray:
+    """Rotates ``x`` [tokens, heads, head_dim] (rotary_embedding.py:138-166, :49-75); returns float64.
+
+    The first ``rotary_dim = cache.shape[1]`` dims of each head rotate, the rest pass through.
+    neox: pairs (i, i + rotary_dim/2); otherwise (2i, 2i+1).  The caller rounds to the model dtype.
+    """
+    xf = _to_f32(x).astype(np.float64)
+    rot = cache.shape[1]
+    cs = cache.detach().cpu().numpy().astype(np.float64)[positions.detach().cpu().numpy().astype(np.int64)]
+    cos, sin = cs[:, None, : rot // 2], cs[:, None, rot // 2:]
+    out = xf.copy()
+    if is_neox:
+        x1, x2 = xf[..., : rot // 2], xf[..., rot // 2: rot]
+        out[..., : rot // 2] = x1 * cos - x2 * sin
+        out[..., rot // 2: rot] = x2 * cos + x1 * sin
+    else:
+        x1, x2 = xf[..., 0:rot:2], xf[..., 1:rot:2]
+        out[..., 0:rot:2] = x1 * cos - x2 * sin
+        out[..., 1:rot:2] = x2 * cos + x1 * sin
+    return out
+
+
+def round_to_dtype(x: np.ndarray, dtype: torch.dtype) -> torch.Tensor:
+    """float64/float32 array -> torch tensor of ``dtype`` with one RNE rounding from float32."""
+    return torch.from_numpy(np.ascontiguousarray(x, dtype=np.float32)).to(dtype)

@@ -219,3 +219,11 @@ def shard_workload(w: Workload, rank: int, tp_size: int) -> Workload:
 def small(name: str, **kw) -> Config:
     """A reduced copy of a named config for oracle-speed tests."""
     return replace(CONFIGS[name], **kw)
+
+
+def cos_sin_cache(rotary_dim: int, max_position: int, base: float = 10000.0) -> torch.Tensor:
+    """Synthetic-input helper: the fp32 ``[max_position, rotary_dim]`` cos | sin table a
+    ``RotaryEmbedding`` holds (python/sglang/srt/layers/rotary_embedding.py:113-136)."""
+    inv_freq = 1.0 / (base ** (torch.arange(0, rotary_dim, 2, dtype=torch.float) / rotary_dim))
+    freqs = torch.einsum("i,j -> ij", torch.arange(max_position, dtype=torch.float), inv_freq)
+    return torch.cat((freqs.cos(), freqs.sin()), dim=-1)

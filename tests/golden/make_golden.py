@@ -187,9 +187,53 @@ def gen_merge():
     print("merge ok")
 
 
+# (head_size, rotary_dim, max_position, base, is_neox, tokens, q heads, kv heads): the shape list of
+# the reference's own RoPE test (sgl-kernel/tests/test_rotary_embedding.py:146-151), fewer tokens.
+ROPE_CASES = {
+    "g9_rope_neox_d64": (64, 64, 32, 8000, True, 24, 1, 1),
+    "g9_rope_neox_d256_r128": (256, 128, 4096, 10000, True, 12, 4, 2),
+    "g9_rope_gptj_d128": (128, 128, 2048, 10000, False, 10, 16, 4),
+    "g9_rope_gptj_d512_r128": (512, 128, 311, 10000, False, 9, 4, 2),
+    "g9_rope_neox_d128_llama": (128, 128, 8192, 500000, True, 11, 32, 8),
+}
+
+
+def gen_rope():
+    """``RotaryEmbedding.forward_native`` (layers/rotary_embedding.py:138-166) of the reference, on
+    fp32 inputs (exact fp32 arithmetic on the fp32 cache: pins the oracle) and on bf16 inputs (the
+    reference's bf16 arithmetic: the 1e-2 comparison its own test makes)."""
+    ref_loader.load()
+    sys.path.insert(0, os.path.join(ref_loader.REFERENCE_ROOT, "python"))
+    from sglang.srt.layers.rotary_embedding import RotaryEmbedding
+    sys.path.pop(0)
+    for name, (hs, rot, maxpos, base, neox, n, hq, hkv) in ROPE_CASES.items():
+        r = RotaryEmbedding.__new__(RotaryEmbedding)   # __init__ probes platform-specific kernels
+        torch.nn.Module.__init__(r)
+        r.head_size, r.rotary_dim, r.max_position_embeddings, r.base = hs, rot, maxpos, base
+        r.is_neox_style, r.dtype = neox, torch.float32
+        r.register_buffer("cos_sin_cache", r._compute_cos_sin_cache(), persistent=False)
+        g = torch.Generator().manual_seed(hs + rot + n)
+        pos = torch.randint(0, maxpos, (n,), generator=g, dtype=torch.int64)
+        q = torch.randn((n, hq * hs), generator=g).to(torch.bfloat16)
+        k = torch.randn((n, hkv * hs), generator=g).to(torch.bfloat16)
+        q32, k32 = r.forward_native(pos, q.float(), k.float())
+        q16, k16 = r.forward_native(pos, q.clone(), k.clone())
+        np.savez_compressed(os.path.join(HERE, name + ".npz"), positions=pos.numpy(), q_in=bits(q), k_in=bits(k),
+                 cache_rows=r.cos_sin_cache[pos].numpy(), q_out_f32=q32.numpy(), k_out_f32=k32.numpy(),
+                 q_out_bf16=bits(q16), k_out_bf16=bits(k16),
+                 meta=np.array([hs, rot, maxpos, base, int(neox), n, hq, hkv], dtype=np.int64))
+    print("rope ok")
+
+
 if __name__ == "__main__":
     torch.manual_seed(0)
+    only = sys.argv[1] if len(sys.argv) > 1 else "all"
     ref = ref_loader.load()
-    gen_decode_cases(ref)
-    gen_fp8_store(ref)
-    gen_merge()
+    if only in ("all", "decode"):
+        gen_decode_cases(ref)
+    if only in ("all", "fp8"):
+        gen_fp8_store(ref)
+    if only in ("all", "merge"):
+        gen_merge()
+    if only in ("all", "rope"):
+        gen_rope()

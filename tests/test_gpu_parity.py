@@ -433,3 +433,99 @@ def test_c2_full_size_properties():
     out3 = run_decode(backend, runner, w, save_kv_cache=False)
     torch.cuda.synchronize()
     assert (out3.float() - 0.75).abs().max().item() <= 1e-2
+
+
+# ----------------------------------------------------------------------------- #
+# fused RoPE + KV store (K4)
+# ----------------------------------------------------------------------------- #
+from tests.golden.make_golden import ROPE_CASES  # noqa: E402
+
+
+def _ulp_close(got: torch.Tensor, ref64: np.ndarray, dtype: torch.dtype):
+    """|got - ref| <= 1 ulp of `dtype` at |ref| (one rounding from fp32 arithmetic)."""
+    eps = 2.0 ** -8 if dtype == torch.bfloat16 else 2.0 ** -11
+    g = got.float().cpu().numpy().astype(np.float64)
+    bound = eps * np.abs(ref64) + 1e-30 + 2.0 ** -24   # f16 subnormal floor
+    bad = np.abs(g - ref64) > bound
+    assert not bad.any(), f"{bad.sum()} elements off by more than 1 ulp; worst {np.abs(g - ref64).max()}"
+
+
+@pytest.mark.parametrize("name", sorted(ROPE_CASES))
+def test_rope_golden(name):
+    """RoPE only (save_kv = 0) on the reference's own test shapes, against the fp32 run of the
+    reference's forward_native."""
+    import b200attn  # noqa: F401
+
+    g = np.load(os.path.join(GOLDEN_DIR, name + ".npz"))
+    hs, rot, maxpos, base, neox, n, hq, hkv = (int(x) for x in g["meta"])
+    rows = torch.from_numpy(g["cache_rows"]).to(DEV)
+    bf = lambda a: torch.from_numpy(a.view(np.int16).copy()).view(torch.bfloat16)  # noqa: E731
+    q = bf(g["q_in"]).view(n, hq, hs).to(DEV)
+    k = bf(g["k_in"]).view(n, hkv, hs).to(DEV)
+    for pos_dtype in (torch.int64, torch.int32):
+        q1, k1 = q.clone(), k.clone()
+        torch.ops.b200attn.rope_kv_store(q1, k1, None, torch.arange(n, device=DEV, dtype=pos_dtype), rows,
+                                         bool(neox), None, None, None, None, None, None, None, 0)
+        torch.cuda.synchronize()
+        _ulp_close(q1.view(n, -1), g["q_out_f32"].astype(np.float64), torch.bfloat16)
+        _ulp_close(k1.view(n, -1), g["k_out_f32"].astype(np.float64), torch.bfloat16)
+
+
+@pytest.mark.parametrize("kv_dtype,q_dtype", [("bf16", "bf16"), ("f16", "f16"), ("fp8_e4m3", "bf16")])
+@pytest.mark.parametrize("neox", [True, False])
+def test_rope_kv_store_fused(kv_dtype, q_dtype, neox):
+    """Fused launch == oracle RoPE (1 ulp) followed by the bit-exact store of the rotated k and v;
+    q / k / v views of one fused qkv buffer (strided), scales as 0-dim CUDA tensors for fp8."""
+    import b200attn
+    from oracle import decode_oracle as oracle
+
+    cfg = synth.Config("rope", 7, 0, 16, 4, 128, kv_dtype=kv_dtype, q_dtype=q_dtype, page_size=4,
+                       ragged=(3, 90), k_scale=0.5, v_scale=2.0, seed=31)
+    w_cpu, w = _pair(cfg)
+    _check_same_inputs(w_cpu, w)
+    c = cfg
+    B, Hq, Hkv, D = c.batch, c.num_q_heads, c.num_kv_heads, c.head_dim
+    cache = oracle.cos_sin_cache(D, 4096, 10000.0)
+    pos = (w_cpu.seq_lens - 1).to(torch.int64)
+    q, k, v = (t.view(B, -1, D) for t in (w.q, w.k, w.v))
+    fp8 = kv_dtype == "fp8_e4m3"
+    kt = torch.tensor(c.k_scale, dtype=torch.float32, device=DEV) if fp8 else None
+    vt = torch.tensor(c.v_scale, dtype=torch.float32, device=DEV) if fp8 else None
+    b200attn.rope_store_kv(q, k, v, pos.to(DEV), cache.to(DEV), neox, w.out_cache_loc, w.k_pool, w.v_pool, kt, vt)
+    torch.cuda.synchronize()
+
+    dt = w_cpu.q.dtype
+    q_ref = oracle.rope(pos, w_cpu.q.reshape(B, Hq, D), cache, neox)
+    k_ref = oracle.rope(pos, w_cpu.k.reshape(B, Hkv, D), cache, neox)
+    _ulp_close(q, q_ref, dt)
+    if not fp8:
+        _ulp_close(k, k_ref, dt)
+    # store parity: bit equality end to end against an fp32 restatement of the kernel arithmetic
+    # (products and sums each rounded to fp32, one rounding to the source dtype)
+    def rot32(x):
+        xf = x.float().numpy().astype(np.float32)
+        cs = cache.numpy()[pos.numpy()]
+        co, si = cs[:, None, : D // 2], cs[:, None, D // 2:]
+        o = xf.copy()
+        if neox:
+            a, b = xf[..., : D // 2], xf[..., D // 2:]
+            o[..., : D // 2] = (a * co).astype(np.float32) - (b * si).astype(np.float32)
+            o[..., D // 2:] = (b * co).astype(np.float32) + (a * si).astype(np.float32)
+        else:
+            a, b = xf[..., 0::2], xf[..., 1::2]
+            o[..., 0::2] = (a * co).astype(np.float32) - (b * si).astype(np.float32)
+            o[..., 1::2] = (b * co).astype(np.float32) + (a * si).astype(np.float32)
+        return torch.from_numpy(o).to(dt)
+
+    k_rot = rot32(w_cpu.k.reshape(B, Hkv, D))
+    q_rot = rot32(w_cpu.q.reshape(B, Hq, D))
+    assert np.array_equal(_bits(q), _bits(q_rot)), "rotated q differs from the fp32 restatement"
+    kp, vp = w_cpu.k_pool.clone(), w_cpu.v_pool.clone()
+    k_after, v_after = k_rot.clone(), w_cpu.v.reshape(B, Hkv, D).clone()
+    oracle.kv_store(kp, vp, w_cpu.out_cache_loc, k_after, v_after, c.k_scale if fp8 else None,
+                    c.v_scale if fp8 else None, oracle.SCALE_TRUE_DIV, True)
+    assert np.array_equal(_bits(w.k_pool), _bits(kp)), "k pool bytes differ"
+    assert np.array_equal(_bits(w.v_pool), _bits(vp)), "v pool bytes differ"
+    # in-place semantics: k holds rot(k) (divided by the scale for fp8, like div_), v likewise
+    assert np.array_equal(_bits(k), _bits(k_after))
+    assert np.array_equal(_bits(v), _bits(v_after))

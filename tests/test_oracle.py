@@ -165,3 +165,34 @@ def test_oracle_vs_live_reference():
     out, _, kp, vp, _, _ = oracle_step(w)
     assert torch.equal(pool.k_buffer[0], kp) and torch.equal(pool.v_buffer[0], vp)
     assert_close_out(out, out_ref.float().numpy().reshape(out.shape), atol=4e-3, rtol=8e-3)
+
+
+# ----------------------------------------------------------------------------- #
+# rotary embedding (producer side of the KV store)
+# ----------------------------------------------------------------------------- #
+from tests.golden.make_golden import ROPE_CASES  # noqa: E402
+
+
+@pytest.mark.parametrize("name", sorted(ROPE_CASES))
+def test_rope_oracle_vs_reference_golden(name):
+    """oracle.rope / oracle.cos_sin_cache against the reference's RotaryEmbedding.forward_native:
+    fp32 run (exact arithmetic) within fp32 rounding; bf16 run (cos/sin and every product rounded to
+    bf16: three roundings of 2^-9 on |x| up to ~4) within 3 bf16 ulps of the operand magnitude -- the
+    reference's own test allows atol = rtol = 1e-2 (sgl-kernel/tests/test_rotary_embedding.py:190-193)."""
+    g = np.load(os.path.join(GOLDEN_DIR, name + ".npz"))
+    hs, rot, maxpos, base, neox, n, hq, hkv = (int(x) for x in g["meta"])
+    pos = torch.from_numpy(g["positions"])
+    cache = oracle.cos_sin_cache(rot, maxpos, float(base))
+    assert np.allclose(cache[pos].numpy(), g["cache_rows"], rtol=0, atol=2e-6)
+    # the golden rows stand in for the cache so the arithmetic check is independent of libm
+    rows = torch.from_numpy(g["cache_rows"])
+    idx = torch.arange(n)
+    for key, heads in (("q", hq), ("k", hkv)):
+        x = _from_bits(g[key + "_in"], torch.bfloat16).view(n, heads, hs)
+        got = oracle.rope(idx, x, rows, bool(neox)).reshape(n, heads * hs)
+        ref32 = g[key + "_out_f32"].astype(np.float64)
+        assert np.abs(got - ref32).max() <= 1e-6 * max(1.0, np.abs(ref32).max())
+        ref16 = _from_bits(g[key + "_out_bf16"], torch.bfloat16).float().numpy()
+        mag = np.abs(x.float().numpy()).reshape(n, heads, hs).max(axis=-1, keepdims=True)
+        bound = np.broadcast_to(3 * 2.0 ** -8 * np.maximum(mag, 1.0), (n, heads, hs)).reshape(n, heads * hs)
+        assert np.all(np.abs(got - ref16) <= bound)
