@@ -277,7 +277,7 @@ class Rank:
             self.flush_src = torch.zeros(2 * L2_BYTES // 8, dtype=torch.int64, device=self.dev)
             self.flush_sink = torch.zeros((), dtype=torch.int64, device=self.dev)
         self.flush_buf.zero_()
-        torch.sum(self.flush_src, out=self.flush_sink)
+        torch.sum(self.flush_src, dim=0, out=self.flush_sink)
 
     def timed(self, fn, steps: int, flush: bool) -> float:
         """ms per step by CUDA events on the current stream.  With `flush` every step is timed on
@@ -378,7 +378,7 @@ def measure(R: Rank, args, gcfg, scaling: str, with_clocks: bool = True) -> dict
     o3 = torch.empty((B, c.num_q_heads, c.head_dim), dtype=w.q.dtype, device=dev)
     pool = runner.token_to_kv_pool
     dargs = (q3, pool.k_buffer[0], pool.v_buffer[0], o3, None, backend.plan_buf, md.indices, backend.workspace,
-             float(layer.scaling), 0.0, c.k_scale if fp8 else 1.0, c.v_scale if fp8 else 1.0, 1)
+             float(layer.scaling), 0.0, c.k_scale if fp8 else 1.0, c.v_scale if fp8 else 1.0, 0)
     for _ in range(3):
         torch.ops.b200attn.decode(*dargs)
     kgraph = torch.cuda.CUDAGraph()
@@ -398,7 +398,7 @@ def measure(R: Rank, args, gcfg, scaling: str, with_clocks: bool = True) -> dict
     peak, peak_src = _measured_peak()
     achieved = decode_bytes / (k_ms * 1e-3) / 1e9
     roofline = {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-                "traffic": _ncu_traffic(gcfg.name, world), "kernel": "decode_kernel (K2, phases=1), per GPU",
+                "traffic": _ncu_traffic(gcfg.name, world), "kernel": "decode_kernel (split-KV decode with the LSE merge fused in; one launch), per GPU",
                 "kernel_ms": k_ms, "algorithmic_bytes": decode_bytes, "peak_source": peak_src,
                 "frac_of_nominal_8TBs": achieved / 8000.0}
 

@@ -39,7 +39,7 @@
 extern "C" {
 #endif
 
-#define B200ATTN_ABI_VERSION 1
+#define B200ATTN_ABI_VERSION 2
 
 /* cudaStream_t without pulling in the CUDA headers. */
 typedef void* b200attn_stream_t;
@@ -167,6 +167,9 @@ typedef struct {
   size_t plan_bytes;
   int32_t max_ctas;             /* 0 = one per SM; tests use small values to force splits */
   int32_t min_chunks_per_cta;   /* 0 = library default */
+  int32_t dynamic_percent;      /* share of the KV chunks CTAs claim dynamically (load balance):
+                                   0 = library default (none: equal static ranges), -1 = none */
+  int32_t dynamic_range_chunks; /* chunks per dynamic range; 0 = library default (~512 KB of KV) */
 } b200attn_plan_args;
 
 size_t b200attn_plan_bytes(int32_t batch);
@@ -200,9 +203,11 @@ typedef struct {
   float logit_cap;             /* 0 disables; cap * tanh(x / cap) otherwise */
   float k_scale;               /* fp8 dequant: K = fp8 * k_scale (1.0 for 16-bit pools) */
   float v_scale;
-  int32_t phases;              /* 0 = split-KV kernel + merge; 1 = split-KV kernel only (K2);
-                                  2 = merge only (K3).  1 and 2 exist so each kernel can be
-                                  timed and profiled alone; 1 followed by 2 equals 0. */
+  int32_t phases;              /* 0 = one launch: the split-KV kernel also merges the partials (the CTA
+                                  that lands a request's last partial merges it); 1 = split-KV kernel
+                                  without the merge (K2 alone); 2 = stand-alone merge kernel (K3).
+                                  1 followed by 2 equals 0; they exist so each stage can be timed and
+                                  tested alone. */
 } b200attn_decode_args;
 
 /* Bytes of split-KV workspace (partial o + lse) for up to `batch` requests. */

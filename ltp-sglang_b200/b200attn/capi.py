@@ -19,7 +19,7 @@ E_INVALID, E_UNSUPPORTED, E_ALIGN, E_CUDA, E_WORKSPACE = -1, -2, -3, -4, -5
 BF16, F16, FP8_E4M3 = 0, 1, 2
 I32, I64 = 0, 1
 SCALE_NONE, SCALE_TRUE_DIV, SCALE_RECIP_MUL = 0, 1, 2
-ABI_VERSION = 1
+ABI_VERSION = 2
 
 
 class KvStoreArgs(C.Structure):
@@ -89,6 +89,8 @@ class PlanArgs(C.Structure):
         ("plan_bytes", C.c_size_t),
         ("max_ctas", C.c_int32),
         ("min_chunks_per_cta", C.c_int32),
+        ("dynamic_percent", C.c_int32),
+        ("dynamic_range_chunks", C.c_int32),
     ]
 
 

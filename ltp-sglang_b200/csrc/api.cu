@@ -86,9 +86,7 @@ extern "C" __attribute__((visibility("default"))) size_t b200attn_workspace_byte
                                            int32_t dv, int32_t kv_dtype) {
   Geometry g;
   if (batch < 0 || dv <= 0 || !make_geometry(hq, hkv, d, kv_dtype, &g)) return 0;
-  int n = sm_count();
-  if (n > kMaxCtas) n = kMaxCtas;
-  return workspace_floats(batch, hq, dv, g, n, nullptr) * sizeof(float);
+  return workspace_floats(batch, hq, dv, g, nullptr) * sizeof(float);
 }
 
 extern "C" __attribute__((visibility("default"))) int b200attn_decode(const b200attn_decode_args* a, b200attn_stream_t stream_) {
@@ -118,9 +116,9 @@ extern "C" __attribute__((visibility("default"))) int b200attn_decode(const b200
     return B200ATTN_E_ALIGN;
 
   int n_sm = sm_count();
-  if (n_sm > kMaxCtas) n_sm = kMaxCtas;
+  if (n_sm > kMaxRanges / 2) n_sm = kMaxRanges / 2;
   size_t lse_off = 0;
-  const size_t need = workspace_floats(a->batch, a->num_q_heads, a->v_head_dim, g, n_sm, &lse_off);
+  const size_t need = workspace_floats(a->batch, a->num_q_heads, a->v_head_dim, g, &lse_off);
   if (a->ws_bytes < need * sizeof(float)) return B200ATTN_E_WORKSPACE;
 
   DecodeParams p;
@@ -150,6 +148,7 @@ extern "C" __attribute__((visibility("default"))) int b200attn_decode(const b200
   p.stage_bytes = g.stage_bytes;
   p.stages = g.stages;
   p.chunk_tokens = g.chunk_tokens;
+  p.fuse_merge = a->phases == 0;
   p.cp_async = g.row_bytes <= cp_async_max_row();
   p.unit_shift = 0;
   while ((16 << p.unit_shift) < g.row_bytes) ++p.unit_shift;
@@ -173,7 +172,7 @@ extern "C" __attribute__((visibility("default"))) int b200attn_decode(const b200
   }
   if (err != cudaSuccess) return B200ATTN_E_CUDA;
   if (a->phases != 2) count_launch();
-  if (a->phases == 1) return B200ATTN_OK;
+  if (a->phases != 2) return B200ATTN_OK;  // phases 0: decode_kernel merged the partials itself
 
   MergeParams m;
   m.plan = a->plan;

@@ -29,8 +29,12 @@ constexpr int kThreads = (kConsumerWarps + kProducerWarps) * 32;
 constexpr int kRowPad = 16;           // bytes
 constexpr int kBarrierBytes = 256;    // mbarrier area at the start of smem
 constexpr int kMaxStages = 8;
+constexpr int kRangeRing = 16;        // range ids in flight between producers and consumers (> kMaxStages)
+constexpr int kRangeRingOff = 128;    // byte offsets inside the barrier area
+constexpr int kMergeFlagOff = 192;
 constexpr int kMaxSmem = 227 * 1024;
-constexpr int kMaxCtas = 1024;
+constexpr int kMaxRanges = 1024;     // static + dynamic chunk ranges of one plan
+constexpr int kMaxHeadGroups = 16;   // num_kv_heads / heads-per-CTA
 constexpr int kMaxRowBytes = 2048;    // per token row per tensor staged by one CTA
 
 struct Geometry {
@@ -58,6 +62,7 @@ inline bool make_geometry(int hq, int hkv, int d, int kv_dtype, Geometry* g) {
   int hc = 8;
   while (hc > 1 && (hkv % hc != 0 || hc * d * e > kMaxRowBytes)) hc >>= 1;
   if (hc * d * e > kMaxRowBytes) return false;
+  if (hkv / hc > kMaxHeadGroups) return false;
   g->hc = hc;
   g->ts = kConsumerWarps / hc;
   g->ng = hkv / hc;
@@ -77,6 +82,12 @@ inline bool make_geometry(int hq, int hkv, int d, int kv_dtype, Geometry* g) {
 // ---------------------------------------------------------------------------
 // Plan buffer layout (device memory, written by plan_kernel, read by the
 // decode and merge kernels).  All offsets are derived from `batch`.
+//
+// The chunk sequence of the whole batch (virtual request = request x head
+// group, chunk = chunk_tokens tokens) is cut into RANGES: n_static ranges of
+// per_static chunks (range c is CTA c's first piece of work) followed by
+// n_dynamic ranges of per_dynamic chunks that CTAs claim through the ticket
+// counter as they run dry -- the tail of slow SMs is absorbed by fast ones.
 // ---------------------------------------------------------------------------
 struct PlanHeader {
   int32_t magic;
@@ -84,21 +95,41 @@ struct PlanHeader {
   int32_t ng;              // head groups
   int32_t chunk_tokens;
   int32_t total_chunks;    // ng * sum_b ceil(S_b / chunk_tokens)
-  int32_t chunks_per_cta;
-  int32_t n_cta;           // CTAs that own at least the slot (c * chunks_per_cta < total)
+  int32_t n_ranges;        // n_static + n_dynamic
+  int32_t n_static;
+  int32_t n_dynamic;
+  int32_t per_static;      // chunks per static range
+  int32_t per_dynamic;     // chunks per dynamic range
+  int32_t grid;            // CTAs that take part (the others exit at once)
   int32_t csr_mode;
   int32_t total_tokens;    // sum_b S_b
-  int32_t pad[7];
+  int32_t n_empty;         // requests of length 0 (the decode kernel defines their rows)
+  unsigned long long ticket;  // dynamic-range tickets; every decode launch consumes n_dynamic + grid
 };
 static_assert(sizeof(PlanHeader) == 64, "PlanHeader is 64 bytes");
-constexpr int32_t kPlanMagic = 0x42323030;  // "B200"
+constexpr int32_t kPlanMagic = 0x42323031;  // "B201"
+
+// First chunk of range r (r == n_ranges gives total_chunks).
+__host__ __device__ inline int range_begin(const PlanHeader& h, int r) {
+  int g = r <= h.n_static ? r * h.per_static : h.n_static * h.per_static + (r - h.n_static) * h.per_dynamic;
+  return g < h.total_chunks ? g : h.total_chunks;
+}
+// Range that holds chunk g (0 <= g < total_chunks).
+__host__ __device__ inline int range_of(const PlanHeader& h, int g) {
+  const int s = h.n_static * h.per_static;
+  return g < s ? g / h.per_static : h.n_static + (g - s) / h.per_dynamic;
+}
 
 struct PlanView {
   PlanHeader* hdr;
   int32_t* seq_len;       // [batch]
   int32_t* chunk_prefix;  // [batch + 1] exclusive prefix of ceil(S_b / T)
   int64_t* row_off;       // [batch] element offset of request b's index row
-  int32_t* cta_start;     // [kMaxCtas] first virtual request of CTA c
+  int32_t* range_vreq;    // [kMaxRanges] first virtual request of range r
+  int32_t* range_vlast;   // [kMaxRanges] last virtual request of range r
+  int32_t* vreq_rfirst;   // [batch * kMaxHeadGroups] first range that touches virtual request v
+  int32_t* vreq_pieces;   // [batch * kMaxHeadGroups] ranges that touch v (its partials to merge)
+  int32_t* vreq_arrived;  // [batch * kMaxHeadGroups] pieces written so far (self-resetting)
 };
 
 __host__ __device__ inline size_t align_up(size_t x, size_t a) { return (x + a - 1) / a * a; }
@@ -108,7 +139,8 @@ __host__ __device__ inline size_t plan_bytes_for(int batch) {
   n += align_up((size_t)batch * 4, 16);        // seq_len
   n += align_up((size_t)(batch + 1) * 4, 16);  // chunk_prefix
   n += align_up((size_t)batch * 8, 16);        // row_off
-  n += (size_t)kMaxCtas * 4;                   // cta_start
+  n += 2 * (size_t)kMaxRanges * 4;             // range_vreq, range_vlast
+  n += 3 * align_up((size_t)batch * kMaxHeadGroups * 4, 16);
   return n;
 }
 
@@ -123,16 +155,24 @@ __host__ __device__ inline PlanView plan_view(void* base, int batch) {
   p += align_up((size_t)(batch + 1) * 4, 16);
   v.row_off = reinterpret_cast<int64_t*>(p);
   p += align_up((size_t)batch * 8, 16);
-  v.cta_start = reinterpret_cast<int32_t*>(p);
+  v.range_vreq = reinterpret_cast<int32_t*>(p);
+  p += (size_t)kMaxRanges * 4;
+  v.range_vlast = reinterpret_cast<int32_t*>(p);
+  p += (size_t)kMaxRanges * 4;
+  const size_t tbl = align_up((size_t)batch * kMaxHeadGroups * 4, 16);
+  v.vreq_rfirst = reinterpret_cast<int32_t*>(p);
+  p += tbl;
+  v.vreq_pieces = reinterpret_cast<int32_t*>(p);
+  p += tbl;
+  v.vreq_arrived = reinterpret_cast<int32_t*>(p);
   return v;
 }
 
-// Workspace: partial outputs.  Piece (virtual request v, CTA c) has id v + c
-// (unique because both only grow along the chunk sequence); each piece holds
-// ts slices of [hq_per_vreq, dv] fp32 plus [hq_per_vreq] lse.
-inline size_t workspace_floats(int batch, int hq, int dv, const Geometry& g, int n_cta,
-                               size_t* lse_off) {
-  size_t pieces = (size_t)batch * g.ng + n_cta;
+// Workspace: partial outputs.  Piece (virtual request v, range r) has id v + r
+// (unique and dense because both only grow along the chunk sequence); each
+// piece holds ts slices of [hq_per_vreq, dv] fp32 plus [hq_per_vreq] lse.
+inline size_t workspace_floats(int batch, int hq, int dv, const Geometry& g, size_t* lse_off) {
+  size_t pieces = (size_t)batch * g.ng + kMaxRanges;
   size_t rows = pieces * g.ts * (size_t)(hq / g.ng);
   if (lse_off) *lse_off = rows * dv;
   return rows * dv + rows;
@@ -203,6 +243,11 @@ __device__ __forceinline__ void cp_async_mbar_arrive_noinc(uint32_t bar) {
 
 __device__ __forceinline__ void fence_proxy_async() {
   asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+}
+
+// Named barrier among `threads` threads (a subset of the CTA's warps).
+__device__ __forceinline__ void named_bar_sync(int id, int threads) {
+  asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(threads) : "memory");
 }
 
 __device__ __forceinline__ void fence_barrier_init() {

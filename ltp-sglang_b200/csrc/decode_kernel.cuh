@@ -25,7 +25,10 @@
 
 #include <math_constants.h>
 
+#include <type_traits>
+
 #include "common.cuh"
+#include "merge.cuh"
 
 namespace b200attn {
 
@@ -46,6 +49,7 @@ struct DecodeParams {
   int32_t hc, ts, ng, group;
   int32_t row_bytes, row_stride, stage_bytes, stages, chunk_tokens;
   int32_t cp_async;              // 1: producers use 16-byte cp.async (small rows), 0: one bulk copy per row
+  int32_t fuse_merge;            // 1: the CTA that writes a request's last partial merges it (no K3 launch)
   int32_t unit_shift;            // log2(row_bytes / 16)
   float scale_log2;              // sm_scale * k_scale * log2(e)
   float sm_scale_k;              // sm_scale * k_scale
@@ -83,28 +87,38 @@ __device__ __forceinline__ void mma_q(float (&d)[4], const uint32_t (&q)[QR], ui
   }
 }
 
-// Walks the (virtual request, local chunk range) pieces of one CTA's range.
+// Walks the pieces (virtual request x local chunk interval) of one range.  Order: the range's LAST
+// piece first, then the others in ascending order.  The first and last piece of a range are the ones
+// shared with the neighbouring ranges (a request cut by the range boundary); visiting both early
+// means every cut request has all its partials -- and its merge -- done long before the kernel ends,
+// and each CTA finishes on whole requests whose epilogue is a plain store.
 struct PieceWalk {
-  int v, g, g1, ng;
+  int v_first, v_last, g0, g1, ng;
+  int i = 0;
+  int left;  // chunks of the range not yet handed out
+  __device__ __forceinline__ PieceWalk(const PlanView& pv, const PlanHeader& H, int rg, int ng_)
+      : v_first(pv.range_vreq[rg]), v_last(pv.range_vlast[rg]), g0(range_begin(H, rg)),
+        g1(range_begin(H, rg + 1)), ng(ng_) {
+    left = g1 - g0;
+  }
   __device__ __forceinline__ bool next(const PlanView& pv, int& b, int& hg, int& lc0, int& lc1,
                                        int& nchunks, int& vreq) {
-    while (g < g1) {
+    const int m = v_last - v_first + 1;
+    while (i < m) {
+      const int v = i == 0 ? v_last : v_first + i - 1;
+      ++i;
       b = v / ng;
       hg = v - b * ng;
       const int cp0 = pv.chunk_prefix[b];
       const int n = pv.chunk_prefix[b + 1] - cp0;
       const int vstart = ng * cp0 + hg * n;
-      const int vend = vstart + n;
-      if (vend <= g) {
-        ++v;
-        continue;
-      }
-      lc0 = g - vstart;
-      lc1 = (vend < g1 ? vend : g1) - vstart;
+      const int lo = vstart > g0 ? vstart : g0;
+      const int hi = vstart + n < g1 ? vstart + n : g1;
+      if (lo >= hi) continue;  // empty request
+      lc0 = lo - vstart;
+      lc1 = hi - vstart;
       nchunks = n;
       vreq = v;
-      g = vstart + lc1;
-      ++v;
       return true;
     }
     return false;
@@ -121,17 +135,27 @@ __global__ void __launch_bounds__(kThreads, 1) decode_kernel(const DecodeParams 
 
   extern __shared__ __align__(128) uint8_t smem[];
   const PlanView pv = plan_view(const_cast<void*>(p.plan), p.batch);
+  const PlanHeader& H = *pv.hdr;  // read where needed (range transitions), not held in registers
   const int cta = blockIdx.x;
-  const int per = pv.hdr->chunks_per_cta;
-  const int total = pv.hdr->total_chunks;
-  if (static_cast<int64_t>(cta) * per >= total) return;
-  const int g0 = cta * per;
-  const int g1 = g0 + per < total ? g0 + per : total;
+  if (cta >= H.grid) return;
+  const int R = H.n_ranges;
+  const int n_dyn = H.n_dynamic, n_grid = H.grid, n_static = H.n_static;
 
   const uint32_t bar_full = smem_u32(smem);
   const uint32_t bar_empty = bar_full + kMaxStages * 8;
   const uint32_t stage0 = bar_full + kBarrierBytes;
+  volatile int32_t* rq = reinterpret_cast<volatile int32_t*>(smem + kRangeRingOff);   // ring of range ids
+  volatile int32_t* merge_flag = reinterpret_cast<volatile int32_t*>(smem + kMergeFlagOff);
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+
+  // Dynamic ranges are claimed through a ticket counter in the plan buffer.  Every launch draws
+  // exactly n_dynamic + grid tickets (each CTA stops at its first ticket past the dynamic ranges),
+  // so the counter never needs a reset between the layers that share one plan.
+  auto take_ticket = [&]() -> int {
+    const unsigned long long t = atomicAdd(&pv.hdr->ticket, 1ull);
+    const unsigned k = static_cast<unsigned>(t % static_cast<unsigned>(n_dyn + n_grid));
+    return k < static_cast<unsigned>(n_dyn) ? n_static + static_cast<int>(k) : R;
+  };
 
   if (threadIdx.x == 0) {
     for (int s = 0; s < p.stages; ++s) {
@@ -139,15 +163,17 @@ __global__ void __launch_bounds__(kThreads, 1) decode_kernel(const DecodeParams 
       mbar_init(bar_empty + s * 8, kConsumerWarps);
     }
     fence_barrier_init();
+    rq[0] = cta < n_static ? cta : take_ticket();
   }
   __syncthreads();
 
   const int T = p.chunk_tokens;
   const uint32_t v_off = T * p.row_stride;  // V rows follow the K rows of a stage
-  PieceWalk walk{pv.cta_start[cta], g0, g1, p.ng};
   int b, hg, lc0, lc1, nchunks, vreq;
   int stage = 0;
   uint32_t phase = 0;
+  int rn = 0;          // ranges done by this CTA
+  int rg = rq[0];      // current range (R = none)
 
   if (warp >= kConsumerWarps) {
     // ------------------------------ producers ------------------------------
@@ -170,6 +196,12 @@ __global__ void __launch_bounds__(kThreads, 1) decode_kernel(const DecodeParams 
       const int Tw = T >> 1;
       const int n_instr = (Tw << ush) >> 5;  // multiple of 8: a tensor-chunk is >= 8 KB
       const int tbase = par * Tw;
+      while (rg < R) {
+        // Claim the range after this one now; the ticket is only looked at when this range's last
+        // chunk is issued, so the atomic's round trip (microseconds under load) hides behind the copies.
+        int next_rg = R;
+        if (pw == 0 && lane == 0) next_rg = take_ticket();
+        PieceWalk walk(pv, H, rg, p.ng);
       while (walk.next(pv, b, hg, lc0, lc1, nchunks, vreq)) {
         const int S = pv.seq_len[b];
         const int32_t* idx = p.indices + pv.row_off[b];
@@ -206,6 +238,10 @@ __global__ void __launch_bounds__(kThreads, 1) decode_kernel(const DecodeParams 
             if (tl < nvalid)
               cp_async16(dst + tl * p.row_stride + col, base + static_cast<int64_t>(slot) * slot_bytes + col);
           }
+          if (pw == 0 && lane == 0 && --walk.left == 0) {
+            rq[(rn + 1) & (kRangeRing - 1)] = next_rg;  // published before this range's last arrival
+            __threadfence_block();
+          }
           cp_async_mbar_arrive_noinc(full);
           if (++stage == p.stages) {
             stage = 0;
@@ -213,8 +249,18 @@ __global__ void __launch_bounds__(kThreads, 1) decode_kernel(const DecodeParams 
           }
         }
       }
+        named_bar_sync(1, kProducerWarps * 32);  // every producer warp sees the ticket written above
+        ++rn;
+        rg = rq[rn & (kRangeRing - 1)];
+      }
       return;
     }
+    while (rg < R) {
+      // Claim the range after this one now; the ticket is only looked at when this range's last
+      // chunk is issued, so the atomic's round trip (microseconds under load) hides behind the copies.
+      int next_rg = R;
+      if (pw == 0 && lane == 0) next_rg = take_ticket();
+      PieceWalk walk(pv, H, rg, p.ng);
     while (walk.next(pv, b, hg, lc0, lc1, nchunks, vreq)) {
       const int S = pv.seq_len[b];
       const int32_t* idx = p.indices + pv.row_off[b];
@@ -241,6 +287,10 @@ __global__ void __launch_bounds__(kThreads, 1) decode_kernel(const DecodeParams 
         const int mine = (nvalid - par + 1) >> 1;  // valid tokens of this warp's parity
         mbar_wait(bar_empty + stage * 8, phase ^ 1);
         const uint32_t full = bar_full + stage * 8;
+        if (pw == 0 && lane == 0 && --walk.left == 0) {
+          rq[(rn + 1) & (kRangeRing - 1)] = next_rg;  // published before this range's last arrival
+          __threadfence_block();
+        }
         if (lane == 0) mbar_arrive_expect_tx(full, static_cast<uint32_t>(mine) * p.row_bytes);
         __syncwarp();
         const uint32_t dst = stage0 + stage * p.stage_bytes + (which ? v_off : 0u);
@@ -256,6 +306,10 @@ __global__ void __launch_bounds__(kThreads, 1) decode_kernel(const DecodeParams 
           phase ^= 1;
         }
       }
+    }
+      named_bar_sync(1, kProducerWarps * 32);  // every producer warp sees the ticket written above
+      ++rn;
+      rg = rq[rn & (kRangeRing - 1)];
     }
     return;
   }
@@ -280,6 +334,20 @@ __global__ void __launch_bounds__(kThreads, 1) decode_kernel(const DecodeParams 
   }
   v_lane += v_off;
 
+  if (H.n_empty > 0) {
+    // Requests of length 0 have no chunks, so no range reaches them: their rows are defined here
+    // (o = 0, lse = -inf), the way the reference's stage 2 leaves an all-masked row.
+    for (int i = cta * kConsumerWarps + warp; i < p.batch * p.hq; i += n_grid * kConsumerWarps) {
+      const int bb = i / p.hq, hh = i - bb * p.hq;
+      if (pv.seq_len[bb] != 0) continue;
+      QT* orow = reinterpret_cast<QT*>(p.o) + bb * p.o_sb + hh * p.o_sh;
+      for (int d = lane; d < D; d += 32) store_q(orow + d, 0.f);
+      if (p.lse && lane == 0) p.lse[static_cast<int64_t>(bb) * p.hq + hh] = -CUDART_INF_F;
+    }
+  }
+
+  while (rg < R) {
+  PieceWalk walk(pv, H, rg, p.ng);
   while (walk.next(pv, b, hg, lc0, lc1, nchunks, vreq)) {
     const int S = pv.seq_len[b];
     const int hq0 = (hg * p.hc + h) * p.group;
@@ -441,55 +509,60 @@ __global__ void __launch_bounds__(kThreads, 1) decode_kernel(const DecodeParams 
         vm1 = (tok0 + 8 < S ? 0x0000ffffu : 0u) | (tok0 + 9 < S ? 0xffff0000u : 0u);
       }
 
-      // ---- O += P.V ----
-      const uint32_t va = sbase + v_lane;
-      if constexpr (!FP8) {
-#pragma unroll
-        for (int n2 = 0; n2 < NTILES / 2; ++n2) {
-          uint32_t vf[4];
-          ldsm_x4_trans(va + n2 * 32, vf);
-          if constexpr (ROWS16) {
-            mma16816<HALF>(o[2 * n2], pa0, pa1, pa2, pa3, vf[0] & vm0, vf[1] & vm1);
-            mma16816<HALF>(o[2 * n2 + 1], pa0, pa1, pa2, pa3, vf[2] & vm0, vf[3] & vm1);
-          } else {
-            float d0[4] = {o[2 * n2][0], o[2 * n2][1], 0.f, 0.f};
-            mma16816<HALF>(d0, pa0, 0u, pa2, 0u, vf[0] & vm0, vf[1] & vm1);
-            o[2 * n2][0] = d0[0];
-            o[2 * n2][1] = d0[1];
-            float d1[4] = {o[2 * n2 + 1][0], o[2 * n2 + 1][1], 0.f, 0.f};
-            mma16816<HALF>(d1, pa0, 0u, pa2, 0u, vf[2] & vm0, vf[3] & vm1);
-            o[2 * n2 + 1][0] = d1[0];
-            o[2 * n2 + 1][1] = d1[1];
+      // ---- O += P.V ----  (the masks cost 32 LOP3 per 16 tokens: only the tail chunk pays them)
+      auto pv_mma = [&](auto tail_tag) {
+        constexpr bool TAIL = decltype(tail_tag)::value;
+        const uint32_t m0 = TAIL ? vm0 : 0xffffffffu, m1 = TAIL ? vm1 : 0xffffffffu;
+        const uint32_t va = sbase + v_lane;
+        if constexpr (!FP8) {
+  #pragma unroll
+          for (int n2 = 0; n2 < NTILES / 2; ++n2) {
+            uint32_t vf[4];
+            ldsm_x4_trans(va + n2 * 32, vf);
+            if constexpr (ROWS16) {
+              mma16816<HALF>(o[2 * n2], pa0, pa1, pa2, pa3, vf[0] & m0, vf[1] & m1);
+              mma16816<HALF>(o[2 * n2 + 1], pa0, pa1, pa2, pa3, vf[2] & m0, vf[3] & m1);
+            } else {
+              float d0[4] = {o[2 * n2][0], o[2 * n2][1], 0.f, 0.f};
+              mma16816<HALF>(d0, pa0, 0u, pa2, 0u, vf[0] & m0, vf[1] & m1);
+              o[2 * n2][0] = d0[0];
+              o[2 * n2][1] = d0[1];
+              float d1[4] = {o[2 * n2 + 1][0], o[2 * n2 + 1][1], 0.f, 0.f};
+              mma16816<HALF>(d1, pa0, 0u, pa2, 0u, vf[2] & m0, vf[3] & m1);
+              o[2 * n2 + 1][0] = d1[0];
+              o[2 * n2 + 1][1] = d1[1];
+            }
           }
-        }
-      } else {
-        // fp8 V: one x4.trans covers 32 d; a b16 transpose leaves each register
-        // with {tok 2j: d, d+1 | tok 2j+1: d, d+1}; PRMT regroups by d parity.
-#pragma unroll
-        for (int n4 = 0; n4 < NTILES / 4; ++n4) {
-          uint32_t vf[4];
-          ldsm_x4_trans(va + n4 * 32, vf);
-#pragma unroll
-          for (int gg = 0; gg < 2; ++gg) {
-#pragma unroll
-            for (int par = 0; par < 2; ++par) {
-              const uint32_t sel = par ? 0x4431u : 0x4420u;
-              const uint32_t b0 = e4m3x2_to_f16x2(__byte_perm(vf[2 * gg], 0u, sel)) & vm0;
-              const uint32_t b1 = e4m3x2_to_f16x2(__byte_perm(vf[2 * gg + 1], 0u, sel)) & vm1;
-              const int n = n4 * 4 + gg * 2 + par;
-              if constexpr (ROWS16) {
-                mma16816<true>(o[n], pa0, pa1, pa2, pa3, b0, b1);
-              } else {
-                float d0[4] = {o[n][0], o[n][1], 0.f, 0.f};
-                mma16816<true>(d0, pa0, 0u, pa2, 0u, b0, b1);
-                o[n][0] = d0[0];
-                o[n][1] = d0[1];
+        } else {
+          // fp8 V: one x4.trans covers 32 d; a b16 transpose leaves each register
+          // with {tok 2j: d, d+1 | tok 2j+1: d, d+1}; PRMT regroups by d parity.
+  #pragma unroll
+          for (int n4 = 0; n4 < NTILES / 4; ++n4) {
+            uint32_t vf[4];
+            ldsm_x4_trans(va + n4 * 32, vf);
+  #pragma unroll
+            for (int gg = 0; gg < 2; ++gg) {
+  #pragma unroll
+              for (int par = 0; par < 2; ++par) {
+                const uint32_t sel = par ? 0x4431u : 0x4420u;
+                const uint32_t b0 = e4m3x2_to_f16x2(__byte_perm(vf[2 * gg], 0u, sel)) & m0;
+                const uint32_t b1 = e4m3x2_to_f16x2(__byte_perm(vf[2 * gg + 1], 0u, sel)) & m1;
+                const int n = n4 * 4 + gg * 2 + par;
+                if constexpr (ROWS16) {
+                  mma16816<true>(o[n], pa0, pa1, pa2, pa3, b0, b1);
+                } else {
+                  float d0[4] = {o[n][0], o[n][1], 0.f, 0.f};
+                  mma16816<true>(d0, pa0, 0u, pa2, 0u, b0, b1);
+                  o[n][0] = d0[0];
+                  o[n][1] = d0[1];
+                }
               }
             }
           }
         }
-      }
 
+      };
+      if (tail) pv_mma(std::true_type{}); else pv_mma(std::false_type{});
       __syncwarp();
       if (lane == 0) mbar_arrive(bar_empty + stage * 8);
       if (++stage == p.stages) {
@@ -539,7 +612,7 @@ __global__ void __launch_bounds__(kThreads, 1) decode_kernel(const DecodeParams 
       }
     } else {
       const int hqv = p.hc * p.group;
-      const int64_t row = (static_cast<int64_t>(vreq + cta) * p.ts + tsi) * hqv + h * p.group + gq;
+      const int64_t row = (static_cast<int64_t>(vreq + rg) * p.ts + tsi) * hqv + h * p.group + gq;
       if (row0) {
         float* w = p.ws_o + row * D;
 #pragma unroll
@@ -560,7 +633,35 @@ __global__ void __launch_bounds__(kThreads, 1) decode_kernel(const DecodeParams 
           if (jq == 0) p.ws_lse[row + 8] = lse1;
         }
       }
+      if (p.fuse_merge) {
+        // Stage 2 without a second launch: the CTA that lands a virtual request's last piece
+        // merges all of them (threadfence + counter, the "last block done" pattern).  The
+        // producers keep streaming the next piece's chunks meanwhile.
+        __threadfence();
+        named_bar_sync(2, kConsumerWarps * 32);
+        if (threadIdx.x == 0) {
+          const int arrived = atomicAdd(&pv.vreq_arrived[vreq], 1) + 1;
+          const int last = arrived == pv.vreq_pieces[vreq];
+          if (last) pv.vreq_arrived[vreq] = 0;  // ready for the next layer's launch
+          *merge_flag = last;
+        }
+        named_bar_sync(2, kConsumerWarps * 32);
+        if (*merge_flag) {
+          __threadfence();
+          const int np = pv.vreq_pieces[vreq] * p.ts;
+          const int64_t prow0 = static_cast<int64_t>(vreq + pv.vreq_rfirst[vreq]) * p.ts * hqv;
+          for (int hl = warp; hl < hqv; hl += kConsumerWarps) {
+            const int hqi = hg * hqv + hl;
+            merge_rows<QT>(p.ws_o, p.ws_lse, prow0 + hl, hqv, np, D,
+                           reinterpret_cast<QT*>(p.o) + b * p.o_sb + hqi * p.o_sh,
+                           p.lse ? p.lse + static_cast<int64_t>(b) * p.hq + hqi : nullptr, lane);
+          }
+        }
+      }
     }
+  }
+  ++rn;
+  rg = rq[rn & (kRangeRing - 1)];
   }
 }
 

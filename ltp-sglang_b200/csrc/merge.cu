@@ -11,9 +11,10 @@
 
 namespace b200attn {
 
-// One warp per (request, q head).  Pieces of virtual request v live at
-// workspace rows ((v + c) * ts + slice) * hqv + head_in_vreq, for every CTA c
-// whose chunk range intersects the request.
+// One warp per (request, q head).  Pieces of virtual request v live at workspace rows
+// ((v + r) * ts + slice) * hqv + head_in_vreq for every range r that touches the request
+// (plan: vreq_rfirst / vreq_pieces).  Stand-alone form of the merge decode_kernel runs itself when
+// fuse_merge is set; kept for phases = 2 (timing / testing each stage alone).
 template <typename QT>
 __global__ void __launch_bounds__(128) merge_kernel(const MergeParams p) {
   const PlanView pv = plan_view(const_cast<void*>(p.plan), p.batch);
@@ -26,45 +27,17 @@ __global__ void __launch_bounds__(128) merge_kernel(const MergeParams p) {
   const int hg = hq / hqv;
   const int hl = hq - hg * hqv;
   const int v = b * p.ng + hg;
-  const int cp0 = pv.chunk_prefix[b];
-  const int n = pv.chunk_prefix[b + 1] - cp0;
   QT* out = reinterpret_cast<QT*>(p.o) + b * p.o_sb + hq * p.o_sh;
-  if (n == 0) {  // empty request: defined output, no pieces were written
+  float* lse_out = p.lse ? p.lse + static_cast<int64_t>(b) * p.hq + hq : nullptr;
+  const int pieces = pv.vreq_pieces[v];
+  if (pieces == 0) {  // empty request: defined output, no pieces were written
     for (int d = lane; d < p.dv; d += 32) out[d] = QT(0.f);
-    if (p.lse && lane == 0) p.lse[static_cast<int64_t>(b) * p.hq + hq] = -CUDART_INF_F;
+    if (lse_out && lane == 0) *lse_out = -CUDART_INF_F;
     return;
   }
-  const int per = pv.hdr->chunks_per_cta;
-  const int vstart = p.ng * cp0 + hg * n;
-  const int c_first = vstart / per;
-  const int c_last = (vstart + n - 1) / per;
-  if (p.ts == 1 && c_first == c_last) return;  // decode_kernel wrote o directly
-
-  const int np = (c_last - c_first + 1) * p.ts;
-  const int64_t row0 = (static_cast<int64_t>(v + c_first) * p.ts) * hqv + hl;
-  // rows of consecutive partials are hqv apart
-  float mx = -CUDART_INF_F;
-  for (int i = lane; i < np; i += 32) mx = fmaxf(mx, p.ws_lse[row0 + static_cast<int64_t>(i) * hqv]);
-#pragma unroll
-  for (int o = 16; o > 0; o >>= 1) mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, o));
-  if (mx == -CUDART_INF_F) {
-    for (int d = lane; d < p.dv; d += 32) out[d] = QT(0.f);
-    if (p.lse && lane == 0) p.lse[static_cast<int64_t>(b) * p.hq + hq] = -CUDART_INF_F;
-    return;
-  }
-  float sum = 0.f;
-  for (int i = 0; i < np; ++i) sum += __expf(p.ws_lse[row0 + static_cast<int64_t>(i) * hqv] - mx);
-  const float inv = 1.f / sum;
-  for (int d = lane; d < p.dv; d += 32) {
-    float acc = 0.f;
-    for (int i = 0; i < np; ++i) {
-      const int64_t row = row0 + static_cast<int64_t>(i) * hqv;
-      const float w = __expf(p.ws_lse[row] - mx);
-      acc = fmaf(w, p.ws_o[row * p.dv + d], acc);
-    }
-    out[d] = QT(acc * inv);
-  }
-  if (p.lse && lane == 0) p.lse[static_cast<int64_t>(b) * p.hq + hq] = mx + logf(sum);
+  if (p.ts == 1 && pieces == 1) return;  // decode_kernel wrote o directly
+  const int64_t row0 = static_cast<int64_t>(v + pv.vreq_rfirst[v]) * p.ts * hqv + hl;
+  merge_rows<QT>(p.ws_o, p.ws_lse, row0, hqv, pieces * p.ts, p.dv, out, lse_out, lane);
 }
 
 template __global__ void merge_kernel<__nv_bfloat16>(const MergeParams);

@@ -7,6 +7,8 @@
 // heuristic (get_num_kv_splits_triton, triton_backend.py:875-924): any split
 // plan gives the same math, so the plan is built for 148 SMs instead.
 // Everything runs on the device: no host sync, CUDA-graph safe.
+#include <cstdlib>
+
 #include "common.cuh"
 
 namespace b200attn {
@@ -25,6 +27,8 @@ struct PlanParams {
   int32_t chunk_tokens;
   int32_t max_ctas;
   int32_t min_chunks;
+  int32_t dyn_pct;      // share of the chunks handed out dynamically, percent
+  int32_t dyn_chunks;   // chunks per dynamic range
 };
 
 constexpr int kPlanThreads = 1024;
@@ -61,12 +65,13 @@ __device__ __forceinline__ int block_scan_incl(int v, int* warp_sums) {
 
 __global__ void __launch_bounds__(kPlanThreads) plan_kernel(PlanParams p) {
   __shared__ int warp_sums[32];
-  __shared__ int carry_tok, carry_chunk;
+  __shared__ int carry_tok, carry_chunk, n_empty;
   PlanView pv = plan_view(p.plan, p.batch);
   const int tid = threadIdx.x;
   if (tid == 0) {
     carry_tok = 0;
     carry_chunk = 0;
+    n_empty = 0;
     pv.chunk_prefix[0] = 0;
     if (p.kv_indptr) p.kv_indptr[0] = 0;
   }
@@ -93,6 +98,7 @@ __global__ void __launch_bounds__(kPlanThreads) plan_kernel(PlanParams p) {
     const int tok_incl = block_scan_incl(s, warp_sums);
     const int ch_incl = block_scan_incl(nch, warp_sums);
     if (b < p.batch) {
+      if (s == 0) atomicAdd(&n_empty, 1);
       pv.seq_len[b] = s;
       pv.row_off[b] = row;
       pv.chunk_prefix[b + 1] = carry_chunk + ch_incl;
@@ -111,10 +117,7 @@ __global__ void __launch_bounds__(kPlanThreads) plan_kernel(PlanParams p) {
   __syncthreads();
 
   const int total = carry_chunk * p.ng;
-  int per = (total + p.max_ctas - 1) / p.max_ctas;
-  if (per < p.min_chunks) per = p.min_chunks;
-  if (per < 1) per = 1;
-  const int n_cta = (total + per - 1) / per;
+  __shared__ PlanHeader sh;
   if (tid == 0) {
     PlanHeader h;
     h.magic = kPlanMagic;
@@ -122,22 +125,54 @@ __global__ void __launch_bounds__(kPlanThreads) plan_kernel(PlanParams p) {
     h.ng = p.ng;
     h.chunk_tokens = T;
     h.total_chunks = total;
-    h.chunks_per_cta = per;
-    h.n_cta = n_cta;
+    h.grid = p.max_ctas;
     h.csr_mode = p.csr_indptr != nullptr;
     h.total_tokens = carry_tok;
-#pragma unroll
-    for (int i = 0; i < 7; ++i) h.pad[i] = 0;
+    h.n_empty = n_empty;
+    h.ticket = 0ull;
+    const int G = p.max_ctas;
+    const int minc = p.min_chunks < 1 ? 1 : p.min_chunks;
+    int per_s, n_static, per_d = 1, n_dyn = 0;
+    if (total <= G * minc || p.dyn_pct <= 0) {
+      // small batch (or dynamic ranges disabled): equal static ranges only
+      per_s = (total + G - 1) / G;
+      if (per_s < minc) per_s = minc;
+      n_static = (total + per_s - 1) / per_s;
+    } else {
+      per_s = static_cast<int>(static_cast<int64_t>(total) * (100 - p.dyn_pct) / (100ll * G));
+      if (per_s < minc) per_s = minc;
+      int64_t covered = static_cast<int64_t>(per_s) * G;
+      if (covered >= total) {
+        per_s = (total + G - 1) / G;
+        n_static = (total + per_s - 1) / per_s;
+      } else {
+        n_static = G;
+        const int rem = total - static_cast<int>(covered);
+        per_d = p.dyn_chunks > minc ? p.dyn_chunks : minc;
+        const int room = kMaxRanges - G;
+        const int need = (rem + room - 1) / room;
+        if (per_d < need) per_d = need;
+        n_dyn = (rem + per_d - 1) / per_d;
+      }
+    }
+    h.per_static = per_s;
+    h.per_dynamic = per_d;
+    h.n_static = n_static;
+    h.n_dynamic = n_dyn;
+    h.n_ranges = n_static + n_dyn;
     *pv.hdr = h;
+    sh = h;
   }
+  __syncthreads();
+  const PlanHeader h = sh;
 
-  // First virtual request (b * ng + hg) of every CTA: the one whose chunk
-  // range contains chunk c * per.  Virtual request (b, hg) starts at
-  // ng * prefix[b] + hg * n_b.
-  for (int c = tid; c < p.max_ctas; c += kPlanThreads) {
-    int start = p.batch * p.ng;
-    const int64_t g0 = static_cast<int64_t>(c) * per;
-    if (g0 < total) {
+  // First and last virtual request (b * ng + hg) of every range: the ones whose chunk interval
+  // contains the range's first / last chunk.  Virtual request (b, hg) starts at ng * prefix[b] + hg * n_b.
+  for (int r = tid; r < 2 * kMaxRanges; r += kPlanThreads) {
+    const int rr = r >> 1, last = r & 1;
+    int vq = p.batch * p.ng;
+    if (rr < h.n_ranges) {
+      const int64_t g0 = last ? range_begin(h, rr + 1) - 1 : range_begin(h, rr);
       int lo = 0, hi = p.batch;  // largest b with ng * prefix[b] <= g0
       while (hi - lo > 1) {
         const int mid = (lo + hi) >> 1;
@@ -145,9 +180,24 @@ __global__ void __launch_bounds__(kPlanThreads) plan_kernel(PlanParams p) {
       }
       const int nb = pv.chunk_prefix[lo + 1] - pv.chunk_prefix[lo];
       const int hg = nb > 0 ? static_cast<int>((g0 - static_cast<int64_t>(pv.chunk_prefix[lo]) * p.ng) / nb) : 0;
-      start = lo * p.ng + hg;
+      vq = lo * p.ng + hg;
     }
-    pv.cta_start[c] = start;
+    (last ? pv.range_vlast : pv.range_vreq)[rr] = vq;
+  }
+  // Per virtual request: the ranges that touch it (= its partial pieces) and the arrival counter.
+  for (int v = tid; v < p.batch * p.ng; v += kPlanThreads) {
+    const int b = v / p.ng, hg = v - b * p.ng;
+    const int cp0 = pv.chunk_prefix[b];
+    const int n = pv.chunk_prefix[b + 1] - cp0;
+    int rf = 0, np = 0;
+    if (n > 0) {
+      const int vstart = p.ng * cp0 + hg * n;
+      rf = range_of(h, vstart);
+      np = range_of(h, vstart + n - 1) - rf + 1;
+    }
+    pv.vreq_rfirst[v] = rf;
+    pv.vreq_pieces[v] = np;
+    pv.vreq_arrived[v] = 0;
   }
 }
 
@@ -168,6 +218,18 @@ __global__ void __launch_bounds__(256) kv_indices_kernel(const int32_t* __restri
 }  // namespace b200attn
 
 using namespace b200attn;
+
+// Tuning aids (read once): B200ATTN_DYN_PCT (1..90; default 0 = equal static ranges only: measured on
+// B200 the per-SM speed spread is smaller than one dynamic range, so the dynamic tail only adds
+// pieces -- profiles/r01_dynamic_ranges.txt), B200ATTN_DYN_BYTES.
+static int plan_default_dyn_pct() {
+  static const int v = [] { const char* e = getenv("B200ATTN_DYN_PCT"); return e ? atoi(e) : 0; }();
+  return v;
+}
+static int plan_default_dyn_bytes() {
+  static const int v = [] { const char* e = getenv("B200ATTN_DYN_BYTES"); return e ? atoi(e) : 512 * 1024; }();
+  return v;
+}
 
 extern "C" __attribute__((visibility("default"))) size_t b200attn_plan_bytes(int32_t batch) {
   if (batch < 0) return 0;
@@ -201,11 +263,16 @@ extern "C" __attribute__((visibility("default"))) int b200attn_plan(const b200at
   p.chunk_tokens = g.chunk_tokens;
   int n = sm_count();
   if (a->max_ctas > 0 && a->max_ctas < n) n = a->max_ctas;
-  if (n > kMaxCtas) n = kMaxCtas;
+  if (n > kMaxRanges / 2) n = kMaxRanges / 2;
   p.max_ctas = n;
   // Default floor: >= 64 tokens per piece so the partial write-out stays small
   // next to the KV bytes a piece streams.
   p.min_chunks = a->min_chunks_per_cta > 0 ? a->min_chunks_per_cta : (64 + g.chunk_tokens - 1) / g.chunk_tokens;
+  // Optional dynamic tail (off by default): a share of the chunks in ranges of ~512 KB of KV.
+  p.dyn_pct = a->dynamic_percent < 0 ? 0 : (a->dynamic_percent == 0 ? plan_default_dyn_pct() : a->dynamic_percent);
+  if (p.dyn_pct > 90) p.dyn_pct = 90;
+  const int chunk_bytes = 2 * g.chunk_tokens * g.row_bytes;
+  p.dyn_chunks = a->dynamic_range_chunks > 0 ? a->dynamic_range_chunks : (plan_default_dyn_bytes() + chunk_bytes - 1) / chunk_bytes;
 
   cudaStream_t stream = static_cast<cudaStream_t>(stream_);
   plan_kernel<<<1, kPlanThreads, 0, stream>>>(p);

@@ -529,3 +529,63 @@ def test_rope_kv_store_fused(kv_dtype, q_dtype, neox):
     # in-place semantics: k holds rot(k) (divided by the scale for fp8, like div_), v likewise
     assert np.array_equal(_bits(k), _bits(k_after))
     assert np.array_equal(_bits(v), _bits(v_after))
+
+
+# ----------------------------------------------------------------------------- #
+# fused merge == separate stages; dynamic ranges; plan reuse across launches
+# ----------------------------------------------------------------------------- #
+@pytest.mark.parametrize("dyn", [-1, 0, 50])
+@pytest.mark.parametrize("tp", [1, 8])
+def test_fused_merge_equals_two_stage(dyn, tp, monkeypatch):
+    """phases 0 (one launch, in-kernel merge) must equal phases 1 + 2 (K2 then K3) bit for bit, for
+    static-only plans, the default dynamic tail and a 50 % dynamic tail; the same plan is then reused
+    for several launches (layers) to exercise the self-resetting ticket / arrival counters."""
+    import b200attn
+    from b200attn import capi, ops
+    import ctypes as C
+
+    cfg = synth.shard(synth.Config("fm", 37, 0, 32, 8, 128, page_size=1, ragged=(1, 3000), seed=41), tp)
+    w = synth.make_workload(cfg, DEV)
+    runner = make_runner(w, DEV)
+    backend = b200attn.B200AttnBackend(runner, return_lse=True)
+    B, Hq, D = cfg.batch, cfg.num_q_heads, cfg.head_dim
+    # plan with an explicit dynamic share through the C-ABI
+    a = capi.PlanArgs()
+    a.req_to_token = w.req_to_token.data_ptr()
+    a.req_to_token_stride = w.req_to_token.stride(0)
+    a.req_pool_indices = w.req_pool_indices.data_ptr()
+    a.seq_lens = w.seq_lens.data_ptr()
+    a.index_dtype = capi.I64
+    a.batch = B
+    a.num_q_heads, a.num_kv_heads, a.head_dim, a.kv_dtype = Hq, cfg.num_kv_heads, D, capi.BF16
+    a.plan = backend.plan_buf.data_ptr()
+    a.plan_bytes = backend.plan_buf.numel()
+    a.dynamic_percent = dyn
+    a.dynamic_range_chunks = 2 if dyn > 0 else 0
+    stream = C.c_void_p(torch.cuda.current_stream().cuda_stream)
+    capi.check("plan", capi.lib().b200attn_plan(C.byref(a), stream))
+    q3 = w.q.view(B, Hq, D)
+
+    def run(phases, o, lse):
+        torch.ops.b200attn.decode(q3, w.k_pool, w.v_pool, o, lse, backend.plan_buf, w.req_to_token,
+                                  backend.workspace, w.sm_scale, 0.0, 1.0, 1.0, phases)
+
+    o2 = torch.zeros((B, Hq, D), dtype=w.q.dtype, device=DEV)
+    l2 = torch.zeros(B * Hq, dtype=torch.float32, device=DEV)
+    run(1, o2, l2)
+    run(2, o2, l2)
+    torch.cuda.synchronize()
+    for it in range(4):   # the plan (tickets, arrival counters) is reused, like layers of one forward
+        o1 = torch.full((B, Hq, D), float("nan"), dtype=w.q.dtype, device=DEV)
+        l1 = torch.full((B * Hq,), float("nan"), dtype=torch.float32, device=DEV)
+        run(0, o1, l1)
+        torch.cuda.synchronize()
+        assert torch.equal(o1, o2), f"launch {it}: fused merge differs from K2 + K3"
+        assert torch.equal(l1, l2)
+    # and against the oracle on a few requests
+    from oracle import decode_oracle as oracle
+
+    ref, ref_lse = oracle.decode_attention(q3.cpu(), w.k_pool.cpu(), w.v_pool.cpu(), w.req_to_token.cpu(),
+                                           w.req_pool_indices.cpu(), w.seq_lens.cpu(), w.sm_scale)
+    assert_close_out(o1.float().cpu().numpy(), ref)
+    assert np.abs(l1.view(B, Hq).cpu().numpy() - ref_lse).max() <= 1e-3
