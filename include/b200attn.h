@@ -170,6 +170,12 @@ typedef struct {
   int32_t dynamic_percent;      /* share of the KV chunks CTAs claim dynamically (load balance):
                                    0 = library default (none: equal static ranges), -1 = none */
   int32_t dynamic_range_chunks; /* chunks per dynamic range; 0 = library default (~512 KB of KV) */
+  int32_t sliding_window;       /* > 0: request b attends to its last min(S_b, W + 1) tokens only, i.e.
+                                   req_to_token[req, S_b - len : S_b] (update_sliding_window_buffer,
+                                   triton_backend.py:927-956); kv_indptr / kv_indices then are the
+                                   reference's window_kv_indptr / window_kv_indices.  0 = full context.
+                                   Not combinable with the CSR input mode. */
+  int32_t pad_;
 } b200attn_plan_args;
 
 size_t b200attn_plan_bytes(int32_t batch);

@@ -109,6 +109,9 @@ class ForwardMetadata:
     indices: torch.Tensor            # req_to_token, or kv_indices in CSR mode
     kv_indptr: Optional[torch.Tensor]
     kv_indices: Optional[torch.Tensor]
+    # sliding-window layers (interleaved with full-attention layers, e.g. Gemma-3) use a second plan
+    window_kv_indptr: Optional[torch.Tensor] = None
+    window_kv_indices: Optional[torch.Tensor] = None
 
 
 class B200AttnBackend(AttentionBackend):
@@ -139,8 +142,10 @@ class B200AttnBackend(AttentionBackend):
         self.head_dim = k0.shape[-1]
         self.v_head_dim = v0.shape[-1]
         self.kv_dtype = ops.dtype_code(k0.dtype)
-        if getattr(model_runner, "sliding_window_size", None):
-            raise NotImplementedError("B200AttnBackend: sliding-window attention is not supported yet")
+        sw = getattr(model_runner, "sliding_window_size", None)
+        self.sliding_window_size = int(sw) if sw is not None and sw > 0 else None
+        if type(self.token_to_kv_pool).__name__ == "SWAKVPool":
+            raise NotImplementedError("B200AttnBackend: the hybrid SWAKVPool (full -> swa slot translation) is not supported yet")
         if getattr(mc, "is_encoder_decoder", False):
             raise NotImplementedError("B200AttnBackend: cross attention is not supported yet")
         if self.head_dim != self.v_head_dim:
@@ -160,6 +165,11 @@ class B200AttnBackend(AttentionBackend):
                                  self.v_head_dim, self.kv_dtype)
         self.workspace = torch.empty(ws // 4, dtype=torch.float32, device=dev)
         self.kv_indptr = torch.zeros(self.max_bs + 1, dtype=torch.int32, device=dev)
+        self.window_plan_buf = self.window_kv_indptr = None
+        if self.sliding_window_size is not None:   # two sets of buffers, as triton_backend.py:77-90
+            self.window_plan_buf = torch.zeros_like(self.plan_buf)
+            self.window_kv_indptr = torch.zeros_like(self.kv_indptr)
+        self.cuda_graph_window_kv_indices: Optional[torch.Tensor] = None
         self.lse = torch.empty(self.max_bs * self.num_head, dtype=torch.float32, device=dev) if return_lse else None
         self.cuda_graph_kv_indices: Optional[torch.Tensor] = None
         self.forward_metadata: Optional[ForwardMetadata] = None
@@ -177,18 +187,31 @@ class B200AttnBackend(AttentionBackend):
                                         self.head_dim, self.kv_dtype, self.max_ctas, self.min_chunks)
             self.forward_metadata = ForwardMetadata(kv_indptr.numel() - 1, kv_indices, kv_indptr, kv_indices)
             return
-        kv_indices = None
+        kv_indices = window_kv_indices = None
         if self.materialize_kv_indices:
             if graph:
                 kv_indices = self.cuda_graph_kv_indices
+                window_kv_indices = self.cuda_graph_window_kv_indices
             else:
                 if seq_lens_sum is None:
                     seq_lens_sum = int(seq_lens[:bs].sum().item())
                 kv_indices = torch.empty(seq_lens_sum, dtype=torch.int32, device=self.device)
+                if self.sliding_window_size is not None:
+                    n = min(seq_lens_sum, bs * (self.sliding_window_size + 1))
+                    window_kv_indices = torch.empty(n, dtype=torch.int32, device=self.device)
         torch.ops.b200attn.plan(self.req_to_token, req_pool_indices[:bs], seq_lens[:bs], self.plan_buf,
                                 self.kv_indptr, kv_indices, self.num_head, self.num_kv_head,
-                                self.head_dim, self.kv_dtype, self.max_ctas, self.min_chunks)
-        self.forward_metadata = ForwardMetadata(bs, self.req_to_token, self.kv_indptr[: bs + 1], kv_indices)
+                                self.head_dim, self.kv_dtype, self.max_ctas, self.min_chunks, 0)
+        md = ForwardMetadata(bs, self.req_to_token, self.kv_indptr[: bs + 1], kv_indices)
+        if self.sliding_window_size is not None:
+            # second plan over the last min(S, W + 1) tokens (update_sliding_window_buffer, triton_backend.py:927-956)
+            torch.ops.b200attn.plan(self.req_to_token, req_pool_indices[:bs], seq_lens[:bs], self.window_plan_buf,
+                                    self.window_kv_indptr, window_kv_indices, self.num_head, self.num_kv_head,
+                                    self.head_dim, self.kv_dtype, self.max_ctas, self.min_chunks,
+                                    self.sliding_window_size)
+            md.window_kv_indptr = self.window_kv_indptr[: bs + 1]
+            md.window_kv_indices = window_kv_indices
+        self.forward_metadata = md
 
     def init_forward_metadata(self, forward_batch):
         mode = forward_batch.forward_mode
@@ -205,6 +228,9 @@ class B200AttnBackend(AttentionBackend):
         if self.materialize_kv_indices:
             self.cuda_graph_kv_indices = torch.zeros(max_num_tokens * self.max_context_len,
                                                      dtype=torch.int32, device=self.device)
+            if self.sliding_window_size is not None:   # triton_backend.py:373-380
+                self.cuda_graph_window_kv_indices = torch.zeros(
+                    max_num_tokens * (self.sliding_window_size + 1), dtype=torch.int32, device=self.device)
         if self.prefill_backend is not None and hasattr(self.prefill_backend, "init_cuda_graph_state"):
             try:
                 self.prefill_backend.init_cuda_graph_state(max_bs, max_num_tokens)
@@ -237,8 +263,12 @@ class B200AttnBackend(AttentionBackend):
         if getattr(layer, "is_cross_attention", False):
             raise NotImplementedError("B200AttnBackend: cross attention is not supported")
         sw = getattr(layer, "sliding_window_size", -1)
-        if sw is not None and sw > -1:
-            raise NotImplementedError("B200AttnBackend: sliding-window layers are not supported")
+        windowed = sw is not None and sw > -1   # triton_backend.py:711-716
+        if windowed and self.window_plan_buf is None:
+            raise RuntimeError("B200AttnBackend: layer has a sliding window but model_runner.sliding_window_size is unset")
+        if windowed and self.forward_metadata is not None and self.forward_metadata.window_kv_indptr is None \
+                and self.forward_metadata.batch > 0:
+            raise NotImplementedError("B200AttnBackend: sliding-window layers with speculative (CSR) metadata")
         if layer.qk_head_dim != layer.v_head_dim:
             raise NotImplementedError("B200AttnBackend: qk_head_dim != v_head_dim is not supported")
 
@@ -266,7 +296,8 @@ class B200AttnBackend(AttentionBackend):
             q.view(bs, layer.tp_q_head_num, layer.qk_head_dim), k_pool, v_pool,
             o.view(bs, layer.tp_q_head_num, layer.v_head_dim),
             self.lse[: bs * self.num_head] if self.lse is not None else None,
-            self.plan_buf, md.indices, self.workspace, float(layer.scaling),
+            self.window_plan_buf if windowed else self.plan_buf,
+            md.indices, self.workspace, float(layer.scaling),
             float(getattr(layer, "logit_cap", 0.0) or 0.0),
             float(k_scale) if (fp8 and k_scale is not None) else 1.0,
             float(v_scale) if (fp8 and v_scale is not None) else 1.0)

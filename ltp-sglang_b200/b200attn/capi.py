@@ -91,6 +91,8 @@ class PlanArgs(C.Structure):
         ("min_chunks_per_cta", C.c_int32),
         ("dynamic_percent", C.c_int32),
         ("dynamic_range_chunks", C.c_int32),
+        ("sliding_window", C.c_int32),
+        ("pad_", C.c_int32),
     ]
 
 

@@ -150,7 +150,7 @@ def _rope_kv_store(q, k, v, positions, cos_sin_cache, is_neox, loc, k_pool, v_po
 
 
 def _plan(req_to_token, req_pool_indices, seq_lens, plan_buf, kv_indptr, kv_indices,
-          num_q_heads, num_kv_heads, head_dim, kv_dtype, max_ctas, min_chunks):
+          num_q_heads, num_kv_heads, head_dim, kv_dtype, max_ctas, min_chunks, sliding_window=0):
     _cuda(req_to_token, req_pool_indices, seq_lens, plan_buf, kv_indptr, kv_indices)
     if req_to_token.dtype != torch.int32 or req_to_token.dim() != 2 or req_to_token.stride(1) != 1:
         raise TypeError("plan: req_to_token must be int32 [max_reqs, max_context_len]")
@@ -179,6 +179,7 @@ def _plan(req_to_token, req_pool_indices, seq_lens, plan_buf, kv_indptr, kv_indi
     a.plan = plan_buf.data_ptr()
     a.plan_bytes = plan_buf.numel() * plan_buf.element_size()
     a.max_ctas, a.min_chunks_per_cta = max_ctas, min_chunks
+    a.sliding_window = sliding_window
     with torch.cuda.device(plan_buf.device):
         capi.check("b200attn_plan", capi.lib().b200attn_plan(C.byref(a), _stream(plan_buf)))
 
@@ -274,7 +275,7 @@ _LIB.define(
 _LIB.define(
     "plan(Tensor req_to_token, Tensor req_pool_indices, Tensor seq_lens, Tensor(a!) plan_buf, "
     "Tensor(b!)? kv_indptr, Tensor(c!)? kv_indices, int num_q_heads, int num_kv_heads, int head_dim, "
-    "int kv_dtype, int max_ctas, int min_chunks) -> ()"
+    "int kv_dtype, int max_ctas, int min_chunks, int sliding_window=0) -> ()"
 )
 _LIB.define(
     "plan_csr(Tensor kv_indptr, Tensor(a!) plan_buf, int num_q_heads, int num_kv_heads, int head_dim, "

@@ -29,6 +29,7 @@ struct PlanParams {
   int32_t min_chunks;
   int32_t dyn_pct;      // share of the chunks handed out dynamically, percent
   int32_t dyn_chunks;   // chunks per dynamic range
+  int32_t window;       // sliding window W (0 = none): the last min(S, W + 1) tokens
 };
 
 constexpr int kPlanThreads = 1024;
@@ -91,6 +92,10 @@ __global__ void __launch_bounds__(kPlanThreads) plan_kernel(PlanParams p) {
         int64_t sl = load_idx(p.seq_lens, b, p.idx64);
         s = sl < 0 ? 0 : static_cast<int>(sl);
         row = load_idx(p.req_pool_indices, b, p.idx64) * p.r2t_stride;
+        if (p.window > 0 && s > p.window + 1) {  // triton_backend.py:936-946: lens = min(S, W + 1), start = S - lens
+          row += s - (p.window + 1);
+          s = p.window + 1;
+        }
       }
       if (s < 0) s = 0;
     }
@@ -243,6 +248,7 @@ extern "C" __attribute__((visibility("default"))) int b200attn_plan(const b200at
   if (!csr && (!a->req_to_token || !a->req_pool_indices || !a->seq_lens)) return B200ATTN_E_INVALID;
   if (a->index_dtype != B200ATTN_I32 && a->index_dtype != B200ATTN_I64) return B200ATTN_E_INVALID;
   if (a->kv_indices && (csr || !a->kv_indptr)) return B200ATTN_E_INVALID;
+  if (a->sliding_window < 0 || (csr && a->sliding_window > 0)) return B200ATTN_E_INVALID;
   if (reinterpret_cast<uintptr_t>(a->plan) % 16 != 0) return B200ATTN_E_ALIGN;
   if (a->plan_bytes < plan_bytes_for(a->batch)) return B200ATTN_E_WORKSPACE;
   Geometry g;
@@ -265,6 +271,7 @@ extern "C" __attribute__((visibility("default"))) int b200attn_plan(const b200at
   if (a->max_ctas > 0 && a->max_ctas < n) n = a->max_ctas;
   if (n > kMaxRanges / 2) n = kMaxRanges / 2;
   p.max_ctas = n;
+  p.window = a->sliding_window;
   // Default floor: >= 64 tokens per piece so the partial write-out stays small
   // next to the KV bytes a piece streams.
   p.min_chunks = a->min_chunks_per_cta > 0 ? a->min_chunks_per_cta : (64 + g.chunk_tokens - 1) / g.chunk_tokens;

@@ -166,14 +166,17 @@ def kv_store(k_pool: torch.Tensor, v_pool: torch.Tensor, loc: torch.Tensor, cach
 # page indexing
 # --------------------------------------------------------------------------- #
 def kv_indices(req_to_token: torch.Tensor, req_pool_indices: torch.Tensor,
-               seq_lens: torch.Tensor) -> Tuple[np.ndarray, np.ndarray]:
-    """(kv_indptr[B+1], kv_indices[sum S]) as int32 numpy arrays."""
+               seq_lens: torch.Tensor, sliding_window: int = 0) -> Tuple[np.ndarray, np.ndarray]:
+    """(kv_indptr[B+1], kv_indices[sum S]) as int32 numpy arrays.  With ``sliding_window`` W > 0 the
+    window_kv_indptr / window_kv_indices of update_sliding_window_buffer (triton_backend.py:927-956):
+    lens = min(S, W + 1), start = S - lens."""
     r2t = req_to_token.detach().cpu().numpy()
     rpi = req_pool_indices.detach().cpu().numpy().astype(np.int64)
     sl = seq_lens.detach().cpu().numpy().astype(np.int64)
+    wl = np.minimum(sl, sliding_window + 1) if sliding_window > 0 else sl
     indptr = np.zeros(len(sl) + 1, dtype=np.int32)
-    indptr[1:] = np.cumsum(sl).astype(np.int32)
-    parts = [r2t[rpi[i], : sl[i]] for i in range(len(sl))]
+    indptr[1:] = np.cumsum(wl).astype(np.int32)
+    parts = [r2t[rpi[i], sl[i] - wl[i]: sl[i]] for i in range(len(sl))]
     flat = np.concatenate(parts).astype(np.int32) if parts else np.zeros(0, dtype=np.int32)
     return indptr, flat
 
@@ -190,14 +193,16 @@ def pool_to_f32(pool: torch.Tensor) -> np.ndarray:
 def decode_attention(q: torch.Tensor, k_pool: torch.Tensor, v_pool: torch.Tensor,
                      req_to_token: torch.Tensor, req_pool_indices: torch.Tensor, seq_lens: torch.Tensor,
                      sm_scale: float, logit_cap: float = 0.0, k_scale: float = 1.0,
-                     v_scale: float = 1.0) -> Tuple[np.ndarray, np.ndarray]:
+                     v_scale: float = 1.0, sliding_window: int = 0) -> Tuple[np.ndarray, np.ndarray]:
     """Returns (out [B, Hq, Dv] float32, lse [B, Hq] float32), computed in float64.
 
     Request b attends to slots ``req_to_token[req_pool_indices[b], :seq_lens[b]]``
     (torch_native_backend.py:160-163); q head h uses kv head ``h // (Hq / Hkv)`` (SDPA
     ``enable_gqa``).  fp8 pools are dequantised as ``fp8 * scale``
     (layers/quantization/kv_cache.py:21-23).  ``logit_cap``: ``cap * tanh(x / cap)`` after the
-    scale (triton_ops/decode_attention.py:349-352).
+    scale (triton_ops/decode_attention.py:349-352).  ``sliding_window`` W > 0: only the last
+    ``min(S, W + 1)`` tokens, ``req_to_token[req, S - len : S]`` (update_sliding_window_buffer,
+    layers/attention/triton_backend.py:927-956).
     """
     qf = _to_f32(q).astype(np.float64)
     B, Hq, D = qf.shape
@@ -214,7 +219,8 @@ def decode_attention(q: torch.Tensor, k_pool: torch.Tensor, v_pool: torch.Tensor
         S = int(sl[b])
         if S == 0:
             continue
-        slots = r2t[rpi[b], :S].astype(np.int64)
+        wl = min(S, sliding_window + 1) if sliding_window > 0 else S
+        slots = r2t[rpi[b], S - wl:S].astype(np.int64)
         K = kf[slots].astype(np.float64) * k_scale  # [S, Hkv, D]
         V = vf[slots].astype(np.float64) * v_scale
         qg = qf[b].reshape(Hkv, G, D)

@@ -589,3 +589,40 @@ def test_fused_merge_equals_two_stage(dyn, tp, monkeypatch):
                                            w.req_pool_indices.cpu(), w.seq_lens.cpu(), w.sm_scale)
     assert_close_out(o1.float().cpu().numpy(), ref)
     assert np.abs(l1.view(B, Hq).cpu().numpy() - ref_lse).max() <= 1e-3
+
+
+# ----------------------------------------------------------------------------- #
+# sliding-window layers (interleaved with full-attention layers)
+# ----------------------------------------------------------------------------- #
+@pytest.mark.parametrize("window", [1, 16, 127, 4096])
+def test_sliding_window_layers(window):
+    """A window layer attends to the last min(S, W + 1) tokens (triton_backend.py:927-956), a full layer
+    of the same forward to everything; window_kv_indptr / window_kv_indices are bit-exact."""
+    import b200attn
+    from oracle import decode_oracle as oracle
+
+    cfg = synth.Config("swa", 9, 0, 16, 4, 128, page_size=4, ragged=(1, 700), seed=51)
+    w_cpu, w = _pair(cfg)
+    _check_same_inputs(w_cpu, w)
+    runner = make_runner(w, DEV)
+    runner.sliding_window_size = window
+    backend = b200attn.B200AttnBackend(runner, return_lse=True, materialize_kv_indices=True, max_ctas=11)
+    c = cfg
+    qc = w_cpu.q.reshape(c.batch, c.num_q_heads, c.head_dim)
+    for layer_window in (window, -1):
+        layer = make_layer(w)
+        layer.sliding_window_size = layer_window
+        out = run_decode(backend, runner, w, layer=layer, save_kv_cache=False)
+        torch.cuda.synchronize()
+        ref, ref_lse = oracle.decode_attention(qc, w_cpu.k_pool, w_cpu.v_pool, w_cpu.req_to_token,
+                                               w_cpu.req_pool_indices, w_cpu.seq_lens, w_cpu.sm_scale,
+                                               sliding_window=max(layer_window, 0))
+        assert_close_out(out.float().cpu().numpy().reshape(ref.shape), ref)
+        assert np.abs(backend.last_lse(c.batch).cpu().numpy() - ref_lse).max() <= 1e-3
+    md = backend.forward_metadata
+    indptr, indices = oracle.kv_indices(w_cpu.req_to_token, w_cpu.req_pool_indices, w_cpu.seq_lens, window)
+    assert np.array_equal(md.window_kv_indptr.cpu().numpy(), indptr)
+    assert np.array_equal(md.window_kv_indices.cpu().numpy()[: indptr[-1]], indices)
+    indptr, indices = oracle.kv_indices(w_cpu.req_to_token, w_cpu.req_pool_indices, w_cpu.seq_lens)
+    assert np.array_equal(md.kv_indptr.cpu().numpy(), indptr)
+    assert np.array_equal(md.kv_indices.cpu().numpy(), indices)
