@@ -24,6 +24,10 @@
  *                       set_kv_buffer (memory_pool.py:369-407); call site models/llama.py:186-189
  *   b200attn_merge_states  sgl-kernel/csrc/attention/merge_attn_states.cu:31-204
  *                       (merge_state_v2: 2-way (o, lse) merge)
+ *   b200attn_extend     python/sglang/srt/layers/attention/triton_ops/extend_attention.py:306-438
+ *                       (extend_attention_fwd: prefill / extend over cached prefix + new tokens,
+ *                       causal, custom-mask (speculative verify), sliding-window and logit-cap
+ *                       variants), and the math of torch_native_backend.py:27-110
  *
  * Error convention: 0 on success, a negative B200ATTN_E_* code otherwise.
  * Nothing is launched when an error is returned.  Launch failures reported by
@@ -39,7 +43,7 @@
 extern "C" {
 #endif
 
-#define B200ATTN_ABI_VERSION 2
+#define B200ATTN_ABI_VERSION 3
 
 /* cudaStream_t without pulling in the CUDA headers. */
 typedef void* b200attn_stream_t;
@@ -220,6 +224,93 @@ typedef struct {
 size_t b200attn_workspace_bytes(int32_t batch, int32_t num_q_heads, int32_t num_kv_heads,
                                 int32_t head_dim, int32_t v_head_dim, int32_t kv_dtype);
 int b200attn_decode(const b200attn_decode_args* args, b200attn_stream_t stream);
+
+/* ------------------------------------------------------------------ */
+/* K5: extend (prefill with cached prefix) attention                   */
+/* ------------------------------------------------------------------ */
+/* Replaces extend_attention_fwd (triton_ops/extend_attention.py:306-438; kernel :41-303) as
+ * TritonAttnBackend.forward_extend calls it (triton_backend.py:632-685) for EXTEND / MIXED /
+ * TARGET_VERIFY / DRAFT_EXTEND batches.  Request b owns the query tokens
+ * [qo_indptr[b], qo_indptr[b+1]) ("extend" tokens) and attends to
+ *   - its cached prefix: Lp = kv_indptr[b+1] - kv_indptr[b] pool slots, listed either in
+ *     kv_indices[kv_indptr[b] ...] (CSR, what the reference materialises) or read in place from
+ *     req_to_token[req_pool_indices[b], prefix_lens[b] - Lp ...] (no kv_indices needed; with a
+ *     sliding window Lp < prefix_lens[b] and the list is the prefix's tail, the reference's
+ *     window_kv_indices, triton_backend.py:927-956);
+ *   - the extend tokens themselves, read back from the pool at extend_loc[token] (out_cache_loc:
+ *     set_kv_buffer / b200attn_kv_store has stored them before this call, :647-650).  The
+ *     reference reads them from the contiguous k_extend / v_extend instead; for a 16-bit pool the
+ *     bytes are identical.
+ * Masks, exactly as the reference kernel applies them (q index i and kv index j are local to the
+ * request's extend tokens / to its prefix list):
+ *   prefix part:  [custom_mask[i, j] unless skip_prefix_custom_mask]  and
+ *                 [i <= j + sliding_window when sliding_window > 0]          (:166-184)
+ *   extend part:  custom_mask[i, Lp + j] when a custom mask is given, else j <= i when causal,
+ *                 else everything                                            (:245-264)
+ * custom_mask is the flattened per-request [Le, Lp + Le] uint8/bool array starting at
+ * mask_indptr[b] (:93-95, :169-177).  A row with no visible key yields o = 0, lse = -inf. */
+typedef struct {
+  const void* q;               /* [tokens, num_q_heads, head_dim], strides in elements */
+  int64_t q_stride_token, q_stride_head;
+  void* o;                     /* [tokens, num_q_heads, v_head_dim], q dtype */
+  int64_t o_stride_token, o_stride_head;
+  float* lse;                  /* optional [tokens, num_q_heads]: ln sum exp(scaled logits) */
+  const void* k_pool;          /* [slots, num_kv_heads, head_dim] */
+  const void* v_pool;
+  int64_t k_pool_stride_slot;  /* elements */
+  int64_t v_pool_stride_slot;
+  const int32_t* qo_indptr;    /* [batch + 1] */
+  const int32_t* kv_indptr;    /* [batch + 1] prefix list lengths (CSR) */
+  const int32_t* kv_indices;   /* prefix slots (CSR mode), or NULL for the req_to_token mode */
+  const int32_t* req_to_token; /* req_to_token mode: [max_reqs, stride] */
+  int64_t req_to_token_stride;
+  const void* req_pool_indices; /* [batch] int32|int64 */
+  const void* prefix_lens;      /* [batch] int32|int64: cached tokens of the request (extend_prefix_lens) */
+  int32_t index_dtype;          /* B200ATTN_I32 | B200ATTN_I64 (req_pool_indices, prefix_lens) */
+  int32_t mask_indptr_dtype;    /* B200ATTN_I32 | B200ATTN_I64 (the reference keeps it in int64) */
+  const int64_t* extend_loc;    /* [tokens] pool slot of every extend token (out_cache_loc) */
+  const uint8_t* custom_mask;   /* optional */
+  const void* mask_indptr;      /* [batch + 1], required with custom_mask */
+  int32_t batch;
+  int32_t total_tokens;         /* rows of q */
+  int32_t max_extend_len;       /* >= max_b (qo_indptr[b+1] - qo_indptr[b]); sizes the grid */
+  int32_t num_q_heads;
+  int32_t num_kv_heads;
+  int32_t head_dim;
+  int32_t v_head_dim;
+  int32_t q_dtype;              /* B200ATTN_BF16 | B200ATTN_F16 */
+  int32_t kv_dtype;             /* == q_dtype (fp8 pools: not yet) */
+  int32_t causal;               /* 1: extend token i sees extend tokens j <= i */
+  int32_t sliding_window;       /* <= 0: off */
+  int32_t skip_prefix_custom_mask; /* 1 (the reference's default): custom_mask covers the extend part only */
+  float sm_scale;
+  float logit_cap;              /* 0 disables */
+  float k_scale, v_scale;       /* reserved for fp8 pools; 1.0 */
+} b200attn_extend_args;
+
+int b200attn_extend(const b200attn_extend_args* args, b200attn_stream_t stream);
+
+/* Index arrays of one extend forward, in one launch (the reference runs 2-3 torch.cumsum launches
+ * plus slicing, triton_backend.py:227-318):
+ *   qo_indptr[b+1]   = sum_{i<=b} Le_i      Le_i = extend_seq_lens[i], or uniform_extend_len when that is
+ *                                           > 0 (TARGET_VERIFY: num_draft_tokens per request, :230-236)
+ *   kv_indptr[b+1]   = sum_{i<=b} Lp_i      Lp_i = prefix_lens[i], or min(prefix_lens[i], W + 1) with a
+ *                                           sliding window (window_kv_indptr, :927-946)
+ *   mask_indptr[b+1] = sum_{i<=b} Le_i * (prefix_lens[i] + Le_i)   (optional, int64; :252-259)
+ * No host synchronisation; CUDA-graph capture safe. */
+typedef struct {
+  const void* extend_seq_lens;  /* [batch] int32|int64, or NULL with uniform_extend_len > 0 */
+  const void* prefix_lens;      /* [batch] int32|int64 */
+  int32_t index_dtype;          /* B200ATTN_I32 | B200ATTN_I64 */
+  int32_t batch;
+  int32_t uniform_extend_len;
+  int32_t sliding_window;       /* <= 0: off */
+  int32_t* qo_indptr;           /* out [batch + 1] */
+  int32_t* kv_indptr;           /* out [batch + 1] */
+  int64_t* mask_indptr;         /* optional out [batch + 1] */
+} b200attn_extend_plan_args;
+
+int b200attn_extend_plan(const b200attn_extend_plan_args* args, b200attn_stream_t stream);
 
 /* ------------------------------------------------------------------ */
 /* 2-way state merge (merge_state_v2 semantics)                        */

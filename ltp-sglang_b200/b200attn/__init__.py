@@ -8,9 +8,10 @@ from . import capi
 capi.lib()
 
 from . import ops  # noqa: E402  (registers torch.ops.b200attn.*)
-from .backend import B200AttnBackend, ForwardMetadata, rope_store_kv, store_kv  # noqa: E402
+from .backend import B200AttnBackend, ExtendMetadata, ForwardMetadata, rope_store_kv, store_kv  # noqa: E402
 from .interfaces import (  # noqa: E402
     AttentionBackend,
+    AttentionType,
     AttnLayer,
     ForwardBatch,
     ForwardMode,
@@ -23,10 +24,12 @@ __all__ = [
     "ops",
     "B200AttnBackend",
     "ForwardMetadata",
+    "ExtendMetadata",
     "store_kv",
     "rope_store_kv",
     "AttentionBackend",
     "AttnLayer",
+    "AttentionType",
     "ForwardBatch",
     "ForwardMode",
     "MHATokenToKVPool",

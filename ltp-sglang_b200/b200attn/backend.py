@@ -114,6 +114,22 @@ class ForwardMetadata:
     window_kv_indices: Optional[torch.Tensor] = None
 
 
+@dataclass
+class ExtendMetadata:
+    """Index arrays of one EXTEND / MIXED / TARGET_VERIFY / DRAFT_EXTEND forward (the extend half of
+    the reference's ``ForwardMetadata``, triton_backend.py:25-38)."""
+    batch: int
+    qo_indptr: torch.Tensor
+    kv_indptr: torch.Tensor
+    kv_indices: Optional[torch.Tensor]        # None: prefix slots are read from req_to_token in place
+    req_pool_indices: Optional[torch.Tensor]
+    prefix_lens: Optional[torch.Tensor]
+    custom_mask: Optional[torch.Tensor]
+    mask_indptr: Optional[torch.Tensor]
+    max_extend_len: Optional[int]             # None: bounded by the token count at forward time
+    window_kv_indptr: Optional[torch.Tensor] = None
+
+
 class B200AttnBackend(AttentionBackend):
     def __init__(self, model_runner: Any, prefill_backend: Optional[AttentionBackend] = None,
                  materialize_kv_indices: bool = False, max_ctas: int = 0, min_chunks: int = 0,
@@ -173,6 +189,15 @@ class B200AttnBackend(AttentionBackend):
         self.lse = torch.empty(self.max_bs * self.num_head, dtype=torch.float32, device=dev) if return_lse else None
         self.cuda_graph_kv_indices: Optional[torch.Tensor] = None
         self.forward_metadata: Optional[ForwardMetadata] = None
+        # extend (prefill) path: index buffers as triton_backend.py:92-99
+        self.qo_indptr = torch.zeros(self.max_bs + 1, dtype=torch.int32, device=dev)
+        self.extend_kv_indptr = torch.zeros(self.max_bs + 1, dtype=torch.int32, device=dev)
+        self.extend_window_kv_indptr = torch.zeros_like(self.extend_kv_indptr) \
+            if self.sliding_window_size is not None else None
+        self.mask_indptr = torch.zeros(self.max_bs + 1, dtype=torch.int64, device=dev)
+        sa = getattr(model_runner, "server_args", None)
+        self.num_draft_tokens = getattr(sa, "speculative_num_draft_tokens", None)
+        self.extend_metadata: Optional[ExtendMetadata] = None
 
     # ------------------------------------------------------------------ #
     # metadata
@@ -221,8 +246,52 @@ class B200AttnBackend(AttentionBackend):
                 return
             self._plan(forward_batch.batch_size, forward_batch.req_pool_indices, forward_batch.seq_lens,
                        forward_batch.seq_lens_sum, forward_batch.spec_info, graph=False)
+        elif self.prefill_backend is not None:
+            self.prefill_backend.init_forward_metadata(forward_batch)
         else:
-            self._prefill().init_forward_metadata(forward_batch)
+            self._plan_extend(forward_batch.batch_size, forward_batch.req_pool_indices, forward_batch.seq_lens,
+                              mode, forward_batch.spec_info, forward_batch)
+
+    def _plan_extend(self, bs: int, req_pool_indices: torch.Tensor, seq_lens: torch.Tensor, mode,
+                     spec_info: Any, forward_batch: Any = None) -> None:
+        """Metadata of the native extend path: what ``TritonAttnBackend.init_forward_metadata`` builds
+        for its three extend modes (triton_backend.py:227-318), in one launch and without
+        materialising ``kv_indices`` for the cached prefix."""
+        if bs > self.max_bs:
+            raise ValueError(f"batch {bs} exceeds req_to_token_pool.size {self.max_bs}")
+        if bs == 0:
+            self.extend_metadata = None
+            return
+        qo, kv, win = self.qo_indptr[: bs + 1], self.extend_kv_indptr[: bs + 1], None
+        rpi = req_pool_indices[:bs]
+        if mode.is_target_verify():
+            # prefix = the whole committed sequence, extend = num_draft_tokens per request, visibility
+            # inside the draft tree from spec_info.custom_mask (:227-263)
+            n = int(getattr(spec_info, "draft_token_num", None) or self.num_draft_tokens)
+            pl = seq_lens[:bs]
+            if pl.dtype != rpi.dtype:
+                pl = pl.to(rpi.dtype)
+            mi = self.mask_indptr[: bs + 1]
+            torch.ops.b200attn.extend_plan(None, pl, qo, kv, mi, n, 0)
+            self.extend_metadata = ExtendMetadata(bs, qo, kv, None, rpi, pl, spec_info.custom_mask, mi, n)
+        elif mode.is_draft_extend():
+            kv_indices, kv_indptr, qo_indptr, custom_mask = spec_info.generate_attn_arg_prefill(
+                req_pool_indices, seq_lens, None, self.req_to_token)   # :265-279
+            self.extend_metadata = ExtendMetadata(bs, qo_indptr, kv_indptr, kv_indices, None, None,
+                                                  custom_mask, None, None)
+        else:
+            pl, el = forward_batch.extend_prefix_lens[:bs], forward_batch.extend_seq_lens[:bs]
+            if pl.dtype != rpi.dtype:
+                pl = pl.to(rpi.dtype)
+            if el.dtype != pl.dtype:
+                el = el.to(pl.dtype)
+            torch.ops.b200attn.extend_plan(el, pl, qo, kv, None, 0, 0)
+            if self.sliding_window_size is not None:
+                win = self.extend_window_kv_indptr[: bs + 1]
+                torch.ops.b200attn.extend_plan(el, pl, qo, win, None, 0, self.sliding_window_size)
+            cpu = getattr(forward_batch, "extend_seq_lens_cpu", None)
+            self.extend_metadata = ExtendMetadata(bs, qo, kv, None, rpi, pl, None, None,
+                                                  max(cpu) if cpu else None, win)
 
     def init_cuda_graph_state(self, max_bs: int, max_num_tokens: int):
         if self.materialize_kv_indices:
@@ -241,16 +310,22 @@ class B200AttnBackend(AttentionBackend):
                                                  encoder_lens, forward_mode, spec_info):
         assert encoder_lens is None, "cross attention is not supported"
         if not forward_mode.is_decode_or_idle():
-            return self._prefill().init_forward_metadata_capture_cuda_graph(
-                bs, num_tokens, req_pool_indices, seq_lens, encoder_lens, forward_mode, spec_info)
+            if self.prefill_backend is not None:
+                return self.prefill_backend.init_forward_metadata_capture_cuda_graph(
+                    bs, num_tokens, req_pool_indices, seq_lens, encoder_lens, forward_mode, spec_info)
+            if not (forward_mode.is_target_verify() or forward_mode.is_draft_extend()):
+                raise ValueError(f"Invalid forward mode for CUDA graph capture: {forward_mode!r}")  # triton_backend.py:509-511
+            return self._plan_extend(bs, req_pool_indices, seq_lens, forward_mode, spec_info)
         self._plan(bs, req_pool_indices, seq_lens, None, spec_info, graph=True)
 
     def init_forward_metadata_replay_cuda_graph(self, bs, req_pool_indices, seq_lens, seq_lens_sum,
                                                 encoder_lens, forward_mode, spec_info, seq_lens_cpu):
         if not forward_mode.is_decode_or_idle():
-            return self._prefill().init_forward_metadata_replay_cuda_graph(
-                bs, req_pool_indices, seq_lens, seq_lens_sum, encoder_lens, forward_mode, spec_info,
-                seq_lens_cpu)
+            if self.prefill_backend is not None:
+                return self.prefill_backend.init_forward_metadata_replay_cuda_graph(
+                    bs, req_pool_indices, seq_lens, seq_lens_sum, encoder_lens, forward_mode, spec_info,
+                    seq_lens_cpu)
+            return self._plan_extend(bs, req_pool_indices, seq_lens, forward_mode, spec_info)
         self._plan(bs, req_pool_indices, seq_lens, seq_lens_sum, spec_info, graph=True)
 
     def get_cuda_graph_seq_len_fill_value(self):
@@ -310,14 +385,64 @@ class B200AttnBackend(AttentionBackend):
         return self.lse[: bs * self.num_head].view(bs, self.num_head)
 
     def forward_extend(self, q, k, v, layer, forward_batch, save_kv_cache: bool = True):
-        return self._prefill().forward_extend(q, k, v, layer, forward_batch, save_kv_cache=save_kv_cache)
+        """Native extend / prefill attention (``TritonAttnBackend.forward_extend``,
+        triton_backend.py:632-685): KV store, then one ``extend`` launch over cached prefix + new
+        tokens.  With a ``prefill_backend`` the call is delegated instead."""
+        if self.prefill_backend is not None:
+            return self.prefill_backend.forward_extend(q, k, v, layer, forward_batch, save_kv_cache=save_kv_cache)
+        if getattr(layer, "is_cross_attention", False):
+            raise NotImplementedError("B200AttnBackend: cross attention is not supported")
+        if layer.qk_head_dim != layer.v_head_dim:
+            raise NotImplementedError("B200AttnBackend: qk_head_dim != v_head_dim is not supported")
+        if self.kv_dtype == capi.FP8_E4M3:
+            raise NotImplementedError("B200AttnBackend: extend attention over an fp8 KV pool is not supported yet; "
+                                      "construct the backend with prefill_backend=...")
+        q = q.reshape(-1, layer.tp_q_head_num * layer.qk_head_dim)
+        o = torch.empty_like(q)
+        pool = forward_batch.token_to_kv_pool
+        start = getattr(pool, "start_layer", 0) or 0
+        k_pool = pool.k_buffer[layer.layer_id - start]
+        v_pool = pool.v_buffer[layer.layer_id - start]
+        loc = forward_batch.out_cache_loc
+        if loc.dtype != torch.int64:
+            loc = loc.to(torch.int64)
+        if save_kv_cache and k is not None:
+            store_kv(k_pool, v_pool, loc, k.view(-1, layer.tp_k_head_num, layer.qk_head_dim),
+                     v.view(-1, layer.tp_v_head_num, layer.v_head_dim))
+        md = self.extend_metadata
+        tokens = q.shape[0]
+        if tokens == 0:
+            return o
+        if md is None:
+            raise RuntimeError("B200AttnBackend.forward_extend: init_forward_metadata was not run for this batch")
+        causal = getattr(getattr(layer, "attn_type", None), "name", "DECODER") != "ENCODER_ONLY"
+        sw = getattr(layer, "sliding_window_size", -1)
+        windowed = sw is not None and sw > -1
+        kv_indptr = md.kv_indptr
+        if windowed:
+            if md.window_kv_indptr is None:
+                raise NotImplementedError("B200AttnBackend: sliding-window layers need model_runner.sliding_window_size "
+                                          "and a plain EXTEND batch")
+            kv_indptr = md.window_kv_indptr
+        max_len = tokens if md.max_extend_len is None else min(md.max_extend_len, tokens)
+        torch.ops.b200attn.extend(
+            q.view(tokens, layer.tp_q_head_num, layer.qk_head_dim),
+            o.view(tokens, layer.tp_q_head_num, layer.v_head_dim),
+            self.lse_extend(tokens) if self.return_lse else None,
+            k_pool, v_pool, md.qo_indptr, kv_indptr, md.kv_indices,
+            self.req_to_token if md.kv_indices is None else None, md.req_pool_indices, md.prefix_lens,
+            loc, md.custom_mask, md.mask_indptr, int(max_len), causal,
+            int(sw) if windowed else -1, True, float(layer.scaling),
+            float(getattr(layer, "logit_cap", 0.0) or 0.0))
+        return o
 
-    def _prefill(self) -> AttentionBackend:
-        if self.prefill_backend is None:
-            raise NotImplementedError(
-                "B200AttnBackend implements decode; construct it with prefill_backend=<an extend-capable "
-                "backend> (or use --prefill-attention-backend) for EXTEND / MIXED / speculative modes")
-        return self.prefill_backend
+    def lse_extend(self, tokens: int) -> torch.Tensor:
+        """fp32 ``[tokens, heads]`` buffer the extend kernel writes ln sum exp(scaled logits) into."""
+        buf = getattr(self, "_lse_extend", None)
+        if buf is None or buf.numel() < tokens * self.num_head:
+            buf = torch.empty(tokens * self.num_head, dtype=torch.float32, device=self.device)
+            self._lse_extend = buf
+        return buf[: tokens * self.num_head]
 
     def support_triton(self):
         return True

@@ -19,7 +19,7 @@ E_INVALID, E_UNSUPPORTED, E_ALIGN, E_CUDA, E_WORKSPACE = -1, -2, -3, -4, -5
 BF16, F16, FP8_E4M3 = 0, 1, 2
 I32, I64 = 0, 1
 SCALE_NONE, SCALE_TRUE_DIV, SCALE_RECIP_MUL = 0, 1, 2
-ABI_VERSION = 2
+ABI_VERSION = 3
 
 
 class KvStoreArgs(C.Structure):
@@ -128,6 +128,64 @@ class DecodeArgs(C.Structure):
     ]
 
 
+class ExtendArgs(C.Structure):
+    _fields_ = [
+        ("q", C.c_void_p),
+        ("q_stride_token", C.c_int64),
+        ("q_stride_head", C.c_int64),
+        ("o", C.c_void_p),
+        ("o_stride_token", C.c_int64),
+        ("o_stride_head", C.c_int64),
+        ("lse", C.c_void_p),
+        ("k_pool", C.c_void_p),
+        ("v_pool", C.c_void_p),
+        ("k_pool_stride_slot", C.c_int64),
+        ("v_pool_stride_slot", C.c_int64),
+        ("qo_indptr", C.c_void_p),
+        ("kv_indptr", C.c_void_p),
+        ("kv_indices", C.c_void_p),
+        ("req_to_token", C.c_void_p),
+        ("req_to_token_stride", C.c_int64),
+        ("req_pool_indices", C.c_void_p),
+        ("prefix_lens", C.c_void_p),
+        ("index_dtype", C.c_int32),
+        ("mask_indptr_dtype", C.c_int32),
+        ("extend_loc", C.c_void_p),
+        ("custom_mask", C.c_void_p),
+        ("mask_indptr", C.c_void_p),
+        ("batch", C.c_int32),
+        ("total_tokens", C.c_int32),
+        ("max_extend_len", C.c_int32),
+        ("num_q_heads", C.c_int32),
+        ("num_kv_heads", C.c_int32),
+        ("head_dim", C.c_int32),
+        ("v_head_dim", C.c_int32),
+        ("q_dtype", C.c_int32),
+        ("kv_dtype", C.c_int32),
+        ("causal", C.c_int32),
+        ("sliding_window", C.c_int32),
+        ("skip_prefix_custom_mask", C.c_int32),
+        ("sm_scale", C.c_float),
+        ("logit_cap", C.c_float),
+        ("k_scale", C.c_float),
+        ("v_scale", C.c_float),
+    ]
+
+
+class ExtendPlanArgs(C.Structure):
+    _fields_ = [
+        ("extend_seq_lens", C.c_void_p),
+        ("prefix_lens", C.c_void_p),
+        ("index_dtype", C.c_int32),
+        ("batch", C.c_int32),
+        ("uniform_extend_len", C.c_int32),
+        ("sliding_window", C.c_int32),
+        ("qo_indptr", C.c_void_p),
+        ("kv_indptr", C.c_void_p),
+        ("mask_indptr", C.c_void_p),
+    ]
+
+
 class MergeStatesArgs(C.Structure):
     _fields_ = [
         ("o_a", C.c_void_p),
@@ -154,6 +212,8 @@ SYMBOLS = {
         [C.c_int32, C.c_int32, C.c_int32, C.c_int32, C.c_int32, C.c_int32],
     ),
     "b200attn_decode": (C.c_int, [C.POINTER(DecodeArgs), C.c_void_p]),
+    "b200attn_extend": (C.c_int, [C.POINTER(ExtendArgs), C.c_void_p]),
+    "b200attn_extend_plan": (C.c_int, [C.POINTER(ExtendPlanArgs), C.c_void_p]),
     "b200attn_merge_states": (C.c_int, [C.POINTER(MergeStatesArgs), C.c_void_p]),
     "b200attn_abi_version": (C.c_int, []),
     "b200attn_strerror": (C.c_char_p, [C.c_int]),

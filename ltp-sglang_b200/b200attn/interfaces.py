@@ -51,6 +51,12 @@ class ForwardMode(enum.IntEnum):
         return self == ForwardMode.DRAFT_EXTEND
 
 
+class AttentionType(enum.Enum):
+    """layers/radix_attention.py:25-36."""
+    DECODER = "decoder"
+    ENCODER_ONLY = "encoder_only"
+
+
 class ReqToTokenPool:
     """request -> token-slot map: int32 ``[size, max_context_len]``."""
 
@@ -140,7 +146,8 @@ class AttnLayer:
 
     def __init__(self, num_heads: int, head_dim: int, scaling: float, num_kv_heads: int, layer_id: int,
                  logit_cap: float = 0.0, v_head_dim: int = -1, sliding_window_size: int = -1,
-                 is_cross_attention: bool = False):
+                 is_cross_attention: bool = False, attn_type: AttentionType = AttentionType.DECODER):
+        self.attn_type = attn_type
         self.tp_q_head_num = num_heads
         self.tp_k_head_num = num_kv_heads
         self.tp_v_head_num = num_kv_heads
@@ -187,6 +194,8 @@ class ForwardBatch:
     positions: Optional[torch.Tensor] = None
     extend_prefix_lens: Optional[torch.Tensor] = None
     extend_seq_lens: Optional[torch.Tensor] = None
+    extend_seq_lens_cpu: Optional[List[int]] = None
+    extend_prefix_lens_cpu: Optional[List[int]] = None
 
 
 class AttentionBackend(ABC):

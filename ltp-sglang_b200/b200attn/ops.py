@@ -241,6 +241,104 @@ def _decode(q, k_pool, v_pool, o, lse, plan_buf, indices, workspace, sm_scale, l
         capi.check("b200attn_decode", capi.lib().b200attn_decode(C.byref(a), _stream(q)))
 
 
+def _extend(q, o, lse, k_pool, v_pool, qo_indptr, kv_indptr, kv_indices, req_to_token, req_pool_indices,
+            prefix_lens, extend_loc, custom_mask, mask_indptr, max_extend_len, causal, sliding_window,
+            skip_prefix_custom_mask, sm_scale, logit_cap):
+    """Extend / prefill attention over cached prefix + new tokens (``extend_attention_fwd``,
+    triton_ops/extend_attention.py:306-438); the new tokens' K/V are read from the pool at
+    ``extend_loc`` (``out_cache_loc``), where ``kv_store`` has put them."""
+    _cuda(q, o, lse, k_pool, v_pool, qo_indptr, kv_indptr, kv_indices, req_to_token, req_pool_indices,
+          prefix_lens, extend_loc, custom_mask, mask_indptr)
+    if q.dim() != 3 or o.dim() != 3 or k_pool.dim() != 3 or v_pool.dim() != 3:
+        raise ValueError("extend: q/o must be [tokens, heads, dim]; pools [slots, kv_heads, dim]")
+    if q.stride(2) != 1 or o.stride(2) != 1 or k_pool.stride(2) != 1 or v_pool.stride(2) != 1:
+        raise ValueError("extend: last dim must be contiguous")
+    if k_pool.stride(1) != k_pool.shape[2] or v_pool.stride(1) != v_pool.shape[2]:
+        raise ValueError("extend: kv heads of a slot must be adjacent ([slots, kv_heads, dim] layout)")
+    if o.dtype != q.dtype or o.shape[0] != q.shape[0] or o.shape[1] != q.shape[1]:
+        raise ValueError("extend: o must match q in dtype, tokens and heads")
+    for name, t in (("qo_indptr", qo_indptr), ("kv_indptr", kv_indptr), ("kv_indices", kv_indices)):
+        if t is not None and (t.dtype != torch.int32 or not t.is_contiguous()):
+            raise TypeError(f"extend: {name} must be contiguous int32")
+    batch = qo_indptr.numel() - 1
+    if kv_indptr.numel() < batch + 1:
+        raise ValueError("extend: kv_indptr needs batch + 1 entries")
+    if extend_loc.dtype != torch.int64 or not extend_loc.is_contiguous() or extend_loc.numel() < q.shape[0]:
+        raise TypeError("extend: extend_loc must be contiguous int64 [tokens] (out_cache_loc)")
+    a = capi.ExtendArgs()
+    if kv_indices is None:
+        if req_to_token is None or req_pool_indices is None or prefix_lens is None:
+            raise ValueError("extend: give kv_indices, or req_to_token + req_pool_indices + prefix_lens")
+        if req_to_token.dtype != torch.int32 or req_to_token.dim() != 2 or req_to_token.stride(1) != 1:
+            raise TypeError("extend: req_to_token must be int32 [max_reqs, max_context_len]")
+        if req_pool_indices.dtype != prefix_lens.dtype or prefix_lens.dtype not in _IDX:
+            raise TypeError("extend: req_pool_indices and prefix_lens must both be int32 or both int64")
+        if not (req_pool_indices.is_contiguous() and prefix_lens.is_contiguous()):
+            raise ValueError("extend: req_pool_indices / prefix_lens must be contiguous")
+        if req_pool_indices.numel() < batch or prefix_lens.numel() < batch:
+            raise ValueError("extend: req_pool_indices / prefix_lens shorter than the batch")
+        a.req_to_token = req_to_token.data_ptr()
+        a.req_to_token_stride = req_to_token.stride(0)
+        a.req_pool_indices, a.prefix_lens = req_pool_indices.data_ptr(), prefix_lens.data_ptr()
+        a.index_dtype = _IDX[prefix_lens.dtype]
+    if custom_mask is not None:
+        if custom_mask.dtype not in (torch.uint8, torch.bool) or not custom_mask.is_contiguous():
+            raise TypeError("extend: custom_mask must be a contiguous bool / uint8 tensor")
+        if mask_indptr is None or mask_indptr.dtype not in _IDX or not mask_indptr.is_contiguous():
+            raise TypeError("extend: mask_indptr must be contiguous int32/int64 [batch + 1]")
+        a.custom_mask, a.mask_indptr = custom_mask.data_ptr(), mask_indptr.data_ptr()
+        a.mask_indptr_dtype = _IDX[mask_indptr.dtype]
+    if lse is not None and (lse.dtype != torch.float32 or not lse.is_contiguous()
+                            or lse.numel() < q.shape[0] * q.shape[1]):
+        raise TypeError("extend: lse must be contiguous float32 [tokens, heads]")
+    a.q, a.o, a.lse = q.data_ptr(), o.data_ptr(), _ptr(lse)
+    a.q_stride_token, a.q_stride_head = q.stride(0), q.stride(1)
+    a.o_stride_token, a.o_stride_head = o.stride(0), o.stride(1)
+    a.k_pool, a.v_pool = k_pool.data_ptr(), v_pool.data_ptr()
+    a.k_pool_stride_slot, a.v_pool_stride_slot = k_pool.stride(0), v_pool.stride(0)
+    a.qo_indptr, a.kv_indptr, a.kv_indices = qo_indptr.data_ptr(), kv_indptr.data_ptr(), _ptr(kv_indices)
+    a.extend_loc = extend_loc.data_ptr()
+    a.batch, a.total_tokens, a.max_extend_len = batch, q.shape[0], max_extend_len
+    a.num_q_heads, a.num_kv_heads = q.shape[1], k_pool.shape[1]
+    a.head_dim, a.v_head_dim = q.shape[2], v_pool.shape[2]
+    a.q_dtype, a.kv_dtype = dtype_code(q.dtype), dtype_code(k_pool.dtype)
+    a.causal = 1 if causal else 0
+    a.sliding_window = sliding_window
+    a.skip_prefix_custom_mask = 1 if skip_prefix_custom_mask else 0
+    a.sm_scale, a.logit_cap, a.k_scale, a.v_scale = sm_scale, logit_cap, 1.0, 1.0
+    with torch.cuda.device(q.device):
+        capi.check("b200attn_extend", capi.lib().b200attn_extend(C.byref(a), _stream(q)))
+
+
+def _extend_plan(extend_seq_lens, prefix_lens, qo_indptr, kv_indptr, mask_indptr, uniform_extend_len,
+                 sliding_window):
+    """qo_indptr / kv_indptr / mask_indptr of one extend forward in one launch."""
+    _cuda(extend_seq_lens, prefix_lens, qo_indptr, kv_indptr, mask_indptr)
+    if prefix_lens.dtype not in _IDX or not prefix_lens.is_contiguous():
+        raise TypeError("extend_plan: prefix_lens must be contiguous int32/int64")
+    batch = prefix_lens.numel()
+    if extend_seq_lens is not None and (extend_seq_lens.dtype != prefix_lens.dtype
+                                        or not extend_seq_lens.is_contiguous()
+                                        or extend_seq_lens.numel() != batch):
+        raise TypeError("extend_plan: extend_seq_lens must match prefix_lens in dtype and length")
+    if extend_seq_lens is None and uniform_extend_len <= 0:
+        raise ValueError("extend_plan: give extend_seq_lens or uniform_extend_len > 0")
+    for name, t in (("qo_indptr", qo_indptr), ("kv_indptr", kv_indptr)):
+        if t.dtype != torch.int32 or not t.is_contiguous() or t.numel() < batch + 1:
+            raise TypeError(f"extend_plan: {name} must be contiguous int32 [batch + 1]")
+    if mask_indptr is not None and (mask_indptr.dtype != torch.int64 or not mask_indptr.is_contiguous()
+                                    or mask_indptr.numel() < batch + 1):
+        raise TypeError("extend_plan: mask_indptr must be contiguous int64 [batch + 1]")
+    a = capi.ExtendPlanArgs()
+    a.extend_seq_lens, a.prefix_lens = _ptr(extend_seq_lens), prefix_lens.data_ptr()
+    a.index_dtype = _IDX[prefix_lens.dtype]
+    a.batch = batch
+    a.uniform_extend_len, a.sliding_window = uniform_extend_len, sliding_window
+    a.qo_indptr, a.kv_indptr, a.mask_indptr = qo_indptr.data_ptr(), kv_indptr.data_ptr(), _ptr(mask_indptr)
+    with torch.cuda.device(prefix_lens.device):
+        capi.check("b200attn_extend_plan", capi.lib().b200attn_extend_plan(C.byref(a), _stream(prefix_lens)))
+
+
 def _merge_states(o_a, lse_a, o_b, lse_b, o_out, lse_out):
     _cuda(o_a, lse_a, o_b, lse_b, o_out, lse_out)
     if o_a.dim() != 3 or o_a.shape != o_b.shape or o_out.shape != o_a.shape:
@@ -287,6 +385,16 @@ _LIB.define(
     "float v_scale, int phases=0) -> ()"
 )
 _LIB.define(
+    "extend(Tensor q, Tensor(a!) o, Tensor(b!)? lse, Tensor k_pool, Tensor v_pool, Tensor qo_indptr, "
+    "Tensor kv_indptr, Tensor? kv_indices, Tensor? req_to_token, Tensor? req_pool_indices, "
+    "Tensor? prefix_lens, Tensor extend_loc, Tensor? custom_mask, Tensor? mask_indptr, int max_extend_len, "
+    "bool causal, int sliding_window, bool skip_prefix_custom_mask, float sm_scale, float logit_cap) -> ()"
+)
+_LIB.define(
+    "extend_plan(Tensor? extend_seq_lens, Tensor prefix_lens, Tensor(a!) qo_indptr, Tensor(b!) kv_indptr, "
+    "Tensor(c!)? mask_indptr, int uniform_extend_len, int sliding_window) -> ()"
+)
+_LIB.define(
     "merge_states(Tensor o_a, Tensor lse_a, Tensor o_b, Tensor lse_b, Tensor(a!) o_out, "
     "Tensor(b!)? lse_out) -> ()"
 )
@@ -295,6 +403,8 @@ _LIB.impl("rope_kv_store", _rope_kv_store, "CUDA")
 _LIB.impl("plan", _plan, "CUDA")
 _LIB.impl("plan_csr", _plan_csr, "CUDA")
 _LIB.impl("decode", _decode, "CUDA")
+_LIB.impl("extend", _extend, "CUDA")
+_LIB.impl("extend_plan", _extend_plan, "CUDA")
 _LIB.impl("merge_states", _merge_states, "CUDA")
 
 

@@ -235,6 +235,19 @@ __device__ __forceinline__ void cp_async16(uint32_t dst, const void* src) {
   asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(dst), "l"(src) : "memory");
 }
 
+// Same, with zero fill: when !valid nothing is read and the 16 destination bytes become zero.
+__device__ __forceinline__ void cp_async16_zfill(uint32_t dst, const void* src, bool valid) {
+  const uint32_t n = valid ? 16u : 0u;
+  asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;" ::"r"(dst), "l"(src), "r"(n) : "memory");
+}
+
+__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
+
+template <int N>
+__device__ __forceinline__ void cp_async_wait() {
+  asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory");
+}
+
 // Arrive on `bar` once all cp.async issued so far by this thread have landed.  .noinc: the
 // arrival is one of the barrier's expected count (init count = arriving threads).
 __device__ __forceinline__ void cp_async_mbar_arrive_noinc(uint32_t bar) {
@@ -298,6 +311,38 @@ __device__ __forceinline__ float fast_exp2(float x) {
   float y;
   asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
   return y;
+}
+constexpr int kPlanThreads = 1024;
+
+__device__ __forceinline__ int64_t load_idx(const void* p, int i, int idx64) {
+  return idx64 ? reinterpret_cast<const int64_t*>(p)[i]
+               : static_cast<int64_t>(reinterpret_cast<const int32_t*>(p)[i]);
+}
+
+// Block-wide inclusive scan of one value per thread (1024 threads).
+template <typename T>
+__device__ __forceinline__ T block_scan_incl(T v, T* warp_sums) {
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+#pragma unroll
+  for (int o = 1; o < 32; o <<= 1) {
+    T t = __shfl_up_sync(0xffffffffu, v, o);
+    if (lane >= o) v += t;
+  }
+  if (lane == 31) warp_sums[warp] = v;
+  __syncthreads();
+  if (warp == 0) {
+    T w = warp_sums[lane];
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+      T t = __shfl_up_sync(0xffffffffu, w, o);
+      if (lane >= o) w += t;
+    }
+    warp_sums[lane] = w;
+  }
+  __syncthreads();
+  if (warp > 0) v += warp_sums[warp - 1];
+  __syncthreads();
+  return v;
 }
 #endif  // __CUDACC__
 

@@ -1,0 +1,172 @@
+// C-ABI entry of the extend (prefill with cached prefix) attention path: argument checks and the
+// launch of extend_kernel (extend_kernel.cuh).
+#include "extend_kernel.cuh"
+
+using namespace b200attn;
+
+namespace {
+
+template <typename QT>
+cudaError_t launch_extend(const ExtendParams& p, int d, dim3 grid, cudaStream_t stream) {
+  void (*fn)(const ExtendParams) = nullptr;
+  if (d == 64) fn = extend_kernel<QT, 64>;
+  else if (d == 128) fn = extend_kernel<QT, 128>;
+  if (!fn) return cudaErrorInvalidValue;
+  const int smem = extend_smem_bytes(d);
+  cudaError_t e = cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
+  if (e != cudaSuccess) return e;
+  fn<<<grid, kExtThreads, smem, stream>>>(p);
+  return cudaGetLastError();
+}
+
+struct ExtendPlanParams {
+  const void* extend_seq_lens;
+  const void* prefix_lens;
+  int32_t idx64, batch, uniform, window;
+  int32_t* qo_indptr;
+  int32_t* kv_indptr;
+  int64_t* mask_indptr;
+};
+
+__global__ void __launch_bounds__(kPlanThreads) extend_plan_kernel(const ExtendPlanParams p) {
+  __shared__ int warp_sums[32];
+  __shared__ long long warp_sums64[32];
+  __shared__ int carry_q, carry_kv;
+  __shared__ long long carry_m;
+  const int tid = threadIdx.x;
+  if (tid == 0) {
+    carry_q = carry_kv = 0;
+    carry_m = 0;
+    p.qo_indptr[0] = 0;
+    p.kv_indptr[0] = 0;
+    if (p.mask_indptr) p.mask_indptr[0] = 0;
+  }
+  __syncthreads();
+  for (int base = 0; base < p.batch; base += kPlanThreads) {
+    const int b = base + tid;
+    int le = 0, lp = 0;
+    long long pl = 0;
+    if (b < p.batch) {
+      le = p.uniform > 0 ? p.uniform : static_cast<int>(load_idx(p.extend_seq_lens, b, p.idx64));
+      pl = load_idx(p.prefix_lens, b, p.idx64);
+      if (le < 0) le = 0;
+      if (pl < 0) pl = 0;
+      lp = static_cast<int>(pl);
+      if (p.window > 0 && lp > p.window + 1) lp = p.window + 1;
+    }
+    const int q_incl = block_scan_incl(le, warp_sums);
+    const int kv_incl = block_scan_incl(lp, warp_sums);
+    long long m_incl = 0;
+    if (p.mask_indptr) m_incl = block_scan_incl(static_cast<long long>(le) * (pl + le), warp_sums64);
+    if (b < p.batch) {
+      p.qo_indptr[b + 1] = carry_q + q_incl;
+      p.kv_indptr[b + 1] = carry_kv + kv_incl;
+      if (p.mask_indptr) p.mask_indptr[b + 1] = carry_m + m_incl;
+    }
+    __syncthreads();
+    if (tid == kPlanThreads - 1) {
+      carry_q += q_incl;
+      carry_kv += kv_incl;
+      carry_m += m_incl;
+    }
+    __syncthreads();
+  }
+}
+
+}  // namespace
+
+extern "C" __attribute__((visibility("default"))) int b200attn_extend_plan(const b200attn_extend_plan_args* a,
+                                                                           b200attn_stream_t stream_) {
+  if (!a || a->batch < 0 || !a->qo_indptr || !a->kv_indptr || !a->prefix_lens) return B200ATTN_E_INVALID;
+  if (!a->extend_seq_lens && a->uniform_extend_len <= 0) return B200ATTN_E_INVALID;
+  if (a->index_dtype != B200ATTN_I32 && a->index_dtype != B200ATTN_I64) return B200ATTN_E_INVALID;
+  ExtendPlanParams p;
+  p.extend_seq_lens = a->extend_seq_lens;
+  p.prefix_lens = a->prefix_lens;
+  p.idx64 = a->index_dtype == B200ATTN_I64;
+  p.batch = a->batch;
+  p.uniform = a->uniform_extend_len > 0 ? a->uniform_extend_len : 0;
+  p.window = a->sliding_window > 0 ? a->sliding_window : 0;
+  p.qo_indptr = a->qo_indptr;
+  p.kv_indptr = a->kv_indptr;
+  p.mask_indptr = a->mask_indptr;
+  extend_plan_kernel<<<1, kPlanThreads, 0, static_cast<cudaStream_t>(stream_)>>>(p);
+  if (cudaGetLastError() != cudaSuccess) return B200ATTN_E_CUDA;
+  count_launch();
+  return B200ATTN_OK;
+}
+
+extern "C" __attribute__((visibility("default"))) int b200attn_extend(const b200attn_extend_args* a,
+                                                                      b200attn_stream_t stream_) {
+  if (!a) return B200ATTN_E_INVALID;
+  if (a->batch < 0 || a->total_tokens < 0 || a->max_extend_len < 0) return B200ATTN_E_INVALID;
+  if (a->batch == 0 || a->total_tokens == 0 || a->max_extend_len == 0) return B200ATTN_OK;
+  if (!a->q || !a->o || !a->k_pool || !a->v_pool || !a->qo_indptr || !a->kv_indptr || !a->extend_loc)
+    return B200ATTN_E_INVALID;
+  if (!a->kv_indices && (!a->req_to_token || !a->req_pool_indices || !a->prefix_lens)) return B200ATTN_E_INVALID;
+  if (a->custom_mask && !a->mask_indptr) return B200ATTN_E_INVALID;
+  if ((a->index_dtype != B200ATTN_I32 && a->index_dtype != B200ATTN_I64) ||
+      (a->mask_indptr_dtype != B200ATTN_I32 && a->mask_indptr_dtype != B200ATTN_I64))
+    return B200ATTN_E_INVALID;
+  if (a->q_dtype != B200ATTN_BF16 && a->q_dtype != B200ATTN_F16) return B200ATTN_E_UNSUPPORTED;
+  if (a->kv_dtype != a->q_dtype) return B200ATTN_E_UNSUPPORTED;  // fp8 pools: decode only, for now
+  if (a->v_head_dim != a->head_dim) return B200ATTN_E_UNSUPPORTED;
+  if (a->head_dim != 64 && a->head_dim != 128) return B200ATTN_E_UNSUPPORTED;
+  if (a->num_q_heads <= 0 || a->num_kv_heads <= 0 || a->num_q_heads % a->num_kv_heads != 0)
+    return B200ATTN_E_INVALID;
+  const int group = a->num_q_heads / a->num_kv_heads;
+  if (group > 16) return B200ATTN_E_UNSUPPORTED;
+  if (a->num_kv_heads > 65535 || a->batch > 65535) return B200ATTN_E_UNSUPPORTED;
+  if (!(a->sm_scale > 0.f) || a->logit_cap < 0.f) return B200ATTN_E_INVALID;
+  if ((reinterpret_cast<uintptr_t>(a->k_pool) | reinterpret_cast<uintptr_t>(a->v_pool)) & 15) return B200ATTN_E_ALIGN;
+  if ((a->k_pool_stride_slot * 2) % 16 != 0 || (a->v_pool_stride_slot * 2) % 16 != 0) return B200ATTN_E_ALIGN;
+  if ((reinterpret_cast<uintptr_t>(a->q) & 3) || a->q_stride_token % 2 != 0 || a->q_stride_head % 2 != 0)
+    return B200ATTN_E_ALIGN;
+  if ((reinterpret_cast<uintptr_t>(a->o) & 3) || a->o_stride_token % 2 != 0 || a->o_stride_head % 2 != 0)
+    return B200ATTN_E_ALIGN;
+
+  ExtendParams p;
+  p.q = a->q;
+  p.q_st = a->q_stride_token;
+  p.q_sh = a->q_stride_head;
+  p.o = a->o;
+  p.o_st = a->o_stride_token;
+  p.o_sh = a->o_stride_head;
+  p.lse = a->lse;
+  p.k_pool = static_cast<const uint8_t*>(a->k_pool);
+  p.v_pool = static_cast<const uint8_t*>(a->v_pool);
+  p.k_slot_bytes = a->k_pool_stride_slot * 2;
+  p.v_slot_bytes = a->v_pool_stride_slot * 2;
+  p.qo_indptr = a->qo_indptr;
+  p.kv_indptr = a->kv_indptr;
+  p.kv_indices = a->kv_indices;
+  p.req_to_token = a->req_to_token;
+  p.r2t_stride = a->req_to_token_stride;
+  p.req_pool_indices = a->req_pool_indices;
+  p.prefix_lens = a->prefix_lens;
+  p.extend_loc = a->extend_loc;
+  p.custom_mask = a->custom_mask;
+  p.mask_indptr = a->mask_indptr;
+  p.idx64 = a->index_dtype == B200ATTN_I64;
+  p.mask64 = a->mask_indptr_dtype == B200ATTN_I64;
+  p.hq = a->num_q_heads;
+  p.group = group;
+  p.gp_shift = 0;
+  while ((1 << p.gp_shift) < group) ++p.gp_shift;
+  p.causal = a->causal != 0;
+  p.window = a->sliding_window > 0 ? a->sliding_window : 0;
+  p.skip_prefix_mask = a->skip_prefix_custom_mask != 0;
+  p.sm_scale = a->sm_scale;
+  p.scale_log2 = a->sm_scale * kLog2e;
+  p.logit_cap = a->logit_cap;
+  p.v_scale = 1.f;
+
+  const int bm_tok = kExtRows >> p.gp_shift;
+  dim3 grid((a->max_extend_len + bm_tok - 1) / bm_tok, a->num_kv_heads, a->batch);
+  cudaStream_t stream = static_cast<cudaStream_t>(stream_);
+  const cudaError_t err = a->q_dtype == B200ATTN_F16 ? launch_extend<__half>(p, a->head_dim, grid, stream)
+                                                     : launch_extend<__nv_bfloat16>(p, a->head_dim, grid, stream);
+  if (err != cudaSuccess) return B200ATTN_E_CUDA;
+  count_launch();
+  return B200ATTN_OK;
+}

@@ -32,38 +32,6 @@ struct PlanParams {
   int32_t window;       // sliding window W (0 = none): the last min(S, W + 1) tokens
 };
 
-constexpr int kPlanThreads = 1024;
-
-__device__ __forceinline__ int64_t load_idx(const void* p, int i, int idx64) {
-  return idx64 ? reinterpret_cast<const int64_t*>(p)[i]
-               : static_cast<int64_t>(reinterpret_cast<const int32_t*>(p)[i]);
-}
-
-// Block-wide inclusive scan of one int per thread (1024 threads).
-__device__ __forceinline__ int block_scan_incl(int v, int* warp_sums) {
-  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-#pragma unroll
-  for (int o = 1; o < 32; o <<= 1) {
-    int t = __shfl_up_sync(0xffffffffu, v, o);
-    if (lane >= o) v += t;
-  }
-  if (lane == 31) warp_sums[warp] = v;
-  __syncthreads();
-  if (warp == 0) {
-    int w = warp_sums[lane];
-#pragma unroll
-    for (int o = 1; o < 32; o <<= 1) {
-      int t = __shfl_up_sync(0xffffffffu, w, o);
-      if (lane >= o) w += t;
-    }
-    warp_sums[lane] = w;
-  }
-  __syncthreads();
-  if (warp > 0) v += warp_sums[warp - 1];
-  __syncthreads();
-  return v;
-}
-
 __global__ void __launch_bounds__(kPlanThreads) plan_kernel(PlanParams p) {
   __shared__ int warp_sums[32];
   __shared__ int carry_tok, carry_chunk, n_empty;

@@ -227,3 +227,95 @@ def cos_sin_cache(rotary_dim: int, max_position: int, base: float = 10000.0) -> 
     inv_freq = 1.0 / (base ** (torch.arange(0, rotary_dim, 2, dtype=torch.float) / rotary_dim))
     freqs = torch.einsum("i,j -> ij", torch.arange(max_position, dtype=torch.float), inv_freq)
     return torch.cat((freqs.cos(), freqs.sin()), dim=-1)
+
+
+# --------------------------------------------------------------------------- #
+# extend (prefill with cached prefix) workloads
+# --------------------------------------------------------------------------- #
+@dataclass
+class ExtendWorkload:
+    """An EXTEND batch: request b has ``prefix_lens[b]`` cached tokens and ``extend_lens[b]`` new
+    ones whose q/k/v rows sit back to back in ``qkv`` (forward_batch_info.py:226-236:
+    extend_prefix_lens / extend_seq_lens; seq_lens = prefix + extend)."""
+    cfg: Config
+    prefix_lens_np: np.ndarray
+    extend_lens_np: np.ndarray
+    req_to_token: torch.Tensor       # int32 [max_reqs, max_ctx]
+    req_pool_indices: torch.Tensor   # int64 [B]
+    seq_lens: torch.Tensor           # int64 [B] prefix + extend
+    extend_prefix_lens: torch.Tensor  # int64 [B]
+    extend_seq_lens: torch.Tensor    # int64 [B]
+    out_cache_loc: torch.Tensor      # int64 [tokens]: slot of every new token
+    qkv: torch.Tensor                # [tokens, (Hq + 2 Hkv) * D]
+    q: torch.Tensor
+    k: torch.Tensor
+    v: torch.Tensor
+    k_pool: torch.Tensor
+    v_pool: torch.Tensor
+    pool_size: int
+    sm_scale: float
+
+    @property
+    def tokens(self) -> int:
+        return int(self.extend_lens_np.sum())
+
+    def flops(self, causal: bool = True) -> int:
+        """4 * D * (visible q-k pairs) * Hq: the algorithmic flops of QK^T and PV."""
+        c = self.cfg
+        pl, el = self.prefix_lens_np.astype(np.int64), self.extend_lens_np.astype(np.int64)
+        pairs = pl * el + (el * (el + 1) // 2 if causal else el * el)
+        return int(4 * c.head_dim * c.num_q_heads * pairs.sum())
+
+
+def make_extend_workload(cfg: Config, prefix_lens, extend_lens, device="cpu", max_reqs: Optional[int] = None,
+                         slack_pages: int = 4) -> ExtendWorkload:
+    rng = np.random.default_rng(cfg.seed)
+    P = cfg.page_size
+    pl = np.asarray(prefix_lens, dtype=np.int64)
+    el = np.asarray(extend_lens, dtype=np.int64)
+    B = len(pl)
+    sl = pl + el
+    max_ctx = int(sl.max()) + 4
+    max_reqs = max_reqs or max(B + 3, 8)
+    pages_per_req = (sl + P - 1) // P
+    n_pages = int(pages_per_req.sum()) + slack_pages
+    perm = rng.permutation(n_pages) + 1
+    r2t = np.zeros((max_reqs, max_ctx), dtype=np.int32)
+    rpi = rng.permutation(max_reqs)[:B].astype(np.int64)
+    offs = np.arange(P, dtype=np.int64)
+    cursor = 0
+    locs = []
+    for b in range(B):
+        npg = int(pages_per_req[b])
+        pages = perm[cursor: cursor + npg]
+        cursor += npg
+        slots = (pages[:, None] * P + offs[None, :]).reshape(-1)[: sl[b]]
+        r2t[rpi[b], : sl[b]] = slots
+        locs.append(slots[pl[b]: sl[b]])
+    loc = np.concatenate(locs).astype(np.int64) if locs else np.zeros(0, dtype=np.int64)
+    pool_size = n_pages * P
+    rows = pool_size + P
+
+    dev = torch.device(device)
+    gen = torch.Generator(device=dev)
+    gen.manual_seed(cfg.seed)
+    qdt = _TORCH_DT[cfg.q_dtype]
+    Hq, Hkv, D = cfg.num_q_heads, cfg.num_kv_heads, cfg.head_dim
+    T = int(el.sum())
+    qkv = torch.randn((T, (Hq + 2 * Hkv) * D), generator=gen, device=dev, dtype=torch.float32).to(qdt)
+    q, k, v = qkv.split([Hq * D, Hkv * D, Hkv * D], dim=-1)
+    kvdt = _TORCH_DT[cfg.kv_dtype]
+    k_pool = torch.empty((rows, Hkv, D), dtype=kvdt, device=dev)
+    v_pool = torch.empty((rows, Hkv, D), dtype=kvdt, device=dev)
+    step = max(1, (1 << 26) // (Hkv * D))
+    for t in (k_pool, v_pool):
+        for r0 in range(0, rows, step):
+            r1 = min(rows, r0 + step)
+            t[r0:r1] = torch.randn((r1 - r0, Hkv, D), generator=gen, device=dev, dtype=torch.float32).to(kvdt)
+    return ExtendWorkload(
+        cfg=cfg, prefix_lens_np=pl, extend_lens_np=el,
+        req_to_token=torch.from_numpy(r2t).to(dev), req_pool_indices=torch.from_numpy(rpi).to(dev),
+        seq_lens=torch.from_numpy(sl).to(dev), extend_prefix_lens=torch.from_numpy(pl).to(dev),
+        extend_seq_lens=torch.from_numpy(el).to(dev), out_cache_loc=torch.from_numpy(loc).to(dev),
+        qkv=qkv, q=q, k=k, v=v, k_pool=k_pool, v_pool=v_pool, pool_size=pool_size,
+        sm_scale=float(D) ** -0.5)

@@ -13,6 +13,8 @@ the outputs come from the reference:
   (layers/radix_attention.py:84-110, layers/attention/torch_native_backend.py:226-267)
 * kv_indptr / kv_indices by the Python gather the reference's own test treats as ground
   truth (test/srt/test_create_kvindices.py:43-49)
+* extend attention of ``RadixAttention`` -> ``TorchNativeAttnBackend.forward_extend``
+  (layers/attention/torch_native_backend.py:27-110, 182-224) on EXTEND batches with cached prefixes
 * 2-way state merge by ``merge_state_torch`` (sgl-kernel/tests/test_merge_state_v2.py:101-141),
   extracted from the test file with ``ast`` because the file imports the CUDA-only sgl_kernel.
 """
@@ -225,6 +227,62 @@ def gen_rope():
     print("rope ok")
 
 
+# name -> (Config, prefix_lens, extend_lens, causal)
+EXTEND_CASES = {
+    "g10_extend_gqa4_d128": (synth.Config("g10a", 3, 0, 8, 2, 128, seed=21), (0, 37, 130), (70, 33, 1), True),
+    "g10_extend_gqa8_d64_p16": (synth.Config("g10b", 2, 0, 16, 2, 64, page_size=16, seed=22), (16, 100), (50, 129), True),
+    "g10_extend_mha_d128_f16": (synth.Config("g10c", 2, 0, 4, 4, 128, kv_dtype="f16", q_dtype="f16", seed=23),
+                                (5, 0), (40, 150), True),
+    "g10_extend_gqa4_d128_noncausal": (synth.Config("g10d", 2, 0, 8, 2, 128, seed=24), (20, 0), (45, 64), False),
+}
+
+
+def digest_extend(w) -> str:
+    h = hashlib.sha256()
+    for t in (w.qkv, w.k_pool, w.v_pool, w.req_to_token, w.req_pool_indices, w.seq_lens, w.out_cache_loc):
+        h.update(bits(t).tobytes())
+    return h.hexdigest()
+
+
+def gen_extend_cases(ref):
+    sys.path.insert(0, os.path.join(ref_loader.REFERENCE_ROOT, "python"))
+    from sglang.srt.layers.radix_attention import AttentionType
+    sys.path.pop(0)
+    for name, (cfg, pl, el, causal) in EXTEND_CASES.items():
+        w = synth.make_extend_workload(cfg, pl, el, "cpu")
+        c = w.cfg
+        pool = ref.MHATokenToKVPool(size=w.pool_size, page_size=c.page_size, dtype=w.k_pool.dtype,
+                                    head_num=c.num_kv_heads, head_dim=c.head_dim, layer_num=1,
+                                    device="cpu", enable_memory_saver=False)
+        pool.k_buffer[0].copy_(w.k_pool)
+        pool.v_buffer[0].copy_(w.v_pool)
+        r2t = ref.ReqToTokenPool(size=w.req_to_token.shape[0], max_context_len=w.req_to_token.shape[1],
+                                 device="cpu", enable_memory_saver=False)
+        r2t.req_to_token.copy_(w.req_to_token)
+        backend = ref.TorchNativeAttnBackend(types.SimpleNamespace(device="cpu"))
+        B = len(pl)
+        fb = ref.ForwardBatch(forward_mode=ref.ForwardMode.EXTEND, batch_size=B,
+                              input_ids=torch.zeros(w.tokens, dtype=torch.int64),
+                              req_pool_indices=w.req_pool_indices, seq_lens=w.seq_lens,
+                              out_cache_loc=w.out_cache_loc, seq_lens_sum=int(w.seq_lens.sum()),
+                              req_to_token_pool=r2t, token_to_kv_pool=pool, attn_backend=backend,
+                              extend_prefix_lens=w.extend_prefix_lens, extend_seq_lens=w.extend_seq_lens)
+        layer = ref.RadixAttention(c.num_q_heads, c.head_dim, w.sm_scale, c.num_kv_heads, layer_id=0,
+                                   attn_type=AttentionType.DECODER if causal else AttentionType.ENCODER_ONLY)
+        qkv = w.qkv.clone()
+        q, k, v = qkv.split([c.num_q_heads * c.head_dim, c.num_kv_heads * c.head_dim,
+                             c.num_kv_heads * c.head_dim], dim=-1)
+        out = layer(q, k, v, fb, save_kv_cache=True)
+        loc = w.out_cache_loc
+        np.savez_compressed(os.path.join(HERE, name + ".npz"),
+                            digest=np.frombuffer(digest_extend(w).encode(), dtype=np.uint8),
+                            prefix_lens=np.asarray(pl, dtype=np.int64), extend_lens=np.asarray(el, dtype=np.int64),
+                            causal=np.int64(causal),
+                            out_bits=bits(out.view(w.tokens, c.num_q_heads, c.head_dim)),
+                            k_rows_after=bits(pool.k_buffer[0][loc]), v_rows_after=bits(pool.v_buffer[0][loc]))
+        print(name, "ok", out.shape)
+
+
 if __name__ == "__main__":
     torch.manual_seed(0)
     only = sys.argv[1] if len(sys.argv) > 1 else "all"
@@ -237,3 +295,5 @@ if __name__ == "__main__":
         gen_merge()
     if only in ("all", "rope"):
         gen_rope()
+    if only in ("all", "extend"):
+        gen_extend_cases(ref)

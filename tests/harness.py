@@ -107,3 +107,65 @@ def canon_e4m3_nan(b: np.ndarray) -> np.ndarray:
     its scalar path 0x7FC0, CUDA 0x7FFF), so NaN bytes are compared up to sign."""
     b = np.asarray(b, dtype=np.uint8)
     return np.where((b & 0x7F) == 0x7F, np.uint8(0x7F), b)
+
+
+# --------------------------------------------------------------------------- #
+# extend (prefill with cached prefix) helpers
+# --------------------------------------------------------------------------- #
+def make_extend_runner(w, device, sliding_window_size=None, num_draft_tokens=None):
+    """Mock model_runner around a ``synth.ExtendWorkload`` (see ``make_runner``)."""
+    import b200attn
+
+    c = w.cfg
+    r2t = b200attn.ReqToTokenPool(w.req_to_token.shape[0], w.req_to_token.shape[1], device)
+    r2t.req_to_token.copy_(w.req_to_token)
+    pool = b200attn.MHATokenToKVPool(w.pool_size, c.page_size, _TORCH_KV[c.kv_dtype], c.num_kv_heads,
+                                     c.head_dim, layer_num=1, device=device)
+    assert pool.k_buffer[0].shape == w.k_pool.shape, (pool.k_buffer[0].shape, w.k_pool.shape)
+    pool.k_buffer[0] = w.k_pool
+    pool.v_buffer[0] = w.v_pool
+    mc = types.SimpleNamespace(num_attention_heads=c.num_q_heads, get_num_kv_heads=lambda tp: c.num_kv_heads,
+                               context_len=w.req_to_token.shape[1] - 4, is_encoder_decoder=False)
+    sa = types.SimpleNamespace(speculative_num_draft_tokens=num_draft_tokens)
+    return types.SimpleNamespace(device=str(device), req_to_token_pool=r2t, token_to_kv_pool=pool,
+                                 model_config=mc, sliding_window_size=sliding_window_size,
+                                 attention_tp_size=1, server_args=sa)
+
+
+def run_extend(backend, runner, w, layer, mode=None, spec_info=None, index_dtype=torch.int64,
+               save_kv_cache=True):
+    """init_forward_metadata + layer call for an extend-type batch; returns [tokens, Hq * D]."""
+    import b200attn
+
+    mode = mode or b200attn.ForwardMode.EXTEND
+    seq_lens = w.seq_lens if not mode.is_target_verify() else w.extend_prefix_lens
+    fb = b200attn.ForwardBatch(
+        forward_mode=mode, batch_size=len(w.prefix_lens_np),
+        req_pool_indices=w.req_pool_indices.to(index_dtype), seq_lens=seq_lens.to(index_dtype),
+        out_cache_loc=w.out_cache_loc, seq_lens_sum=int(seq_lens.sum()),
+        req_to_token_pool=runner.req_to_token_pool, token_to_kv_pool=runner.token_to_kv_pool,
+        attn_backend=backend, spec_info=spec_info,
+        extend_prefix_lens=w.extend_prefix_lens.to(index_dtype), extend_seq_lens=w.extend_seq_lens.to(index_dtype),
+        extend_seq_lens_cpu=[int(x) for x in w.extend_lens_np])
+    backend.init_forward_metadata(fb)
+    return layer(w.q, w.k, w.v, fb, save_kv_cache=save_kv_cache)
+
+
+def oracle_extend(w_cpu, causal=True, logit_cap=0.0, custom_mask=None, sliding_window=-1):
+    """kv_store + extend_attention on the CPU oracle; returns (out, lse, k_pool, v_pool)."""
+    from oracle import decode_oracle, extend_oracle
+
+    c = w_cpu.cfg
+    kp, vp = w_cpu.k_pool.clone(), w_cpu.v_pool.clone()
+    T = w_cpu.tokens
+    decode_oracle.kv_store(kp, vp, w_cpu.out_cache_loc, w_cpu.k.reshape(T, c.num_kv_heads, c.head_dim).clone(),
+                           w_cpu.v.reshape(T, c.num_kv_heads, c.head_dim).clone())
+    ps, es = extend_oracle.slots_from_req_to_token(w_cpu.req_to_token, w_cpu.req_pool_indices,
+                                                   w_cpu.prefix_lens_np, w_cpu.extend_lens_np, sliding_window)
+    mask_indptr = None
+    if custom_mask is not None:
+        _, _, mask_indptr = extend_oracle.extend_indptrs(w_cpu.prefix_lens_np, w_cpu.extend_lens_np)
+    out, lse = extend_oracle.extend_attention(
+        w_cpu.q.reshape(T, c.num_q_heads, c.head_dim), kp, vp, ps, es, w_cpu.sm_scale, causal=causal,
+        logit_cap=logit_cap, custom_mask=custom_mask, mask_indptr=mask_indptr, sliding_window=sliding_window)
+    return out, lse, kp, vp

@@ -41,7 +41,7 @@ def test_library_exports_every_declared_symbol():
 def test_abi_version_and_strerror():
     from b200attn import capi
 
-    assert capi.lib().b200attn_abi_version() == capi.ABI_VERSION == 2
+    assert capi.lib().b200attn_abi_version() == capi.ABI_VERSION == 3
     for code in (0, -1, -2, -3, -4, -5, -99):
         assert isinstance(capi.strerror(code), str) and capi.strerror(code)
     assert "unsupported" in capi.strerror(capi.E_UNSUPPORTED)
@@ -52,7 +52,9 @@ def test_ctypes_layout_matches_c_header():
     from b200attn import capi
 
     structs = {"b200attn_kv_store_args": capi.KvStoreArgs, "b200attn_plan_args": capi.PlanArgs,
-               "b200attn_decode_args": capi.DecodeArgs, "b200attn_merge_states_args": capi.MergeStatesArgs}
+               "b200attn_decode_args": capi.DecodeArgs, "b200attn_merge_states_args": capi.MergeStatesArgs,
+               "b200attn_rope_kv_store_args": capi.RopeKvStoreArgs, "b200attn_extend_args": capi.ExtendArgs,
+               "b200attn_extend_plan_args": capi.ExtendPlanArgs}
     lines = ['#include <stdio.h>', '#include <stddef.h>', '#include "b200attn.h"', 'int main(void){']
     for cname, cls in structs.items():
         lines.append(f'printf("{cname} %zu\\n", sizeof({cname}));')
@@ -110,6 +112,13 @@ def test_argument_errors_need_no_gpu():
     assert lib.b200attn_plan(None, None) == capi.E_INVALID
     assert lib.b200attn_decode(None, None) == capi.E_INVALID
     assert lib.b200attn_merge_states(None, None) == capi.E_INVALID
+    assert lib.b200attn_extend(None, None) == capi.E_INVALID
+    assert lib.b200attn_extend_plan(None, None) == capi.E_INVALID
+    e = capi.ExtendArgs()
+    e.batch, e.total_tokens, e.max_extend_len = 2, 16, 8
+    assert lib.b200attn_extend(C.byref(e), None) == capi.E_INVALID            # null pointers
+    e.batch = 0
+    assert lib.b200attn_extend(C.byref(e), None) == capi.OK                   # empty batch is a no-op
     a = capi.KvStoreArgs()
     a.n_tokens, a.num_kv_heads, a.head_dim, a.v_head_dim = 4, 2, 64, 64
     assert lib.b200attn_kv_store(C.byref(a), None) == capi.E_INVALID          # null pointers

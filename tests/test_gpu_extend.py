@@ -1,0 +1,270 @@
+"""GPU parity tests of the native extend (prefill with cached prefix) path, through the C-ABI:
+``B200AttnBackend.forward_extend`` -> ``torch.ops.b200attn.extend`` against the CPU oracle
+(``oracle/extend_oracle.py``) and the goldens produced by the reference's own
+``TorchNativeAttnBackend.forward_extend``.
+
+Bars: KV store bit-exact on the raw pool bytes; qo_indptr / kv_indptr / mask_indptr bit-exact;
+output within max-abs 2e-2 / rel 1e-2 of the float64 oracle; LSE within 1e-3.
+"""
+from __future__ import annotations
+
+import os
+import types
+
+import numpy as np
+import pytest
+import torch
+
+import synth
+from tests.golden.make_golden import EXTEND_CASES
+from tests.harness import (GOLDEN_DIR, assert_close_out, make_extend_runner, oracle_extend, run_extend)
+
+pytestmark = pytest.mark.gpu
+
+DEV = "cuda:0"
+
+
+def _bits(t: torch.Tensor) -> np.ndarray:
+    return t.detach().cpu().contiguous().view(torch.int16).numpy().view(np.uint16)
+
+
+def _pair(cfg, pl, el):
+    w_cpu = synth.make_extend_workload(cfg, pl, el, "cpu")
+    w = synth.make_extend_workload(cfg, pl, el, DEV)
+    w.qkv.copy_(w_cpu.qkv)   # CPU and CUDA generators differ: both sides get the CPU data
+    w.k_pool.copy_(w_cpu.k_pool)
+    w.v_pool.copy_(w_cpu.v_pool)
+    return w_cpu, w
+
+
+def _layer(w, causal=True, logit_cap=0.0, window=-1):
+    import b200attn
+
+    c = w.cfg
+    at = b200attn.AttentionType.DECODER if causal else b200attn.AttentionType.ENCODER_ONLY
+    return b200attn.AttnLayer(c.num_q_heads, c.head_dim, w.sm_scale, c.num_kv_heads, layer_id=0,
+                              logit_cap=logit_cap, sliding_window_size=window, attn_type=at)
+
+
+def _run(cfg, pl, el, causal=True, logit_cap=0.0, window=-1, index_dtype=torch.int64, check_pool=True):
+    import b200attn
+
+    w_cpu, w = _pair(cfg, pl, el)
+    runner = make_extend_runner(w, DEV, sliding_window_size=window if window > 0 else None)
+    backend = b200attn.B200AttnBackend(runner, return_lse=True)
+    out = run_extend(backend, runner, w, _layer(w, causal, logit_cap, window), index_dtype=index_dtype)
+    torch.cuda.synchronize()
+    ref, ref_lse, kp, vp = oracle_extend(w_cpu, causal=causal, logit_cap=logit_cap, sliding_window=window)
+    c = cfg
+    if check_pool:
+        pool = runner.token_to_kv_pool
+        assert torch.equal(pool.k_buffer[0].cpu(), kp) and torch.equal(pool.v_buffer[0].cpu(), vp), \
+            "kv_store: pool bytes differ from the oracle"
+    got = out.float().cpu().numpy().reshape(ref.shape)
+    err = assert_close_out(got, ref)
+    lse = backend.lse_extend(w.tokens).view(w.tokens, c.num_q_heads).cpu().numpy()
+    fin = np.isfinite(ref_lse)
+    assert np.array_equal(np.isfinite(lse), fin)
+    assert np.abs(lse[fin] - ref_lse[fin]).max() <= 1e-3, np.abs(lse[fin] - ref_lse[fin]).max()
+    md = backend.extend_metadata
+    from oracle import extend_oracle
+    qo, kv, _ = extend_oracle.extend_indptrs(pl, el)
+    assert np.array_equal(md.qo_indptr.cpu().numpy(), qo) and np.array_equal(md.kv_indptr.cpu().numpy(), kv)
+    if window > 0:
+        _, wkv, _ = extend_oracle.extend_indptrs(pl, el, window)
+        assert np.array_equal(md.window_kv_indptr.cpu().numpy(), wkv)
+    return err, got, w_cpu
+
+
+@pytest.mark.parametrize("name", sorted(EXTEND_CASES))
+def test_golden_extend(name):
+    """The reference's own torch_native forward_extend output (bf16/f16) on identical inputs."""
+    cfg, pl, el, causal = EXTEND_CASES[name]
+    g = np.load(os.path.join(GOLDEN_DIR, name + ".npz"))
+    _, got, w_cpu = _run(cfg, pl, el, causal=causal)
+    dt = w_cpu.k_pool.dtype
+    ref = torch.from_numpy(g["out_bits"].view(np.int16).copy()).view(dt).float().numpy()
+    assert_close_out(got, ref, what=f"{name}: CUDA vs reference torch_native")
+
+
+# (name, Hq, Hkv, D, page, prefix_lens, extend_lens)
+SHAPES = [
+    ("mha_d128", 4, 4, 128, 1, (0, 33, 200), (130, 64, 1)),
+    ("gqa2_d64", 8, 4, 64, 1, (7, 0), (129, 65)),
+    ("gqa3_d128", 6, 2, 128, 1, (64, 5), (31, 70)),
+    ("gqa4_d128_long_extend", 8, 2, 128, 16, (100, 0), (700, 257)),
+    ("gqa4_d128_long_prefix", 32, 8, 128, 1, (1500, 64), (3, 40)),
+    ("gqa5_d128", 10, 2, 128, 1, (17,), (90,)),
+    ("gqa7_d128", 28, 4, 128, 1, (40, 0), (50, 20)),
+    ("gqa8_d128", 64, 8, 128, 1, (300,), (140,)),
+    ("gqa16_d64", 32, 2, 64, 4, (10, 90), (33, 8)),
+    ("tile_edges", 8, 2, 128, 1, (0, 0, 0, 0, 63, 64, 65), (32, 33, 64, 65, 1, 1, 1)),
+    ("many_short", 8, 2, 64, 1, tuple(range(0, 24)), tuple(1 + (i * 7) % 13 for i in range(24))),
+]
+
+
+@pytest.mark.parametrize("shape", SHAPES, ids=[s[0] for s in SHAPES])
+def test_extend_shapes(shape):
+    name, hq, hkv, d, page, pl, el = shape
+    _run(synth.Config(name, len(pl), 0, hq, hkv, d, page_size=page, seed=101), pl, el)
+
+
+def test_extend_f16_and_int32_indices():
+    cfg = synth.Config("f16", 2, 0, 8, 2, 128, kv_dtype="f16", q_dtype="f16", seed=102)
+    _run(cfg, (20, 0), (70, 33), index_dtype=torch.int32)
+
+
+def test_extend_noncausal():
+    _run(synth.Config("enc", 2, 0, 8, 2, 128, seed=103), (0, 12), (100, 77), causal=False)
+
+
+@pytest.mark.parametrize("cap", [30.0, 5.0])
+def test_extend_logit_cap(cap):
+    _run(synth.Config("cap", 2, 0, 8, 2, 64, seed=104), (30, 0), (70, 40), logit_cap=cap)
+
+
+@pytest.mark.parametrize("window", [3, 16, 200])
+def test_extend_sliding_window(window):
+    """The reference kernel's window rule (extend_attention.py:179-184) over the windowed prefix list
+    (triton_backend.py:927-956)."""
+    _run(synth.Config("win", 3, 0, 8, 2, 128, seed=105), (150, 10, 0), (40, 70, 20), window=window)
+
+
+def _verify_case(n_draft, pl, seed, mask_fn):
+    """TARGET_VERIFY: uniform extend = n_draft tokens per request, visibility from
+    spec_info.custom_mask (triton_backend.py:227-263)."""
+    import b200attn
+    from oracle import extend_oracle
+
+    cfg = synth.Config("verify", len(pl), 0, 32, 8, 128, seed=seed)
+    el = (n_draft,) * len(pl)
+    w_cpu, w = _pair(cfg, pl, el)
+    _, _, mi = extend_oracle.extend_indptrs(pl, el)
+    rng = np.random.default_rng(seed)
+    mask = np.zeros(int(mi[-1]), dtype=np.uint8)
+    for b in range(len(pl)):
+        mask[mi[b]:mi[b + 1]] = mask_fn(rng, n_draft, pl[b]).reshape(-1)
+    runner = make_extend_runner(w, DEV, num_draft_tokens=n_draft)
+    backend = b200attn.B200AttnBackend(runner, return_lse=True)
+    spec = types.SimpleNamespace(custom_mask=torch.from_numpy(mask).to(DEV).view(torch.bool), draft_token_num=n_draft)
+    out = run_extend(backend, runner, w, _layer(w), mode=b200attn.ForwardMode.TARGET_VERIFY, spec_info=spec)
+    torch.cuda.synchronize()
+    assert np.array_equal(backend.extend_metadata.mask_indptr.cpu().numpy(), mi)
+    ref, ref_lse, _, _ = oracle_extend(w_cpu, custom_mask=mask)
+    got = out.float().cpu().numpy().reshape(ref.shape)
+    assert_close_out(got, ref)
+    lse = backend.lse_extend(w.tokens).view(w.tokens, cfg.num_q_heads).cpu().numpy()
+    fin = np.isfinite(ref_lse)
+    assert np.array_equal(np.isfinite(lse), fin) and np.abs(lse[fin] - ref_lse[fin]).max() <= 1e-3
+    return got, w_cpu
+
+
+def test_target_verify_tree_mask():
+    def tree(rng, n, p):
+        m = np.ones((n, p + n), dtype=np.uint8)
+        t = np.tril(rng.integers(0, 2, size=(n, n), dtype=np.uint8))
+        np.fill_diagonal(t, 1)     # every draft token sees itself
+        m[:, p:] = t
+        return m
+    _verify_case(8, (100, 37, 1, 260), 201, tree)
+
+
+def test_target_verify_causal_mask_equals_causal():
+    """test_triton_attention_kernels.py:189-224: a custom mask equal to the causal mask gives the
+    causal result."""
+    def causal(rng, n, p):
+        m = np.ones((n, p + n), dtype=np.uint8)
+        m[:, p:] = np.tril(np.ones((n, n), dtype=np.uint8))
+        return m
+    pl = (50, 3)
+    got, w_cpu = _verify_case(16, pl, 202, causal)
+    ref, _, _, _ = oracle_extend(w_cpu, causal=True)
+    assert_close_out(got, ref)
+
+
+def test_target_verify_fully_masked_rows():
+    """A row whose mask hides every draft token still sees its prefix; with an empty prefix it sees
+    nothing: o = 0, lse = -inf."""
+    def none(rng, n, p):
+        m = np.ones((n, p + n), dtype=np.uint8)
+        m[:, p:] = 0
+        m[0, p] = 1
+        return m
+    _verify_case(4, (0, 20), 203, none)
+
+
+def test_draft_extend_csr_indices():
+    """DRAFT_EXTEND: kv_indices / kv_indptr / qo_indptr come from spec_info.generate_attn_arg_prefill
+    (triton_backend.py:265-279): the kernel's CSR mode."""
+    import b200attn
+    from oracle import decode_oracle
+
+    cfg = synth.Config("draft", 3, 0, 8, 2, 128, seed=301)
+    pl, el = (40, 7, 130), (3, 1, 4)
+    w_cpu, w = _pair(cfg, pl, el)
+
+    def gen(req_pool_indices, paged_kernel_lens, paged_kernel_lens_sum, req_to_token):
+        indptr, indices = decode_oracle.kv_indices(w_cpu.req_to_token, w_cpu.req_pool_indices, w_cpu.extend_prefix_lens)
+        qo = np.zeros(len(pl) + 1, dtype=np.int32)
+        qo[1:] = np.cumsum(el)
+        return (torch.from_numpy(indices).to(DEV), torch.from_numpy(indptr).to(DEV), torch.from_numpy(qo).to(DEV), None)
+
+    runner = make_extend_runner(w, DEV)
+    backend = b200attn.B200AttnBackend(runner, return_lse=True)
+    spec = types.SimpleNamespace(generate_attn_arg_prefill=gen)
+    out = run_extend(backend, runner, w, _layer(w), mode=b200attn.ForwardMode.DRAFT_EXTEND, spec_info=spec)
+    torch.cuda.synchronize()
+    ref, _, _, _ = oracle_extend(w_cpu)
+    assert_close_out(out.float().cpu().numpy().reshape(ref.shape), ref)
+
+
+def test_extend_errors_are_loud():
+    import b200attn
+
+    cfg = synth.Config("err", 1, 0, 8, 2, 128, seed=401)
+    w = synth.make_extend_workload(cfg, (4,), (8,), DEV)
+    runner = make_extend_runner(w, DEV)
+    backend = b200attn.B200AttnBackend(runner)
+    with pytest.raises(RuntimeError):   # no metadata
+        backend.forward_extend(w.q, w.k.view(-1, 2, 128), w.v.view(-1, 2, 128), _layer(w),
+                               types.SimpleNamespace(token_to_kv_pool=runner.token_to_kv_pool,
+                                                     out_cache_loc=w.out_cache_loc))
+    q3 = w.q.view(-1, 8, 128)
+    o3 = torch.empty_like(q3)
+    qo = torch.tensor([0, 8], dtype=torch.int32, device=DEV)
+    with pytest.raises(ValueError):     # neither kv_indices nor req_to_token
+        torch.ops.b200attn.extend(q3, o3, None, w.k_pool, w.v_pool, qo, qo, None, None, None, None,
+                                  w.out_cache_loc, None, None, 8, True, -1, True, 0.1, 0.0)
+    with pytest.raises(RuntimeError):   # CPU tensors: CUDA-only op
+        torch.ops.b200attn.extend(q3.cpu(), o3.cpu(), None, w.k_pool.cpu(), w.v_pool.cpu(), qo.cpu(), qo.cpu(),
+                                  qo.cpu(), None, None, None, w.out_cache_loc.cpu(), None, None, 8, True, -1,
+                                  True, 0.1, 0.0)
+
+
+def test_extend_full_size_split_invariance():
+    """Llama-3.1-8B-shaped prefill of 4096 tokens at full size, through a size-independent property:
+    prefilling [0, 4096) in one pass equals prefilling [0, 2048) and then extending [2048, 4096) over
+    the cached prefix (same pool rows), row for row on the second half; and the first token's output
+    is its own V row."""
+    import b200attn
+
+    cfg = synth.Config("full", 1, 0, 32, 8, 128, seed=501)
+    w = synth.make_extend_workload(cfg, (0,), (4096,), DEV)
+    runner = make_extend_runner(w, DEV)
+    backend = b200attn.B200AttnBackend(runner)
+    layer = _layer(w)
+    whole = run_extend(backend, runner, w, layer).view(4096, 32, 128).float()
+    v0 = w.v.view(4096, 8, 128)[0].float().repeat_interleave(4, dim=0)
+    assert torch.allclose(whole[0], v0, atol=1e-2)
+    # second pass: same request, first 2048 tokens are now the cached prefix
+    w2 = types.SimpleNamespace(**{**w.__dict__})
+    w2.prefix_lens_np = np.array([2048])
+    w2.extend_lens_np = np.array([2048])
+    w2.extend_prefix_lens = torch.tensor([2048], device=DEV)
+    w2.extend_seq_lens = torch.tensor([2048], device=DEV)
+    w2.out_cache_loc = w.out_cache_loc[2048:].contiguous()
+    w2.q, w2.k, w2.v = w.q[2048:], w.k[2048:], w.v[2048:]
+    w2.tokens = 2048
+    half = run_extend(backend, runner, w2, layer, save_kv_cache=False).view(2048, 32, 128).float()
+    torch.cuda.synchronize()
+    assert (half - whole[2048:]).abs().max().item() <= 2e-2

@@ -13,8 +13,8 @@ import torch
 import synth
 from oracle import decode_oracle as oracle
 from oracle import ref_loader
-from tests.golden.make_golden import CASES, KAT, digest
-from tests.harness import GOLDEN_DIR, assert_close_out, canon_e4m3_nan, oracle_step
+from tests.golden.make_golden import CASES, EXTEND_CASES, KAT, digest, digest_extend
+from tests.harness import GOLDEN_DIR, assert_close_out, canon_e4m3_nan, oracle_extend, oracle_step
 
 
 def _from_bits(a: np.ndarray, dt: torch.dtype) -> torch.Tensor:
@@ -196,3 +196,54 @@ def test_rope_oracle_vs_reference_golden(name):
         mag = np.abs(x.float().numpy()).reshape(n, heads, hs).max(axis=-1, keepdims=True)
         bound = np.broadcast_to(3 * 2.0 ** -8 * np.maximum(mag, 1.0), (n, heads, hs)).reshape(n, heads * hs)
         assert np.all(np.abs(got - ref16) <= bound)
+
+
+# --------------------------------------------------------------------------- #
+# extend (prefill with cached prefix)
+# --------------------------------------------------------------------------- #
+@pytest.mark.parametrize("name", sorted(EXTEND_CASES))
+def test_extend_oracle_vs_reference_golden(name):
+    """``extend_oracle.extend_attention`` against the reference's own
+    ``TorchNativeAttnBackend.forward_extend`` output (bf16/f16-rounded SDPA), and the multi-token KV
+    store against the reference's pool rows, bit for bit."""
+    cfg, pl, el, causal = EXTEND_CASES[name]
+    g = np.load(os.path.join(GOLDEN_DIR, name + ".npz"))
+    w = synth.make_extend_workload(cfg, pl, el, "cpu")
+    assert digest_extend(w) == g["digest"].tobytes().decode(), "synthetic inputs drifted: regenerate goldens"
+    out, lse, kp, vp = oracle_extend(w, causal=causal)
+    dt = w.k_pool.dtype
+    assert torch.equal(kp[w.out_cache_loc], _from_bits(g["k_rows_after"], dt))
+    assert torch.equal(vp[w.out_cache_loc], _from_bits(g["v_rows_after"], dt))
+    ref = _from_bits(g["out_bits"], dt).float().numpy()
+    assert_close_out(out, ref, atol=4e-3, rtol=8e-3, what=f"{name}: extend oracle vs reference")
+    assert np.isfinite(lse).all()
+
+
+def test_extend_oracle_mask_properties():
+    """Properties the reference's own Triton test asserts (test_triton_attention_kernels.py:189-224):
+    a custom mask equal to the causal mask reproduces the causal result; plus: a window wider than
+    every prefix changes nothing, and logit_cap -> large approaches the uncapped result."""
+    from oracle import extend_oracle
+
+    cfg = synth.Config("m", 3, 0, 8, 2, 64, seed=31)
+    pl, el = (9, 0, 40), (17, 30, 5)
+    w = synth.make_extend_workload(cfg, pl, el, "cpu")
+    base, base_lse, _, _ = oracle_extend(w, causal=True)
+    _, _, mi = extend_oracle.extend_indptrs(w.prefix_lens_np, w.extend_lens_np)
+    mask = np.zeros(int(mi[-1]), dtype=np.uint8)
+    for b in range(3):
+        m = np.ones((el[b], pl[b] + el[b]), dtype=np.uint8)
+        m[:, pl[b]:] = np.tril(np.ones((el[b], el[b]), dtype=np.uint8))
+        mask[mi[b]:mi[b + 1]] = m.reshape(-1)
+    got, got_lse, _, _ = oracle_extend(w, causal=True, custom_mask=mask)
+    assert np.array_equal(got, base) and np.array_equal(got_lse, base_lse)
+    wide, _, _, _ = oracle_extend(w, causal=True, sliding_window=1000)
+    assert np.array_equal(wide, base)
+    capped, _, _, _ = oracle_extend(w, causal=True, logit_cap=1e4)
+    assert np.abs(capped - base).max() < 1e-5
+    # window semantics of the reference kernel: query i sees window-list entry j iff i <= j + W
+    W = 4
+    win, _, _, _ = oracle_extend(w, causal=True, sliding_window=W)
+    assert np.abs(win - base).max() > 1e-3   # request 2 (prefix 40 > W + 1) changes
+    qo, kv, _ = extend_oracle.extend_indptrs(w.prefix_lens_np, w.extend_lens_np, W)
+    assert list(np.diff(kv)) == [min(p, W + 1) for p in pl] and list(np.diff(qo)) == list(el)
