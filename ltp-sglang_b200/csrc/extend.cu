@@ -1,6 +1,8 @@
 // C-ABI entry of the extend (prefill with cached prefix) attention path: argument checks and the
 // launch of extend_kernel (extend_kernel.cuh).
-#include "extend_kernel.cuh"
+#include <cstdlib>
+
+#include "extend_tc_kernel.cuh"
 
 using namespace b200attn;
 
@@ -17,6 +19,24 @@ cudaError_t launch_extend(const ExtendParams& p, int d, dim3 grid, cudaStream_t 
   if (e != cudaSuccess) return e;
   fn<<<grid, kExtThreads, smem, stream>>>(p);
   return cudaGetLastError();
+}
+
+template <typename QT>
+cudaError_t launch_extend_tc(const ExtendParams& p, dim3 grid, cudaStream_t stream) {
+  void (*fn)(const ExtendParams) = extend_tc_kernel<QT>;
+  cudaError_t e = cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, kTcSmemBytes);
+  if (e != cudaSuccess) return e;
+  fn<<<grid, kTcThreads, kTcSmemBytes, stream>>>(p);
+  return cudaGetLastError();
+}
+
+// B200ATTN_EXTEND_IMPL=mma forces the mma.sync kernel (a test / tuning aid; read once).
+bool extend_force_mma() {
+  static const bool v = [] {
+    const char* e = getenv("B200ATTN_EXTEND_IMPL");
+    return e && e[0] == 'm';
+  }();
+  return v;
 }
 
 struct ExtendPlanParams {
@@ -161,11 +181,25 @@ extern "C" __attribute__((visibility("default"))) int b200attn_extend(const b200
   p.logit_cap = a->logit_cap;
   p.v_scale = 1.f;
 
-  const int bm_tok = kExtRows >> p.gp_shift;
-  dim3 grid((a->max_extend_len + bm_tok - 1) / bm_tok, a->num_kv_heads, a->batch);
   cudaStream_t stream = static_cast<cudaStream_t>(stream_);
-  const cudaError_t err = a->q_dtype == B200ATTN_F16 ? launch_extend<__half>(p, a->head_dim, grid, stream)
-                                                     : launch_extend<__nv_bfloat16>(p, a->head_dim, grid, stream);
+  // head_dim 128 with 16-byte aligned q / o rows runs on tcgen05 (extend_tc_kernel.cuh); head_dim 64 and
+  // odd layouts on the mma.sync kernel.
+  const bool tc_ok = a->head_dim == kTcD && !extend_force_mma() &&
+                     !((reinterpret_cast<uintptr_t>(a->q) | reinterpret_cast<uintptr_t>(a->o)) & 15) &&
+                     a->q_stride_token % 8 == 0 && a->q_stride_head % 8 == 0 && a->o_stride_token % 8 == 0 &&
+                     a->o_stride_head % 8 == 0;
+  cudaError_t err;
+  if (tc_ok) {
+    const int tok = (2 * kTcBM) >> p.gp_shift;
+    dim3 grid((a->max_extend_len + tok - 1) / tok, a->num_kv_heads, a->batch);
+    err = a->q_dtype == B200ATTN_F16 ? launch_extend_tc<__half>(p, grid, stream)
+                                     : launch_extend_tc<__nv_bfloat16>(p, grid, stream);
+  } else {
+    const int bm_tok = kExtRows >> p.gp_shift;
+    dim3 grid((a->max_extend_len + bm_tok - 1) / bm_tok, a->num_kv_heads, a->batch);
+    err = a->q_dtype == B200ATTN_F16 ? launch_extend<__half>(p, a->head_dim, grid, stream)
+                                     : launch_extend<__nv_bfloat16>(p, a->head_dim, grid, stream);
+  }
   if (err != cudaSuccess) return B200ATTN_E_CUDA;
   count_launch();
   return B200ATTN_OK;

@@ -1,0 +1,491 @@
+// K5 (tensor-core generation 5): extend / prefill attention on tcgen05 + TMEM (sm_100a).
+//
+// Same contract as extend_kernel.cuh (the reference's Triton extend kernel,
+// python/sglang/srt/layers/attention/triton_ops/extend_attention.py:41-303), head_dim 128.
+//
+// One CTA = (request, kv head, q tile of 256 MMA rows) = two 128-row sub-tiles that share every
+// K/V tile.  A row is a (token, q head of the kv head's group) pair, so GQA packs G heads into M.
+//   warps 0-3 / 4-7   softmax warpgroup of sub-tile 0 / 1: thread r owns row r = TMEM lane r.  Reads
+//                     its S row from TMEM (tcgen05.ld 32x32b), masks, keeps the running max / sum
+//                     (no shuffles: one thread, one row), writes P as packed 16-bit pairs back into
+//                     the columns S occupied (tcgen05.st), rescales its O row in TMEM only when the
+//                     max grew by more than 2^8 (lazy rescale), and writes the final O row.
+//   warps 8-11        loaders: gather K / V rows of the paged pool (prefix through the index list,
+//                     new tokens through out_cache_loc) with 16-byte cp.async straight into the
+//                     128-byte-swizzled K-major layout tcgen05 reads (row r, chunk c -> c ^ (r & 7)),
+//                     ring of kSlots 32 KB slots, full / empty mbarriers; also the Q tile.
+//   warp 12           one elected thread issues every MMA:  S_i = Q_i . K^T   (SS, both K-major)
+//                                                           O_i += P_i . V     (TS: P from TMEM,
+//                                                           V MN-major = the same row layout)
+//                     in the order PV0(n) S0(n+1) PV1(n) S1(n+1), so the softmax of one sub-tile
+//                     overlaps the MMAs of the other; tcgen05.commit signals the mbarriers.
+// TMEM (512 columns): S0 [0,128) S1 [128,256) O0 [256,384) O1 [384,512); P_i aliases S_i [0,64).
+// The descriptor encodings are pinned by tools/probe_umma.cu.
+#pragma once
+
+#include <math_constants.h>
+
+#include <type_traits>
+
+#include "extend_kernel.cuh"
+
+namespace b200attn {
+
+constexpr int kTcThreads = 512;
+constexpr int kTcBM = 128;            // rows per sub-tile (TMEM lanes)
+constexpr int kTcBN = 128;            // kv tokens per tile
+constexpr int kTcD = 128;
+constexpr int kTcSlots = 5;           // K / V ring slots
+constexpr int kTcSlab = kTcBN * 128;  // bytes of one 64-element-wide slab of 128 rows
+constexpr int kTcSlotBytes = 2 * kTcSlab;
+constexpr int kTcQBytes = 2 * kTcSlotBytes;  // two sub-tiles
+constexpr int kTcLag = 2;             // cp.async groups a loader thread keeps in flight
+constexpr int kTcBarBytes = 1024;
+constexpr int kTcSmemBytes = kTcQBytes + kTcSlots * kTcSlotBytes + kTcBarBytes + 1024;  // + alignment slack
+constexpr float kTcRescaleLog2 = 8.f;  // lazy rescale threshold (log2 units)
+
+// ---- tcgen05 wrappers ----
+__device__ __forceinline__ uint64_t umma_desc_sw128(uint32_t addr, uint32_t lbo_bytes, uint32_t sbo_bytes) {
+  uint64_t d = static_cast<uint64_t>((addr & 0x3FFFF) >> 4);
+  d |= static_cast<uint64_t>((lbo_bytes >> 4) & 0x3FFF) << 16;
+  d |= static_cast<uint64_t>((sbo_bytes >> 4) & 0x3FFF) << 32;
+  d |= 1ull << 46;  // descriptor version (sm_100)
+  d |= 2ull << 61;  // SWIZZLE_128B
+  return d;
+}
+// kind::f16 instruction descriptor: fp32 accumulate, A/B format fmt (0 = f16, 1 = bf16)
+__host__ __device__ constexpr uint32_t umma_idesc(int m, int n, int fmt, int b_mn_major) {
+  return (1u << 4) | (static_cast<uint32_t>(fmt) << 7) | (static_cast<uint32_t>(fmt) << 10) |
+         (static_cast<uint32_t>(b_mn_major) << 16) | (static_cast<uint32_t>(n >> 3) << 17) |
+         (static_cast<uint32_t>(m >> 4) << 24);
+}
+__device__ __forceinline__ void umma_ss(uint32_t d, uint64_t a, uint64_t b, uint32_t idesc, uint32_t acc) {
+  asm volatile(
+      "{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\t"
+      "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t}" ::"r"(d),
+      "l"(a), "l"(b), "r"(idesc), "r"(acc)
+      : "memory");
+}
+__device__ __forceinline__ void umma_ts(uint32_t d, uint32_t a_tmem, uint64_t b, uint32_t idesc, uint32_t acc) {
+  asm volatile(
+      "{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\t"
+      "tcgen05.mma.cta_group::1.kind::f16 [%0], [%1], %2, %3, p;\n\t}" ::"r"(d),
+      "r"(a_tmem), "l"(b), "r"(idesc), "r"(acc)
+      : "memory");
+}
+__device__ __forceinline__ void umma_commit(uint32_t bar) {
+  asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(bar) : "memory");
+}
+__device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
+__device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
+__device__ __forceinline__ void tmem_wait_ld() { asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory"); }
+__device__ __forceinline__ void tmem_wait_st() { asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory"); }
+
+#define B200_R16(r, o) r[o + 0], r[o + 1], r[o + 2], r[o + 3], r[o + 4], r[o + 5], r[o + 6], r[o + 7], r[o + 8], \
+    r[o + 9], r[o + 10], r[o + 11], r[o + 12], r[o + 13], r[o + 14], r[o + 15]
+
+// 32 lanes x 32 consecutive columns -> 32 registers per thread (thread = lane); no wait.
+template <int OFF, int LEN>
+__device__ __forceinline__ void tmem_ld32(uint32_t taddr, float (&r)[LEN]) {
+  uint32_t* u = reinterpret_cast<uint32_t*>(&r[OFF]);
+  asm volatile(
+      "tcgen05.ld.sync.aligned.32x32b.x32.b32 "
+      "{%0,%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15,%16,%17,%18,%19,%20,%21,%22,%23,%24,%25,%26,%27,%28,"
+      "%29,%30,%31}, [%32];"
+      : "=r"(u[0]), "=r"(u[1]), "=r"(u[2]), "=r"(u[3]), "=r"(u[4]), "=r"(u[5]), "=r"(u[6]), "=r"(u[7]), "=r"(u[8]),
+        "=r"(u[9]), "=r"(u[10]), "=r"(u[11]), "=r"(u[12]), "=r"(u[13]), "=r"(u[14]), "=r"(u[15]), "=r"(u[16]),
+        "=r"(u[17]), "=r"(u[18]), "=r"(u[19]), "=r"(u[20]), "=r"(u[21]), "=r"(u[22]), "=r"(u[23]), "=r"(u[24]),
+        "=r"(u[25]), "=r"(u[26]), "=r"(u[27]), "=r"(u[28]), "=r"(u[29]), "=r"(u[30]), "=r"(u[31])
+      : "r"(taddr));
+}
+template <int OFF, int LEN>
+__device__ __forceinline__ void tmem_st32(uint32_t taddr, const float (&r)[LEN]) {
+  const uint32_t* u = reinterpret_cast<const uint32_t*>(&r[OFF]);
+  asm volatile(
+      "tcgen05.st.sync.aligned.32x32b.x32.b32 [%32], "
+      "{%0,%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15,%16,%17,%18,%19,%20,%21,%22,%23,%24,%25,%26,%27,%28,"
+      "%29,%30,%31};" ::"r"(u[0]),
+      "r"(u[1]), "r"(u[2]), "r"(u[3]), "r"(u[4]), "r"(u[5]), "r"(u[6]), "r"(u[7]), "r"(u[8]), "r"(u[9]), "r"(u[10]),
+      "r"(u[11]), "r"(u[12]), "r"(u[13]), "r"(u[14]), "r"(u[15]), "r"(u[16]), "r"(u[17]), "r"(u[18]), "r"(u[19]),
+      "r"(u[20]), "r"(u[21]), "r"(u[22]), "r"(u[23]), "r"(u[24]), "r"(u[25]), "r"(u[26]), "r"(u[27]), "r"(u[28]),
+      "r"(u[29]), "r"(u[30]), "r"(u[31]), "r"(taddr)
+      : "memory");
+}
+__device__ __forceinline__ void tmem_st16(uint32_t taddr, const uint32_t (&u)[16]) {
+  asm volatile(
+      "tcgen05.st.sync.aligned.32x32b.x16.b32 [%16], {%0,%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15};" ::"r"(
+          u[0]),
+      "r"(u[1]), "r"(u[2]), "r"(u[3]), "r"(u[4]), "r"(u[5]), "r"(u[6]), "r"(u[7]), "r"(u[8]), "r"(u[9]), "r"(u[10]),
+      "r"(u[11]), "r"(u[12]), "r"(u[13]), "r"(u[14]), "r"(u[15]), "r"(taddr)
+      : "memory");
+}
+
+// mbarrier wait with a watchdog: a protocol bug traps instead of hanging the GPU.
+__device__ __forceinline__ void mbar_wait_wd(uint32_t bar, uint32_t parity) {
+  uint32_t spins = 0;
+  while (!mbar_try_wait(bar, parity)) {
+    if (++spins > (1u << 26)) __trap();
+  }
+}
+
+template <int REGS>
+__device__ __forceinline__ void setmaxnreg_inc() {
+  asm volatile("setmaxnreg.inc.sync.aligned.u32 %0;" ::"n"(REGS));
+}
+template <int REGS>
+__device__ __forceinline__ void setmaxnreg_dec() {
+  asm volatile("setmaxnreg.dec.sync.aligned.u32 %0;" ::"n"(REGS));
+}
+
+template <typename QT>
+__global__ void __launch_bounds__(kTcThreads, 1) extend_tc_kernel(const ExtendParams p) {
+  constexpr bool HALF = std::is_same<QT, __half>::value;
+  constexpr uint32_t IDESC_QK = umma_idesc(kTcBM, kTcBN, HALF ? 0 : 1, 0);
+  constexpr uint32_t IDESC_PV = umma_idesc(kTcBM, kTcD, HALF ? 0 : 1, 1);
+
+  extern __shared__ uint8_t smem_raw[];
+  const uint32_t smem0 = (smem_u32(smem_raw) + 1023u) & ~1023u;  // swizzle atoms are 1024-byte aligned
+  const uint32_t q_base = smem0;
+  const uint32_t kv_base = smem0 + kTcQBytes;
+  const uint32_t bars = kv_base + kTcSlots * kTcSlotBytes;
+  const uint32_t bar_kv_full = bars;                      // [kTcSlots]
+  const uint32_t bar_kv_empty = bars + 8 * kTcSlots;      // [kTcSlots]
+  const uint32_t bar_q_full = bars + 16 * kTcSlots;
+  const uint32_t bar_s_full = bar_q_full + 8;             // [2]
+  const uint32_t bar_p_full = bar_s_full + 16;            // [2]
+  const uint32_t bar_o_full = bar_p_full + 16;
+  const uint32_t tmem_slot = bar_o_full + 8;
+  volatile uint32_t* tmem_slot_ptr = reinterpret_cast<volatile uint32_t*>(smem_raw + (tmem_slot - smem_u32(smem_raw)));
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int b = blockIdx.z, h = blockIdx.y;
+
+  // ---- tile geometry (CTA-uniform) ----
+  const int q0 = p.qo_indptr[b];
+  const int Le = p.qo_indptr[b + 1] - q0;
+  const int tok_per_cta = (2 * kTcBM) >> p.gp_shift;
+  const int ntq = (Le + tok_per_cta - 1) / tok_per_cta;
+  const int t = ntq - 1 - static_cast<int>(blockIdx.x);  // longest tiles first
+  if (t < 0) return;
+  const int tok0 = t * tok_per_cta;
+  const int kv0 = p.kv_indptr[b];
+  const int Lp = p.kv_indptr[b + 1] - kv0;
+  const bool use_mask = p.custom_mask != nullptr;
+  const int tile_tok_end = tok0 + tok_per_cta < Le ? tok0 + tok_per_cta : Le;
+  const int ext_end = (p.causal && !use_mask) ? tile_tok_end : Le;
+  const int Ltot = Lp + ext_end;
+  const int N = (Ltot + kTcBN - 1) / kTcBN;
+  const int rows_valid = (tile_tok_end - tok0) << p.gp_shift;
+  const int nsub = rows_valid > kTcBM ? 2 : 1;
+
+  if (threadIdx.x == 0) {
+    for (int s = 0; s < kTcSlots; ++s) {
+      mbar_init(bar_kv_full + 8 * s, 128);
+      mbar_init(bar_kv_empty + 8 * s, 1);
+    }
+    mbar_init(bar_q_full, 128);
+    for (int i = 0; i < 2; ++i) {
+      mbar_init(bar_s_full + 8 * i, 1);
+      mbar_init(bar_p_full + 8 * i, 128);
+    }
+    mbar_init(bar_o_full, 1);
+    fence_barrier_init();
+  }
+  if (warp == 12) {
+    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], 512;" ::"r"(tmem_slot));
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;");
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem = *tmem_slot_ptr;
+
+  if (warp < 8) {
+    // =============================== softmax warpgroups ===============================
+    setmaxnreg_inc<200>();
+    const int sub = warp >> 2;
+    if (sub < nsub) {
+      const int r = threadIdx.x & 127;
+      const int R = sub * kTcBM + r;
+      const int itok = tok0 + (R >> p.gp_shift);
+      const int hd = R & ((1 << p.gp_shift) - 1);
+      const bool rv = hd < p.group && itok < Le;
+      const int i_min_sub = tok0 + ((sub * kTcBM) >> p.gp_shift);
+      const uint32_t lane_off = static_cast<uint32_t>((warp & 3) * 32) << 16;
+      const uint32_t tS = tmem + lane_off + sub * kTcBN;
+      const uint32_t tO = tmem + lane_off + 2 * kTcBN + sub * kTcD;
+      const bool cap = p.logit_cap > 0.f;
+      const float c = cap ? kLog2e : p.scale_log2;
+      const float cap_pre = cap ? p.sm_scale / p.logit_cap : 0.f;
+      const int64_t mask_row_len = static_cast<int64_t>(Lp) + Le;
+      const uint8_t* mrow = nullptr;
+      if (use_mask) {
+        const int64_t ms = p.mask64 ? static_cast<const int64_t*>(p.mask_indptr)[b]
+                                    : static_cast<const int32_t*>(p.mask_indptr)[b];
+        mrow = p.custom_mask + ms + (rv ? itok : 0) * mask_row_len;
+      }
+      float m = -CUDART_INF_F, l = 0.f;
+
+      for (int n = 0; n < N; ++n) {
+        mbar_wait_wd(bar_s_full + 8 * sub, n & 1);
+        tc_fence_after();
+        float s[kTcBN];
+        tmem_ld32<0>(tS, s);
+        tmem_ld32<32>(tS + 32, s);
+        tmem_ld32<64>(tS + 64, s);
+        tmem_ld32<96>(tS + 96, s);
+        tmem_wait_ld();
+        if (cap) {
+#pragma unroll
+          for (int j = 0; j < kTcBN; ++j) s[j] = p.logit_cap * tanhf(s[j] * cap_pre);
+        }
+        const int j0 = n * kTcBN, j_end = j0 + kTcBN;
+        const bool need_mask = j_end > Ltot || (p.window > 0 && j0 < Lp) ||
+                               (use_mask && (!p.skip_prefix_mask || j_end > Lp)) ||
+                               (!use_mask && p.causal && j_end - 1 - Lp > i_min_sub);
+        if (need_mask) {
+#pragma unroll
+          for (int jj = 0; jj < kTcBN; ++jj) {
+            const int j = j0 + jj;
+            bool vis = rv && j < Ltot;
+            if (j < Lp) {
+              if (p.window > 0) vis = vis && (itok <= j + p.window);
+              if (use_mask && !p.skip_prefix_mask && vis) vis = mrow[j] != 0;
+            } else if (use_mask) {
+              if (vis) vis = mrow[j] != 0;
+            } else if (p.causal) {
+              vis = vis && (j - Lp <= itok);
+            }
+            if (!vis) s[jj] = -CUDART_INF_F;
+          }
+        }
+        float mx0 = -CUDART_INF_F, mx1 = -CUDART_INF_F, mx2 = -CUDART_INF_F, mx3 = -CUDART_INF_F;
+#pragma unroll
+        for (int j = 0; j < kTcBN; j += 4) {
+          mx0 = fmaxf(mx0, s[j]);
+          mx1 = fmaxf(mx1, s[j + 1]);
+          mx2 = fmaxf(mx2, s[j + 2]);
+          mx3 = fmaxf(mx3, s[j + 3]);
+        }
+        const float mx = fmaxf(fmaxf(mx0, mx1), fmaxf(mx2, mx3));
+        // lazy rescale: keep the stale max while the new one is within 2^8 of it (p stays <= 256)
+        const bool grow = mx > m && (m == -CUDART_INF_F || (mx - m) * c > kTcRescaleLog2);
+        if (__any_sync(0xffffffffu, grow)) {
+          float corr = 1.f;
+          if (grow) {
+            corr = fast_exp2((m - mx) * c);  // m = -inf -> 0
+            m = mx;
+            l *= corr;
+          }
+          if (n > 0) {
+            // PV_i(n-1) has completed: its commit precedes the one that signalled s_full(n)
+#pragma unroll
+            for (int cc = 0; cc < kTcD; cc += 32) {
+              float o[32];
+              tmem_ld32<0>(tO + cc, o);
+              tmem_wait_ld();
+#pragma unroll
+              for (int j = 0; j < 32; ++j) o[j] *= corr;
+              tmem_st32<0>(tO + cc, o);
+            }
+          }
+        }
+        const float mc = (m == -CUDART_INF_F ? 0.f : m) * c;
+        float sum0 = 0.f, sum1 = 0.f;
+#pragma unroll
+        for (int cc = 0; cc < kTcBN; cc += 32) {
+          uint32_t pk[16];
+#pragma unroll
+          for (int j = 0; j < 32; j += 2) {
+            const float p0 = fast_exp2(fmaf(s[cc + j], c, -mc));
+            const float p1 = fast_exp2(fmaf(s[cc + j + 1], c, -mc));
+            sum0 += p0;
+            sum1 += p1;
+            pk[j >> 1] = pack2<HALF>(p0, p1);
+          }
+          tmem_st16(tS + (cc >> 1), pk);
+        }
+        l += sum0 + sum1;
+        tmem_wait_st();
+        tc_fence_before();
+        mbar_arrive(bar_p_full + 8 * sub);
+      }
+
+      // ---- epilogue: O row / l -> global ----
+      mbar_wait_wd(bar_o_full, 0);
+      tc_fence_after();
+      const float inv = l > 0.f ? p.v_scale / l : 0.f;
+      QT* orow = reinterpret_cast<QT*>(p.o) + static_cast<int64_t>(q0 + (rv ? itok : 0)) * p.o_st +
+                 static_cast<int64_t>(h * p.group + (rv ? hd : 0)) * p.o_sh;
+#pragma unroll
+      for (int cc = 0; cc < kTcD; cc += 32) {
+        float o[32];
+        tmem_ld32<0>(tO + cc, o);
+        tmem_wait_ld();
+        if (rv) {
+#pragma unroll
+          for (int j = 0; j < 32; j += 8) {
+            uint4 v;
+            v.x = pack2<HALF>(o[j] * inv, o[j + 1] * inv);
+            v.y = pack2<HALF>(o[j + 2] * inv, o[j + 3] * inv);
+            v.z = pack2<HALF>(o[j + 4] * inv, o[j + 5] * inv);
+            v.w = pack2<HALF>(o[j + 6] * inv, o[j + 7] * inv);
+            *reinterpret_cast<uint4*>(orow + cc + j) = v;
+          }
+        }
+      }
+      if (rv && p.lse)
+        p.lse[static_cast<int64_t>(q0 + itok) * p.hq + h * p.group + hd] =
+            l > 0.f ? m * c * kLn2 + logf(l) : -CUDART_INF_F;
+      tc_fence_before();
+    }
+  } else if (warp < 12) {
+    // =============================== loaders ===============================
+    setmaxnreg_dec<56>();
+    const int tid = threadIdx.x - 256;       // 0..127
+    const int chunk = tid & 15, rbase = tid >> 4;  // row = rbase + 8 * i
+    const uint32_t sw_col = static_cast<uint32_t>(chunk >> 3) * kTcSlab;
+    // ---- Q: rows of both sub-tiles ----
+    {
+      const int gmask = (1 << p.gp_shift) - 1;
+      const int nrows = nsub * kTcBM;
+      for (int i = 0; i < nrows / 8; ++i) {
+        const int R = rbase + 8 * i;
+        const int itok = tok0 + (R >> p.gp_shift), hd = R & gmask;
+        const bool ok = hd < p.group && itok < Le;
+        const QT* src = reinterpret_cast<const QT*>(p.q) + (ok ? static_cast<int64_t>(q0 + itok) * p.q_st +
+                                                                     static_cast<int64_t>(h * p.group + hd) * p.q_sh
+                                                               : 0) + chunk * 8;
+        const int rr = R & (kTcBM - 1);
+        const uint32_t dst = q_base + (R >> 7) * kTcSlotBytes + sw_col + rr * 128 + (((chunk & 7) ^ (rr & 7)) << 4);
+        cp_async16_zfill(dst, src, ok);
+      }
+      cp_async_commit();
+      cp_async_wait<0>();
+      fence_proxy_async();
+      mbar_arrive(bar_q_full);
+    }
+    // ---- K / V ring ----
+    const int32_t* pidx;
+    if (p.kv_indices) {
+      pidx = p.kv_indices + kv0;
+    } else {
+      const int64_t req = p.idx64 ? static_cast<const int64_t*>(p.req_pool_indices)[b]
+                                  : static_cast<const int32_t*>(p.req_pool_indices)[b];
+      const int64_t pl = p.idx64 ? static_cast<const int64_t*>(p.prefix_lens)[b]
+                                 : static_cast<const int32_t*>(p.prefix_lens)[b];
+      pidx = p.req_to_token + req * p.r2t_stride + (pl - Lp);
+    }
+    const uint8_t* k_head = p.k_pool + static_cast<int64_t>(h) * kTcD * 2 + chunk * 16;
+    const uint8_t* v_head = p.v_pool + static_cast<int64_t>(h) * kTcD * 2 + chunk * 16;
+    int32_t slots[16];
+    auto fetch = [&](int n) {
+#pragma unroll
+      for (int i = 0; i < 16; ++i) {
+        const int j = n * kTcBN + rbase + 8 * i;
+        int32_t s = -1;
+        if (j < Ltot) s = j < Lp ? pidx[j] : static_cast<int32_t>(p.extend_loc[q0 + j - Lp]);
+        slots[i] = s;
+      }
+    };
+    fetch(0);
+    const int S = 2 * N;
+    for (int st = 0; st < S; ++st) {
+      const int slot = st % kTcSlots;
+      const uint32_t ph = static_cast<uint32_t>(st / kTcSlots) & 1u;
+      mbar_wait_wd(bar_kv_empty + 8 * slot, ph ^ 1u);
+      const bool is_v = st & 1;
+      const uint8_t* base = is_v ? v_head : k_head;
+      const int64_t sb = is_v ? p.v_slot_bytes : p.k_slot_bytes;
+      const uint32_t dst0 = kv_base + slot * kTcSlotBytes + sw_col;
+#pragma unroll
+      for (int i = 0; i < 16; ++i) {
+        const int row = rbase + 8 * i;
+        const bool ok = slots[i] >= 0;
+        cp_async16_zfill(dst0 + row * 128 + (((chunk & 7) ^ (row & 7)) << 4), base + (ok ? slots[i] : 0) * sb, ok);
+      }
+      cp_async_commit();
+      if (is_v && (st >> 1) + 1 < N) fetch((st >> 1) + 1);  // slot ids of the next tile
+      if (st >= kTcLag) {
+        cp_async_wait<kTcLag>();
+        fence_proxy_async();
+        mbar_arrive(bar_kv_full + 8 * ((st - kTcLag) % kTcSlots));
+      }
+    }
+    // drain: the last min(S, kTcLag) stages
+    cp_async_wait<0>();
+    fence_proxy_async();
+    for (int st = (S > kTcLag ? S - kTcLag : 0); st < S; ++st) mbar_arrive(bar_kv_full + 8 * (st % kTcSlots));
+  } else {
+    // =============================== MMA issuer (warp 12) ===============================
+    setmaxnreg_dec<56>();
+    if (warp == 12 && lane == 0) {
+      auto issue_qk = [&](int sub, int slot) {
+        const uint32_t a0 = q_base + sub * kTcSlotBytes, b0 = kv_base + slot * kTcSlotBytes;
+#pragma unroll
+        for (int k = 0; k < kTcD / 16; ++k) {
+          const uint32_t off = (k >> 2) * kTcSlab + (k & 3) * 32;
+          umma_ss(tmem + sub * kTcBN, umma_desc_sw128(a0 + off, 16, 1024), umma_desc_sw128(b0 + off, 16, 1024),
+                  IDESC_QK, k > 0);
+        }
+      };
+      auto issue_pv = [&](int sub, int slot, bool acc) {
+        const uint32_t v0 = kv_base + slot * kTcSlotBytes;
+#pragma unroll
+        for (int k = 0; k < kTcBN / 16; ++k)
+          umma_ts(tmem + 2 * kTcBN + sub * kTcD, tmem + sub * kTcBN + k * 8,
+                  umma_desc_sw128(v0 + k * 2048, kTcSlab, 1024), IDESC_PV, (acc || k > 0) ? 1u : 0u);
+      };
+      auto full_wait = [&](int st) {
+        mbar_wait_wd(bar_kv_full + 8 * (st % kTcSlots), static_cast<uint32_t>(st / kTcSlots) & 1u);
+      };
+      mbar_wait_wd(bar_q_full, 0);
+      full_wait(0);
+      tc_fence_after();
+      issue_qk(0, 0);
+      umma_commit(bar_s_full);
+      if (nsub == 2) {
+        issue_qk(1, 0);
+        umma_commit(bar_s_full + 8);
+      }
+      umma_commit(bar_kv_empty);  // K_0's slot
+      for (int n = 0; n < N; ++n) {
+        const int vst = 2 * n + 1, kst = 2 * n + 2;
+        const int vslot = vst % kTcSlots, kslot = kst % kTcSlots;
+        const bool more = n + 1 < N;
+        full_wait(vst);
+        mbar_wait_wd(bar_p_full, n & 1);
+        tc_fence_after();
+        issue_pv(0, vslot, n > 0);
+        if (more) {
+          full_wait(kst);
+          tc_fence_after();
+          issue_qk(0, kslot);
+          umma_commit(bar_s_full);
+        }
+        if (nsub == 2) {
+          mbar_wait_wd(bar_p_full + 8, n & 1);
+          tc_fence_after();
+          issue_pv(1, vslot, n > 0);
+        }
+        umma_commit(bar_kv_empty + 8 * vslot);
+        if (more) {
+          if (nsub == 2) {
+            issue_qk(1, kslot);
+            umma_commit(bar_s_full + 8);
+          }
+          umma_commit(bar_kv_empty + 8 * kslot);
+        }
+      }
+      umma_commit(bar_o_full);
+      tc_fence_before();
+    }
+  }
+  __syncthreads();
+  if (warp == 12) {
+    tc_fence_after();
+    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, 512;" ::"r"(tmem));
+  }
+}
+
+}  // namespace b200attn
