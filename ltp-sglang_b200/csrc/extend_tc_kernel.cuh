@@ -137,6 +137,14 @@ __device__ __forceinline__ void setmaxnreg_dec() {
   asm volatile("setmaxnreg.dec.sync.aligned.u32 %0;" ::"n"(REGS));
 }
 
+// -DB200ATTN_TC_TRACE: CTA (0,0,0) writes clock64() timestamps of its pipeline events into the lse
+// buffer (tools/trace_tc.py decodes them); a tuning build, never the shipped library.
+#ifdef B200ATTN_TC_TRACE
+#define TC_TR(kind, n) do { if (tr && (n) < 256) tr[(kind) * 256 + (n)] = clock64(); } while (0)
+#else
+#define TC_TR(kind, n) do { } while (0)
+#endif
+
 template <typename QT>
 __global__ void __launch_bounds__(kTcThreads, 1) extend_tc_kernel(const ExtendParams p) {
   constexpr bool HALF = std::is_same<QT, __half>::value;
@@ -159,6 +167,10 @@ __global__ void __launch_bounds__(kTcThreads, 1) extend_tc_kernel(const ExtendPa
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int b = blockIdx.z, h = blockIdx.y;
+#ifdef B200ATTN_TC_TRACE
+  long long* tr = (blockIdx.x == 0 && blockIdx.y == 0 && blockIdx.z == 0 && (threadIdx.x & 127) == 0)
+                      ? reinterpret_cast<long long*>(p.lse) : nullptr;
+#endif
 
   // ---- tile geometry (CTA-uniform) ----
   const int q0 = p.qo_indptr[b];
@@ -229,12 +241,14 @@ __global__ void __launch_bounds__(kTcThreads, 1) extend_tc_kernel(const ExtendPa
       for (int n = 0; n < N; ++n) {
         mbar_wait_wd(bar_s_full + 8 * sub, n & 1);
         tc_fence_after();
+        TC_TR(sub * 3, n);
         float s[kTcBN];
         tmem_ld32<0>(tS, s);
         tmem_ld32<32>(tS + 32, s);
         tmem_ld32<64>(tS + 64, s);
         tmem_ld32<96>(tS + 96, s);
         tmem_wait_ld();
+        TC_TR(sub * 3 + 1, n);
         if (cap) {
 #pragma unroll
           for (int j = 0; j < kTcBN; ++j) s[j] = p.logit_cap * tanhf(s[j] * cap_pre);
@@ -309,6 +323,7 @@ __global__ void __launch_bounds__(kTcThreads, 1) extend_tc_kernel(const ExtendPa
         tmem_wait_st();
         tc_fence_before();
         mbar_arrive(bar_p_full + 8 * sub);
+        TC_TR(sub * 3 + 2, n);
       }
 
       // ---- epilogue: O row / l -> global ----
@@ -334,9 +349,11 @@ __global__ void __launch_bounds__(kTcThreads, 1) extend_tc_kernel(const ExtendPa
           }
         }
       }
+#ifndef B200ATTN_TC_TRACE
       if (rv && p.lse)
         p.lse[static_cast<int64_t>(q0 + itok) * p.hq + h * p.group + hd] =
             l > 0.f ? m * c * kLn2 + logf(l) : -CUDART_INF_F;
+#endif
       tc_fence_before();
     }
   } else if (warp < 12) {
@@ -379,13 +396,33 @@ __global__ void __launch_bounds__(kTcThreads, 1) extend_tc_kernel(const ExtendPa
     const uint8_t* k_head = p.k_pool + static_cast<int64_t>(h) * kTcD * 2 + chunk * 16;
     const uint8_t* v_head = p.v_pool + static_cast<int64_t>(h) * kTcD * 2 + chunk * 16;
     int32_t slots[16];
+    // Slot ids of tile n.  A tile lies wholly in the prefix list or wholly in the extend tokens except
+    // for the one tile that holds the boundary: the two common cases are branch-free batches of 16
+    // independent loads (clamped index, selected afterwards), so their latencies overlap.
     auto fetch = [&](int n) {
+      const int jb = n * kTcBN + rbase;
+      if (n * kTcBN + kTcBN <= Lp) {
 #pragma unroll
-      for (int i = 0; i < 16; ++i) {
-        const int j = n * kTcBN + rbase + 8 * i;
-        int32_t s = -1;
-        if (j < Ltot) s = j < Lp ? pidx[j] : static_cast<int32_t>(p.extend_loc[q0 + j - Lp]);
-        slots[i] = s;
+        for (int i = 0; i < 16; ++i) slots[i] = pidx[jb + 8 * i];
+      } else if (n * kTcBN >= Lp) {
+        const int64_t* el = p.extend_loc + (q0 - Lp);
+        const int jmax = Ltot - 1;
+        int64_t v[16];
+#pragma unroll
+        for (int i = 0; i < 16; ++i) {
+          const int j = jb + 8 * i;
+          v[i] = el[j < jmax ? j : jmax];
+        }
+#pragma unroll
+        for (int i = 0; i < 16; ++i) slots[i] = jb + 8 * i <= jmax ? static_cast<int32_t>(v[i]) : -1;
+      } else {
+#pragma unroll
+        for (int i = 0; i < 16; ++i) {
+          const int j = jb + 8 * i;
+          int32_t sl = -1;
+          if (j < Ltot) sl = j < Lp ? pidx[j] : static_cast<int32_t>(p.extend_loc[q0 + j - Lp]);
+          slots[i] = sl;
+        }
       }
     };
     fetch(0);
@@ -394,6 +431,7 @@ __global__ void __launch_bounds__(kTcThreads, 1) extend_tc_kernel(const ExtendPa
       const int slot = st % kTcSlots;
       const uint32_t ph = static_cast<uint32_t>(st / kTcSlots) & 1u;
       mbar_wait_wd(bar_kv_empty + 8 * slot, ph ^ 1u);
+      TC_TR(10, st);
       const bool is_v = st & 1;
       const uint8_t* base = is_v ? v_head : k_head;
       const int64_t sb = is_v ? p.v_slot_bytes : p.k_slot_bytes;
@@ -410,6 +448,7 @@ __global__ void __launch_bounds__(kTcThreads, 1) extend_tc_kernel(const ExtendPa
         cp_async_wait<kTcLag>();
         fence_proxy_async();
         mbar_arrive(bar_kv_full + 8 * ((st - kTcLag) % kTcSlots));
+        TC_TR(11, st - kTcLag);
       }
     }
     // drain: the last min(S, kTcLag) stages
@@ -420,6 +459,9 @@ __global__ void __launch_bounds__(kTcThreads, 1) extend_tc_kernel(const ExtendPa
     // =============================== MMA issuer (warp 12) ===============================
     setmaxnreg_dec<56>();
     if (warp == 12 && lane == 0) {
+#ifdef B200ATTN_TC_TRACE
+      if (blockIdx.x == 0 && blockIdx.y == 0 && blockIdx.z == 0) tr = reinterpret_cast<long long*>(p.lse);
+#endif
       auto issue_qk = [&](int sub, int slot) {
         const uint32_t a0 = q_base + sub * kTcSlotBytes, b0 = kv_base + slot * kTcSlotBytes;
 #pragma unroll
@@ -454,18 +496,22 @@ __global__ void __launch_bounds__(kTcThreads, 1) extend_tc_kernel(const ExtendPa
         const int vslot = vst % kTcSlots, kslot = kst % kTcSlots;
         const bool more = n + 1 < N;
         full_wait(vst);
+        TC_TR(6, n);
         mbar_wait_wd(bar_p_full, n & 1);
         tc_fence_after();
+        TC_TR(7, n);
         issue_pv(0, vslot, n > 0);
         if (more) {
           full_wait(kst);
           tc_fence_after();
+          TC_TR(8, n);
           issue_qk(0, kslot);
           umma_commit(bar_s_full);
         }
         if (nsub == 2) {
           mbar_wait_wd(bar_p_full + 8, n & 1);
           tc_fence_after();
+          TC_TR(9, n);
           issue_pv(1, vslot, n > 0);
         }
         umma_commit(bar_kv_empty + 8 * vslot);

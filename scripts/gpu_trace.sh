@@ -1,0 +1,7 @@
+B200ATTN_LIB=tools/bin/libb200attn_trace.so timeout 120 python tools/trace_tc.py 2>&1 | tail -${1:-12}
+timeout 200 python bench_extend.py --steps 10 2>/dev/null > gpurun_out/bext_last.json
+python - <<'P'
+import json
+for l in open('gpurun_out/bext_last.json'):
+    d=json.loads(l); r=d["roofline"]; print(d["config"]["workload"][:3], round(r["kernel_ms"],3), "ms", round(r["tflops"]), "TFLOP/s", round(r["gb_per_s"]), "GB/s")
+P

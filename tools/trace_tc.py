@@ -1,0 +1,37 @@
+"""Pipeline timeline of one CTA of extend_tc_kernel (tuning aid; needs the -DB200ATTN_TC_TRACE build):
+    make -C ltp-sglang_b200/csrc EXTRA=-DB200ATTN_TC_TRACE BUILD=/tmp/trace_build OUT=$PWD/tools/bin/libb200attn_trace.so
+    B200ATTN_LIB=tools/bin/libb200attn_trace.so python tools/trace_tc.py
+Kinds: 0/3 softmax0/1 saw s_full, 1/4 S row loaded, 2/5 P published, 6 MMA saw V full, 7 saw p_full0,
+8 saw K(n+1) full, 9 saw p_full1, 10 loader got the empty slot (per stage), 11 loader published stage."""
+import os, sys
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path[:0] = [ROOT, os.path.join(ROOT, "ltp-sglang_b200")]
+import numpy as np, torch
+import b200attn, synth
+
+dev = torch.device("cuda:0")
+L = int(sys.argv[1]) if len(sys.argv) > 1 else 8192
+w = synth.make_extend_workload(synth.Config("t", 1, 0, 32, 8, 128, seed=7), [0], [L], dev)
+q = w.q.view(L, 32, 128); o = torch.empty_like(q)
+b200attn.store_kv(w.k_pool, w.v_pool, w.out_cache_loc, w.k.view(L, 8, 128), w.v.view(L, 8, 128))
+qo = torch.tensor([0, L], dtype=torch.int32, device=dev); kv = torch.zeros(2, dtype=torch.int32, device=dev)
+lse = torch.zeros(L * 32, dtype=torch.float32, device=dev)
+for _ in range(2):
+    lse.zero_()
+    torch.ops.b200attn.extend(q, o, lse, w.k_pool, w.v_pool, qo, kv, None, w.req_to_token, w.req_pool_indices,
+                              w.extend_prefix_lens, w.out_cache_loc, None, None, L, True, -1, True, w.sm_scale, 0.0)
+torch.cuda.synchronize()
+t = lse.view(torch.int64)[: 12 * 256].cpu().numpy().reshape(12, 256)
+N = (L + 127) // 128
+t0 = t[0, 0]
+np.set_printoptions(linewidth=200)
+print("tiles", N)
+for n in list(range(0, 6)) + list(range(30, 34)):
+    if n >= N: break
+    r = [int(t[k, n] - t0) if t[k, n] else -1 for k in range(10)]
+    print(f"n={n:3d} sm0: s {r[0]:7d} ld {r[1]:7d} p {r[2]:7d} | sm1: s {r[3]:7d} ld {r[4]:7d} p {r[5]:7d} | mma: V {r[6]:7d} p0 {r[7]:7d} K {r[8]:7d} p1 {r[9]:7d}")
+for st in list(range(0, 8)) + list(range(60, 66)):
+    print(f"st={st:3d} loader empty {int(t[10, st]-t0):7d} published {int(t[11, st]-t0):7d}")
+d = np.diff(t[0, 8:N-2]).astype(float)
+print("steady period per tile (clk): mean %.0f" % d.mean(), " softmax0 busy (s->p): %.0f" % (t[2, 8:N-2] - t[0, 8:N-2]).mean(),
+      " ld: %.0f" % (t[1, 8:N-2] - t[0, 8:N-2]).mean(), " p0->next s0: %.0f" % (t[0, 9:N-1] - t[2, 8:N-2]).mean())
