@@ -45,6 +45,9 @@ constexpr int kTcSmemBytes = kTcQBytes + kTcSlots * kTcSlotBytes + kTcBarBytes +
 constexpr float kTcRescaleLog2 = 8.f;  // lazy rescale threshold (log2 units)
 
 // ---- tcgen05 wrappers ----
+// The MMA / commit wrappers are executed by a WHOLE warp (uniform control flow) and elect one lane
+// inside the asm: operands then live in uniform registers.  Issued from a lane == 0 branch instead,
+// every MMA costs ~125 clk of R2UR / waterfall code on the issuing thread (tools/probe_umma.cu).
 __device__ __forceinline__ uint64_t umma_desc_sw128(uint32_t addr, uint32_t lbo_bytes, uint32_t sbo_bytes) {
   uint64_t d = static_cast<uint64_t>((addr & 0x3FFFF) >> 4);
   d |= static_cast<uint64_t>((lbo_bytes >> 4) & 0x3FFF) << 16;
@@ -61,20 +64,23 @@ __host__ __device__ constexpr uint32_t umma_idesc(int m, int n, int fmt, int b_m
 }
 __device__ __forceinline__ void umma_ss(uint32_t d, uint64_t a, uint64_t b, uint32_t idesc, uint32_t acc) {
   asm volatile(
-      "{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\t"
-      "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t}" ::"r"(d),
+      "{\n\t.reg .pred p, e;\n\telect.sync _|e, 0xffffffff;\n\tsetp.ne.b32 p, %4, 0;\n\t"
+      "@e tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t}" ::"r"(d),
       "l"(a), "l"(b), "r"(idesc), "r"(acc)
       : "memory");
 }
 __device__ __forceinline__ void umma_ts(uint32_t d, uint32_t a_tmem, uint64_t b, uint32_t idesc, uint32_t acc) {
   asm volatile(
-      "{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\t"
-      "tcgen05.mma.cta_group::1.kind::f16 [%0], [%1], %2, %3, p;\n\t}" ::"r"(d),
+      "{\n\t.reg .pred p, e;\n\telect.sync _|e, 0xffffffff;\n\tsetp.ne.b32 p, %4, 0;\n\t"
+      "@e tcgen05.mma.cta_group::1.kind::f16 [%0], [%1], %2, %3, p;\n\t}" ::"r"(d),
       "r"(a_tmem), "l"(b), "r"(idesc), "r"(acc)
       : "memory");
 }
 __device__ __forceinline__ void umma_commit(uint32_t bar) {
-  asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(bar) : "memory");
+  asm volatile(
+      "{\n\t.reg .pred e;\n\telect.sync _|e, 0xffffffff;\n\t"
+      "@e tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];\n\t}" ::"r"(bar)
+      : "memory");
 }
 __device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
 __device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
@@ -210,7 +216,7 @@ __global__ void __launch_bounds__(kTcThreads, 1) extend_tc_kernel(const ExtendPa
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
-  const uint32_t tmem = *tmem_slot_ptr;
+  const uint32_t tmem = __shfl_sync(0xffffffffu, *tmem_slot_ptr, 0);  // provably warp-uniform
 
   if (warp < 8) {
     // =============================== softmax warpgroups ===============================
@@ -428,6 +434,14 @@ __global__ void __launch_bounds__(kTcThreads, 1) extend_tc_kernel(const ExtendPa
     fetch(0);
     const int S = 2 * N;
     for (int st = 0; st < S; ++st) {
+      // publish stage st - kTcLag first: its copies have landed once at most kTcLag - 1 newer groups are
+      // pending.  Doing this before the empty-slot wait keeps publication independent of the ring.
+      if (st >= kTcLag) {
+        cp_async_wait<kTcLag - 1>();
+        fence_proxy_async();
+        mbar_arrive(bar_kv_full + 8 * ((st - kTcLag) % kTcSlots));
+        TC_TR(11, st - kTcLag);
+      }
       const int slot = st % kTcSlots;
       const uint32_t ph = static_cast<uint32_t>(st / kTcSlots) & 1u;
       mbar_wait_wd(bar_kv_empty + 8 * slot, ph ^ 1u);
@@ -444,12 +458,6 @@ __global__ void __launch_bounds__(kTcThreads, 1) extend_tc_kernel(const ExtendPa
       }
       cp_async_commit();
       if (is_v && (st >> 1) + 1 < N) fetch((st >> 1) + 1);  // slot ids of the next tile
-      if (st >= kTcLag) {
-        cp_async_wait<kTcLag>();
-        fence_proxy_async();
-        mbar_arrive(bar_kv_full + 8 * ((st - kTcLag) % kTcSlots));
-        TC_TR(11, st - kTcLag);
-      }
     }
     // drain: the last min(S, kTcLag) stages
     cp_async_wait<0>();
@@ -458,25 +466,31 @@ __global__ void __launch_bounds__(kTcThreads, 1) extend_tc_kernel(const ExtendPa
   } else {
     // =============================== MMA issuer (warp 12) ===============================
     setmaxnreg_dec<56>();
-    if (warp == 12 && lane == 0) {
+    if (warp == 12) {
 #ifdef B200ATTN_TC_TRACE
-      if (blockIdx.x == 0 && blockIdx.y == 0 && blockIdx.z == 0) tr = reinterpret_cast<long long*>(p.lse);
+      tr = (blockIdx.x == 0 && blockIdx.y == 0 && blockIdx.z == 0 && lane == 0) ? reinterpret_cast<long long*>(p.lse) : nullptr;
 #endif
+      // descriptors differ only in the 14-bit start-address field: build one base per operand kind and
+      // add the (compile-time) offsets, in 16-byte units
+      const uint64_t dq = umma_desc_sw128(q_base, 16, 1024);
+      const uint64_t dk = umma_desc_sw128(kv_base, 16, 1024);
+      const uint64_t dv = umma_desc_sw128(kv_base, kTcSlab, 1024);
       auto issue_qk = [&](int sub, int slot) {
-        const uint32_t a0 = q_base + sub * kTcSlotBytes, b0 = kv_base + slot * kTcSlotBytes;
+        const uint64_t a0 = dq + static_cast<uint32_t>(sub * (kTcSlotBytes >> 4));
+        const uint64_t b0 = dk + static_cast<uint32_t>(slot * (kTcSlotBytes >> 4));
+        const uint32_t d = tmem + sub * kTcBN;
 #pragma unroll
         for (int k = 0; k < kTcD / 16; ++k) {
-          const uint32_t off = (k >> 2) * kTcSlab + (k & 3) * 32;
-          umma_ss(tmem + sub * kTcBN, umma_desc_sw128(a0 + off, 16, 1024), umma_desc_sw128(b0 + off, 16, 1024),
-                  IDESC_QK, k > 0);
+          const uint32_t off = ((k >> 2) * kTcSlab + (k & 3) * 32) >> 4;
+          umma_ss(d, a0 + off, b0 + off, IDESC_QK, k > 0);
         }
       };
       auto issue_pv = [&](int sub, int slot, bool acc) {
-        const uint32_t v0 = kv_base + slot * kTcSlotBytes;
+        const uint64_t v0 = dv + static_cast<uint32_t>(slot * (kTcSlotBytes >> 4));
+        const uint32_t d = tmem + 2 * kTcBN + sub * kTcD, a = tmem + sub * kTcBN;
+        umma_ts(d, a, v0, IDESC_PV, acc ? 1u : 0u);
 #pragma unroll
-        for (int k = 0; k < kTcBN / 16; ++k)
-          umma_ts(tmem + 2 * kTcBN + sub * kTcD, tmem + sub * kTcBN + k * 8,
-                  umma_desc_sw128(v0 + k * 2048, kTcSlab, 1024), IDESC_PV, (acc || k > 0) ? 1u : 0u);
+        for (int k = 1; k < kTcBN / 16; ++k) umma_ts(d, a + k * 8, v0 + k * (2048 >> 4), IDESC_PV, 1u);
       };
       auto full_wait = [&](int st) {
         mbar_wait_wd(bar_kv_full + 8 * (st % kTcSlots), static_cast<uint32_t>(st / kTcSlots) & 1u);

@@ -1,4 +1,5 @@
-B200ATTN_LIB=tools/bin/libb200attn_trace.so timeout 120 python tools/trace_tc.py 2>&1 | tail -${1:-12}
+timeout 300 python -m pytest tests/test_gpu_extend.py -x -q --timeout 120 2>&1 | tail -2
+B200ATTN_LIB=tools/bin/libb200attn_trace.so timeout 120 python tools/trace_tc.py 2>&1 | grep -E "^n= 3|steady"
 timeout 200 python bench_extend.py --steps 10 2>/dev/null > gpurun_out/bext_last.json
 python - <<'P'
 import json

@@ -32,18 +32,18 @@ __device__ __forceinline__ uint32_t make_idesc(int M, int N, int a_major, int b_
 
 __device__ __forceinline__ void mma_ss(uint32_t d, uint64_t a, uint64_t b, uint32_t idesc, uint32_t acc) {
   asm volatile(
-      "{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\t"
-      "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t}"
+      "{\n\t.reg .pred p, e;\n\telect.sync _|e, 0xffffffff;\n\tsetp.ne.b32 p, %4, 0;\n\t"
+      "@e tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t}"
       ::"r"(d), "l"(a), "l"(b), "r"(idesc), "r"(acc) : "memory");
 }
 __device__ __forceinline__ void mma_ts(uint32_t d, uint32_t a_tmem, uint64_t b, uint32_t idesc, uint32_t acc) {
   asm volatile(
-      "{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\t"
-      "tcgen05.mma.cta_group::1.kind::f16 [%0], [%1], %2, %3, p;\n\t}"
+      "{\n\t.reg .pred p, e;\n\telect.sync _|e, 0xffffffff;\n\tsetp.ne.b32 p, %4, 0;\n\t"
+      "@e tcgen05.mma.cta_group::1.kind::f16 [%0], [%1], %2, %3, p;\n\t}"
       ::"r"(d), "r"(a_tmem), "l"(b), "r"(idesc), "r"(acc) : "memory");
 }
 __device__ __forceinline__ void commit(uint32_t bar) {
-  asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(bar) : "memory");
+  asm volatile("{\n\t.reg .pred e;\n\telect.sync _|e, 0xffffffff;\n\t@e tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];\n\t}" ::"r"(bar) : "memory");
 }
 __device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
   uint32_t ok = 0;
@@ -76,8 +76,40 @@ __device__ __forceinline__ void tmem_st32(uint32_t taddr, const uint32_t (&r)[32
   asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory");
 }
 
-constexpr int M = 128, N = 128, K = 128;
 constexpr int SLAB = 128 * 128;  // bytes: 128 rows of 128 B
+template <int VARIANT>
+__device__ __forceinline__ uint32_t time_variant(uint32_t tmem, uint8_t* sA, uint8_t* sB, uint8_t* sV, uint64_t* bar,
+                                                 uint32_t par, float* D2, int t) {
+  constexpr bool ts = VARIANT == 2 || VARIANT == 3, mn = VARIANT & 1;
+  constexpr int nn = VARIANT == 6 ? 256 : (VARIANT == 7 ? 64 : 128);
+  constexpr bool alt = VARIANT == 4 || VARIANT == 5;
+  const uint32_t idesc = make_idesc(128, nn, 0, mn);
+  const uint64_t a_base = make_desc(smem_u32(sA), 16, 1024);
+  const uint64_t b_base = mn ? make_desc(smem_u32(sV), SLAB, 1024) : make_desc(smem_u32(sB), 16, 1024);
+  const long long c0 = clock64();
+#pragma unroll 1
+  for (int it = 0; it < 8; ++it) {
+#pragma unroll
+    for (int k = 0; k < 8; ++k) {
+      const uint32_t koff = (k >> 2) * SLAB + (k & 3) * 32;
+      const uint64_t bd = b_base + (mn ? (k * 2048) >> 4 : koff >> 4);
+      const uint32_t dd = tmem + ((alt && (k & 1)) ? 384 : 128);
+      if (ts) mma_ts(dd, tmem + 256 + k * 8, bd, idesc, 1);
+      else mma_ss(dd, a_base + (koff >> 4), bd, idesc, 1);
+    }
+  }
+  const long long c1 = clock64();
+  commit(smem_u32(bar));
+  mbar_wait(smem_u32(bar), par);
+  const long long c2 = clock64();
+  if (t == 0) {
+    D2[128 * 128 + VARIANT * 2] = (float)(c1 - c0);
+    D2[128 * 128 + VARIANT * 2 + 1] = (float)(c2 - c0);
+  }
+  return par ^ 1;
+}
+
+constexpr int M = 128, N = 128, K = 128;
 
 // A, B: [128][K] row-major bf16 (K-major).  P: [128][K].  V: [K tokens][N d] row-major.
 __global__ void __launch_bounds__(128) probe(const __nv_bfloat16* A, const __nv_bfloat16* B, const __nv_bfloat16* P,
@@ -111,11 +143,11 @@ __global__ void __launch_bounds__(128) probe(const __nv_bfloat16* A, const __nv_
   asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
   __syncthreads();
   asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
-  const uint32_t tmem = tmem_base_s;
+  const uint32_t tmem = __shfl_sync(0xffffffffu, tmem_base_s, 0);
   const uint32_t lane_addr = tmem + ((uint32_t)(warp * 32) << 16);
 
   // ---- test 1: SS ----
-  if (t == 0) {
+  if (warp == 0) {
     const uint32_t idesc = make_idesc(M, N, 0, 0);
     for (int k = 0; k < K / 16; ++k) {
       const uint32_t off = (k >> 2) * SLAB + (k & 3) * 32;
@@ -140,7 +172,7 @@ __global__ void __launch_bounds__(128) probe(const __nv_bfloat16* A, const __nv_
   asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
   __syncthreads();
   asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
-  if (t == 0) {
+  if (warp == 0) {
     const uint32_t idesc = make_idesc(M, N, 0, 1);  // B = V is MN-major
     for (int k = 0; k < K / 16; ++k) {
       // 16 tokens per step = two 8-row groups of 1024 B; the two 64-wide d slabs are SLAB apart
@@ -154,6 +186,21 @@ __global__ void __launch_bounds__(128) probe(const __nv_bfloat16* A, const __nv_
     uint32_t r[32];
     tmem_ld32(lane_addr + 128 + c0, r);
     for (int j = 0; j < 32; ++j) D2[(size_t)t * N + c0 + j] = __uint_as_float(r[j]);
+  }
+  // ---- timing: 64 back-to-back MMAs (M=128, N=128, K=16 each) per variant, one commit at the end ----
+  asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+  __syncthreads();
+  asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+  if (warp == 0) {
+    uint32_t par = 0;
+    par = time_variant<0>(tmem, sA, sB, sV, &bar, par, D2, t);
+    par = time_variant<1>(tmem, sA, sB, sV, &bar, par, D2, t);
+    par = time_variant<2>(tmem, sA, sB, sV, &bar, par, D2, t);
+    par = time_variant<3>(tmem, sA, sB, sV, &bar, par, D2, t);
+    par = time_variant<4>(tmem, sA, sB, sV, &bar, par, D2, t);
+    par = time_variant<5>(tmem, sA, sB, sV, &bar, par, D2, t);
+    par = time_variant<6>(tmem, sA, sB, sV, &bar, par, D2, t);
+    par = time_variant<7>(tmem, sA, sB, sV, &bar, par, D2, t);
   }
   asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
   __syncthreads();
@@ -171,7 +218,7 @@ int main() {
   __nv_bfloat16 *dA, *dB, *dP, *dV;
   float *d1, *d2;
   cudaMalloc(&dA, A.size() * 2); cudaMalloc(&dB, B.size() * 2); cudaMalloc(&dP, P.size() * 2); cudaMalloc(&dV, V.size() * 2);
-  cudaMalloc(&d1, M * N * 4); cudaMalloc(&d2, M * N * 4);
+  cudaMalloc(&d1, M * N * 4); cudaMalloc(&d2, M * N * 4 + 64);
   cudaMemcpy(dA, A.data(), A.size() * 2, cudaMemcpyHostToDevice);
   cudaMemcpy(dB, B.data(), B.size() * 2, cudaMemcpyHostToDevice);
   cudaMemcpy(dP, P.data(), P.size() * 2, cudaMemcpyHostToDevice);
@@ -196,6 +243,12 @@ int main() {
       e1 = fmax(e1, fabs(s1 - h1[i * N + j]));
       e2 = fmax(e2, fabs(s2 - h2[i * N + j]));
     }
+  {
+    float tm[16];
+    cudaMemcpy(tm, d2 + M * N, sizeof(tm), cudaMemcpyDeviceToHost);
+    const char* nm[8] = {"SS B K-major", "SS B MN-major", "TS B K-major", "TS B MN-major", "SS K alt-acc", "SS MN alt-acc", "SS K N=256", "SS MN N=64"};
+    for (int v = 0; v < 8; ++v) printf("timing %-14s: issue %.0f clk, done %.0f clk for 64 MMAs (%.1f clk / MMA)\n", nm[v], tm[2 * v], tm[2 * v + 1], tm[2 * v + 1] / 64);
+  }
   printf("test1 SS K-major x K-major SW128: max err %.3e %s\n", e1, e1 < 1e-3 ? "PASS" : "FAIL");
   printf("test2 TS P(tmem) x V MN-major SW128: max err %.3e %s\n", e2, e2 < 1e-3 ? "PASS" : "FAIL");
   return (e1 < 1e-3 && e2 < 1e-3) ? 0 : 2;
