@@ -19,7 +19,7 @@
 //                                                           V MN-major = the same row layout)
 //                     in the order PV0(n) S0(n+1) PV1(n) S1(n+1), so the softmax of one sub-tile
 //                     overlaps the MMAs of the other; tcgen05.commit signals the mbarriers.
-// TMEM (512 columns): S0 [0,128) S1 [128,256) O0 [256,384) O1 [384,512); P_i aliases S_i [0,64).
+// TMEM (512 columns): S0 [0,128) S1 [128,256) O0 [256,384) O1 [384,512); P_i aliases S_i [0,32) + [64,96).
 // The descriptor encodings are pinned by tools/probe_umma.cu.
 #pragma once
 
@@ -31,16 +31,19 @@
 
 namespace b200attn {
 
-constexpr int kTcThreads = 512;
+constexpr int kTcSoftmaxWarps = 16;   // 2 sub-tiles x 2 column halves x 4 lane quarters
+constexpr int kTcLoaderWarp0 = 16;    // warps 16-19 load, warp 20 issues the MMAs
+constexpr int kTcMmaWarp = 20;
+constexpr int kTcThreads = 21 * 32;   // 16 softmax + 4 loader + 1 MMA warps, 80 registers each
 constexpr int kTcBM = 128;            // rows per sub-tile (TMEM lanes)
 constexpr int kTcBN = 128;            // kv tokens per tile
 constexpr int kTcD = 128;
-constexpr int kTcSlots = 5;           // K / V ring slots
+constexpr int kTcSlots = 4;           // K / V ring slots
 constexpr int kTcSlab = kTcBN * 128;  // bytes of one 64-element-wide slab of 128 rows
 constexpr int kTcSlotBytes = 2 * kTcSlab;
 constexpr int kTcQBytes = 2 * kTcSlotBytes;  // two sub-tiles
 constexpr int kTcLag = 2;             // cp.async groups a loader thread keeps in flight
-constexpr int kTcBarBytes = 1024;
+constexpr int kTcBarBytes = 8192;    // mbarriers, TMEM base, row max / row sum exchange
 constexpr int kTcSmemBytes = kTcQBytes + kTcSlots * kTcSlotBytes + kTcBarBytes + 1024;  // + alignment slack
 constexpr float kTcRescaleLog2 = 8.f;  // lazy rescale threshold (log2 units)
 
@@ -130,7 +133,7 @@ __device__ __forceinline__ void tmem_st16(uint32_t taddr, const uint32_t (&u)[16
 __device__ __forceinline__ void mbar_wait_wd(uint32_t bar, uint32_t parity) {
   uint32_t spins = 0;
   while (!mbar_try_wait(bar, parity)) {
-    if (++spins > (1u << 26)) __trap();
+    if (++spins > (1u << 20)) __trap();
   }
 }
 
@@ -169,12 +172,16 @@ __global__ void __launch_bounds__(kTcThreads, 1) extend_tc_kernel(const ExtendPa
   const uint32_t bar_p_full = bar_s_full + 16;            // [2]
   const uint32_t bar_o_full = bar_p_full + 16;
   const uint32_t tmem_slot = bar_o_full + 8;
+  // row max [parity][sub][half][row] and row sum [sub][half][row] exchanged between the two threads of a row
+  float* xch = reinterpret_cast<float*>(smem_raw + (bars + 1024 - smem_u32(smem_raw)));
+  float* lxch = xch + 2 * 2 * 2 * kTcBM;
+  int32_t* sid = reinterpret_cast<int32_t*>(lxch + 2 * 2 * kTcBM);  // [2][kTcBN] slot ids of a tile
   volatile uint32_t* tmem_slot_ptr = reinterpret_cast<volatile uint32_t*>(smem_raw + (tmem_slot - smem_u32(smem_raw)));
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int b = blockIdx.z, h = blockIdx.y;
 #ifdef B200ATTN_TC_TRACE
-  long long* tr = (blockIdx.x == 0 && blockIdx.y == 0 && blockIdx.z == 0 && (threadIdx.x & 127) == 0)
+  long long* tr = (blockIdx.x == 0 && blockIdx.y == 0 && blockIdx.z == 0 && ((threadIdx.x & 255) == 0 || threadIdx.x == kTcLoaderWarp0 * 32 || threadIdx.x == kTcMmaWarp * 32))
                       ? reinterpret_cast<long long*>(p.lse) : nullptr;
 #endif
 
@@ -204,12 +211,12 @@ __global__ void __launch_bounds__(kTcThreads, 1) extend_tc_kernel(const ExtendPa
     mbar_init(bar_q_full, 128);
     for (int i = 0; i < 2; ++i) {
       mbar_init(bar_s_full + 8 * i, 1);
-      mbar_init(bar_p_full + 8 * i, 128);
+      mbar_init(bar_p_full + 8 * i, 256);
     }
     mbar_init(bar_o_full, 1);
     fence_barrier_init();
   }
-  if (warp == 12) {
+  if (warp == kTcMmaWarp) {
     asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], 512;" ::"r"(tmem_slot));
     asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;");
   }
@@ -218,20 +225,23 @@ __global__ void __launch_bounds__(kTcThreads, 1) extend_tc_kernel(const ExtendPa
   tc_fence_after();
   const uint32_t tmem = __shfl_sync(0xffffffffu, *tmem_slot_ptr, 0);  // provably warp-uniform
 
-  if (warp < 8) {
-    // =============================== softmax warpgroups ===============================
-    setmaxnreg_inc<200>();
-    const int sub = warp >> 2;
+  if (warp < kTcSoftmaxWarps) {
+    // =============================== softmax warps ===============================
+    // Two threads per row: warp w serves sub-tile w / 8, column half (w / 4) & 1, TMEM lane quarter w & 3
+    // (a warp reaches only the 32 lanes of quarter warp_id % 4).  The halves exchange their row max
+    // through shared memory (one named barrier per tile) and their row sum once at the end.
+    const int sub = warp >> 3;
     if (sub < nsub) {
-      const int r = threadIdx.x & 127;
+      const int half = (warp >> 2) & 1;
+      const int r = (warp & 3) * 32 + lane;
       const int R = sub * kTcBM + r;
       const int itok = tok0 + (R >> p.gp_shift);
       const int hd = R & ((1 << p.gp_shift) - 1);
       const bool rv = hd < p.group && itok < Le;
       const int i_min_sub = tok0 + ((sub * kTcBM) >> p.gp_shift);
       const uint32_t lane_off = static_cast<uint32_t>((warp & 3) * 32) << 16;
-      const uint32_t tS = tmem + lane_off + sub * kTcBN;
-      const uint32_t tO = tmem + lane_off + 2 * kTcBN + sub * kTcD;
+      const uint32_t tS = tmem + lane_off + sub * kTcBN + half * 64;        // this thread's S columns
+      const uint32_t tO = tmem + lane_off + 2 * kTcBN + sub * kTcD + half * 64;
       const bool cap = p.logit_cap > 0.f;
       const float c = cap ? kLog2e : p.scale_log2;
       const float cap_pre = cap ? p.sm_scale / p.logit_cap : 0.f;
@@ -242,53 +252,66 @@ __global__ void __launch_bounds__(kTcThreads, 1) extend_tc_kernel(const ExtendPa
                                     : static_cast<const int32_t*>(p.mask_indptr)[b];
         mrow = p.custom_mask + ms + (rv ? itok : 0) * mask_row_len;
       }
+      float* xmine = xch + (sub * 2 + half) * kTcBM + r;
+      float* xother = xch + (sub * 2 + (half ^ 1)) * kTcBM + r;
       float m = -CUDART_INF_F, l = 0.f;
 
       for (int n = 0; n < N; ++n) {
         mbar_wait_wd(bar_s_full + 8 * sub, n & 1);
         tc_fence_after();
         TC_TR(sub * 3, n);
-        float s[kTcBN];
-        tmem_ld32<0>(tS, s);
-        tmem_ld32<32>(tS + 32, s);
-        tmem_ld32<64>(tS + 64, s);
-        tmem_ld32<96>(tS + 96, s);
-        tmem_wait_ld();
-        TC_TR(sub * 3 + 1, n);
-        if (cap) {
-#pragma unroll
-          for (int j = 0; j < kTcBN; ++j) s[j] = p.logit_cap * tanhf(s[j] * cap_pre);
-        }
         const int j0 = n * kTcBN, j_end = j0 + kTcBN;
         const bool need_mask = j_end > Ltot || (p.window > 0 && j0 < Lp) ||
                                (use_mask && (!p.skip_prefix_mask || j_end > Lp)) ||
                                (!use_mask && p.causal && j_end - 1 - Lp > i_min_sub);
-        if (need_mask) {
+        // 32 of this thread's 64 S columns -> registers, logit cap and masks applied.  The row is read
+        // twice (max pass, exp pass): TMEM loads are cheap, 64 live values per thread are not.
+        auto load_chunk = [&](int cc, float (&s)[32]) {
+          tmem_ld32<0>(tS + cc, s);
+          tmem_wait_ld();
+          if (cap) {
 #pragma unroll
-          for (int jj = 0; jj < kTcBN; ++jj) {
-            const int j = j0 + jj;
-            bool vis = rv && j < Ltot;
-            if (j < Lp) {
-              if (p.window > 0) vis = vis && (itok <= j + p.window);
-              if (use_mask && !p.skip_prefix_mask && vis) vis = mrow[j] != 0;
-            } else if (use_mask) {
-              if (vis) vis = mrow[j] != 0;
-            } else if (p.causal) {
-              vis = vis && (j - Lp <= itok);
-            }
-            if (!vis) s[jj] = -CUDART_INF_F;
+            for (int j = 0; j < 32; ++j) s[j] = p.logit_cap * tanhf(s[j] * cap_pre);
           }
-        }
+          if (need_mask) {
+#pragma unroll
+            for (int jj = 0; jj < 32; ++jj) {
+              const int j = j0 + half * 64 + cc + jj;
+              bool vis = rv && j < Ltot;
+              if (j < Lp) {
+                if (p.window > 0) vis = vis && (itok <= j + p.window);
+                if (use_mask && !p.skip_prefix_mask && vis) vis = mrow[j] != 0;
+              } else if (use_mask) {
+                if (vis) vis = mrow[j] != 0;
+              } else if (p.causal) {
+                vis = vis && (j - Lp <= itok);
+              }
+              if (!vis) s[jj] = -CUDART_INF_F;
+            }
+          }
+        };
         float mx0 = -CUDART_INF_F, mx1 = -CUDART_INF_F, mx2 = -CUDART_INF_F, mx3 = -CUDART_INF_F;
 #pragma unroll
-        for (int j = 0; j < kTcBN; j += 4) {
-          mx0 = fmaxf(mx0, s[j]);
-          mx1 = fmaxf(mx1, s[j + 1]);
-          mx2 = fmaxf(mx2, s[j + 2]);
-          mx3 = fmaxf(mx3, s[j + 3]);
+        for (int cc = 0; cc < 64; cc += 32) {
+          float s[32];
+          load_chunk(cc, s);
+#pragma unroll
+          for (int j = 0; j < 32; j += 4) {
+            mx0 = fmaxf(mx0, s[j]);
+            mx1 = fmaxf(mx1, s[j + 1]);
+            mx2 = fmaxf(mx2, s[j + 2]);
+            mx3 = fmaxf(mx3, s[j + 3]);
+          }
         }
-        const float mx = fmaxf(fmaxf(mx0, mx1), fmaxf(mx2, mx3));
-        // lazy rescale: keep the stale max while the new one is within 2^8 of it (p stays <= 256)
+        TC_TR(sub * 3 + 1, n);
+        float mx = fmaxf(fmaxf(mx0, mx1), fmaxf(mx2, mx3));
+        // row max over both halves
+        const int par = (n & 1) * (2 * 2 * kTcBM);
+        xmine[par] = mx;
+        named_bar_sync(1 + sub, 256);
+        mx = fmaxf(mx, xother[par]);
+        // lazy rescale: keep the stale max while the new one is within 2^8 of it (p stays <= 256).
+        // Both threads of a row see the same m and mx, so they take the same decision.
         const bool grow = mx > m && (m == -CUDART_INF_F || (mx - m) * c > kTcRescaleLog2);
         if (__any_sync(0xffffffffu, grow)) {
           float corr = 1.f;
@@ -300,7 +323,7 @@ __global__ void __launch_bounds__(kTcThreads, 1) extend_tc_kernel(const ExtendPa
           if (n > 0) {
             // PV_i(n-1) has completed: its commit precedes the one that signalled s_full(n)
 #pragma unroll
-            for (int cc = 0; cc < kTcD; cc += 32) {
+            for (int cc = 0; cc < 64; cc += 32) {
               float o[32];
               tmem_ld32<0>(tO + cc, o);
               tmem_wait_ld();
@@ -313,16 +336,20 @@ __global__ void __launch_bounds__(kTcThreads, 1) extend_tc_kernel(const ExtendPa
         const float mc = (m == -CUDART_INF_F ? 0.f : m) * c;
         float sum0 = 0.f, sum1 = 0.f;
 #pragma unroll
-        for (int cc = 0; cc < kTcBN; cc += 32) {
+        for (int cc = 0; cc < 64; cc += 32) {
+          float s[32];
+          load_chunk(cc, s);
           uint32_t pk[16];
 #pragma unroll
           for (int j = 0; j < 32; j += 2) {
-            const float p0 = fast_exp2(fmaf(s[cc + j], c, -mc));
-            const float p1 = fast_exp2(fmaf(s[cc + j + 1], c, -mc));
+            const float p0 = fast_exp2(fmaf(s[j], c, -mc));
+            const float p1 = fast_exp2(fmaf(s[j + 1], c, -mc));
             sum0 += p0;
             sum1 += p1;
             pk[j >> 1] = pack2<HALF>(p0, p1);
           }
+          // packed P of these 32 tokens goes into the first 32 columns of this thread's OWN S half
+          // (columns it has already consumed): no thread ever overwrites S data another still needs
           tmem_st16(tS + (cc >> 1), pk);
         }
         l += sum0 + sum1;
@@ -332,14 +359,17 @@ __global__ void __launch_bounds__(kTcThreads, 1) extend_tc_kernel(const ExtendPa
         TC_TR(sub * 3 + 2, n);
       }
 
-      // ---- epilogue: O row / l -> global ----
+      // ---- epilogue: row sum over both halves, then this thread's 64 columns of O / l -> global ----
+      lxch[(sub * 2 + half) * kTcBM + r] = l;
+      named_bar_sync(1 + sub, 256);
+      l += lxch[(sub * 2 + (half ^ 1)) * kTcBM + r];
       mbar_wait_wd(bar_o_full, 0);
       tc_fence_after();
       const float inv = l > 0.f ? p.v_scale / l : 0.f;
       QT* orow = reinterpret_cast<QT*>(p.o) + static_cast<int64_t>(q0 + (rv ? itok : 0)) * p.o_st +
-                 static_cast<int64_t>(h * p.group + (rv ? hd : 0)) * p.o_sh;
+                 static_cast<int64_t>(h * p.group + (rv ? hd : 0)) * p.o_sh + half * 64;
 #pragma unroll
-      for (int cc = 0; cc < kTcD; cc += 32) {
+      for (int cc = 0; cc < 64; cc += 32) {
         float o[32];
         tmem_ld32<0>(tO + cc, o);
         tmem_wait_ld();
@@ -356,17 +386,17 @@ __global__ void __launch_bounds__(kTcThreads, 1) extend_tc_kernel(const ExtendPa
         }
       }
 #ifndef B200ATTN_TC_TRACE
-      if (rv && p.lse)
+      if (rv && half == 0 && p.lse)
         p.lse[static_cast<int64_t>(q0 + itok) * p.hq + h * p.group + hd] =
             l > 0.f ? m * c * kLn2 + logf(l) : -CUDART_INF_F;
 #endif
       tc_fence_before();
     }
-  } else if (warp < 12) {
-    // =============================== loaders ===============================
-    setmaxnreg_dec<56>();
-    const int tid = threadIdx.x - 256;       // 0..127
-    const int chunk = tid & 15, rbase = tid >> 4;  // row = rbase + 8 * i
+  } else {
+  if (warp < kTcMmaWarp) {
+    // =============================== loaders (4 warps) ===============================
+    const int tid = threadIdx.x - kTcLoaderWarp0 * 32;  // 0..127
+    const int chunk = tid & 15, rbase = tid >> 4;       // row = rbase + 8 * i
     const uint32_t sw_col = static_cast<uint32_t>(chunk >> 3) * kTcSlab;
     // ---- Q: rows of both sub-tiles ----
     {
@@ -401,35 +431,14 @@ __global__ void __launch_bounds__(kTcThreads, 1) extend_tc_kernel(const ExtendPa
     }
     const uint8_t* k_head = p.k_pool + static_cast<int64_t>(h) * kTcD * 2 + chunk * 16;
     const uint8_t* v_head = p.v_pool + static_cast<int64_t>(h) * kTcD * 2 + chunk * 16;
-    int32_t slots[16];
-    // Slot ids of tile n.  A tile lies wholly in the prefix list or wholly in the extend tokens except
-    // for the one tile that holds the boundary: the two common cases are branch-free batches of 16
-    // independent loads (clamped index, selected afterwards), so their latencies overlap.
+    // Slot ids of a tile are read once (one per thread, coalesced) into a double-buffered shared
+    // array; a 128-thread named barrier at the tile's K stage publishes them to both loader warps.
     auto fetch = [&](int n) {
-      const int jb = n * kTcBN + rbase;
-      if (n * kTcBN + kTcBN <= Lp) {
-#pragma unroll
-        for (int i = 0; i < 16; ++i) slots[i] = pidx[jb + 8 * i];
-      } else if (n * kTcBN >= Lp) {
-        const int64_t* el = p.extend_loc + (q0 - Lp);
-        const int jmax = Ltot - 1;
-        int64_t v[16];
-#pragma unroll
-        for (int i = 0; i < 16; ++i) {
-          const int j = jb + 8 * i;
-          v[i] = el[j < jmax ? j : jmax];
-        }
-#pragma unroll
-        for (int i = 0; i < 16; ++i) slots[i] = jb + 8 * i <= jmax ? static_cast<int32_t>(v[i]) : -1;
-      } else {
-#pragma unroll
-        for (int i = 0; i < 16; ++i) {
-          const int j = jb + 8 * i;
-          int32_t sl = -1;
-          if (j < Ltot) sl = j < Lp ? pidx[j] : static_cast<int32_t>(p.extend_loc[q0 + j - Lp]);
-          slots[i] = sl;
-        }
-      }
+      int32_t* dst = sid + (n & 1) * kTcBN;
+      const int j = n * kTcBN + tid;
+      int32_t sl = -1;
+      if (j < Ltot) sl = j < Lp ? pidx[j] : static_cast<int32_t>(p.extend_loc[q0 + j - Lp]);
+      dst[tid] = sl;
     };
     fetch(0);
     const int S = 2 * N;
@@ -447,14 +456,17 @@ __global__ void __launch_bounds__(kTcThreads, 1) extend_tc_kernel(const ExtendPa
       mbar_wait_wd(bar_kv_empty + 8 * slot, ph ^ 1u);
       TC_TR(10, st);
       const bool is_v = st & 1;
+      if (!is_v) named_bar_sync(3, 128);  // slot ids of tile st / 2 are visible
+      const int32_t* ids = sid + ((st >> 1) & 1) * kTcBN + rbase;
       const uint8_t* base = is_v ? v_head : k_head;
       const int64_t sb = is_v ? p.v_slot_bytes : p.k_slot_bytes;
       const uint32_t dst0 = kv_base + slot * kTcSlotBytes + sw_col;
 #pragma unroll
       for (int i = 0; i < 16; ++i) {
         const int row = rbase + 8 * i;
-        const bool ok = slots[i] >= 0;
-        cp_async16_zfill(dst0 + row * 128 + (((chunk & 7) ^ (row & 7)) << 4), base + (ok ? slots[i] : 0) * sb, ok);
+        const int32_t sl = ids[8 * i];
+        const bool ok = sl >= 0;
+        cp_async16_zfill(dst0 + row * 128 + (((chunk & 7) ^ (row & 7)) << 4), base + (ok ? sl : 0) * sb, ok);
       }
       cp_async_commit();
       if (is_v && (st >> 1) + 1 < N) fetch((st >> 1) + 1);  // slot ids of the next tile
@@ -463,10 +475,9 @@ __global__ void __launch_bounds__(kTcThreads, 1) extend_tc_kernel(const ExtendPa
     cp_async_wait<0>();
     fence_proxy_async();
     for (int st = (S > kTcLag ? S - kTcLag : 0); st < S; ++st) mbar_arrive(bar_kv_full + 8 * (st % kTcSlots));
-  } else {
-    // =============================== MMA issuer (warp 12) ===============================
-    setmaxnreg_dec<56>();
-    if (warp == 12) {
+  } else if (warp == kTcMmaWarp) {
+    // =============================== MMA issuer (warp 20) ===============================
+    {
 #ifdef B200ATTN_TC_TRACE
       tr = (blockIdx.x == 0 && blockIdx.y == 0 && blockIdx.z == 0 && lane == 0) ? reinterpret_cast<long long*>(p.lse) : nullptr;
 #endif
@@ -490,7 +501,8 @@ __global__ void __launch_bounds__(kTcThreads, 1) extend_tc_kernel(const ExtendPa
         const uint32_t d = tmem + 2 * kTcBN + sub * kTcD, a = tmem + sub * kTcBN;
         umma_ts(d, a, v0, IDESC_PV, acc ? 1u : 0u);
 #pragma unroll
-        for (int k = 1; k < kTcBN / 16; ++k) umma_ts(d, a + k * 8, v0 + k * (2048 >> 4), IDESC_PV, 1u);
+        for (int k = 1; k < kTcBN / 16; ++k)  // P: columns [0, 32) hold tokens 0-63, [64, 96) tokens 64-127
+          umma_ts(d, a + k * 8 + (k >= 4 ? 32 : 0), v0 + k * (2048 >> 4), IDESC_PV, 1u);
       };
       auto full_wait = [&](int st) {
         mbar_wait_wd(bar_kv_full + 8 * (st % kTcSlots), static_cast<uint32_t>(st / kTcSlots) & 1u);
@@ -541,8 +553,9 @@ __global__ void __launch_bounds__(kTcThreads, 1) extend_tc_kernel(const ExtendPa
       tc_fence_before();
     }
   }
+  }
   __syncthreads();
-  if (warp == 12) {
+  if (warp == kTcMmaWarp) {
     tc_fence_after();
     asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, 512;" ::"r"(tmem));
   }

@@ -1,6 +1,6 @@
-timeout 300 python -m pytest tests/test_gpu_extend.py -x -q --timeout 120 2>&1 | tail -2
-B200ATTN_LIB=tools/bin/libb200attn_trace.so timeout 120 python tools/trace_tc.py 2>&1 | grep -E "^n= 3|steady"
-timeout 200 python bench_extend.py --steps 10 2>/dev/null > gpurun_out/bext_last.json
+timeout 120 python -m pytest tests/test_gpu_extend.py -x -q --timeout 40 2>&1 | tail -2
+B200ATTN_LIB=tools/bin/libb200attn_trace.so timeout 60 python tools/trace_tc.py 2>&1 | grep -E "^n= 3[01]|steady|st= 6"
+timeout 90 python bench_extend.py --steps 10 2>/dev/null > gpurun_out/bext_last.json
 python - <<'P'
 import json
 for l in open('gpurun_out/bext_last.json'):

@@ -26,7 +26,7 @@ N = (L + 127) // 128
 t0 = t[0, 0]
 np.set_printoptions(linewidth=200)
 print("tiles", N)
-for n in list(range(0, 6)) + list(range(30, 34)):
+for n in list(range(0, 3)) + list(range(30, 34)):
     if n >= N: break
     r = [int(t[k, n] - t0) if t[k, n] else -1 for k in range(10)]
     print(f"n={n:3d} sm0: s {r[0]:7d} ld {r[1]:7d} p {r[2]:7d} | sm1: s {r[3]:7d} ld {r[4]:7d} p {r[5]:7d} | mma: V {r[6]:7d} p0 {r[7]:7d} K {r[8]:7d} p1 {r[9]:7d}")
