@@ -1,4 +1,4 @@
-"""``B200AttnBackend``: the sm_100a paged decode-attention backend.
+"""``B200AttnBackend``: the sm_100a paged attention backend (decode + extend).
 
 Drop-in for the reference's ``AttentionBackend`` plug-in surface
 (python/sglang/srt/layers/attention/base_attn_backend.py:14-117); host logic
@@ -11,8 +11,10 @@ mirrors ``TritonAttnBackend`` (layers/attention/triton_backend.py:41-732):
   instead of 2-6 ATen launches + 2 Triton launches (:687-732);
 * CUDA-graph hooks               all buffers are allocated once in ``__init__``,
   so capture / replay only re-run the plan (:338-627);
-* ``forward_extend``             delegates to a prefill backend, the way
-  ``HybridAttnBackend`` does (layers/attention/hybrid_attn_backend.py:88-100).
+* ``forward_extend``             ``kv_store`` + ``extend`` (tcgen05 / TMEM kernel for head_dim 128,
+  mma.sync kernel for head_dim 64) over cached prefix + new tokens, for EXTEND / MIXED /
+  TARGET_VERIFY / DRAFT_EXTEND batches (:227-318, :632-685); with ``prefill_backend=`` it
+  delegates instead, the way ``HybridAttnBackend`` does (hybrid_attn_backend.py:88-100).
 
 Registration in sglang is one ``elif`` in
 ``ModelRunner._get_attention_backend_from_str`` (model_runner.py:1374-1460) and
