@@ -396,9 +396,7 @@ class B200AttnBackend(AttentionBackend):
             raise NotImplementedError("B200AttnBackend: cross attention is not supported")
         if layer.qk_head_dim != layer.v_head_dim:
             raise NotImplementedError("B200AttnBackend: qk_head_dim != v_head_dim is not supported")
-        if self.kv_dtype == capi.FP8_E4M3:
-            raise NotImplementedError("B200AttnBackend: extend attention over an fp8 KV pool is not supported yet; "
-                                      "construct the backend with prefill_backend=...")
+        fp8 = self.kv_dtype == capi.FP8_E4M3
         q = q.reshape(-1, layer.tp_q_head_num * layer.qk_head_dim)
         o = torch.empty_like(q)
         pool = forward_batch.token_to_kv_pool
@@ -410,7 +408,8 @@ class B200AttnBackend(AttentionBackend):
             loc = loc.to(torch.int64)
         if save_kv_cache and k is not None:
             store_kv(k_pool, v_pool, loc, k.view(-1, layer.tp_k_head_num, layer.qk_head_dim),
-                     v.view(-1, layer.tp_v_head_num, layer.v_head_dim))
+                     v.view(-1, layer.tp_v_head_num, layer.v_head_dim),
+                     getattr(layer, "k_scale", None), getattr(layer, "v_scale", None))
         md = self.extend_metadata
         tokens = q.shape[0]
         if tokens == 0:
@@ -427,6 +426,8 @@ class B200AttnBackend(AttentionBackend):
                                           "and a plain EXTEND batch")
             kv_indptr = md.window_kv_indptr
         max_len = tokens if md.max_extend_len is None else min(md.max_extend_len, tokens)
+        k_scale = getattr(layer, "k_scale_float", None)
+        v_scale = getattr(layer, "v_scale_float", None)
         torch.ops.b200attn.extend(
             q.view(tokens, layer.tp_q_head_num, layer.qk_head_dim),
             o.view(tokens, layer.tp_q_head_num, layer.v_head_dim),
@@ -435,7 +436,9 @@ class B200AttnBackend(AttentionBackend):
             self.req_to_token if md.kv_indices is None else None, md.req_pool_indices, md.prefix_lens,
             loc, md.custom_mask, md.mask_indptr, int(max_len), causal,
             int(sw) if windowed else -1, True, float(layer.scaling),
-            float(getattr(layer, "logit_cap", 0.0) or 0.0))
+            float(getattr(layer, "logit_cap", 0.0) or 0.0),
+            float(k_scale) if (fp8 and k_scale is not None) else 1.0,
+            float(v_scale) if (fp8 and v_scale is not None) else 1.0)
         return o
 
     def lse_extend(self, tokens: int) -> torch.Tensor:

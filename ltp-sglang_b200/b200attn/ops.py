@@ -243,10 +243,11 @@ def _decode(q, k_pool, v_pool, o, lse, plan_buf, indices, workspace, sm_scale, l
 
 def _extend(q, o, lse, k_pool, v_pool, qo_indptr, kv_indptr, kv_indices, req_to_token, req_pool_indices,
             prefix_lens, extend_loc, custom_mask, mask_indptr, max_extend_len, causal, sliding_window,
-            skip_prefix_custom_mask, sm_scale, logit_cap):
+            skip_prefix_custom_mask, sm_scale, logit_cap, k_scale=1.0, v_scale=1.0):
     """Extend / prefill attention over cached prefix + new tokens (``extend_attention_fwd``,
     triton_ops/extend_attention.py:306-438); the new tokens' K/V are read from the pool at
-    ``extend_loc`` (``out_cache_loc``), where ``kv_store`` has put them."""
+    ``extend_loc`` (``out_cache_loc``), where ``kv_store`` has put them.  An fp8-e4m3 pool is read as
+    ``k_scale * K`` / ``v_scale * V`` (the per-tensor scales ``kv_store`` divided by)."""
     _cuda(q, o, lse, k_pool, v_pool, qo_indptr, kv_indptr, kv_indices, req_to_token, req_pool_indices,
           prefix_lens, extend_loc, custom_mask, mask_indptr)
     if q.dim() != 3 or o.dim() != 3 or k_pool.dim() != 3 or v_pool.dim() != 3:
@@ -305,7 +306,7 @@ def _extend(q, o, lse, k_pool, v_pool, qo_indptr, kv_indptr, kv_indices, req_to_
     a.causal = 1 if causal else 0
     a.sliding_window = sliding_window
     a.skip_prefix_custom_mask = 1 if skip_prefix_custom_mask else 0
-    a.sm_scale, a.logit_cap, a.k_scale, a.v_scale = sm_scale, logit_cap, 1.0, 1.0
+    a.sm_scale, a.logit_cap, a.k_scale, a.v_scale = sm_scale, logit_cap, k_scale, v_scale
     with torch.cuda.device(q.device):
         capi.check("b200attn_extend", capi.lib().b200attn_extend(C.byref(a), _stream(q)))
 
@@ -388,7 +389,8 @@ _LIB.define(
     "extend(Tensor q, Tensor(a!) o, Tensor(b!)? lse, Tensor k_pool, Tensor v_pool, Tensor qo_indptr, "
     "Tensor kv_indptr, Tensor? kv_indices, Tensor? req_to_token, Tensor? req_pool_indices, "
     "Tensor? prefix_lens, Tensor extend_loc, Tensor? custom_mask, Tensor? mask_indptr, int max_extend_len, "
-    "bool causal, int sliding_window, bool skip_prefix_custom_mask, float sm_scale, float logit_cap) -> ()"
+    "bool causal, int sliding_window, bool skip_prefix_custom_mask, float sm_scale, float logit_cap, "
+    "float k_scale=1.0, float v_scale=1.0) -> ()"
 )
 _LIB.define(
     "extend_plan(Tensor? extend_seq_lens, Tensor prefix_lens, Tensor(a!) qo_indptr, Tensor(b!) kv_indptr, "

@@ -8,11 +8,11 @@ using namespace b200attn;
 
 namespace {
 
-template <typename QT>
+template <typename QT, bool FP8>
 cudaError_t launch_extend(const ExtendParams& p, int d, dim3 grid, cudaStream_t stream) {
   void (*fn)(const ExtendParams) = nullptr;
-  if (d == 64) fn = extend_kernel<QT, 64>;
-  else if (d == 128) fn = extend_kernel<QT, 128>;
+  if (d == 64) fn = extend_kernel<QT, 64, FP8>;
+  else if (d == 128) fn = extend_kernel<QT, 128, FP8>;
   if (!fn) return cudaErrorInvalidValue;
   const int smem = extend_smem_bytes(d);
   cudaError_t e = cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
@@ -21,9 +21,9 @@ cudaError_t launch_extend(const ExtendParams& p, int d, dim3 grid, cudaStream_t 
   return cudaGetLastError();
 }
 
-template <typename QT>
+template <typename QT, bool FP8>
 cudaError_t launch_extend_tc(const ExtendParams& p, dim3 grid, cudaStream_t stream) {
-  void (*fn)(const ExtendParams) = extend_tc_kernel<QT>;
+  void (*fn)(const ExtendParams) = extend_tc_kernel<QT, FP8>;
   cudaError_t e = cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, kTcSmemBytes);
   if (e != cudaSuccess) return e;
   fn<<<grid, kTcThreads, kTcSmemBytes, stream>>>(p);
@@ -129,7 +129,11 @@ extern "C" __attribute__((visibility("default"))) int b200attn_extend(const b200
       (a->mask_indptr_dtype != B200ATTN_I32 && a->mask_indptr_dtype != B200ATTN_I64))
     return B200ATTN_E_INVALID;
   if (a->q_dtype != B200ATTN_BF16 && a->q_dtype != B200ATTN_F16) return B200ATTN_E_UNSUPPORTED;
-  if (a->kv_dtype != a->q_dtype) return B200ATTN_E_UNSUPPORTED;  // fp8 pools: decode only, for now
+  const bool fp8 = a->kv_dtype == B200ATTN_FP8_E4M3;
+  if (!fp8 && a->kv_dtype != a->q_dtype) return B200ATTN_E_UNSUPPORTED;
+  const int esz = fp8 ? 1 : 2;
+  const float k_scale = fp8 ? a->k_scale : 1.f, v_scale = fp8 ? a->v_scale : 1.f;
+  if (fp8 && (!(k_scale > 0.f) || !(v_scale > 0.f))) return B200ATTN_E_INVALID;
   if (a->v_head_dim != a->head_dim) return B200ATTN_E_UNSUPPORTED;
   if (a->head_dim != 64 && a->head_dim != 128) return B200ATTN_E_UNSUPPORTED;
   if (a->num_q_heads <= 0 || a->num_kv_heads <= 0 || a->num_q_heads % a->num_kv_heads != 0)
@@ -139,7 +143,7 @@ extern "C" __attribute__((visibility("default"))) int b200attn_extend(const b200
   if (a->num_kv_heads > 65535 || a->batch > 65535) return B200ATTN_E_UNSUPPORTED;
   if (!(a->sm_scale > 0.f) || a->logit_cap < 0.f) return B200ATTN_E_INVALID;
   if ((reinterpret_cast<uintptr_t>(a->k_pool) | reinterpret_cast<uintptr_t>(a->v_pool)) & 15) return B200ATTN_E_ALIGN;
-  if ((a->k_pool_stride_slot * 2) % 16 != 0 || (a->v_pool_stride_slot * 2) % 16 != 0) return B200ATTN_E_ALIGN;
+  if ((a->k_pool_stride_slot * esz) % 16 != 0 || (a->v_pool_stride_slot * esz) % 16 != 0) return B200ATTN_E_ALIGN;
   if ((reinterpret_cast<uintptr_t>(a->q) & 3) || a->q_stride_token % 2 != 0 || a->q_stride_head % 2 != 0)
     return B200ATTN_E_ALIGN;
   if ((reinterpret_cast<uintptr_t>(a->o) & 3) || a->o_stride_token % 2 != 0 || a->o_stride_head % 2 != 0)
@@ -155,8 +159,8 @@ extern "C" __attribute__((visibility("default"))) int b200attn_extend(const b200
   p.lse = a->lse;
   p.k_pool = static_cast<const uint8_t*>(a->k_pool);
   p.v_pool = static_cast<const uint8_t*>(a->v_pool);
-  p.k_slot_bytes = a->k_pool_stride_slot * 2;
-  p.v_slot_bytes = a->v_pool_stride_slot * 2;
+  p.k_slot_bytes = a->k_pool_stride_slot * esz;
+  p.v_slot_bytes = a->v_pool_stride_slot * esz;
   p.qo_indptr = a->qo_indptr;
   p.kv_indptr = a->kv_indptr;
   p.kv_indices = a->kv_indices;
@@ -176,10 +180,10 @@ extern "C" __attribute__((visibility("default"))) int b200attn_extend(const b200
   p.causal = a->causal != 0;
   p.window = a->sliding_window > 0 ? a->sliding_window : 0;
   p.skip_prefix_mask = a->skip_prefix_custom_mask != 0;
-  p.sm_scale = a->sm_scale;
-  p.scale_log2 = a->sm_scale * kLog2e;
+  p.sm_scale = a->sm_scale * k_scale;  // fp8: K is read unscaled, k_scale rides in the softmax scale
+  p.scale_log2 = p.sm_scale * kLog2e;
   p.logit_cap = a->logit_cap;
-  p.v_scale = 1.f;
+  p.v_scale = v_scale;
 
   cudaStream_t stream = static_cast<cudaStream_t>(stream_);
   // head_dim 128 with 16-byte aligned q / o rows runs on tcgen05 (extend_tc_kernel.cuh); head_dim 64 and
@@ -192,13 +196,21 @@ extern "C" __attribute__((visibility("default"))) int b200attn_extend(const b200
   if (tc_ok) {
     const int tok = (2 * kTcBM) >> p.gp_shift;
     dim3 grid((a->max_extend_len + tok - 1) / tok, a->num_kv_heads, a->batch);
-    err = a->q_dtype == B200ATTN_F16 ? launch_extend_tc<__half>(p, grid, stream)
-                                     : launch_extend_tc<__nv_bfloat16>(p, grid, stream);
+    if (fp8)
+      err = a->q_dtype == B200ATTN_F16 ? launch_extend_tc<__half, true>(p, grid, stream)
+                                       : launch_extend_tc<__nv_bfloat16, true>(p, grid, stream);
+    else
+      err = a->q_dtype == B200ATTN_F16 ? launch_extend_tc<__half, false>(p, grid, stream)
+                                       : launch_extend_tc<__nv_bfloat16, false>(p, grid, stream);
   } else {
     const int bm_tok = kExtRows >> p.gp_shift;
     dim3 grid((a->max_extend_len + bm_tok - 1) / bm_tok, a->num_kv_heads, a->batch);
-    err = a->q_dtype == B200ATTN_F16 ? launch_extend<__half>(p, a->head_dim, grid, stream)
-                                     : launch_extend<__nv_bfloat16>(p, a->head_dim, grid, stream);
+    if (fp8)
+      err = a->q_dtype == B200ATTN_F16 ? launch_extend<__half, true>(p, a->head_dim, grid, stream)
+                                       : launch_extend<__nv_bfloat16, true>(p, a->head_dim, grid, stream);
+    else
+      err = a->q_dtype == B200ATTN_F16 ? launch_extend<__half, false>(p, a->head_dim, grid, stream)
+                                       : launch_extend<__nv_bfloat16, false>(p, a->head_dim, grid, stream);
   }
   if (err != cudaSuccess) return B200ATTN_E_CUDA;
   count_launch();

@@ -59,13 +59,54 @@ __host__ __device__ inline int extend_smem_bytes(int d) {
   return kExtStages * 2 * kExtBN * (d * 2 + kRowPad);
 }
 
-template <typename QT, int D>
+// 16 e4m3 bytes -> 16 f16 values (exact), in element order.
+__device__ __forceinline__ void e4m3x16_to_f16(const uint4& r, uint4& lo, uint4& hi) {
+  lo.x = e4m3x2_to_f16x2(r.x);
+  lo.y = e4m3x2_to_f16x2(r.x >> 16);
+  lo.z = e4m3x2_to_f16x2(r.y);
+  lo.w = e4m3x2_to_f16x2(r.y >> 16);
+  hi.x = e4m3x2_to_f16x2(r.z);
+  hi.y = e4m3x2_to_f16x2(r.z >> 16);
+  hi.z = e4m3x2_to_f16x2(r.w);
+  hi.w = e4m3x2_to_f16x2(r.w >> 16);
+}
+
+// Two q elements -> the MMA operand type: unchanged, or (fp8 pool with bf16 q) f16 clamped to its range,
+// the same conversion the decode kernel applies to q.
+template <typename QT, bool TO_HALF>
+__device__ __forceinline__ uint32_t q_pair(uint32_t x) {
+  if constexpr (TO_HALF && !std::is_same<QT, __half>::value) {
+    const float lo = fminf(fmaxf(__uint_as_float(x << 16), -65504.f), 65504.f);
+    const float hi = fminf(fmaxf(__uint_as_float(x & 0xffff0000u), -65504.f), 65504.f);
+    return pack2<true>(lo, hi);
+  } else {
+    return x;
+  }
+}
+
+__device__ __forceinline__ uint4 lds128(uint32_t addr) {
+  uint4 v;
+  asm volatile("ld.shared.v4.b32 {%0,%1,%2,%3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "r"(addr));
+  return v;
+}
+__device__ __forceinline__ void sts128(uint32_t addr, const uint4& v) {
+  asm volatile("st.shared.v4.b32 [%0], {%1,%2,%3,%4};" ::"r"(addr), "r"(v.x), "r"(v.y), "r"(v.z), "r"(v.w) : "memory");
+}
+
+// FP8: the pool holds float8_e4m3fn bytes.  Rows travel as stored (1 B / element) into the upper half
+// of their shared-memory row and are widened in place to f16 (exact) once landed; both MMAs then run in
+// f16 (q converted and clamped like the decode kernel does), k_scale rides in the softmax scale and
+// v_scale in the final normalisation (FlashInfer's semantics, flashinfer_backend.py:560-567).
+template <typename QT, int D, bool FP8>
 __global__ void __launch_bounds__(kExtThreads, 1) extend_kernel(const ExtendParams p) {
-  constexpr bool HALF = std::is_same<QT, __half>::value;
+  constexpr bool OUT_HALF = std::is_same<QT, __half>::value;
+  constexpr bool HALF = OUT_HALF || FP8;     // MMA operand type
+  constexpr int ESZ = FP8 ? 1 : 2;           // pool element bytes
   constexpr int KSTEPS = D / 16;
   constexpr int NTILES = D / 8;
   constexpr int RS = D * 2 + kRowPad;        // smem row stride, bytes
-  constexpr int CH = D * 2 / 16;             // 16-byte chunks per row
+  constexpr int CH = D * ESZ / 16;           // 16-byte chunks per pool row
+  constexpr int RAW_OFF = FP8 ? D : 0;       // fp8 bytes land in the upper half of the row
   constexpr int RPP = kExtThreads / CH;      // rows per loader pass
   constexpr int PASSES = kExtBN / RPP;
   constexpr int TENSOR_BYTES = kExtBN * RS;
@@ -111,8 +152,8 @@ __global__ void __launch_bounds__(kExtThreads, 1) extend_kernel(const ExtendPara
 
   // ------------------------------ loader ------------------------------
   const int ld_row = threadIdx.x / CH, ld_chunk = threadIdx.x % CH;
-  const uint8_t* k_head = p.k_pool + static_cast<int64_t>(h) * D * 2 + ld_chunk * 16;
-  const uint8_t* v_head = p.v_pool + static_cast<int64_t>(h) * D * 2 + ld_chunk * 16;
+  const uint8_t* k_head = p.k_pool + static_cast<int64_t>(h) * D * ESZ + ld_chunk * 16;
+  const uint8_t* v_head = p.v_pool + static_cast<int64_t>(h) * D * ESZ + ld_chunk * 16;
   int32_t nslot[PASSES];
   auto fetch_slots = [&](int tile) {
 #pragma unroll
@@ -124,7 +165,7 @@ __global__ void __launch_bounds__(kExtThreads, 1) extend_kernel(const ExtendPara
     }
   };
   auto issue = [&](int stage) {
-    const uint32_t dst = stage0 + stage * STAGE_BYTES + ld_row * RS + ld_chunk * 16;
+    const uint32_t dst = stage0 + stage * STAGE_BYTES + ld_row * RS + RAW_OFF + ld_chunk * 16;
 #pragma unroll
     for (int i = 0; i < PASSES; ++i) {
       const bool ok = nslot[i] >= 0;
@@ -165,10 +206,10 @@ __global__ void __launch_bounds__(kExtThreads, 1) extend_kernel(const ExtendPara
 #pragma unroll
     for (int kk = 0; kk < KSTEPS; ++kk) {
       const int d0 = kk * 16 + 2 * jq;
-      qf[kk][0] = row0 ? *reinterpret_cast<const uint32_t*>(qr0 + d0) : 0u;
-      qf[kk][1] = row0 ? *reinterpret_cast<const uint32_t*>(qr0 + d0 + 8) : 0u;
-      qf[kk][2] = row1 ? *reinterpret_cast<const uint32_t*>(qr1 + d0) : 0u;
-      qf[kk][3] = row1 ? *reinterpret_cast<const uint32_t*>(qr1 + d0 + 8) : 0u;
+      qf[kk][0] = row0 ? q_pair<QT, FP8>(*reinterpret_cast<const uint32_t*>(qr0 + d0)) : 0u;
+      qf[kk][1] = row0 ? q_pair<QT, FP8>(*reinterpret_cast<const uint32_t*>(qr0 + d0 + 8)) : 0u;
+      qf[kk][2] = row1 ? q_pair<QT, FP8>(*reinterpret_cast<const uint32_t*>(qr1 + d0)) : 0u;
+      qf[kk][3] = row1 ? q_pair<QT, FP8>(*reinterpret_cast<const uint32_t*>(qr1 + d0 + 8)) : 0u;
     }
   }
 
@@ -182,6 +223,18 @@ __global__ void __launch_bounds__(kExtThreads, 1) extend_kernel(const ExtendPara
 
   for (int n = 0; n < ntiles; ++n) {
     cp_async_wait<1>();
+    int stage = n - (n / kExtStages) * kExtStages;
+    const uint32_t sbase = stage0 + stage * STAGE_BYTES;
+    uint4 raw[FP8 ? PASSES : 1][2];
+    if constexpr (FP8) {
+      // this thread's own raw bytes of tile n have landed: lift them out before anyone widens over them
+      const uint32_t src = sbase + ld_row * RS + RAW_OFF + ld_chunk * 16;
+#pragma unroll
+      for (int i = 0; i < PASSES; ++i) {
+        raw[i][0] = lds128(src + i * RPP * RS);
+        raw[i][1] = lds128(src + i * RPP * RS + TENSOR_BYTES);
+      }
+    }
     __syncthreads();  // tile n has landed for every thread; everyone is done with tile n - 1
     if (n + 2 < ntiles) {
       int st = n + 2;
@@ -190,9 +243,20 @@ __global__ void __launch_bounds__(kExtThreads, 1) extend_kernel(const ExtendPara
     }
     cp_async_commit();
     fetch_slots(n + 3);
-
-    int stage = n - (n / kExtStages) * kExtStages;
-    const uint32_t sbase = stage0 + stage * STAGE_BYTES;
+    if constexpr (FP8) {
+      const uint32_t dst = sbase + ld_row * RS + ld_chunk * 32;
+#pragma unroll
+      for (int i = 0; i < PASSES; ++i) {
+#pragma unroll
+        for (int kv = 0; kv < 2; ++kv) {
+          uint4 lo, hi;
+          e4m3x16_to_f16(raw[i][kv], lo, hi);
+          sts128(dst + i * RPP * RS + kv * TENSOR_BYTES, lo);
+          sts128(dst + i * RPP * RS + kv * TENSOR_BYTES + 16, hi);
+        }
+      }
+      __syncthreads();  // widened tile visible to every warp
+    }
 
     // ---- S = Q.K^T (16 rows x 64 tokens) ----
     float s[NT][4];
@@ -316,7 +380,7 @@ __global__ void __launch_bounds__(kExtThreads, 1) extend_kernel(const ExtendPara
                static_cast<int64_t>(h * p.group + hd0) * p.o_sh;
 #pragma unroll
     for (int nn = 0; nn < NTILES; ++nn)
-      *reinterpret_cast<uint32_t*>(orow + nn * 8 + 2 * jq) = pack2<HALF>(o[nn][0] * inv0, o[nn][1] * inv0);
+      *reinterpret_cast<uint32_t*>(orow + nn * 8 + 2 * jq) = pack2<OUT_HALF>(o[nn][0] * inv0, o[nn][1] * inv0);
     if (p.lse && jq == 0)
       p.lse[static_cast<int64_t>(q0 + i0) * p.hq + h * p.group + hd0] =
           l0 > 0.f ? m0 * c * kLn2 + logf(l0) : -CUDART_INF_F;
@@ -326,7 +390,7 @@ __global__ void __launch_bounds__(kExtThreads, 1) extend_kernel(const ExtendPara
                static_cast<int64_t>(h * p.group + hd1) * p.o_sh;
 #pragma unroll
     for (int nn = 0; nn < NTILES; ++nn)
-      *reinterpret_cast<uint32_t*>(orow + nn * 8 + 2 * jq) = pack2<HALF>(o[nn][2] * inv1, o[nn][3] * inv1);
+      *reinterpret_cast<uint32_t*>(orow + nn * 8 + 2 * jq) = pack2<OUT_HALF>(o[nn][2] * inv1, o[nn][3] * inv1);
     if (p.lse && jq == 0)
       p.lse[static_cast<int64_t>(q0 + i1) * p.hq + h * p.group + hd1] =
           l1 > 0.f ? m1 * c * kLn2 + logf(l1) : -CUDART_INF_F;

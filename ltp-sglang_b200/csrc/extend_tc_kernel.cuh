@@ -42,8 +42,11 @@ constexpr int kTcSlots = 4;           // K / V ring slots
 constexpr int kTcSlab = kTcBN * 128;  // bytes of one 64-element-wide slab of 128 rows
 constexpr int kTcSlotBytes = 2 * kTcSlab;
 constexpr int kTcQBytes = 2 * kTcSlotBytes;  // two sub-tiles
-constexpr int kTcLag = 2;             // cp.async groups a loader thread keeps in flight
-constexpr int kTcBarBytes = 8192;    // mbarriers, TMEM base, row max / row sum exchange
+#ifndef B200ATTN_TC_LAG
+#define B200ATTN_TC_LAG 2
+#endif
+constexpr int kTcLag = B200ATTN_TC_LAG;  // cp.async groups a loader thread keeps in flight (< kTcSlots)
+constexpr int kTcBarBytes = 9216;    // mbarriers, TMEM base, row max / row sum exchange, 4 slot-id buffers
 constexpr int kTcSmemBytes = kTcQBytes + kTcSlots * kTcSlotBytes + kTcBarBytes + 1024;  // + alignment slack
 constexpr float kTcRescaleLog2 = 8.f;  // lazy rescale threshold (log2 units)
 
@@ -120,6 +123,14 @@ __device__ __forceinline__ void tmem_st32(uint32_t taddr, const float (&r)[LEN])
       "r"(u[29]), "r"(u[30]), "r"(u[31]), "r"(taddr)
       : "memory");
 }
+__device__ __forceinline__ void tmem_ld16(uint32_t taddr, float (&r)[16]) {
+  uint32_t* u = reinterpret_cast<uint32_t*>(&r[0]);
+  asm volatile(
+      "tcgen05.ld.sync.aligned.32x32b.x16.b32 {%0,%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15}, [%16];"
+      : "=r"(u[0]), "=r"(u[1]), "=r"(u[2]), "=r"(u[3]), "=r"(u[4]), "=r"(u[5]), "=r"(u[6]), "=r"(u[7]), "=r"(u[8]),
+        "=r"(u[9]), "=r"(u[10]), "=r"(u[11]), "=r"(u[12]), "=r"(u[13]), "=r"(u[14]), "=r"(u[15])
+      : "r"(taddr));
+}
 __device__ __forceinline__ void tmem_st16(uint32_t taddr, const uint32_t (&u)[16]) {
   asm volatile(
       "tcgen05.st.sync.aligned.32x32b.x16.b32 [%16], {%0,%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15};" ::"r"(
@@ -154,9 +165,14 @@ __device__ __forceinline__ void setmaxnreg_dec() {
 #define TC_TR(kind, n) do { } while (0)
 #endif
 
-template <typename QT>
+// FP8: the pool holds float8_e4m3fn bytes.  The loaders cp.async the raw rows (128 B per token and head)
+// into the upper slab of the ring slot and, once landed, widen them in place to f16 (exact) in the swizzled
+// layout; both MMAs then run in f16 with q converted (and clamped) once, k_scale folded into the softmax
+// scale and v_scale into the final normalisation -- the decode kernel's fp8 semantics.
+template <typename QT, bool FP8>
 __global__ void __launch_bounds__(kTcThreads, 1) extend_tc_kernel(const ExtendParams p) {
-  constexpr bool HALF = std::is_same<QT, __half>::value;
+  constexpr bool OUT_HALF = std::is_same<QT, __half>::value;
+  constexpr bool HALF = OUT_HALF || FP8;  // MMA operand type
   constexpr uint32_t IDESC_QK = umma_idesc(kTcBM, kTcBN, HALF ? 0 : 1, 0);
   constexpr uint32_t IDESC_PV = umma_idesc(kTcBM, kTcD, HALF ? 0 : 1, 1);
 
@@ -175,7 +191,7 @@ __global__ void __launch_bounds__(kTcThreads, 1) extend_tc_kernel(const ExtendPa
   // row max [parity][sub][half][row] and row sum [sub][half][row] exchanged between the two threads of a row
   float* xch = reinterpret_cast<float*>(smem_raw + (bars + 1024 - smem_u32(smem_raw)));
   float* lxch = xch + 2 * 2 * 2 * kTcBM;
-  int32_t* sid = reinterpret_cast<int32_t*>(lxch + 2 * 2 * kTcBM);  // [2][kTcBN] slot ids of a tile
+  int32_t* sid = reinterpret_cast<int32_t*>(lxch + 2 * 2 * kTcBM);  // [4][kTcBN] slot ids of tile n at n & 3
   volatile uint32_t* tmem_slot_ptr = reinterpret_cast<volatile uint32_t*>(smem_raw + (tmem_slot - smem_u32(smem_raw)));
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -202,6 +218,12 @@ __global__ void __launch_bounds__(kTcThreads, 1) extend_tc_kernel(const ExtendPa
   const int N = (Ltot + kTcBN - 1) / kTcBN;
   const int rows_valid = (tile_tok_end - tok0) << p.gp_shift;
   const int nsub = rows_valid > kTcBM ? 2 : 1;
+  // Small-q mode ("KV ping-pong"): a tile of at most 128 rows (decode-like batches, TARGET_VERIFY) would
+  // leave sub-tile 1 idle and serialise S -> softmax -> PV on one accumulator.  Instead both sub-tiles
+  // take the SAME 128 q rows and alternate over the KV tiles (sub-tile v owns tiles n = v mod 2), each
+  // with its own running max / sum / O; the two partial states are merged in the epilogue (an in-CTA
+  // 2-way split-KV).  K / V stages are then consumed in the order K0 K1 V0 K2 V1 K3 ...
+  const bool alt = nsub == 1 && N >= 2;
 
   if (threadIdx.x == 0) {
     for (int s = 0; s < kTcSlots; ++s) {
@@ -231,14 +253,15 @@ __global__ void __launch_bounds__(kTcThreads, 1) extend_tc_kernel(const ExtendPa
     // (a warp reaches only the 32 lanes of quarter warp_id % 4).  The halves exchange their row max
     // through shared memory (one named barrier per tile) and their row sum once at the end.
     const int sub = warp >> 3;
-    if (sub < nsub) {
+    if (sub < nsub || alt) {
       const int half = (warp >> 2) & 1;
       const int r = (warp & 3) * 32 + lane;
-      const int R = sub * kTcBM + r;
+      const int R = alt ? r : sub * kTcBM + r;
       const int itok = tok0 + (R >> p.gp_shift);
       const int hd = R & ((1 << p.gp_shift) - 1);
       const bool rv = hd < p.group && itok < Le;
-      const int i_min_sub = tok0 + ((sub * kTcBM) >> p.gp_shift);
+      const int i_min_sub = alt ? tok0 : tok0 + ((sub * kTcBM) >> p.gp_shift);
+      const int dn = alt ? 2 : 1;
       const uint32_t lane_off = static_cast<uint32_t>((warp & 3) * 32) << 16;
       const uint32_t tS = tmem + lane_off + sub * kTcBN + half * 64;        // this thread's S columns
       const uint32_t tO = tmem + lane_off + 2 * kTcBN + sub * kTcD + half * 64;
@@ -256,8 +279,9 @@ __global__ void __launch_bounds__(kTcThreads, 1) extend_tc_kernel(const ExtendPa
       float* xother = xch + (sub * 2 + (half ^ 1)) * kTcBM + r;
       float m = -CUDART_INF_F, l = 0.f;
 
-      for (int n = 0; n < N; ++n) {
-        mbar_wait_wd(bar_s_full + 8 * sub, n & 1);
+      int it = 0;  // tiles this sub-tile has processed
+      for (int n = alt ? sub : 0; n < N; n += dn, ++it) {
+        mbar_wait_wd(bar_s_full + 8 * sub, it & 1);
         tc_fence_after();
         TC_TR(sub * 3, n);
         const int j0 = n * kTcBN, j_end = j0 + kTcBN;
@@ -306,7 +330,7 @@ __global__ void __launch_bounds__(kTcThreads, 1) extend_tc_kernel(const ExtendPa
         TC_TR(sub * 3 + 1, n);
         float mx = fmaxf(fmaxf(mx0, mx1), fmaxf(mx2, mx3));
         // row max over both halves
-        const int par = (n & 1) * (2 * 2 * kTcBM);
+        const int par = (it & 1) * (2 * 2 * kTcBM);
         xmine[par] = mx;
         named_bar_sync(1 + sub, 256);
         mx = fmaxf(mx, xother[par]);
@@ -320,8 +344,8 @@ __global__ void __launch_bounds__(kTcThreads, 1) extend_tc_kernel(const ExtendPa
             m = mx;
             l *= corr;
           }
-          if (n > 0) {
-            // PV_i(n-1) has completed: its commit precedes the one that signalled s_full(n)
+          if (it > 0) {
+            // this sub-tile's previous PV has completed: its commit precedes the one that signalled s_full
 #pragma unroll
             for (int cc = 0; cc < 64; cc += 32) {
               float o[32];
@@ -363,6 +387,25 @@ __global__ void __launch_bounds__(kTcThreads, 1) extend_tc_kernel(const ExtendPa
       lxch[(sub * 2 + half) * kTcBM + r] = l;
       named_bar_sync(1 + sub, 256);
       l += lxch[(sub * 2 + (half ^ 1)) * kTcBM + r];
+      // small-q mode: sub-tile 1 hands its state (max in log2 units, sum) to sub-tile 0, which merges
+      float a0 = 1.f, a1 = 0.f, mlog2 = (m == -CUDART_INF_F ? 0.f : m) * c;
+      if (alt) {
+        if (sub == 1 && half == 0) {
+          xch[2 * kTcBM + r] = m == -CUDART_INF_F ? -CUDART_INF_F : m * c;
+          xch[3 * kTcBM + r] = l;
+        }
+        named_bar_sync(5, 512);
+        if (sub == 0) {
+          const float m0c = m == -CUDART_INF_F ? -CUDART_INF_F : m * c;
+          const float m1c = xch[2 * kTcBM + r], l1 = xch[3 * kTcBM + r];
+          const float mm = fmaxf(m0c, m1c);
+          a0 = (l > 0.f) ? fast_exp2(m0c - mm) : 0.f;
+          a1 = (l1 > 0.f) ? fast_exp2(m1c - mm) : 0.f;
+          l = a0 * l + a1 * l1;
+          mlog2 = mm == -CUDART_INF_F ? 0.f : mm;
+        }
+      }
+      if (!alt || sub == 0) {
       mbar_wait_wd(bar_o_full, 0);
       tc_fence_after();
       const float inv = l > 0.f ? p.v_scale / l : 0.f;
@@ -373,14 +416,27 @@ __global__ void __launch_bounds__(kTcThreads, 1) extend_tc_kernel(const ExtendPa
         float o[32];
         tmem_ld32<0>(tO + cc, o);
         tmem_wait_ld();
+        if (alt) {
+          // O = a0 O0 + a1 O1 in two 16-column passes (register budget); a factor of 0 drops its term
+#pragma unroll
+          for (int j = 0; j < 32; ++j) o[j] = a0 > 0.f ? o[j] * a0 : 0.f;
+#pragma unroll
+          for (int c16 = 0; c16 < 32; c16 += 16) {  // tcgen05.ld is warp-collective: no per-row branch around it
+            float o1[16];
+            tmem_ld16(tO + kTcD + cc + c16, o1);
+            tmem_wait_ld();
+#pragma unroll
+            for (int j = 0; j < 16; ++j) o[c16 + j] = a1 > 0.f ? fmaf(o1[j], a1, o[c16 + j]) : o[c16 + j];
+          }
+        }
         if (rv) {
 #pragma unroll
           for (int j = 0; j < 32; j += 8) {
             uint4 v;
-            v.x = pack2<HALF>(o[j] * inv, o[j + 1] * inv);
-            v.y = pack2<HALF>(o[j + 2] * inv, o[j + 3] * inv);
-            v.z = pack2<HALF>(o[j + 4] * inv, o[j + 5] * inv);
-            v.w = pack2<HALF>(o[j + 6] * inv, o[j + 7] * inv);
+            v.x = pack2<OUT_HALF>(o[j] * inv, o[j + 1] * inv);
+            v.y = pack2<OUT_HALF>(o[j + 2] * inv, o[j + 3] * inv);
+            v.z = pack2<OUT_HALF>(o[j + 4] * inv, o[j + 5] * inv);
+            v.w = pack2<OUT_HALF>(o[j + 6] * inv, o[j + 7] * inv);
             *reinterpret_cast<uint4*>(orow + cc + j) = v;
           }
         }
@@ -388,8 +444,9 @@ __global__ void __launch_bounds__(kTcThreads, 1) extend_tc_kernel(const ExtendPa
 #ifndef B200ATTN_TC_TRACE
       if (rv && half == 0 && p.lse)
         p.lse[static_cast<int64_t>(q0 + itok) * p.hq + h * p.group + hd] =
-            l > 0.f ? m * c * kLn2 + logf(l) : -CUDART_INF_F;
+            l > 0.f ? mlog2 * kLn2 + logf(l) : -CUDART_INF_F;
 #endif
+      }
       tc_fence_before();
     }
   } else {
@@ -411,7 +468,17 @@ __global__ void __launch_bounds__(kTcThreads, 1) extend_tc_kernel(const ExtendPa
                                                                : 0) + chunk * 8;
         const int rr = R & (kTcBM - 1);
         const uint32_t dst = q_base + (R >> 7) * kTcSlotBytes + sw_col + rr * 128 + (((chunk & 7) ^ (rr & 7)) << 4);
-        cp_async16_zfill(dst, src, ok);
+        if constexpr (FP8 && !OUT_HALF) {  // bf16 q -> f16, clamped to the f16 range
+          uint4 v = make_uint4(0u, 0u, 0u, 0u);
+          if (ok) v = *reinterpret_cast<const uint4*>(src);
+          v.x = q_pair<QT, true>(v.x);
+          v.y = q_pair<QT, true>(v.y);
+          v.z = q_pair<QT, true>(v.z);
+          v.w = q_pair<QT, true>(v.w);
+          sts128(dst, v);
+        } else {
+          cp_async16_zfill(dst, src, ok);
+        }
       }
       cp_async_commit();
       cp_async_wait<0>();
@@ -429,52 +496,99 @@ __global__ void __launch_bounds__(kTcThreads, 1) extend_tc_kernel(const ExtendPa
                                  : static_cast<const int32_t*>(p.prefix_lens)[b];
       pidx = p.req_to_token + req * p.r2t_stride + (pl - Lp);
     }
-    const uint8_t* k_head = p.k_pool + static_cast<int64_t>(h) * kTcD * 2 + chunk * 16;
-    const uint8_t* v_head = p.v_pool + static_cast<int64_t>(h) * kTcD * 2 + chunk * 16;
+    // fp8: a row is 8 x 16 bytes, thread (rb8, chunk8) moves rows rb8 + 16 i
+    const int chunk8 = tid & 7, rb8 = tid >> 3;
+    const uint8_t* k_head = p.k_pool + static_cast<int64_t>(h) * kTcD * (FP8 ? 1 : 2) + (FP8 ? chunk8 : chunk) * 16;
+    const uint8_t* v_head = p.v_pool + static_cast<int64_t>(h) * kTcD * (FP8 ? 1 : 2) + (FP8 ? chunk8 : chunk) * 16;
+    // stage st is complete for this thread: (fp8: widen it in place) and hand it to the MMA warp
+    auto publish = [&](int st) {
+      if constexpr (FP8) {
+        const uint32_t slot0 = kv_base + (st % kTcSlots) * kTcSlotBytes;
+        uint4 raw[8];
+#pragma unroll
+        for (int i = 0; i < 8; ++i) raw[i] = lds128(slot0 + kTcSlab + (rb8 + 16 * i) * 128 + chunk8 * 16);
+        named_bar_sync(4, 128);  // every loader thread holds its raw bytes: the slot may be overwritten
+        const uint32_t dslab = slot0 + static_cast<uint32_t>(chunk8 >> 2) * kTcSlab;
+#pragma unroll
+        for (int i = 0; i < 8; ++i) {
+          const int row = rb8 + 16 * i;
+          uint4 lo, hi;
+          e4m3x16_to_f16(raw[i], lo, hi);
+          const uint32_t rowa = dslab + row * 128;
+          sts128(rowa + ((((2 * chunk8) & 7) ^ (row & 7)) << 4), lo);
+          sts128(rowa + ((((2 * chunk8 + 1) & 7) ^ (row & 7)) << 4), hi);
+        }
+      }
+      fence_proxy_async();
+      mbar_arrive(bar_kv_full + 8 * (st % kTcSlots));
+    };
     // Slot ids of a tile are read once (one per thread, coalesced) into a double-buffered shared
     // array; a 128-thread named barrier at the tile's K stage publishes them to both loader warps.
-    auto fetch = [&](int n) {
-      int32_t* dst = sid + (n & 1) * kTcBN;
+    // Slot ids run ahead of the copies: tiles n + 1 and n + 2 sit in shared memory, tile n + 3 is in flight
+    // in a register (`pending`), so the index load's latency never joins the K / V copy's on the critical path.
+    auto load_id = [&](int n) {
       const int j = n * kTcBN + tid;
       int32_t sl = -1;
       if (j < Ltot) sl = j < Lp ? pidx[j] : static_cast<int32_t>(p.extend_loc[q0 + j - Lp]);
-      dst[tid] = sl;
+      return sl;
     };
-    fetch(0);
+    sid[tid] = load_id(0);
+    sid[kTcBN + tid] = load_id(1);
+    int32_t pending = load_id(2);
     const int S = 2 * N;
     for (int st = 0; st < S; ++st) {
       // publish stage st - kTcLag first: its copies have landed once at most kTcLag - 1 newer groups are
       // pending.  Doing this before the empty-slot wait keeps publication independent of the ring.
       if (st >= kTcLag) {
         cp_async_wait<kTcLag - 1>();
-        fence_proxy_async();
-        mbar_arrive(bar_kv_full + 8 * ((st - kTcLag) % kTcSlots));
+        publish(st - kTcLag);
         TC_TR(11, st - kTcLag);
       }
       const int slot = st % kTcSlots;
       const uint32_t ph = static_cast<uint32_t>(st / kTcSlots) & 1u;
       mbar_wait_wd(bar_kv_empty + 8 * slot, ph ^ 1u);
       TC_TR(10, st);
-      const bool is_v = st & 1;
-      if (!is_v) named_bar_sync(3, 128);  // slot ids of tile st / 2 are visible
-      const int32_t* ids = sid + ((st >> 1) & 1) * kTcBN + rbase;
+      // stage -> (tensor, tile): K0 V0 K1 V1 ..., or in small-q mode K0 K1 V0 K2 V1 ... K(N-1) V(N-2) V(N-1)
+      bool is_v = st & 1;
+      int tile = st >> 1;
+      if (alt && st > 0) {
+        is_v = st == S - 1 || !(st & 1);
+        tile = st == S - 1 ? N - 1 : ((st & 1) ? (st + 1) >> 1 : (st >> 1) - 1);
+      }
+      if (!is_v) named_bar_sync(3, 128);  // slot ids of this tile are visible
       const uint8_t* base = is_v ? v_head : k_head;
       const int64_t sb = is_v ? p.v_slot_bytes : p.k_slot_bytes;
-      const uint32_t dst0 = kv_base + slot * kTcSlotBytes + sw_col;
+      if constexpr (FP8) {
+        const int32_t* ids = sid + (tile & 3) * kTcBN + rb8;
+        const uint32_t dst0 = kv_base + slot * kTcSlotBytes + kTcSlab + chunk8 * 16;
 #pragma unroll
-      for (int i = 0; i < 16; ++i) {
-        const int row = rbase + 8 * i;
-        const int32_t sl = ids[8 * i];
-        const bool ok = sl >= 0;
-        cp_async16_zfill(dst0 + row * 128 + (((chunk & 7) ^ (row & 7)) << 4), base + (ok ? sl : 0) * sb, ok);
+        for (int i = 0; i < 8; ++i) {
+          const int32_t sl = ids[16 * i];
+          const bool ok = sl >= 0;
+          cp_async16_zfill(dst0 + (rb8 + 16 * i) * 128, base + (ok ? sl : 0) * sb, ok);
+        }
+      } else {
+        const int32_t* ids = sid + (tile & 3) * kTcBN + rbase;
+        const uint32_t dst0 = kv_base + slot * kTcSlotBytes + sw_col;
+#pragma unroll
+        for (int i = 0; i < 16; ++i) {
+          const int row = rbase + 8 * i;
+          const int32_t sl = ids[8 * i];
+          const bool ok = sl >= 0;
+          cp_async16_zfill(dst0 + row * 128 + (((chunk & 7) ^ (row & 7)) << 4), base + (ok ? sl : 0) * sb, ok);
+        }
       }
       cp_async_commit();
-      if (is_v && (st >> 1) + 1 < N) fetch((st >> 1) + 1);  // slot ids of the next tile
+      // publish the ids of tile + 2: their buffer last served tile - 2, whose V stage every loader thread had
+      // issued before this thread could pass the barrier of K(tile); then start the load for tile + 3
+      if (is_v && tile + 2 < N) {
+        sid[((tile + 2) & 3) * kTcBN + tid] = pending;
+        pending = load_id(tile + 3);
+      }
     }
     // drain: the last min(S, kTcLag) stages
     cp_async_wait<0>();
-    fence_proxy_async();
-    for (int st = (S > kTcLag ? S - kTcLag : 0); st < S; ++st) mbar_arrive(bar_kv_full + 8 * (st % kTcSlots));
+    for (int st = (S > kTcLag ? S - kTcLag : 0); st < S; ++st) publish(st);
   } else if (warp == kTcMmaWarp) {
     // =============================== MMA issuer (warp 20) ===============================
     {
@@ -487,7 +601,7 @@ __global__ void __launch_bounds__(kTcThreads, 1) extend_tc_kernel(const ExtendPa
       const uint64_t dk = umma_desc_sw128(kv_base, 16, 1024);
       const uint64_t dv = umma_desc_sw128(kv_base, kTcSlab, 1024);
       auto issue_qk = [&](int sub, int slot) {
-        const uint64_t a0 = dq + static_cast<uint32_t>(sub * (kTcSlotBytes >> 4));
+        const uint64_t a0 = dq + static_cast<uint32_t>((alt ? 0 : sub) * (kTcSlotBytes >> 4));
         const uint64_t b0 = dk + static_cast<uint32_t>(slot * (kTcSlotBytes >> 4));
         const uint32_t d = tmem + sub * kTcBN;
 #pragma unroll
@@ -512,6 +626,32 @@ __global__ void __launch_bounds__(kTcThreads, 1) extend_tc_kernel(const ExtendPa
       tc_fence_after();
       issue_qk(0, 0);
       umma_commit(bar_s_full);
+      if (alt) {
+        // one chain: S0(0) S1(1) | PV_v(j) S_v(j+2) with v = j & 1 -- every stage feeds one sub-tile
+        umma_commit(bar_kv_empty);
+        full_wait(1);
+        tc_fence_after();
+        issue_qk(1, 1);
+        umma_commit(bar_s_full + 8);
+        umma_commit(bar_kv_empty + 8);
+        for (int j = 0; j < N; ++j) {
+          const int v = j & 1;
+          const int vst = j < N - 1 ? 2 * j + 2 : 2 * N - 1;
+          full_wait(vst);
+          mbar_wait_wd(bar_p_full + 8 * v, (j >> 1) & 1);
+          tc_fence_after();
+          issue_pv(v, vst % kTcSlots, j >= 2);
+          umma_commit(bar_kv_empty + 8 * (vst % kTcSlots));
+          if (j + 2 < N) {
+            const int kst = 2 * j + 3;
+            full_wait(kst);
+            tc_fence_after();
+            issue_qk(v, kst % kTcSlots);
+            umma_commit(bar_s_full + 8 * v);
+            umma_commit(bar_kv_empty + 8 * (kst % kTcSlots));
+          }
+        }
+      } else {
       if (nsub == 2) {
         issue_qk(1, 0);
         umma_commit(bar_s_full + 8);
@@ -548,6 +688,7 @@ __global__ void __launch_bounds__(kTcThreads, 1) extend_tc_kernel(const ExtendPa
           }
           umma_commit(bar_kv_empty + 8 * kslot);
         }
+      }
       }
       umma_commit(bar_o_full);
       tc_fence_before();

@@ -304,14 +304,19 @@ def make_extend_workload(cfg: Config, prefix_lens, extend_lens, device="cpu", ma
     T = int(el.sum())
     qkv = torch.randn((T, (Hq + 2 * Hkv) * D), generator=gen, device=dev, dtype=torch.float32).to(qdt)
     q, k, v = qkv.split([Hq * D, Hkv * D, Hkv * D], dim=-1)
-    kvdt = _TORCH_DT[cfg.kv_dtype]
+    fp8 = cfg.kv_dtype == "fp8_e4m3"
+    kvdt = torch.uint8 if fp8 else _TORCH_DT[cfg.kv_dtype]   # fp8 pools are stored as raw bytes
     k_pool = torch.empty((rows, Hkv, D), dtype=kvdt, device=dev)
     v_pool = torch.empty((rows, Hkv, D), dtype=kvdt, device=dev)
     step = max(1, (1 << 26) // (Hkv * D))
-    for t in (k_pool, v_pool):
+    for t, scale in ((k_pool, cfg.k_scale), (v_pool, cfg.v_scale)):
         for r0 in range(0, rows, step):
             r1 = min(rows, r0 + step)
-            t[r0:r1] = torch.randn((r1 - r0, Hkv, D), generator=gen, device=dev, dtype=torch.float32).to(kvdt)
+            x = torch.randn((r1 - r0, Hkv, D), generator=gen, device=dev, dtype=torch.float32)
+            if fp8:
+                t[r0:r1] = (x / scale).to(torch.bfloat16).to(torch.float8_e4m3fn).view(torch.uint8)
+            else:
+                t[r0:r1] = x.to(kvdt)
     return ExtendWorkload(
         cfg=cfg, prefix_lens_np=pl, extend_lens_np=el,
         req_to_token=torch.from_numpy(r2t).to(dev), req_pool_indices=torch.from_numpy(rpi).to(dev),

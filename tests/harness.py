@@ -158,8 +158,10 @@ def oracle_extend(w_cpu, causal=True, logit_cap=0.0, custom_mask=None, sliding_w
     c = w_cpu.cfg
     kp, vp = w_cpu.k_pool.clone(), w_cpu.v_pool.clone()
     T = w_cpu.tokens
+    fp8 = c.kv_dtype == "fp8_e4m3"
     decode_oracle.kv_store(kp, vp, w_cpu.out_cache_loc, w_cpu.k.reshape(T, c.num_kv_heads, c.head_dim).clone(),
-                           w_cpu.v.reshape(T, c.num_kv_heads, c.head_dim).clone())
+                           w_cpu.v.reshape(T, c.num_kv_heads, c.head_dim).clone(),
+                           c.k_scale if fp8 else None, c.v_scale if fp8 else None)
     ps, es = extend_oracle.slots_from_req_to_token(w_cpu.req_to_token, w_cpu.req_pool_indices,
                                                    w_cpu.prefix_lens_np, w_cpu.extend_lens_np, sliding_window)
     mask_indptr = None
@@ -167,5 +169,6 @@ def oracle_extend(w_cpu, causal=True, logit_cap=0.0, custom_mask=None, sliding_w
         _, _, mask_indptr = extend_oracle.extend_indptrs(w_cpu.prefix_lens_np, w_cpu.extend_lens_np)
     out, lse = extend_oracle.extend_attention(
         w_cpu.q.reshape(T, c.num_q_heads, c.head_dim), kp, vp, ps, es, w_cpu.sm_scale, causal=causal,
-        logit_cap=logit_cap, custom_mask=custom_mask, mask_indptr=mask_indptr, sliding_window=sliding_window)
+        logit_cap=logit_cap, custom_mask=custom_mask, mask_indptr=mask_indptr, sliding_window=sliding_window,
+        k_scale=c.k_scale if fp8 else 1.0, v_scale=c.v_scale if fp8 else 1.0)
     return out, lse, kp, vp

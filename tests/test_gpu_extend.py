@@ -42,8 +42,14 @@ def _layer(w, causal=True, logit_cap=0.0, window=-1):
 
     c = w.cfg
     at = b200attn.AttentionType.DECODER if causal else b200attn.AttentionType.ENCODER_ONLY
-    return b200attn.AttnLayer(c.num_q_heads, c.head_dim, w.sm_scale, c.num_kv_heads, layer_id=0,
-                              logit_cap=logit_cap, sliding_window_size=window, attn_type=at)
+    layer = b200attn.AttnLayer(c.num_q_heads, c.head_dim, w.sm_scale, c.num_kv_heads, layer_id=0,
+                               logit_cap=logit_cap, sliding_window_size=window, attn_type=at)
+    if c.kv_dtype == "fp8_e4m3":   # per-tensor scales the way RadixAttention carries them (radix_attention.py:61-82)
+        dev = w.k_pool.device
+        layer.k_scale = torch.tensor(c.k_scale, dtype=torch.float32, device=dev)
+        layer.v_scale = torch.tensor(c.v_scale, dtype=torch.float32, device=dev)
+        layer.k_scale_float, layer.v_scale_float = c.k_scale, c.v_scale
+    return layer
 
 
 def _run(cfg, pl, el, causal=True, logit_cap=0.0, window=-1, index_dtype=torch.int64, check_pool=True):
@@ -114,6 +120,32 @@ def test_extend_f16_and_int32_indices():
     _run(cfg, (20, 0), (70, 33), index_dtype=torch.int32)
 
 
+# fp8-e4m3 pools (C3's cache dtype): new tokens are quantised by the store (bit-exact bytes), the kernel
+# reads k_scale * K / v_scale * V (FlashInfer's paged-prefill semantics, flashinfer_backend.py:560-567).
+FP8_SHAPES = [
+    ("fp8_gqa4_d128", 32, 8, 128, 1, "bf16", (300, 0, 64), (140, 257, 1), 1.0, 1.0),
+    ("fp8_gqa4_d128_scaled", 8, 2, 128, 16, "bf16", (1500, 64), (3, 400), 0.5, 2.0),
+    ("fp8_gqa2_d64_scaled", 8, 4, 64, 1, "bf16", (7, 0, 200), (129, 65, 2), 0.5, 2.0),
+    ("fp8_f16q_d128", 8, 2, 128, 1, "f16", (20, 0), (70, 133), 2.0, 0.25),
+    ("fp8_f16q_d64", 32, 2, 64, 4, "f16", (10, 90), (33, 8), 1.0, 1.0),
+    ("fp8_tile_edges", 8, 2, 128, 1, "bf16", (0, 0, 127, 128, 129), (128, 129, 1, 1, 1), 0.5, 2.0),
+]
+
+
+@pytest.mark.parametrize("shape", FP8_SHAPES, ids=[s[0] for s in FP8_SHAPES])
+def test_extend_fp8_pool(shape):
+    name, hq, hkv, d, page, qdt, pl, el, ks, vs = shape
+    cfg = synth.Config(name, len(pl), 0, hq, hkv, d, kv_dtype="fp8_e4m3", q_dtype=qdt, page_size=page,
+                       k_scale=ks, v_scale=vs, seed=601)
+    _run(cfg, pl, el)
+
+
+def test_extend_fp8_window_and_cap():
+    cfg = synth.Config("fp8_win", 2, 0, 8, 2, 128, kv_dtype="fp8_e4m3", k_scale=0.5, v_scale=2.0, seed=602)
+    _run(cfg, (150, 10), (40, 70), window=16)
+    _run(cfg, (150, 10), (40, 70), logit_cap=5.0)
+
+
 def test_extend_noncausal():
     _run(synth.Config("enc", 2, 0, 8, 2, 128, seed=103), (0, 12), (100, 77), causal=False)
 
@@ -130,13 +162,14 @@ def test_extend_sliding_window(window):
     _run(synth.Config("win", 3, 0, 8, 2, 128, seed=105), (150, 10, 0), (40, 70, 20), window=window)
 
 
-def _verify_case(n_draft, pl, seed, mask_fn):
+def _verify_case(n_draft, pl, seed, mask_fn, kv_dtype="bf16"):
     """TARGET_VERIFY: uniform extend = n_draft tokens per request, visibility from
     spec_info.custom_mask (triton_backend.py:227-263)."""
     import b200attn
     from oracle import extend_oracle
 
-    cfg = synth.Config("verify", len(pl), 0, 32, 8, 128, seed=seed)
+    cfg = synth.Config("verify", len(pl), 0, 32, 8, 128, kv_dtype=kv_dtype, k_scale=0.5 if kv_dtype != "bf16" else 1.0,
+                       v_scale=2.0 if kv_dtype != "bf16" else 1.0, seed=seed)
     el = (n_draft,) * len(pl)
     w_cpu, w = _pair(cfg, pl, el)
     _, _, mi = extend_oracle.extend_indptrs(pl, el)
@@ -167,6 +200,25 @@ def test_target_verify_tree_mask():
         m[:, p:] = t
         return m
     _verify_case(8, (100, 37, 1, 260), 201, tree)
+
+
+def _tree(rng, n, p):
+    m = np.ones((n, p + n), dtype=np.uint8)
+    t = np.tril(rng.integers(0, 2, size=(n, n), dtype=np.uint8))
+    np.fill_diagonal(t, 1)
+    m[:, p:] = t
+    return m
+
+
+def test_target_verify_fp8_pool():
+    _verify_case(8, (100, 37, 1, 260), 204, _tree, kv_dtype="fp8_e4m3")
+
+
+@pytest.mark.parametrize("pl", [(1000, 129, 0, 255, 256, 257), (4096, 3000)])
+def test_target_verify_long_prefix(pl):
+    """Few query rows over a long prefix: the shape the small-q (KV ping-pong) mode of the tcgen05 kernel
+    serves -- odd and even tile counts, and a request with no prefix at all."""
+    _verify_case(8, pl, 205, _tree)
 
 
 def test_target_verify_causal_mask_equals_causal():
