@@ -22,8 +22,8 @@ cudaError_t launch_extend(const ExtendParams& p, int d, dim3 grid, cudaStream_t 
 }
 
 template <typename QT, bool FP8>
-cudaError_t launch_extend_tc(const ExtendParams& p, dim3 grid, cudaStream_t stream) {
-  void (*fn)(const ExtendParams) = extend_tc_kernel<QT, FP8>;
+cudaError_t launch_extend_tc(const ExtendParams& p, dim3 grid, bool small_q, cudaStream_t stream) {
+  void (*fn)(const ExtendParams) = small_q ? extend_tc_kernel<QT, FP8, true> : extend_tc_kernel<QT, FP8, false>;
   cudaError_t e = cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, kTcSmemBytes);
   if (e != cudaSuccess) return e;
   fn<<<grid, kTcThreads, kTcSmemBytes, stream>>>(p);
@@ -196,12 +196,15 @@ extern "C" __attribute__((visibility("default"))) int b200attn_extend(const b200
   if (tc_ok) {
     const int tok = (2 * kTcBM) >> p.gp_shift;
     dim3 grid((a->max_extend_len + tok - 1) / tok, a->num_kv_heads, a->batch);
+    // every request has at most 128 (token, head) rows -- decode-like and TARGET_VERIFY batches: the small-q
+    // kernel splits each CTA's KV range over its two accumulators instead of leaving one idle
+    const bool small_q = (static_cast<int64_t>(a->max_extend_len) << p.gp_shift) <= kTcBM;
     if (fp8)
-      err = a->q_dtype == B200ATTN_F16 ? launch_extend_tc<__half, true>(p, grid, stream)
-                                       : launch_extend_tc<__nv_bfloat16, true>(p, grid, stream);
+      err = a->q_dtype == B200ATTN_F16 ? launch_extend_tc<__half, true>(p, grid, small_q, stream)
+                                       : launch_extend_tc<__nv_bfloat16, true>(p, grid, small_q, stream);
     else
-      err = a->q_dtype == B200ATTN_F16 ? launch_extend_tc<__half, false>(p, grid, stream)
-                                       : launch_extend_tc<__nv_bfloat16, false>(p, grid, stream);
+      err = a->q_dtype == B200ATTN_F16 ? launch_extend_tc<__half, false>(p, grid, small_q, stream)
+                                       : launch_extend_tc<__nv_bfloat16, false>(p, grid, small_q, stream);
   } else {
     const int bm_tok = kExtRows >> p.gp_shift;
     dim3 grid((a->max_extend_len + bm_tok - 1) / bm_tok, a->num_kv_heads, a->batch);

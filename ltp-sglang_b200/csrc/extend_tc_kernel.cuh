@@ -169,7 +169,9 @@ __device__ __forceinline__ void setmaxnreg_dec() {
 // into the upper slab of the ring slot and, once landed, widen them in place to f16 (exact) in the swizzled
 // layout; both MMAs then run in f16 with q converted (and clamped) once, k_scale folded into the softmax
 // scale and v_scale into the final normalisation -- the decode kernel's fp8 semantics.
-template <typename QT, bool FP8>
+// ALT: compiled-in support for the small-q mode (launched when no CTA of the grid can have more than 128
+// rows); the general kernel carries none of its bookkeeping in the softmax loop's registers.
+template <typename QT, bool FP8, bool ALT>
 __global__ void __launch_bounds__(kTcThreads, 1) extend_tc_kernel(const ExtendParams p) {
   constexpr bool OUT_HALF = std::is_same<QT, __half>::value;
   constexpr bool HALF = OUT_HALF || FP8;  // MMA operand type
@@ -201,16 +203,40 @@ __global__ void __launch_bounds__(kTcThreads, 1) extend_tc_kernel(const ExtendPa
                       ? reinterpret_cast<long long*>(p.lse) : nullptr;
 #endif
 
+#ifdef B200ATTN_TC_TRACE
+  // every CTA: globaltimer at entry / exit and its SM id, at byte offset 32 KB of the lse buffer
+  long long* cta_tr = reinterpret_cast<long long*>(p.lse) + 4096 +
+                      4 * ((blockIdx.z * gridDim.y + blockIdx.y) * gridDim.x + blockIdx.x);
+  if (threadIdx.x == 0) {
+    unsigned long long gt;
+    unsigned smid;
+    asm volatile("mov.u64 %0, %globaltimer;" : "=l"(gt));
+    asm volatile("mov.u32 %0, %smid;" : "=r"(smid));
+    cta_tr[0] = static_cast<long long>(gt);
+    cta_tr[2] = smid;
+    if (blockIdx.x == 0 && blockIdx.y == 0 && blockIdx.z == 0) reinterpret_cast<long long*>(p.lse)[12 * 256 + 255] = clock64();
+  }
+#endif
   // ---- tile geometry (CTA-uniform) ----
+  // all of the request's scalars in one round trip (the loads are independent; the early return below would
+  // otherwise serialise them into three)
   const int q0 = p.qo_indptr[b];
-  const int Le = p.qo_indptr[b + 1] - q0;
+  const int q1 = p.qo_indptr[b + 1];
+  const int kv0 = p.kv_indptr[b];
+  const int kv1 = p.kv_indptr[b + 1];
+  int64_t req_row = 0, pl_full = 0;
+  if (!p.kv_indices) {
+    req_row = p.idx64 ? static_cast<const int64_t*>(p.req_pool_indices)[b]
+                      : static_cast<const int32_t*>(p.req_pool_indices)[b];
+    pl_full = p.idx64 ? static_cast<const int64_t*>(p.prefix_lens)[b] : static_cast<const int32_t*>(p.prefix_lens)[b];
+  }
+  const int Le = q1 - q0;
   const int tok_per_cta = (2 * kTcBM) >> p.gp_shift;
   const int ntq = (Le + tok_per_cta - 1) / tok_per_cta;
   const int t = ntq - 1 - static_cast<int>(blockIdx.x);  // longest tiles first
   if (t < 0) return;
   const int tok0 = t * tok_per_cta;
-  const int kv0 = p.kv_indptr[b];
-  const int Lp = p.kv_indptr[b + 1] - kv0;
+  const int Lp = kv1 - kv0;
   const bool use_mask = p.custom_mask != nullptr;
   const int tile_tok_end = tok0 + tok_per_cta < Le ? tok0 + tok_per_cta : Le;
   const int ext_end = (p.causal && !use_mask) ? tile_tok_end : Le;
@@ -223,7 +249,8 @@ __global__ void __launch_bounds__(kTcThreads, 1) extend_tc_kernel(const ExtendPa
   // take the SAME 128 q rows and alternate over the KV tiles (sub-tile v owns tiles n = v mod 2), each
   // with its own running max / sum / O; the two partial states are merged in the epilogue (an in-CTA
   // 2-way split-KV).  K / V stages are then consumed in the order K0 K1 V0 K2 V1 K3 ...
-  const bool alt = nsub == 1 && N >= 2;
+  const bool alt = ALT && nsub == 1 && N >= 2;
+  const int32_t* pidx = p.kv_indices ? p.kv_indices + kv0 : p.req_to_token + req_row * p.r2t_stride + (pl_full - Lp);
 
   if (threadIdx.x == 0) {
     for (int s = 0; s < kTcSlots; ++s) {
@@ -262,6 +289,10 @@ __global__ void __launch_bounds__(kTcThreads, 1) extend_tc_kernel(const ExtendPa
       const bool rv = hd < p.group && itok < Le;
       const int i_min_sub = alt ? tok0 : tok0 + ((sub * kTcBM) >> p.gp_shift);
       const int dn = alt ? 2 : 1;
+      // a warp whose 32 rows all lie past the tile's last valid row (small-q batches: 8 draft tokens x 4 heads
+      // fill one warp of four) only keeps the barriers moving: its P rows are never written (whatever bits sit
+      // there feed O rows nobody reads -- rows are independent) and it touches neither TMEM nor the MUFU
+      const bool dead = ALT && (alt ? 0 : sub * kTcBM) + (warp & 3) * 32 >= rows_valid;
       const uint32_t lane_off = static_cast<uint32_t>((warp & 3) * 32) << 16;
       const uint32_t tS = tmem + lane_off + sub * kTcBN + half * 64;        // this thread's S columns
       const uint32_t tO = tmem + lane_off + 2 * kTcBN + sub * kTcD + half * 64;
@@ -284,6 +315,11 @@ __global__ void __launch_bounds__(kTcThreads, 1) extend_tc_kernel(const ExtendPa
         mbar_wait_wd(bar_s_full + 8 * sub, it & 1);
         tc_fence_after();
         TC_TR(sub * 3, n);
+        if (dead) {
+          named_bar_sync(1 + sub, 256);  // a sync, not an arrive: the warp must not run ahead into the epilogue's use
+          mbar_arrive(bar_p_full + 8 * sub);
+          continue;
+        }
         const int j0 = n * kTcBN, j_end = j0 + kTcBN;
         const bool need_mask = j_end > Ltot || (p.window > 0 && j0 < Lp) ||
                                (use_mask && (!p.skip_prefix_mask || j_end > Lp)) ||
@@ -298,19 +334,24 @@ __global__ void __launch_bounds__(kTcThreads, 1) extend_tc_kernel(const ExtendPa
             for (int j = 0; j < 32; ++j) s[j] = p.logit_cap * tanhf(s[j] * cap_pre);
           }
           if (need_mask) {
+            // Visibility of key j for this row, custom-mask bytes aside, is one range [lo, lo + span): the
+            // sliding window cuts the front of the prefix part (i <= j + W, prefix keys only), causality /
+            // the tile's end the back.  The mask bytes (speculative verify) are read only from mask_from on.
+            // (Derived here, on masked tiles only, to keep them out of the main loop's live registers.)
+            const int hi = !rv ? 0 : ((p.causal && !use_mask) ? min(Ltot, Lp + itok + 1) : Ltot);
+            const int lo = p.window > 0 ? min(max(itok - p.window, 0), Lp) : 0;
+            const unsigned span = hi > lo ? static_cast<unsigned>(hi - lo) : 0u;
+            const int mask_from = !use_mask ? 0x7fffffff : (p.skip_prefix_mask ? Lp : 0);
+            const int jb = j0 + half * 64 + cc;
 #pragma unroll
-            for (int jj = 0; jj < 32; ++jj) {
-              const int j = j0 + half * 64 + cc + jj;
-              bool vis = rv && j < Ltot;
-              if (j < Lp) {
-                if (p.window > 0) vis = vis && (itok <= j + p.window);
-                if (use_mask && !p.skip_prefix_mask && vis) vis = mrow[j] != 0;
-              } else if (use_mask) {
-                if (vis) vis = mrow[j] != 0;
-              } else if (p.causal) {
-                vis = vis && (j - Lp <= itok);
+            for (int jj = 0; jj < 32; ++jj)
+              s[jj] = static_cast<unsigned>(jb + jj - lo) < span ? s[jj] : -CUDART_INF_F;
+            if (jb + 32 > mask_from) {
+#pragma unroll
+              for (int jj = 0; jj < 32; ++jj) {
+                const int j = jb + jj;
+                if (j >= mask_from && j < hi && mrow[j] == 0) s[jj] = -CUDART_INF_F;
               }
-              if (!vis) s[jj] = -CUDART_INF_F;
             }
           }
         };
@@ -405,7 +446,7 @@ __global__ void __launch_bounds__(kTcThreads, 1) extend_tc_kernel(const ExtendPa
           mlog2 = mm == -CUDART_INF_F ? 0.f : mm;
         }
       }
-      if (!alt || sub == 0) {
+      if ((!alt || sub == 0) && !dead) {
       mbar_wait_wd(bar_o_full, 0);
       tc_fence_after();
       const float inv = l > 0.f ? p.v_scale / l : 0.f;
@@ -480,22 +521,10 @@ __global__ void __launch_bounds__(kTcThreads, 1) extend_tc_kernel(const ExtendPa
           cp_async16_zfill(dst, src, ok);
         }
       }
-      cp_async_commit();
-      cp_async_wait<0>();
-      fence_proxy_async();
-      mbar_arrive(bar_q_full);
+      cp_async_commit();  // the oldest group: complete at the first publish below, which also releases Q
     }
+    bool q_pub = false;
     // ---- K / V ring ----
-    const int32_t* pidx;
-    if (p.kv_indices) {
-      pidx = p.kv_indices + kv0;
-    } else {
-      const int64_t req = p.idx64 ? static_cast<const int64_t*>(p.req_pool_indices)[b]
-                                  : static_cast<const int32_t*>(p.req_pool_indices)[b];
-      const int64_t pl = p.idx64 ? static_cast<const int64_t*>(p.prefix_lens)[b]
-                                 : static_cast<const int32_t*>(p.prefix_lens)[b];
-      pidx = p.req_to_token + req * p.r2t_stride + (pl - Lp);
-    }
     // fp8: a row is 8 x 16 bytes, thread (rb8, chunk8) moves rows rb8 + 16 i
     const int chunk8 = tid & 7, rb8 = tid >> 3;
     const uint8_t* k_head = p.k_pool + static_cast<int64_t>(h) * kTcD * (FP8 ? 1 : 2) + (FP8 ? chunk8 : chunk) * 16;
@@ -520,6 +549,10 @@ __global__ void __launch_bounds__(kTcThreads, 1) extend_tc_kernel(const ExtendPa
         }
       }
       fence_proxy_async();
+      if (!q_pub) {
+        mbar_arrive(bar_q_full);
+        q_pub = true;
+      }
       mbar_arrive(bar_kv_full + 8 * (st % kTcSlots));
     };
     // Slot ids of a tile are read once (one per thread, coalesced) into a double-buffered shared
@@ -532,13 +565,19 @@ __global__ void __launch_bounds__(kTcThreads, 1) extend_tc_kernel(const ExtendPa
       if (j < Ltot) sl = j < Lp ? pidx[j] : static_cast<int32_t>(p.extend_loc[q0 + j - Lp]);
       return sl;
     };
-    sid[tid] = load_id(0);
-    sid[kTcBN + tid] = load_id(1);
+    // Layout of a slot-id buffer: the ids of the rows ONE loader thread copies are adjacent, so a stage reads
+    // them with vector loads into registers BEFORE its first cp.async.  (Read one by one between the copies
+    // -- each asm volatile cp.async orders the next shared load behind it -- the issue loop ran LDS ->
+    // address -> LDGSTS serially, ~90 clk per copy, 1400 clk per stage: the whole kernel was bound by it.)
+    const int sid_pos = FP8 ? (tid & 15) * 8 + (tid >> 4) : (tid & 7) * 16 + (tid >> 3);
+    sid[sid_pos] = load_id(0);
+    sid[kTcBN + sid_pos] = load_id(1);
     int32_t pending = load_id(2);
     const int S = 2 * N;
     for (int st = 0; st < S; ++st) {
       // publish stage st - kTcLag first: its copies have landed once at most kTcLag - 1 newer groups are
       // pending.  Doing this before the empty-slot wait keeps publication independent of the ring.
+      TC_TR(13, st);
       if (st >= kTcLag) {
         cp_async_wait<kTcLag - 1>();
         publish(st - kTcLag);
@@ -559,30 +598,36 @@ __global__ void __launch_bounds__(kTcThreads, 1) extend_tc_kernel(const ExtendPa
       const uint8_t* base = is_v ? v_head : k_head;
       const int64_t sb = is_v ? p.v_slot_bytes : p.k_slot_bytes;
       if constexpr (FP8) {
-        const int32_t* ids = sid + (tile & 3) * kTcBN + rb8;
+        const int4* idv = reinterpret_cast<const int4*>(sid + (tile & 3) * kTcBN + rb8 * 8);
+        const int4 i0 = idv[0], i1 = idv[1];
+        const int32_t ids[8] = {i0.x, i0.y, i0.z, i0.w, i1.x, i1.y, i1.z, i1.w};
         const uint32_t dst0 = kv_base + slot * kTcSlotBytes + kTcSlab + chunk8 * 16;
 #pragma unroll
         for (int i = 0; i < 8; ++i) {
-          const int32_t sl = ids[16 * i];
+          const int32_t sl = ids[i];
           const bool ok = sl >= 0;
           cp_async16_zfill(dst0 + (rb8 + 16 * i) * 128, base + (ok ? sl : 0) * sb, ok);
         }
       } else {
-        const int32_t* ids = sid + (tile & 3) * kTcBN + rbase;
+        const int4* idv = reinterpret_cast<const int4*>(sid + (tile & 3) * kTcBN + rbase * 16);
+        const int4 i0 = idv[0], i1 = idv[1], i2 = idv[2], i3 = idv[3];
+        const int32_t ids[16] = {i0.x, i0.y, i0.z, i0.w, i1.x, i1.y, i1.z, i1.w,
+                                 i2.x, i2.y, i2.z, i2.w, i3.x, i3.y, i3.z, i3.w};
         const uint32_t dst0 = kv_base + slot * kTcSlotBytes + sw_col;
 #pragma unroll
         for (int i = 0; i < 16; ++i) {
           const int row = rbase + 8 * i;
-          const int32_t sl = ids[8 * i];
+          const int32_t sl = ids[i];
           const bool ok = sl >= 0;
           cp_async16_zfill(dst0 + row * 128 + (((chunk & 7) ^ (row & 7)) << 4), base + (ok ? sl : 0) * sb, ok);
         }
       }
       cp_async_commit();
+      TC_TR(12, st);
       // publish the ids of tile + 2: their buffer last served tile - 2, whose V stage every loader thread had
       // issued before this thread could pass the barrier of K(tile); then start the load for tile + 3
       if (is_v && tile + 2 < N) {
-        sid[((tile + 2) & 3) * kTcBN + tid] = pending;
+        sid[((tile + 2) & 3) * kTcBN + sid_pos] = pending;
         pending = load_id(tile + 3);
       }
     }
@@ -638,14 +683,17 @@ __global__ void __launch_bounds__(kTcThreads, 1) extend_tc_kernel(const ExtendPa
           const int v = j & 1;
           const int vst = j < N - 1 ? 2 * j + 2 : 2 * N - 1;
           full_wait(vst);
+          TC_TR(6, j);
           mbar_wait_wd(bar_p_full + 8 * v, (j >> 1) & 1);
           tc_fence_after();
+          TC_TR(7, j);
           issue_pv(v, vst % kTcSlots, j >= 2);
           umma_commit(bar_kv_empty + 8 * (vst % kTcSlots));
           if (j + 2 < N) {
             const int kst = 2 * j + 3;
             full_wait(kst);
             tc_fence_after();
+            TC_TR(8, j);
             issue_qk(v, kst % kTcSlots);
             umma_commit(bar_s_full + 8 * v);
             umma_commit(bar_kv_empty + 8 * (kst % kTcSlots));
@@ -696,6 +744,14 @@ __global__ void __launch_bounds__(kTcThreads, 1) extend_tc_kernel(const ExtendPa
   }
   }
   __syncthreads();
+#ifdef B200ATTN_TC_TRACE
+  if (threadIdx.x == 0) {
+    unsigned long long gt;
+    asm volatile("mov.u64 %0, %globaltimer;" : "=l"(gt));
+    cta_tr[1] = static_cast<long long>(gt);
+    if (blockIdx.x == 0 && blockIdx.y == 0 && blockIdx.z == 0) reinterpret_cast<long long*>(p.lse)[13 * 256 + 255] = clock64();
+  }
+#endif
   if (warp == kTcMmaWarp) {
     tc_fence_after();
     asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, 512;" ::"r"(tmem));

@@ -21,7 +21,7 @@ for _ in range(2):
     torch.ops.b200attn.extend(q, o, lse, w.k_pool, w.v_pool, qo, kv, None, w.req_to_token, w.req_pool_indices,
                               w.extend_prefix_lens, w.out_cache_loc, None, None, L, True, -1, True, w.sm_scale, 0.0)
 torch.cuda.synchronize()
-t = lse.view(torch.int64)[: 12 * 256].cpu().numpy().reshape(12, 256)
+t = lse.view(torch.int64)[: 14 * 256].cpu().numpy().reshape(14, 256)
 N = (L + 127) // 128
 t0 = t[0, 0]
 np.set_printoptions(linewidth=200)
@@ -31,7 +31,8 @@ for n in list(range(0, 3)) + list(range(30, 34)):
     r = [int(t[k, n] - t0) if t[k, n] else -1 for k in range(10)]
     print(f"n={n:3d} sm0: s {r[0]:7d} ld {r[1]:7d} p {r[2]:7d} | sm1: s {r[3]:7d} ld {r[4]:7d} p {r[5]:7d} | mma: V {r[6]:7d} p0 {r[7]:7d} K {r[8]:7d} p1 {r[9]:7d}")
 for st in list(range(0, 8)) + list(range(60, 66)):
-    print(f"st={st:3d} loader empty {int(t[10, st]-t0):7d} published {int(t[11, st]-t0):7d}")
+    print(f"st={st:3d} loader: iter start {int(t[13, st]-t0):7d} landed(st-2) +{int(t[11, st-2]-t[13, st]) if st >= 2 else 0:5d} "
+          f"empty +{int(t[10, st]-(t[11, st-2] if st >= 2 else t[13, st])):5d} issue +{int(t[12, st]-t[10, st]):5d}")
 d = np.diff(t[0, 8:N-2]).astype(float)
 print("steady period per tile (clk): mean %.0f" % d.mean(), " softmax0 busy (s->p): %.0f" % (t[2, 8:N-2] - t[0, 8:N-2]).mean(),
       " ld: %.0f" % (t[1, 8:N-2] - t[0, 8:N-2]).mean(), " p0->next s0: %.0f" % (t[0, 9:N-1] - t[2, 8:N-2]).mean())
