@@ -23,7 +23,11 @@ cudaError_t launch_extend(const ExtendParams& p, int d, dim3 grid, cudaStream_t 
 
 template <typename QT, bool FP8>
 cudaError_t launch_extend_tc(const ExtendParams& p, dim3 grid, bool small_q, cudaStream_t stream) {
-  void (*fn)(const ExtendParams) = small_q ? extend_tc_kernel<QT, FP8, true> : extend_tc_kernel<QT, FP8, false>;
+  void (*fn)(const ExtendParams);
+  if (p.logit_cap > 0.f)
+    fn = small_q ? extend_tc_kernel<QT, FP8, true, true> : extend_tc_kernel<QT, FP8, false, true>;
+  else
+    fn = small_q ? extend_tc_kernel<QT, FP8, true, false> : extend_tc_kernel<QT, FP8, false, false>;
   cudaError_t e = cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, kTcSmemBytes);
   if (e != cudaSuccess) return e;
   fn<<<grid, kTcThreads, kTcSmemBytes, stream>>>(p);

@@ -171,7 +171,10 @@ __device__ __forceinline__ void setmaxnreg_dec() {
 // scale and v_scale into the final normalisation -- the decode kernel's fp8 semantics.
 // ALT: compiled-in support for the small-q mode (launched when no CTA of the grid can have more than 128
 // rows); the general kernel carries none of its bookkeeping in the softmax loop's registers.
-template <typename QT, bool FP8, bool ALT>
+// CAP: logit cap (cap * tanh(x / cap)) compiled in.  As a run-time flag the compiler if-converted it: the
+// softmax loop evaluated tanh for every element and selected afterwards -- ~17 instructions and two extra
+// MUFU ops per element on a loop that is issue-bound -- although no Llama-class model sets a cap.
+template <typename QT, bool FP8, bool ALT, bool CAP>
 __global__ void __launch_bounds__(kTcThreads, 1) extend_tc_kernel(const ExtendParams p) {
   constexpr bool OUT_HALF = std::is_same<QT, __half>::value;
   constexpr bool HALF = OUT_HALF || FP8;  // MMA operand type
@@ -273,6 +276,7 @@ __global__ void __launch_bounds__(kTcThreads, 1) extend_tc_kernel(const ExtendPa
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem = __shfl_sync(0xffffffffu, *tmem_slot_ptr, 0);  // provably warp-uniform
+  TC_TR(12, 250);  // roles start (each tracing thread overwrites: the last one wins, they are close)
 
   if (warp < kTcSoftmaxWarps) {
     // =============================== softmax warps ===============================
@@ -296,7 +300,7 @@ __global__ void __launch_bounds__(kTcThreads, 1) extend_tc_kernel(const ExtendPa
       const uint32_t lane_off = static_cast<uint32_t>((warp & 3) * 32) << 16;
       const uint32_t tS = tmem + lane_off + sub * kTcBN + half * 64;        // this thread's S columns
       const uint32_t tO = tmem + lane_off + 2 * kTcBN + sub * kTcD + half * 64;
-      const bool cap = p.logit_cap > 0.f;
+      constexpr bool cap = CAP;
       const float c = cap ? kLog2e : p.scale_log2;
       const float cap_pre = cap ? p.sm_scale / p.logit_cap : 0.f;
       const int64_t mask_row_len = static_cast<int64_t>(Lp) + Le;
@@ -324,16 +328,20 @@ __global__ void __launch_bounds__(kTcThreads, 1) extend_tc_kernel(const ExtendPa
         const bool need_mask = j_end > Ltot || (p.window > 0 && j0 < Lp) ||
                                (use_mask && (!p.skip_prefix_mask || j_end > Lp)) ||
                                (!use_mask && p.causal && j_end - 1 - Lp > i_min_sub);
+        // The tile body exists twice, with and without the mask code: left to the compiler, the range test is
+        // if-converted into the unmasked path too (3 instructions per element on an issue-bound loop).
+        auto tile_body = [&](auto masked_tag) {
+        constexpr bool MASKED = decltype(masked_tag)::value;
         // 32 of this thread's 64 S columns -> registers, logit cap and masks applied.  The row is read
         // twice (max pass, exp pass): TMEM loads are cheap, 64 live values per thread are not.
         auto load_chunk = [&](int cc, float (&s)[32]) {
           tmem_ld32<0>(tS + cc, s);
           tmem_wait_ld();
-          if (cap) {
+          if constexpr (cap) {
 #pragma unroll
             for (int j = 0; j < 32; ++j) s[j] = p.logit_cap * tanhf(s[j] * cap_pre);
           }
-          if (need_mask) {
+          if constexpr (MASKED) {
             // Visibility of key j for this row, custom-mask bytes aside, is one range [lo, lo + span): the
             // sliding window cuts the front of the prefix part (i <= j + W, prefix keys only), causality /
             // the tile's end the back.  The mask bytes (speculative verify) are read only from mask_from on.
@@ -422,6 +430,9 @@ __global__ void __launch_bounds__(kTcThreads, 1) extend_tc_kernel(const ExtendPa
         tc_fence_before();
         mbar_arrive(bar_p_full + 8 * sub);
         TC_TR(sub * 3 + 2, n);
+        };
+        if (need_mask) tile_body(std::true_type{});
+        else tile_body(std::false_type{});
       }
 
       // ---- epilogue: row sum over both halves, then this thread's 64 columns of O / l -> global ----
@@ -449,6 +460,7 @@ __global__ void __launch_bounds__(kTcThreads, 1) extend_tc_kernel(const ExtendPa
       if ((!alt || sub == 0) && !dead) {
       mbar_wait_wd(bar_o_full, 0);
       tc_fence_after();
+      TC_TR(13, 250);  // epilogue: O complete
       const float inv = l > 0.f ? p.v_scale / l : 0.f;
       QT* orow = reinterpret_cast<QT*>(p.o) + static_cast<int64_t>(q0 + (rv ? itok : 0)) * p.o_st +
                  static_cast<int64_t>(h * p.group + (rv ? hd : 0)) * p.o_sh + half * 64;
@@ -488,6 +500,7 @@ __global__ void __launch_bounds__(kTcThreads, 1) extend_tc_kernel(const ExtendPa
             l > 0.f ? mlog2 * kLn2 + logf(l) : -CUDART_INF_F;
 #endif
       }
+      TC_TR(13, 251);  // epilogue: outputs stored
       tc_fence_before();
     }
   } else {
@@ -522,6 +535,7 @@ __global__ void __launch_bounds__(kTcThreads, 1) extend_tc_kernel(const ExtendPa
         }
       }
       cp_async_commit();  // the oldest group: complete at the first publish below, which also releases Q
+      TC_TR(12, 251);  // Q issued
     }
     bool q_pub = false;
     // ---- K / V ring ----
@@ -573,6 +587,7 @@ __global__ void __launch_bounds__(kTcThreads, 1) extend_tc_kernel(const ExtendPa
     sid[sid_pos] = load_id(0);
     sid[kTcBN + sid_pos] = load_id(1);
     int32_t pending = load_id(2);
+    TC_TR(12, 252);  // first slot ids stored
     const int S = 2 * N;
     for (int st = 0; st < S; ++st) {
       // publish stage st - kTcLag first: its copies have landed once at most kTcLag - 1 newer groups are
@@ -634,6 +649,7 @@ __global__ void __launch_bounds__(kTcThreads, 1) extend_tc_kernel(const ExtendPa
     // drain: the last min(S, kTcLag) stages
     cp_async_wait<0>();
     for (int st = (S > kTcLag ? S - kTcLag : 0); st < S; ++st) publish(st);
+    TC_TR(13, 252);  // loader done
   } else if (warp == kTcMmaWarp) {
     // =============================== MMA issuer (warp 20) ===============================
     {
@@ -739,6 +755,7 @@ __global__ void __launch_bounds__(kTcThreads, 1) extend_tc_kernel(const ExtendPa
       }
       }
       umma_commit(bar_o_full);
+      TC_TR(13, 253);  // last MMA committed
       tc_fence_before();
     }
   }

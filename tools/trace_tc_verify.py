@@ -29,6 +29,8 @@ N = (Lp + Le + 127) // 128
 t0 = t[0, 0]
 print("tiles", N)
 print("CTA entry %d exit %d (clk rel. to first s_full)" % (t[12, 255] - t0, t[13, 255] - t0))
+print("prologue: roles start %d, Q issued %d, first slot ids %d | tail: loader done %d, last MMA committed %d, O complete %d, "
+      "outputs stored %d" % tuple(int(x - t0) for x in (t[12, 250], t[12, 251], t[12, 252], t[13, 252], t[13, 253], t[13, 250], t[13, 251])))
 for n in range(0, 64):
     if n >= N: break
     v = n & 1
