@@ -31,6 +31,8 @@ CONFIGS = {
     "P1": dict(prefix=[0], extend=[8192], note="1 x 8192 new tokens, no prefix"),
     "P2": dict(prefix=[2048] * 16, extend=[2048] * 16, note="16 x 2048 new tokens over 2048 cached"),
     "P3": dict(prefix=[4096] * 128, extend=[8] * 128, note="128 x 8 draft tokens over 4096 cached (verify shape)"),
+    # Llama-3.2-1B shape (head_dim 64, BASELINE configs[0]'s model): the mma.sync kernel
+    "P1d64": dict(prefix=[0], extend=[8192], d=64, note="1 x 8192 new tokens, no prefix, head_dim 64"),
     # the same shapes over an fp8-e4m3 pool with per-tensor scales (C3's cache dtype)
     "P2f": dict(prefix=[2048] * 16, extend=[2048] * 16, kv="fp8_e4m3",
                 note="16 x 2048 new tokens over 2048 cached, fp8-e4m3 pool"),
@@ -71,12 +73,13 @@ def main():
     for name in names:
         spec = CONFIGS[name]
         fp8 = spec.get("kv") == "fp8_e4m3"
-        cfg = synth.Config(name, len(spec["prefix"]), 0, 32, 8, 128, seed=77, kv_dtype=spec.get("kv", "bf16"),
+        D = spec.get("d", 128)
+        cfg = synth.Config(name, len(spec["prefix"]), 0, 32, 8, D, seed=77, kv_dtype=spec.get("kv", "bf16"),
                            k_scale=0.5 if fp8 else 1.0, v_scale=2.0 if fp8 else 1.0)
         w = synth.make_extend_workload(cfg, spec["prefix"], spec["extend"], dev)
         runner = make_extend_runner(w, dev)
         backend = b200attn.B200AttnBackend(runner)
-        layer = b200attn.AttnLayer(32, 128, w.sm_scale, 8, layer_id=0)
+        layer = b200attn.AttnLayer(32, D, w.sm_scale, 8, layer_id=0)
         if fp8:
             layer.k_scale = torch.tensor(cfg.k_scale, dtype=torch.float32, device=dev)
             layer.v_scale = torch.tensor(cfg.v_scale, dtype=torch.float32, device=dev)
@@ -117,8 +120,8 @@ def main():
         clk = clocks.stop()
 
         flops = w.flops(causal=True)
-        kv_bytes = int((w.prefix_lens_np + w.extend_lens_np).sum()) * 8 * 2 * 128 * (1 if fp8 else 2)
-        io_bytes = kv_bytes + 2 * w.tokens * 32 * 128 * 2
+        kv_bytes = int((w.prefix_lens_np + w.extend_lens_np).sum()) * 8 * 2 * D * (1 if fp8 else 2)
+        io_bytes = kv_bytes + 2 * w.tokens * 32 * D * 2
         tflops = flops / (kms * 1e-3) / 1e12
         gbs = io_bytes / (kms * 1e-3) / 1e9
         tensor_bound = flops / (tf_peak * 1e12) >= io_bytes / (hbm_peak * 1e9)
@@ -127,7 +130,7 @@ def main():
             "value": w.tokens / (ms * 1e-3), "unit": "tokens/s", "n_gpus": 1, "steps": args.steps,
             "warmup": max(args.warmup, 3), "ms_per_step": ms, "higher_is_better": True, "dtype": "bf16",
             "data": "synthetic",
-            "config": {"workload": f"{name}: {spec['note']}; 32q/8kv heads, head_dim 128, {'fp8-e4m3' if fp8 else 'bf16'} pool, page_size 1, "
+            "config": {"workload": f"{name}: {spec['note']}; 32q/8kv heads, head_dim {D}, {'fp8-e4m3' if fp8 else 'bf16'} pool, page_size 1, "
                                    "permuted slots", "l2": "working set > L2 for P2/P3; P1 (32 MB KV) is L2-resident "
                                                            "by nature: a prefill re-reads its own KV"},
             "roofline": {"bound": "tensor" if tensor_bound else "hbm",
@@ -145,8 +148,8 @@ def main():
             import torch.nn.functional as F
 
             Le, Lp = spec["extend"][0], spec["prefix"][0]
-            q = torch.randn(B, 32, Le, 128, device=dev, dtype=torch.bfloat16)
-            k = torch.randn(B, 8, Lp + Le, 128, device=dev, dtype=torch.bfloat16)
+            q = torch.randn(B, 32, Le, D, device=dev, dtype=torch.bfloat16)
+            k = torch.randn(B, 8, Lp + Le, D, device=dev, dtype=torch.bfloat16)
             v = torch.randn_like(k)
             mask = None
             if Lp > 0:

@@ -11,8 +11,9 @@ namespace {
 template <typename QT, bool FP8>
 cudaError_t launch_extend(const ExtendParams& p, int d, dim3 grid, cudaStream_t stream) {
   void (*fn)(const ExtendParams) = nullptr;
-  if (d == 64) fn = extend_kernel<QT, 64, FP8>;
-  else if (d == 128) fn = extend_kernel<QT, 128, FP8>;
+  const bool cap = p.logit_cap > 0.f;
+  if (d == 64) fn = cap ? extend_kernel<QT, 64, FP8, true> : extend_kernel<QT, 64, FP8, false>;
+  else if (d == 128) fn = cap ? extend_kernel<QT, 128, FP8, true> : extend_kernel<QT, 128, FP8, false>;
   if (!fn) return cudaErrorInvalidValue;
   const int smem = extend_smem_bytes(d);
   cudaError_t e = cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
@@ -22,12 +23,21 @@ cudaError_t launch_extend(const ExtendParams& p, int d, dim3 grid, cudaStream_t 
 }
 
 template <typename QT, bool FP8>
-cudaError_t launch_extend_tc(const ExtendParams& p, dim3 grid, bool small_q, cudaStream_t stream) {
+cudaError_t launch_extend_tc(const ExtendParams& p, int d, dim3 grid, bool small_q, cudaStream_t stream) {
   void (*fn)(const ExtendParams);
-  if (p.logit_cap > 0.f)
-    fn = small_q ? extend_tc_kernel<QT, FP8, true, true> : extend_tc_kernel<QT, FP8, false, true>;
-  else
-    fn = small_q ? extend_tc_kernel<QT, FP8, true, false> : extend_tc_kernel<QT, FP8, false, false>;
+  if constexpr (!FP8) {
+    if (d == 64) {  // head_dim 64: 16-bit pools without a logit cap (the caller checked)
+      fn = small_q ? extend_tc_kernel<QT, 64, false, true, false> : extend_tc_kernel<QT, 64, false, false, false>;
+    } else if (p.logit_cap > 0.f) {
+      fn = small_q ? extend_tc_kernel<QT, 128, false, true, true> : extend_tc_kernel<QT, 128, false, false, true>;
+    } else {
+      fn = small_q ? extend_tc_kernel<QT, 128, false, true, false> : extend_tc_kernel<QT, 128, false, false, false>;
+    }
+  } else if (p.logit_cap > 0.f) {
+    fn = small_q ? extend_tc_kernel<QT, 128, true, true, true> : extend_tc_kernel<QT, 128, true, false, true>;
+  } else {
+    fn = small_q ? extend_tc_kernel<QT, 128, true, true, false> : extend_tc_kernel<QT, 128, true, false, false>;
+  }
   cudaError_t e = cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, kTcSmemBytes);
   if (e != cudaSuccess) return e;
   fn<<<grid, kTcThreads, kTcSmemBytes, stream>>>(p);
@@ -190,9 +200,10 @@ extern "C" __attribute__((visibility("default"))) int b200attn_extend(const b200
   p.v_scale = v_scale;
 
   cudaStream_t stream = static_cast<cudaStream_t>(stream_);
-  // head_dim 128 with 16-byte aligned q / o rows runs on tcgen05 (extend_tc_kernel.cuh); head_dim 64 and
-  // odd layouts on the mma.sync kernel.
-  const bool tc_ok = a->head_dim == kTcD && !extend_force_mma() &&
+  // head_dim 128 (and 64 over a 16-bit pool without logit cap) with 16-byte aligned q / o rows runs on tcgen05
+  // (extend_tc_kernel.cuh); everything else on the mma.sync kernel.
+  const bool tc_ok = (a->head_dim == kTcD || (a->head_dim == 64 && !fp8 && !(a->logit_cap > 0.f))) &&
+                     !extend_force_mma() &&
                      !((reinterpret_cast<uintptr_t>(a->q) | reinterpret_cast<uintptr_t>(a->o)) & 15) &&
                      a->q_stride_token % 8 == 0 && a->q_stride_head % 8 == 0 && a->o_stride_token % 8 == 0 &&
                      a->o_stride_head % 8 == 0;
@@ -204,11 +215,11 @@ extern "C" __attribute__((visibility("default"))) int b200attn_extend(const b200
     // kernel splits each CTA's KV range over its two accumulators instead of leaving one idle
     const bool small_q = (static_cast<int64_t>(a->max_extend_len) << p.gp_shift) <= kTcBM;
     if (fp8)
-      err = a->q_dtype == B200ATTN_F16 ? launch_extend_tc<__half, true>(p, grid, small_q, stream)
-                                       : launch_extend_tc<__nv_bfloat16, true>(p, grid, small_q, stream);
+      err = a->q_dtype == B200ATTN_F16 ? launch_extend_tc<__half, true>(p, a->head_dim, grid, small_q, stream)
+                                       : launch_extend_tc<__nv_bfloat16, true>(p, a->head_dim, grid, small_q, stream);
     else
-      err = a->q_dtype == B200ATTN_F16 ? launch_extend_tc<__half, false>(p, grid, small_q, stream)
-                                       : launch_extend_tc<__nv_bfloat16, false>(p, grid, small_q, stream);
+      err = a->q_dtype == B200ATTN_F16 ? launch_extend_tc<__half, false>(p, a->head_dim, grid, small_q, stream)
+                                       : launch_extend_tc<__nv_bfloat16, false>(p, a->head_dim, grid, small_q, stream);
   } else {
     const int bm_tok = kExtRows >> p.gp_shift;
     dim3 grid((a->max_extend_len + bm_tok - 1) / bm_tok, a->num_kv_heads, a->batch);

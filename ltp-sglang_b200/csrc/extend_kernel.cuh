@@ -97,7 +97,9 @@ __device__ __forceinline__ void sts128(uint32_t addr, const uint4& v) {
 // of their shared-memory row and are widened in place to f16 (exact) once landed; both MMAs then run in
 // f16 (q converted and clamped like the decode kernel does), k_scale rides in the softmax scale and
 // v_scale in the final normalisation (FlashInfer's semantics, flashinfer_backend.py:560-567).
-template <typename QT, int D, bool FP8>
+// CAP: logit cap compiled in (as a run-time flag the compiler if-converts it and evaluates tanh for every
+// element of every tile, cap or not).
+template <typename QT, int D, bool FP8, bool CAP>
 __global__ void __launch_bounds__(kExtThreads, 1) extend_kernel(const ExtendParams p) {
   constexpr bool OUT_HALF = std::is_same<QT, __half>::value;
   constexpr bool HALF = OUT_HALF || FP8;     // MMA operand type
@@ -193,7 +195,7 @@ __global__ void __launch_bounds__(kExtThreads, 1) extend_kernel(const ExtendPara
   const bool row0 = hd0 < p.group && i0 < Le;
   const bool row1 = hd1 < p.group && i1 < Le;
   const int i_min_warp = tok0 + ((warp * 16) >> p.gp_shift);
-  const bool cap = p.logit_cap > 0.f;
+  constexpr bool cap = CAP;
   const float c = cap ? kLog2e : p.scale_log2;
   const float cap_pre = cap ? p.sm_scale / p.logit_cap : 0.f;
 
@@ -273,7 +275,7 @@ __global__ void __launch_bounds__(kExtThreads, 1) extend_kernel(const ExtendPara
                        kf[2], kf[3]);
       }
     }
-    if (cap) {
+    if constexpr (cap) {
 #pragma unroll
       for (int nt = 0; nt < NT; ++nt)
 #pragma unroll

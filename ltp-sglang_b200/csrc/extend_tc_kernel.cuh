@@ -37,7 +37,7 @@ constexpr int kTcMmaWarp = 20;
 constexpr int kTcThreads = 21 * 32;   // 16 softmax + 4 loader + 1 MMA warps, 80 registers each
 constexpr int kTcBM = 128;            // rows per sub-tile (TMEM lanes)
 constexpr int kTcBN = 128;            // kv tokens per tile
-constexpr int kTcD = 128;
+constexpr int kTcD = 128;            // widest head_dim; the shared / tensor memory geometry is laid out for it
 constexpr int kTcSlots = 4;           // K / V ring slots
 constexpr int kTcSlab = kTcBN * 128;  // bytes of one 64-element-wide slab of 128 rows
 constexpr int kTcSlotBytes = 2 * kTcSlab;
@@ -174,12 +174,17 @@ __device__ __forceinline__ void setmaxnreg_dec() {
 // CAP: logit cap (cap * tanh(x / cap)) compiled in.  As a run-time flag the compiler if-converted it: the
 // softmax loop evaluated tanh for every element and selected afterwards -- ~17 instructions and two extra
 // MUFU ops per element on a loop that is issue-bound -- although no Llama-class model sets a cap.
-template <typename QT, bool FP8, bool ALT, bool CAP>
+// D: head_dim 128 or 64.  64 keeps the 128-wide geometry (ring slots, O columns) and uses its first slab /
+// first 64 O columns: rows are one 128-byte swizzle atom wide, Q.K^T takes 4 k-steps, P.V has N = 64.
+template <typename QT, int D, bool FP8, bool ALT, bool CAP>
 __global__ void __launch_bounds__(kTcThreads, 1) extend_tc_kernel(const ExtendParams p) {
+  static_assert(D == 128 || (D == 64 && !FP8), "head_dim 128, or 64 over a 16-bit pool");
+  constexpr bool NARROW = FP8 || D == 64;  // a pool row (one head) is 128 bytes: 8 chunks, 8 rows per loader thread
+  constexpr int OH = D / 2;                // O columns per thread (two threads per row)
   constexpr bool OUT_HALF = std::is_same<QT, __half>::value;
   constexpr bool HALF = OUT_HALF || FP8;  // MMA operand type
   constexpr uint32_t IDESC_QK = umma_idesc(kTcBM, kTcBN, HALF ? 0 : 1, 0);
-  constexpr uint32_t IDESC_PV = umma_idesc(kTcBM, kTcD, HALF ? 0 : 1, 1);
+  constexpr uint32_t IDESC_PV = umma_idesc(kTcBM, D, HALF ? 0 : 1, 1);
 
   extern __shared__ uint8_t smem_raw[];
   const uint32_t smem0 = (smem_u32(smem_raw) + 1023u) & ~1023u;  // swizzle atoms are 1024-byte aligned
@@ -299,7 +304,7 @@ __global__ void __launch_bounds__(kTcThreads, 1) extend_tc_kernel(const ExtendPa
       const bool dead = ALT && (alt ? 0 : sub * kTcBM) + (warp & 3) * 32 >= rows_valid;
       const uint32_t lane_off = static_cast<uint32_t>((warp & 3) * 32) << 16;
       const uint32_t tS = tmem + lane_off + sub * kTcBN + half * 64;        // this thread's S columns
-      const uint32_t tO = tmem + lane_off + 2 * kTcBN + sub * kTcD + half * 64;
+      const uint32_t tO = tmem + lane_off + 2 * kTcBN + sub * kTcD + half * OH;
       constexpr bool cap = CAP;
       const float c = cap ? kLog2e : p.scale_log2;
       const float cap_pre = cap ? p.sm_scale / p.logit_cap : 0.f;
@@ -396,7 +401,7 @@ __global__ void __launch_bounds__(kTcThreads, 1) extend_tc_kernel(const ExtendPa
           if (it > 0) {
             // this sub-tile's previous PV has completed: its commit precedes the one that signalled s_full
 #pragma unroll
-            for (int cc = 0; cc < 64; cc += 32) {
+            for (int cc = 0; cc < OH; cc += 32) {
               float o[32];
               tmem_ld32<0>(tO + cc, o);
               tmem_wait_ld();
@@ -463,9 +468,9 @@ __global__ void __launch_bounds__(kTcThreads, 1) extend_tc_kernel(const ExtendPa
       TC_TR(13, 250);  // epilogue: O complete
       const float inv = l > 0.f ? p.v_scale / l : 0.f;
       QT* orow = reinterpret_cast<QT*>(p.o) + static_cast<int64_t>(q0 + (rv ? itok : 0)) * p.o_st +
-                 static_cast<int64_t>(h * p.group + (rv ? hd : 0)) * p.o_sh + half * 64;
+                 static_cast<int64_t>(h * p.group + (rv ? hd : 0)) * p.o_sh + half * OH;
 #pragma unroll
-      for (int cc = 0; cc < 64; cc += 32) {
+      for (int cc = 0; cc < OH; cc += 32) {
         float o[32];
         tmem_ld32<0>(tO + cc, o);
         tmem_wait_ld();
@@ -507,21 +512,25 @@ __global__ void __launch_bounds__(kTcThreads, 1) extend_tc_kernel(const ExtendPa
   if (warp < kTcMmaWarp) {
     // =============================== loaders (4 warps) ===============================
     const int tid = threadIdx.x - kTcLoaderWarp0 * 32;  // 0..127
-    const int chunk = tid & 15, rbase = tid >> 4;       // row = rbase + 8 * i
+    const int chunk = tid & 15, rbase = tid >> 4;       // 256-byte rows: row = rbase + 8 * i
     const uint32_t sw_col = static_cast<uint32_t>(chunk >> 3) * kTcSlab;
+    const int chunk8 = tid & 7, rb8 = tid >> 3;         // 128-byte rows (fp8, head_dim 64): row = rb8 + 16 * i
     // ---- Q: rows of both sub-tiles ----
     {
       const int gmask = (1 << p.gp_shift) - 1;
       const int nrows = nsub * kTcBM;
-      for (int i = 0; i < nrows / 8; ++i) {
-        const int R = rbase + 8 * i;
+      constexpr int QSTEP = D == 64 ? 16 : 8;
+      const int qchunk = D == 64 ? chunk8 : chunk, qrb = D == 64 ? rb8 : rbase;
+      for (int i = 0; i < nrows / QSTEP; ++i) {
+        const int R = qrb + QSTEP * i;
         const int itok = tok0 + (R >> p.gp_shift), hd = R & gmask;
         const bool ok = hd < p.group && itok < Le;
         const QT* src = reinterpret_cast<const QT*>(p.q) + (ok ? static_cast<int64_t>(q0 + itok) * p.q_st +
                                                                      static_cast<int64_t>(h * p.group + hd) * p.q_sh
-                                                               : 0) + chunk * 8;
+                                                               : 0) + qchunk * 8;
         const int rr = R & (kTcBM - 1);
-        const uint32_t dst = q_base + (R >> 7) * kTcSlotBytes + sw_col + rr * 128 + (((chunk & 7) ^ (rr & 7)) << 4);
+        const uint32_t dst = q_base + (R >> 7) * kTcSlotBytes + (D == 64 ? 0u : sw_col) + rr * 128 +
+                             (((qchunk & 7) ^ (rr & 7)) << 4);
         if constexpr (FP8 && !OUT_HALF) {  // bf16 q -> f16, clamped to the f16 range
           uint4 v = make_uint4(0u, 0u, 0u, 0u);
           if (ok) v = *reinterpret_cast<const uint4*>(src);
@@ -539,10 +548,8 @@ __global__ void __launch_bounds__(kTcThreads, 1) extend_tc_kernel(const ExtendPa
     }
     bool q_pub = false;
     // ---- K / V ring ----
-    // fp8: a row is 8 x 16 bytes, thread (rb8, chunk8) moves rows rb8 + 16 i
-    const int chunk8 = tid & 7, rb8 = tid >> 3;
-    const uint8_t* k_head = p.k_pool + static_cast<int64_t>(h) * kTcD * (FP8 ? 1 : 2) + (FP8 ? chunk8 : chunk) * 16;
-    const uint8_t* v_head = p.v_pool + static_cast<int64_t>(h) * kTcD * (FP8 ? 1 : 2) + (FP8 ? chunk8 : chunk) * 16;
+    const uint8_t* k_head = p.k_pool + static_cast<int64_t>(h) * D * (FP8 ? 1 : 2) + (NARROW ? chunk8 : chunk) * 16;
+    const uint8_t* v_head = p.v_pool + static_cast<int64_t>(h) * D * (FP8 ? 1 : 2) + (NARROW ? chunk8 : chunk) * 16;
     // stage st is complete for this thread: (fp8: widen it in place) and hand it to the MMA warp
     auto publish = [&](int st) {
       if constexpr (FP8) {
@@ -583,7 +590,7 @@ __global__ void __launch_bounds__(kTcThreads, 1) extend_tc_kernel(const ExtendPa
     // them with vector loads into registers BEFORE its first cp.async.  (Read one by one between the copies
     // -- each asm volatile cp.async orders the next shared load behind it -- the issue loop ran LDS ->
     // address -> LDGSTS serially, ~90 clk per copy, 1400 clk per stage: the whole kernel was bound by it.)
-    const int sid_pos = FP8 ? (tid & 15) * 8 + (tid >> 4) : (tid & 7) * 16 + (tid >> 3);
+    const int sid_pos = NARROW ? (tid & 15) * 8 + (tid >> 4) : (tid & 7) * 16 + (tid >> 3);
     sid[sid_pos] = load_id(0);
     sid[kTcBN + sid_pos] = load_id(1);
     int32_t pending = load_id(2);
@@ -612,16 +619,19 @@ __global__ void __launch_bounds__(kTcThreads, 1) extend_tc_kernel(const ExtendPa
       if (!is_v) named_bar_sync(3, 128);  // slot ids of this tile are visible
       const uint8_t* base = is_v ? v_head : k_head;
       const int64_t sb = is_v ? p.v_slot_bytes : p.k_slot_bytes;
-      if constexpr (FP8) {
+      if constexpr (NARROW) {
         const int4* idv = reinterpret_cast<const int4*>(sid + (tile & 3) * kTcBN + rb8 * 8);
         const int4 i0 = idv[0], i1 = idv[1];
         const int32_t ids[8] = {i0.x, i0.y, i0.z, i0.w, i1.x, i1.y, i1.z, i1.w};
-        const uint32_t dst0 = kv_base + slot * kTcSlotBytes + kTcSlab + chunk8 * 16;
+        // fp8: raw bytes, linear, into the upper slab (widened in place at publish time);
+        // head_dim 64: the row is the whole 128-byte swizzle atom of slab 0
+        const uint32_t dst0 = kv_base + slot * kTcSlotBytes + (FP8 ? kTcSlab + chunk8 * 16 : 0);
 #pragma unroll
         for (int i = 0; i < 8; ++i) {
           const int32_t sl = ids[i];
           const bool ok = sl >= 0;
-          cp_async16_zfill(dst0 + (rb8 + 16 * i) * 128, base + (ok ? sl : 0) * sb, ok);
+          const int row = rb8 + 16 * i;
+          cp_async16_zfill(dst0 + row * 128 + (FP8 ? 0 : ((chunk8 ^ (row & 7)) << 4)), base + (ok ? sl : 0) * sb, ok);
         }
       } else {
         const int4* idv = reinterpret_cast<const int4*>(sid + (tile & 3) * kTcBN + rbase * 16);
@@ -666,7 +676,7 @@ __global__ void __launch_bounds__(kTcThreads, 1) extend_tc_kernel(const ExtendPa
         const uint64_t b0 = dk + static_cast<uint32_t>(slot * (kTcSlotBytes >> 4));
         const uint32_t d = tmem + sub * kTcBN;
 #pragma unroll
-        for (int k = 0; k < kTcD / 16; ++k) {
+        for (int k = 0; k < D / 16; ++k) {
           const uint32_t off = ((k >> 2) * kTcSlab + (k & 3) * 32) >> 4;
           umma_ss(d, a0 + off, b0 + off, IDESC_QK, k > 0);
         }

@@ -104,6 +104,8 @@ SHAPES = [
     ("gqa7_d128", 28, 4, 128, 1, (40, 0), (50, 20)),
     ("gqa8_d128", 64, 8, 128, 1, (300,), (140,)),
     ("gqa16_d64", 32, 2, 64, 4, (10, 90), (33, 8)),
+    ("gqa4_d64_long", 32, 8, 64, 1, (300, 0, 1500), (140, 257, 3)),
+    ("mha_d64_tile_edges", 2, 2, 64, 16, (0, 0, 127, 128, 129), (128, 129, 1, 256, 257)),
     ("tile_edges", 8, 2, 128, 1, (0, 0, 0, 0, 63, 64, 65), (32, 33, 64, 65, 1, 1, 1)),
     ("many_short", 8, 2, 64, 1, tuple(range(0, 24)), tuple(1 + (i * 7) % 13 for i in range(24))),
 ]
@@ -144,6 +146,11 @@ def test_extend_fp8_window_and_cap():
     cfg = synth.Config("fp8_win", 2, 0, 8, 2, 128, kv_dtype="fp8_e4m3", k_scale=0.5, v_scale=2.0, seed=602)
     _run(cfg, (150, 10), (40, 70), window=16)
     _run(cfg, (150, 10), (40, 70), logit_cap=5.0)
+
+
+def test_extend_f16_d64():
+    cfg = synth.Config("f16d64", 2, 0, 16, 4, 64, kv_dtype="f16", q_dtype="f16", seed=106)
+    _run(cfg, (200, 0), (70, 133))
 
 
 def test_extend_noncausal():
