@@ -279,13 +279,13 @@ typedef struct {
   int32_t head_dim;
   int32_t v_head_dim;
   int32_t q_dtype;              /* B200ATTN_BF16 | B200ATTN_F16 */
-  int32_t kv_dtype;             /* == q_dtype (fp8 pools: not yet) */
+  int32_t kv_dtype;             /* == q_dtype, or B200ATTN_FP8_E4M3 (raw bytes; strides then count bytes) */
   int32_t causal;               /* 1: extend token i sees extend tokens j <= i */
   int32_t sliding_window;       /* <= 0: off */
   int32_t skip_prefix_custom_mask; /* 1 (the reference's default): custom_mask covers the extend part only */
   float sm_scale;
   float logit_cap;              /* 0 disables */
-  float k_scale, v_scale;       /* reserved for fp8 pools; 1.0 */
+  float k_scale, v_scale;       /* fp8 pools: K = k_scale * stored, V = v_scale * stored; ignored otherwise */
 } b200attn_extend_args;
 
 int b200attn_extend(const b200attn_extend_args* args, b200attn_stream_t stream);
