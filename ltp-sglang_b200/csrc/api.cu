@@ -29,16 +29,6 @@ int sm_count() {
   return n;
 }
 
-// Rows up to this many bytes are staged with 16-byte cp.async instead of one bulk copy per row.
-// B200ATTN_CPASYNC_MAX_ROW overrides the default (a tuning aid; read once).
-static int cp_async_max_row() {
-  static const int v = [] {
-    const char* e = getenv("B200ATTN_CPASYNC_MAX_ROW");
-    return e ? atoi(e) : 256;
-  }();
-  return v;
-}
-
 template <>
 cudaError_t launch_decode<__nv_bfloat16, false>(const DecodeParams&, int, bool, int, int, cudaStream_t);
 template <>
@@ -110,6 +100,10 @@ extern "C" __attribute__((visibility("default"))) int b200attn_decode(const b200
     return B200ATTN_E_ALIGN;
   if ((a->k_pool_stride_slot * e) % 16 != 0 || (a->v_pool_stride_slot * e) % 16 != 0)
     return B200ATTN_E_ALIGN;
+  // the producers form a row address as base + slot (u32) x slot bytes (u32)
+  if (a->k_pool_stride_slot <= 0 || a->v_pool_stride_slot <= 0 || a->k_pool_stride_slot * e > 0xffffffffll ||
+      a->v_pool_stride_slot * e > 0xffffffffll)
+    return B200ATTN_E_UNSUPPORTED;
   if ((reinterpret_cast<uintptr_t>(a->q) & 3) || a->q_stride_batch % 2 != 0 || a->q_stride_head % 2 != 0)
     return B200ATTN_E_ALIGN;
   if ((reinterpret_cast<uintptr_t>(a->plan) & 15) || (reinterpret_cast<uintptr_t>(a->ws_o) & 15))
@@ -149,7 +143,9 @@ extern "C" __attribute__((visibility("default"))) int b200attn_decode(const b200
   p.stages = g.stages;
   p.chunk_tokens = g.chunk_tokens;
   p.fuse_merge = a->phases == 0;
-  p.cp_async = g.row_bytes <= cp_async_max_row();
+  p.cp_async = g.cp_async;
+  p.swizzle = g.swizzle;
+  p.xch_off = a->phases == 0 ? g.xch_off : 0;  // K2 + K3 as separate launches keep every slice in the workspace
   p.unit_shift = 0;
   while ((16 << p.unit_shift) < g.row_bytes) ++p.unit_shift;
   p.sm_scale_k = a->sm_scale * a->k_scale;

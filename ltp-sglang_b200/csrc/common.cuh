@@ -8,6 +8,8 @@
 #include <cuda_runtime.h>
 #include <stdint.h>
 
+#include <cstdlib>
+
 #include "b200attn.h"
 
 namespace b200attn {
@@ -29,6 +31,7 @@ constexpr int kThreads = (kConsumerWarps + kProducerWarps) * 32;
 constexpr int kRowPad = 16;           // bytes
 constexpr int kBarrierBytes = 256;    // mbarrier area at the start of smem
 constexpr int kMaxStages = 8;
+constexpr int kXchWarps = 8;           // = kConsumerWarps: warps that exchange their slice state
 constexpr int kRangeRing = 16;        // range ids in flight between producers and consumers (> kMaxStages)
 constexpr int kRangeRingOff = 128;    // byte offsets inside the barrier area
 constexpr int kMergeFlagOff = 192;
@@ -44,11 +47,42 @@ struct Geometry {
   int group;         // q heads per kv head
   int chunk_tokens;  // 16 * ts
   int row_bytes;     // hc * head_dim * elem
-  int row_stride;    // row_bytes + pad
+  int row_stride;    // row_bytes + pad, or row_bytes (swizzled rows)
   int stage_bytes;   // K + V
   int stages;
   int smem_bytes;
+  int cp_async;      // rows staged by 16-byte cp.async (<= 512 B) instead of one bulk copy per row
+  int swizzle;       // cp.async path: unpadded rows, 16-byte unit u of row r at u ^ (r & 7)
+  int xch_off;       // byte offset of the slice-exchange area (whole requests merge their ts token slices
+                     // inside the CTA), 0 = none
 };
+
+// Tuning aids, read once: B200ATTN_CPASYNC_MAX_ROW (default and maximum 512: one warp instruction covers at
+// most one 512-byte row), B200ATTN_NO_SWIZZLE=1 (padded rows on the cp.async path), B200ATTN_NO_XCH=1 (token
+// slices always merged through the global workspace).
+inline int cp_async_max_row() {
+  static const int v = [] {
+    const char* e = getenv("B200ATTN_CPASYNC_MAX_ROW");
+    const int x = e ? atoi(e) : 512;
+    return x > 512 ? 512 : x;
+  }();
+  return v;
+}
+inline bool env_flag(const char* name) {
+  const char* e = getenv(name);
+  return e && e[0] == '1';
+}
+inline bool no_swizzle() {
+  static const bool v = env_flag("B200ATTN_NO_SWIZZLE");
+  return v;
+}
+inline bool no_xch() {
+  static const bool v = env_flag("B200ATTN_NO_XCH");
+  return v;
+}
+// Slice exchange: per consumer warp [head_dim / 8 tiles][group * 4 lanes] float2 of unnormalised O, then
+// [8 warps][8 rows] float2 (max in log2 units, sum).
+inline int xch_bytes(int group, int d) { return kXchWarps * (d / 8) * group * 4 * 8 + kXchWarps * 8 * 8; }
 
 __host__ __device__ inline int elem_bytes(int dtype) { return dtype == B200ATTN_FP8_E4M3 ? 1 : 2; }
 
@@ -69,13 +103,24 @@ inline bool make_geometry(int hq, int hkv, int d, int kv_dtype, Geometry* g) {
   g->group = group;
   g->chunk_tokens = 16 * g->ts;
   g->row_bytes = hc * d * e;
-  g->row_stride = g->row_bytes + kRowPad;
+  g->cp_async = g->row_bytes <= cp_async_max_row();
+  g->swizzle = g->cp_async && (d * e) % 128 == 0 && !no_swizzle();  // heads start on 128-byte lines
+  g->row_stride = g->swizzle ? g->row_bytes : g->row_bytes + kRowPad;
   g->stage_bytes = 2 * g->chunk_tokens * g->row_stride;
   int stages = (kMaxSmem - kBarrierBytes) / g->stage_bytes;
   if (stages > kMaxStages) stages = kMaxStages;
   if (stages < 2) return false;
+  g->xch_off = 0;
+  int xb = 0;
+  if (g->ts > 1 && group <= 8 && !no_xch()) {  // only where it costs no pipeline stage
+    xb = xch_bytes(group, d);
+    int with = (kMaxSmem - kBarrierBytes - xb) / g->stage_bytes;
+    if (with > kMaxStages) with = kMaxStages;
+    if (with == stages) g->xch_off = kBarrierBytes + stages * g->stage_bytes;
+    else xb = 0;
+  }
   g->stages = stages;
-  g->smem_bytes = kBarrierBytes + stages * g->stage_bytes;
+  g->smem_bytes = kBarrierBytes + stages * g->stage_bytes + xb;
   return true;
 }
 

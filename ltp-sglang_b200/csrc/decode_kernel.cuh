@@ -51,6 +51,8 @@ struct DecodeParams {
   int32_t cp_async;              // 1: producers use 16-byte cp.async (small rows), 0: one bulk copy per row
   int32_t fuse_merge;            // 1: the CTA that writes a request's last partial merges it (no K3 launch)
   int32_t unit_shift;            // log2(row_bytes / 16)
+  int32_t swizzle;               // 1: stage rows unpadded, 16-byte unit u of row r at u ^ (r & 7) (cp.async path)
+  int32_t xch_off;               // smem offset of the slice-exchange area (0 = none): whole requests merge in the CTA
   float scale_log2;              // sm_scale * k_scale * log2(e)
   float sm_scale_k;              // sm_scale * k_scale
   float logit_cap;
@@ -185,17 +187,35 @@ __global__ void __launch_bounds__(kThreads, 1) decode_kernel(const DecodeParams 
     const uint8_t* pool = which ? p.v_pool : p.k_pool;
     const int64_t slot_bytes = which ? p.v_slot_bytes : p.k_slot_bytes;
     if (p.cp_async) {
-      // Small rows (<= 256 B): a bulk copy is issued per row at ~20 clk / row / SM whatever its
-      // size (4.2 TB/s at 256 B, 2.0 TB/s at 128 B, profiles/ r01 tp-sim), so rows are moved as
-      // 16-byte cp.async units instead: one warp instruction carries 512 B (6.1 / 4.2 TB/s).
-      // From 512 B up the bulk copy wins (its issue costs the SM nothing).  Warp (tensor, half)
+      // Small rows (<= 512 B): a bulk copy is issued per row at ~20 clk / row / SM whatever its
+      // size (4.2 TB/s at 256 B, 2.0 TB/s at 128 B, 6.2 at 512 B, profiles/ r01 tp-sim), so rows are
+      // moved as 16-byte cp.async units instead: one warp instruction carries 512 B (6.4 TB/s at 512 B,
+      // 6.1-6.5 at 256 B, 4.4 at 128 B = the memory system's own random-row ceiling, tools/gather_roofline.cu).
+      // From 1 KB up the bulk copy is used (its issue costs the SM nothing).  Warp (tensor, half)
       // owns tokens [half * T/2, (half + 1) * T/2) of every chunk; lane l holds the slot ids of
       // tokens l and l + 32 of that range (one chunk ahead) and hands them out by shuffle.
+      // The issue loop is the producers' whole job and was this path's bound (ncu r01 tp8: ~31 instructions
+      // per LDGSTS, producer warps never idle, consumers starved): everything lane-invariant is hoisted, a copy
+      // costs one shuffle (slot id), one 32 x 32 -> 64 bit multiply-add (address), the copy, two adds.
       const int ush = p.unit_shift;
       const int umask = (1 << ush) - 1;
       const int Tw = T >> 1;
-      const int n_instr = (Tw << ush) >> 5;  // multiple of 8: a tensor-chunk is >= 8 KB
       const int tbase = par * Tw;
+      const int rsh = 5 - ush;                 // log2(rows one warp instruction covers)
+      const int rpi = 1 << rsh;
+      const int r_in = lane >> ush;            // this lane's row inside an instruction
+      const int col = (lane & umask) << 4;     // this lane's 16-byte unit inside the row
+      const uint32_t sb32 = static_cast<uint32_t>(slot_bytes);  // < 2^32: checked by the host
+      const uint32_t dstep = static_cast<uint32_t>(rpi) * p.row_stride;
+      // destination unit of this lane in instruction i: i & 7 decides (rows advance by rpi = 1, 2 or 4 per
+      // instruction; every issue run starts on a row that is a multiple of 8 and is a multiple of 8 long,
+      // except over 64-byte rows, which are never swizzled)
+      uint32_t scol[8];
+#pragma unroll
+      for (int j = 0; j < 8; ++j)
+        scol[j] = p.swizzle ? static_cast<uint32_t>((lane & umask) ^ ((r_in + j * rpi) & 7)) << 4 : static_cast<uint32_t>(col);
+      const int cnt0 = (Tw < 32 ? Tw : 32) >> rsh;  // instructions fed by the ids of tokens [0, 32) / [32, 64)
+      const int cnt1 = (Tw > 32 ? Tw - 32 : 0) >> rsh;
       while (rg < R) {
         // Claim the range after this one now; the ticket is only looked at when this range's last
         // chunk is issued, so the atomic's round trip (microseconds under load) hides behind the copies.
@@ -226,17 +246,30 @@ __global__ void __launch_bounds__(kThreads, 1) decode_kernel(const DecodeParams 
           const int nvalid = S - lc * T - tbase;  // valid tokens of this warp's range (may be <= 0)
           mbar_wait(bar_empty + stage * 8, phase ^ 1);
           const uint32_t full = bar_full + stage * 8;
-          const uint32_t dst = stage0 + stage * p.stage_bytes + (which ? v_off : 0u) + tbase * p.row_stride;
-#pragma unroll 8
-          for (int i = 0; i < n_instr; ++i) {
-            const int u = i * 32 + lane;
-            const int tl = u >> ush;
-            const int col = (u & umask) << 4;
-            const int32_t s0 = __shfl_sync(0xffffffffu, cur0, tl & 31);
-            const int32_t s1 = __shfl_sync(0xffffffffu, cur1, tl & 31);
-            const int32_t slot = tl < 32 ? s0 : s1;
-            if (tl < nvalid)
-              cp_async16(dst + tl * p.row_stride + col, base + static_cast<int64_t>(slot) * slot_bytes + col);
+          uint32_t dstp = stage0 + stage * p.stage_bytes + (which ? v_off : 0u) + (tbase + r_in) * p.row_stride;
+          const uint8_t* bl = base + col;
+          auto issue = [&](auto pred_tag, int32_t cur, int cnt, int tl) {
+            constexpr bool PRED = decltype(pred_tag)::value;
+            int srcl = r_in;
+            for (int i = 0; i < cnt; i += 8) {  // cnt is a multiple of 8, or 4 (64-byte rows)
+#pragma unroll
+              for (int j = 0; j < 8; ++j) {
+                if (j == 4 && cnt == 4) break;
+                const uint32_t sl = static_cast<uint32_t>(__shfl_sync(0xffffffffu, cur, srcl));
+                const uint8_t* src = bl + static_cast<uint64_t>(sl) * sb32;
+                if (!PRED || tl < nvalid) cp_async16(dstp + scol[j], src);
+                srcl += rpi;
+                dstp += dstep;
+                if constexpr (PRED) tl += rpi;
+              }
+            }
+          };
+          if (nvalid >= Tw) {  // every chunk but a request's last
+            issue(std::false_type{}, cur0, cnt0, 0);
+            issue(std::false_type{}, cur1, cnt1, 0);
+          } else {
+            issue(std::true_type{}, cur0, cnt0, r_in);
+            issue(std::true_type{}, cur1, cnt1, 32 + r_in);
           }
           if (pw == 0 && lane == 0 && --walk.left == 0) {
             rq[(rn + 1) & (kRangeRing - 1)] = next_rg;  // published before this range's last arrival
@@ -324,15 +357,31 @@ __global__ void __launch_bounds__(kThreads, 1) decode_kernel(const DecodeParams 
   const float cap_pre = cap ? p.sm_scale_k / p.logit_cap : 0.f;
 
   // lane-constant parts of the ldmatrix addresses (bytes inside a stage)
-  uint32_t k_lane, v_lane;
-  if constexpr (!FP8) {
-    k_lane = (tsi * 16 + mr) * p.row_stride + h * D * 2 + mat * 16;
-    v_lane = (tsi * 16 + (mat & 1) * 8 + mr) * p.row_stride + h * D * 2 + (mat >> 1) * 16;
-  } else {
-    k_lane = (tsi * 16 + mr) * p.row_stride + h * D + mat * 16;
-    v_lane = (tsi * 16 + (mat & 1) * 8 + mr) * p.row_stride + h * D + (mat >> 1) * 16;
+  // Two stage layouts.  Padded (bulk-copy path): row stride = row bytes + 16, so the 8 rows of an ldmatrix
+  // fall into distinct bank groups.  Swizzled (cp.async path): row stride = row bytes and the 16-byte unit u of
+  // row r sits at u ^ (r & 7) -- a quarter warp of LDGSTS then writes one aligned 128-byte line.  (With the
+  // padded rows each quarter warp straddled two lines, L1 split the instruction into ~10 wavefronts instead
+  // of 4 and fetched 1.5x the sectors from L2, with 2x the tag lookups: ncu r01 tp8.)  Every row a lane
+  // addresses has r & 7 == mr, and a head starts on a 128-byte boundary, so the swizzle folds into
+  // lane-constant offsets: K unit (mat + 4 k) ^ mr = (mat ^ (mr & 3)) + 4 ((k & 1) ^ (mr >> 2)) + 8 (k >> 1),
+  // V unit ((mat >> 1) + 2 n) ^ mr = ((mat >> 1) ^ (mr & 1)) + 2 ((n & 3) ^ (mr >> 1)) + 8 (n >> 2).
+  const bool swz = p.swizzle != 0;
+  const uint32_t head_off = h * D * EB;
+  uint32_t k_lane[2], v_lane;
+  {
+    const uint32_t krow = (tsi * 16 + mr) * p.row_stride + head_off;
+    const uint32_t vrow = (tsi * 16 + (mat & 1) * 8 + mr) * p.row_stride + head_off + v_off;
+    if (swz) {
+      k_lane[0] = krow + 16 * ((mat ^ (mr & 3)) + 4 * (mr >> 2));
+      k_lane[1] = krow + 16 * ((mat ^ (mr & 3)) + 4 * ((mr >> 2) ^ 1));
+      v_lane = vrow + 16 * ((mat >> 1) ^ (mr & 1));
+    } else {
+      k_lane[0] = krow + mat * 16;
+      k_lane[1] = k_lane[0] + 64;
+      v_lane = vrow + (mat >> 1) * 16;
+    }
   }
-  v_lane += v_off;
+  const uint32_t v_x = swz ? (mr >> 1) * 32 : 0u;
 
   if (H.n_empty > 0) {
     // Requests of length 0 have no chunks, so no range reaches them: their rows are defined here
@@ -408,12 +457,13 @@ __global__ void __launch_bounds__(kThreads, 1) decode_kernel(const DecodeParams 
 #pragma unroll
       for (int nt = 0; nt < 2; ++nt) {
         s[nt][0] = s[nt][1] = s[nt][2] = s[nt][3] = 0.f;
-        const uint32_t ka = sbase + k_lane + nt * 8 * p.row_stride;
+        const uint32_t ka0 = sbase + k_lane[0] + nt * 8 * p.row_stride;
+        const uint32_t ka1 = sbase + k_lane[1] + nt * 8 * p.row_stride;
         if constexpr (!FP8) {
 #pragma unroll
           for (int k2 = 0; k2 < KSTEPS / 2; ++k2) {
             uint32_t kf[4];
-            ldsm_x4(ka + k2 * 64, kf);
+            ldsm_x4(((k2 & 1) ? ka1 : ka0) + (k2 >> 1) * 128, kf);
             mma_q<HALF, ROWS16, QR>(s[nt], qf[2 * k2], kf[0], kf[1]);
             mma_q<HALF, ROWS16, QR>(s[nt], qf[2 * k2 + 1], kf[2], kf[3]);
           }
@@ -421,7 +471,7 @@ __global__ void __launch_bounds__(kThreads, 1) decode_kernel(const DecodeParams 
 #pragma unroll
           for (int k4 = 0; k4 < KSTEPS / 4; ++k4) {
             uint32_t kf[4];
-            ldsm_x4(ka + k4 * 64, kf);
+            ldsm_x4(((k4 & 1) ? ka1 : ka0) + (k4 >> 1) * 128, kf);
 #pragma unroll
             for (int mm = 0; mm < 4; ++mm) {
               const int kk = 4 * k4 + mm;
@@ -518,7 +568,7 @@ __global__ void __launch_bounds__(kThreads, 1) decode_kernel(const DecodeParams 
   #pragma unroll
           for (int n2 = 0; n2 < NTILES / 2; ++n2) {
             uint32_t vf[4];
-            ldsm_x4_trans(va + n2 * 32, vf);
+            ldsm_x4_trans(va + (((n2 & 3) * 32) ^ v_x) + (n2 >> 2) * 128, vf);
             if constexpr (ROWS16) {
               mma16816<HALF>(o[2 * n2], pa0, pa1, pa2, pa3, vf[0] & m0, vf[1] & m1);
               mma16816<HALF>(o[2 * n2 + 1], pa0, pa1, pa2, pa3, vf[2] & m0, vf[3] & m1);
@@ -539,7 +589,7 @@ __global__ void __launch_bounds__(kThreads, 1) decode_kernel(const DecodeParams 
   #pragma unroll
           for (int n4 = 0; n4 < NTILES / 4; ++n4) {
             uint32_t vf[4];
-            ldsm_x4_trans(va + n4 * 32, vf);
+            ldsm_x4_trans(va + (((n4 & 3) * 32) ^ v_x) + (n4 >> 2) * 128, vf);
   #pragma unroll
             for (int gg = 0; gg < 2; ++gg) {
   #pragma unroll
@@ -583,7 +633,8 @@ __global__ void __launch_bounds__(kThreads, 1) decode_kernel(const DecodeParams 
       inv1 = l1 > 0.f ? p.v_scale / l1 : 0.f;
       lse1 = l1 > 0.f ? m1 * c * kLn2 + logf(l1) : -CUDART_INF_F;
     }
-    const bool whole = p.ts == 1 && lc0 == 0 && lc1 == nchunks;
+    const bool full_req = lc0 == 0 && lc1 == nchunks;
+    const bool whole = p.ts == 1 && full_req;
     // column (head-dim index) of accumulator element e (0/1) of tile n
     auto col_of = [&](int n, int e) -> int {
       if constexpr (!FP8) return n * 8 + 2 * jq + e;
@@ -610,6 +661,57 @@ __global__ void __launch_bounds__(kThreads, 1) decode_kernel(const DecodeParams 
           if (p.lse && jq == 0) p.lse[static_cast<int64_t>(b) * p.hq + hq0 + gq + 8] = lse1;
         }
       }
+    } else if (!ROWS16 && full_req && p.xch_off != 0) {
+      // A whole request, cut into ts token slices only by this CTA's own warps: the slices meet in shared
+      // memory (unnormalised O, max, sum) and each warp finishes 1 / ts of the head's columns.  Through the
+      // workspace the same merge cost a write -> fence -> atomic -> read-back chain of global round trips
+      // (~3 us per request with the consumers idle: 7 % of a 4096-token request on the 8-way shard shape).
+      const int g4 = p.group * 4;
+      float2* xall = reinterpret_cast<float2*>(smem + p.xch_off);
+      float2* xml = xall + kXchWarps * NTILES * g4;
+      const int li = gq * 4 + jq;
+      if (row0) {
+        float2* xo = xall + warp * (NTILES * g4) + li;
+#pragma unroll
+        for (int n = 0; n < NTILES; ++n) xo[n * g4] = make_float2(o[n][0], o[n][1]);
+        if (jq == 0) xml[warp * 8 + gq] = make_float2(l0 > 0.f ? m0 * c : -CUDART_INF_F, l0);
+      }
+      named_bar_sync(2, kConsumerWarps * 32);
+      if (row0) {
+        float wgt[kXchWarps];
+        float mm = -CUDART_INF_F;
+#pragma unroll
+        for (int s = 0; s < kXchWarps; ++s)
+          if (s < p.ts) mm = fmaxf(mm, xml[(s * p.hc + h) * 8 + gq].x);
+        float L = 0.f;
+#pragma unroll
+        for (int s = 0; s < kXchWarps; ++s) {
+          wgt[s] = 0.f;
+          if (s < p.ts) {
+            const float2 ml = xml[(s * p.hc + h) * 8 + gq];
+            wgt[s] = ml.y > 0.f ? fast_exp2(ml.x - mm) : 0.f;
+            L = fmaf(wgt[s], ml.y, L);
+          }
+        }
+        const float inv = L > 0.f ? p.v_scale / L : 0.f;
+        QT* o0 = reinterpret_cast<QT*>(p.o) + b * p.o_sb + (hq0 + gq) * p.o_sh;
+        for (int n = tsi; n < NTILES; n += p.ts) {
+          float a0 = 0.f, a1 = 0.f;
+#pragma unroll
+          for (int s = 0; s < kXchWarps; ++s) {
+            if (s < p.ts) {
+              const float2 v = xall[(s * p.hc + h) * (NTILES * g4) + n * g4 + li];
+              a0 = fmaf(wgt[s], v.x, a0);
+              a1 = fmaf(wgt[s], v.y, a1);
+            }
+          }
+          store_q(o0 + col_of(n, 0), a0 * inv);
+          store_q(o0 + col_of(n, 1), a1 * inv);
+        }
+        if (p.lse && jq == 0 && tsi == 0)
+          p.lse[static_cast<int64_t>(b) * p.hq + hq0 + gq] = L > 0.f ? mm * kLn2 + logf(L) : -CUDART_INF_F;
+      }
+      named_bar_sync(2, kConsumerWarps * 32);  // the area is free for the next request
     } else {
       const int hqv = p.hc * p.group;
       const int64_t row = (static_cast<int64_t>(vreq + rg) * p.ts + tsi) * hqv + h * p.group + gq;

@@ -198,6 +198,7 @@ extern "C" __attribute__((visibility("default"))) int b200attn_extend(const b200
   p.scale_log2 = p.sm_scale * kLog2e;
   p.logit_cap = a->logit_cap;
   p.v_scale = v_scale;
+  p.batch = a->batch;
 
   cudaStream_t stream = static_cast<cudaStream_t>(stream_);
   // head_dim 128 (and 64 over a 16-bit pool without logit cap) with 16-byte aligned q / o rows runs on tcgen05

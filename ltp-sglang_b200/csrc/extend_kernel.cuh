@@ -53,6 +53,7 @@ struct ExtendParams {
   float sm_scale;
   float logit_cap;
   float v_scale;
+  int32_t batch;
 };
 
 __host__ __device__ inline int extend_smem_bytes(int d) {

@@ -209,6 +209,8 @@ SHAPES = [
     ("gqa12_d128", 2, 12, 1, 128, 1, (300, 600)),
     ("mha32_d128", 2, 32, 32, 128, 1, (50, 400)),
     ("hkv3", 3, 12, 3, 64, 1, (30, 500)),
+    ("gqa4_d64_tp8", 5, 4, 1, 64, 1, (1, 900)),      # 128-byte rows: swizzled cp.async stage, 4 rows per copy
+    ("gqa8_d64_hkv2", 4, 16, 2, 64, 16, (100, 777)),  # two 128-byte heads per 256-byte row
 ]
 
 
@@ -580,8 +582,19 @@ def test_fused_merge_equals_two_stage(dyn, tp, monkeypatch):
         l1 = torch.full((B * Hq,), float("nan"), dtype=torch.float32, device=DEV)
         run(0, o1, l1)
         torch.cuda.synchronize()
-        assert torch.equal(o1, o2), f"launch {it}: fused merge differs from K2 + K3"
-        assert torch.equal(l1, l2)
+        if tp == 1:
+            assert torch.equal(o1, o2), f"launch {it}: fused merge differs from K2 + K3"
+            assert torch.equal(l1, l2)
+        else:
+            # token slices (ts = 8): in the one-launch form a request that one CTA holds whole is merged in
+            # shared memory from the unnormalised slice states, not through the workspace -- the same sum
+            # in another order, so equal to rounding (a bf16 ulp is 2^-8), and bit-stable across launches
+            torch.testing.assert_close(o1.float(), o2.float(), rtol=1.6e-2, atol=2e-3)
+            torch.testing.assert_close(l1, l2, rtol=0, atol=1e-5)
+            if it == 0:
+                o_first, l_first = o1, l1
+            else:
+                assert torch.equal(o1, o_first) and torch.equal(l1, l_first), f"launch {it} differs from launch 0"
     # and against the oracle on a few requests
     from oracle import decode_oracle as oracle
 
