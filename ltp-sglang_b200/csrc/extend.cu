@@ -2,7 +2,7 @@
 // launch of extend_kernel (extend_kernel.cuh).
 #include <cstdlib>
 
-#include "extend_tc_kernel.cuh"
+#include "extend_tc_smallq.cuh"
 
 using namespace b200attn;
 
@@ -42,6 +42,39 @@ cudaError_t launch_extend_tc(const ExtendParams& p, int d, dim3 grid, bool small
   if (e != cudaSuccess) return e;
   fn<<<grid, kTcThreads, kTcSmemBytes, stream>>>(p);
   return cudaGetLastError();
+}
+
+// Small-q batches (no request has more than 128 (token, head) rows): the persistent kernel of
+// extend_tc_smallq.cuh, one CTA per SM looping over (request, kv head) items.
+template <typename QT, bool FP8>
+cudaError_t launch_extend_tc_smallq(const ExtendParams& p, int d, int items, cudaStream_t stream) {
+  void (*fn)(const ExtendParams);
+  if constexpr (!FP8) {
+    if (d == 64) fn = extend_tc_smallq_kernel<QT, 64, false, false>;
+    else fn = p.logit_cap > 0.f ? extend_tc_smallq_kernel<QT, 128, false, true> : extend_tc_smallq_kernel<QT, 128, false, false>;
+  } else {
+    fn = p.logit_cap > 0.f ? extend_tc_smallq_kernel<QT, 128, true, true> : extend_tc_smallq_kernel<QT, 128, true, false>;
+  }
+  cudaError_t e = cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, kSqSmemBytes);
+  if (e != cudaSuccess) return e;
+  const int sms = sm_count();
+  fn<<<items < sms ? items : sms, kTcThreads, kSqSmemBytes, stream>>>(p);
+  return cudaGetLastError();
+}
+
+// Small-q batches have two kernels (measured, tools/time_smallq.py, profiles/r01_smallq_persistent_vs_oneshot.txt):
+// the persistent one wins wherever per-item overhead matters -- prefixes up to ~1k tokens (1.05-1.27x), every
+// fp8 pool (1.02-1.55x: the in-place widening hides behind the next item's loads) -- the one-CTA-per-item kernel
+// on long 16-bit prefixes (1.07-1.17x at 4k-16k tokens: its loader loop is leaner; at 80 registers per thread the
+// persistent loader's extra cursor state costs ~500 instructions per stage).  The host does not know the prefix
+// lengths (device arrays), so the default goes by pool type; B200ATTN_SMALLQ=persistent|oneshot forces one
+// (a test / tuning aid; read once).
+int smallq_mode() {
+  static const int v = [] {
+    const char* e = getenv("B200ATTN_SMALLQ");
+    return !e ? 0 : e[0] == 'p' ? 1 : e[0] == 'o' ? 2 : 0;
+  }();
+  return v;
 }
 
 // B200ATTN_EXTEND_IMPL=mma forces the mma.sync kernel (a test / tuning aid; read once).
@@ -215,7 +248,15 @@ extern "C" __attribute__((visibility("default"))) int b200attn_extend(const b200
     // every request has at most 128 (token, head) rows -- decode-like and TARGET_VERIFY batches: the small-q
     // kernel splits each CTA's KV range over its two accumulators instead of leaving one idle
     const bool small_q = (static_cast<int64_t>(a->max_extend_len) << p.gp_shift) <= kTcBM;
-    if (fp8)
+    if (small_q && (smallq_mode() == 1 || (smallq_mode() == 0 && fp8))) {
+      const int items = a->batch * a->num_kv_heads;
+      if (fp8)
+        err = a->q_dtype == B200ATTN_F16 ? launch_extend_tc_smallq<__half, true>(p, a->head_dim, items, stream)
+                                         : launch_extend_tc_smallq<__nv_bfloat16, true>(p, a->head_dim, items, stream);
+      else
+        err = a->q_dtype == B200ATTN_F16 ? launch_extend_tc_smallq<__half, false>(p, a->head_dim, items, stream)
+                                         : launch_extend_tc_smallq<__nv_bfloat16, false>(p, a->head_dim, items, stream);
+    } else if (fp8)
       err = a->q_dtype == B200ATTN_F16 ? launch_extend_tc<__half, true>(p, a->head_dim, grid, small_q, stream)
                                        : launch_extend_tc<__nv_bfloat16, true>(p, a->head_dim, grid, small_q, stream);
     else

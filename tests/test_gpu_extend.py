@@ -327,3 +327,16 @@ def test_extend_full_size_split_invariance():
     half = run_extend(backend, runner, w2, layer, save_kv_cache=False).view(2048, 32, 128).float()
     torch.cuda.synchronize()
     assert (half - whole[2048:]).abs().max().item() <= 2e-2
+
+
+@pytest.mark.parametrize("mode", ["persistent", "oneshot"])
+def test_small_q_kernels_forced(mode):
+    """Small-q batches (verify / decode-like) have two kernels, chosen by pool type; B200ATTN_SMALLQ forces one
+    (read once per process, hence the subprocess): the small-q cases of this file must pass on either."""
+    import os, subprocess, sys
+    env = dict(os.environ, B200ATTN_SMALLQ=mode)
+    r = subprocess.run([sys.executable, "-m", "pytest", os.path.abspath(__file__), "-q", "-x", "-m", "gpu", "-p", "no:cacheprovider",
+                        "-k", "(verify or mask or fp8 or decode_like or draft or golden or shapes) and not forced"],
+                       env=env, capture_output=True, text=True, timeout=600)
+    assert r.returncode == 0, r.stdout[-3000:] + r.stderr[-2000:]
+    assert " passed" in r.stdout
