@@ -43,7 +43,7 @@
 extern "C" {
 #endif
 
-#define B200ATTN_ABI_VERSION 3
+#define B200ATTN_ABI_VERSION 4
 
 /* cudaStream_t without pulling in the CUDA headers. */
 typedef void* b200attn_stream_t;
@@ -286,6 +286,9 @@ typedef struct {
   float sm_scale;
   float logit_cap;              /* 0 disables */
   float k_scale, v_scale;       /* fp8 pools: K = k_scale * stored, V = v_scale * stored; ignored otherwise */
+  int32_t avg_kv_len_hint;      /* ABI 4.  Mean prefix + extend length per request if the host knows it (sglang:
+                                   seq_lens_sum / batch_size, forward_batch_info.py:163-311), 0 = unknown.  Only
+                                   picks between the two small-q kernels (same results); never read for sizes */
 } b200attn_extend_args;
 
 int b200attn_extend(const b200attn_extend_args* args, b200attn_stream_t stream);

@@ -130,6 +130,7 @@ class ExtendMetadata:
     mask_indptr: Optional[torch.Tensor]
     max_extend_len: Optional[int]             # None: bounded by the token count at forward time
     window_kv_indptr: Optional[torch.Tensor] = None
+    avg_kv_len: int = 0                       # seq_lens_sum / batch when the host knows it (eager forwards): kernel choice only
 
 
 class B200AttnBackend(AttentionBackend):
@@ -266,6 +267,10 @@ class B200AttnBackend(AttentionBackend):
             return
         qo, kv, win = self.qo_indptr[: bs + 1], self.extend_kv_indptr[: bs + 1], None
         rpi = req_pool_indices[:bs]
+        # host-side length hint (forward_batch.seq_lens_sum, forward_batch_info.py:163-311); a captured graph
+        # has none -- its kernel choice is fixed at capture
+        sls = getattr(forward_batch, "seq_lens_sum", None) if forward_batch is not None else None
+        avg = int(sls) // bs if sls else 0
         if mode.is_target_verify():
             # prefix = the whole committed sequence, extend = num_draft_tokens per request, visibility
             # inside the draft tree from spec_info.custom_mask (:227-263)
@@ -275,12 +280,12 @@ class B200AttnBackend(AttentionBackend):
                 pl = pl.to(rpi.dtype)
             mi = self.mask_indptr[: bs + 1]
             torch.ops.b200attn.extend_plan(None, pl, qo, kv, mi, n, 0)
-            self.extend_metadata = ExtendMetadata(bs, qo, kv, None, rpi, pl, spec_info.custom_mask, mi, n)
+            self.extend_metadata = ExtendMetadata(bs, qo, kv, None, rpi, pl, spec_info.custom_mask, mi, n, None, avg)
         elif mode.is_draft_extend():
             kv_indices, kv_indptr, qo_indptr, custom_mask = spec_info.generate_attn_arg_prefill(
                 req_pool_indices, seq_lens, None, self.req_to_token)   # :265-279
             self.extend_metadata = ExtendMetadata(bs, qo_indptr, kv_indptr, kv_indices, None, None,
-                                                  custom_mask, None, None)
+                                                  custom_mask, None, None, None, avg)
         else:
             pl, el = forward_batch.extend_prefix_lens[:bs], forward_batch.extend_seq_lens[:bs]
             if pl.dtype != rpi.dtype:
@@ -293,7 +298,7 @@ class B200AttnBackend(AttentionBackend):
                 torch.ops.b200attn.extend_plan(el, pl, qo, win, None, 0, self.sliding_window_size)
             cpu = getattr(forward_batch, "extend_seq_lens_cpu", None)
             self.extend_metadata = ExtendMetadata(bs, qo, kv, None, rpi, pl, None, None,
-                                                  max(cpu) if cpu else None, win)
+                                                  max(cpu) if cpu else None, win, avg)
 
     def init_cuda_graph_state(self, max_bs: int, max_num_tokens: int):
         if self.materialize_kv_indices:
@@ -438,7 +443,7 @@ class B200AttnBackend(AttentionBackend):
             int(sw) if windowed else -1, True, float(layer.scaling),
             float(getattr(layer, "logit_cap", 0.0) or 0.0),
             float(k_scale) if (fp8 and k_scale is not None) else 1.0,
-            float(v_scale) if (fp8 and v_scale is not None) else 1.0)
+            float(v_scale) if (fp8 and v_scale is not None) else 1.0, int(md.avg_kv_len))
         return o
 
     def lse_extend(self, tokens: int) -> torch.Tensor:

@@ -19,7 +19,7 @@ E_INVALID, E_UNSUPPORTED, E_ALIGN, E_CUDA, E_WORKSPACE = -1, -2, -3, -4, -5
 BF16, F16, FP8_E4M3 = 0, 1, 2
 I32, I64 = 0, 1
 SCALE_NONE, SCALE_TRUE_DIV, SCALE_RECIP_MUL = 0, 1, 2
-ABI_VERSION = 3
+ABI_VERSION = 4
 
 
 class KvStoreArgs(C.Structure):
@@ -169,6 +169,7 @@ class ExtendArgs(C.Structure):
         ("logit_cap", C.c_float),
         ("k_scale", C.c_float),
         ("v_scale", C.c_float),
+        ("avg_kv_len_hint", C.c_int32),
     ]
 
 

@@ -243,7 +243,7 @@ def _decode(q, k_pool, v_pool, o, lse, plan_buf, indices, workspace, sm_scale, l
 
 def _extend(q, o, lse, k_pool, v_pool, qo_indptr, kv_indptr, kv_indices, req_to_token, req_pool_indices,
             prefix_lens, extend_loc, custom_mask, mask_indptr, max_extend_len, causal, sliding_window,
-            skip_prefix_custom_mask, sm_scale, logit_cap, k_scale=1.0, v_scale=1.0):
+            skip_prefix_custom_mask, sm_scale, logit_cap, k_scale=1.0, v_scale=1.0, avg_kv_len=0):
     """Extend / prefill attention over cached prefix + new tokens (``extend_attention_fwd``,
     triton_ops/extend_attention.py:306-438); the new tokens' K/V are read from the pool at
     ``extend_loc`` (``out_cache_loc``), where ``kv_store`` has put them.  An fp8-e4m3 pool is read as
@@ -307,6 +307,7 @@ def _extend(q, o, lse, k_pool, v_pool, qo_indptr, kv_indptr, kv_indices, req_to_
     a.sliding_window = sliding_window
     a.skip_prefix_custom_mask = 1 if skip_prefix_custom_mask else 0
     a.sm_scale, a.logit_cap, a.k_scale, a.v_scale = sm_scale, logit_cap, k_scale, v_scale
+    a.avg_kv_len_hint = max(0, min(int(avg_kv_len), 2**31 - 1))
     with torch.cuda.device(q.device):
         capi.check("b200attn_extend", capi.lib().b200attn_extend(C.byref(a), _stream(q)))
 
@@ -390,7 +391,7 @@ _LIB.define(
     "Tensor kv_indptr, Tensor? kv_indices, Tensor? req_to_token, Tensor? req_pool_indices, "
     "Tensor? prefix_lens, Tensor extend_loc, Tensor? custom_mask, Tensor? mask_indptr, int max_extend_len, "
     "bool causal, int sliding_window, bool skip_prefix_custom_mask, float sm_scale, float logit_cap, "
-    "float k_scale=1.0, float v_scale=1.0) -> ()"
+    "float k_scale=1.0, float v_scale=1.0, int avg_kv_len=0) -> ()"
 )
 _LIB.define(
     "extend_plan(Tensor? extend_seq_lens, Tensor prefix_lens, Tensor(a!) qo_indptr, Tensor(b!) kv_indptr, "

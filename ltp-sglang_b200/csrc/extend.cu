@@ -67,7 +67,8 @@ cudaError_t launch_extend_tc_smallq(const ExtendParams& p, int d, int items, cud
 // fp8 pool (1.02-1.55x: the in-place widening hides behind the next item's loads) -- the one-CTA-per-item kernel
 // on long 16-bit prefixes (1.07-1.17x at 4k-16k tokens: its loader loop is leaner; at 80 registers per thread the
 // persistent loader's extra cursor state costs ~500 instructions per stage).  The host does not know the prefix
-// lengths (device arrays), so the default goes by pool type; B200ATTN_SMALLQ=persistent|oneshot forces one
+// lengths (device arrays) unless the caller passes avg_kv_len_hint (sglang has seq_lens_sum on the host): the
+// default goes by pool type and, when given, by the hint; B200ATTN_SMALLQ=persistent|oneshot forces one
 // (a test / tuning aid; read once).
 int smallq_mode() {
   static const int v = [] {
@@ -248,7 +249,10 @@ extern "C" __attribute__((visibility("default"))) int b200attn_extend(const b200
     // every request has at most 128 (token, head) rows -- decode-like and TARGET_VERIFY batches: the small-q
     // kernel splits each CTA's KV range over its two accumulators instead of leaving one idle
     const bool small_q = (static_cast<int64_t>(a->max_extend_len) << p.gp_shift) <= kTcBM;
-    if (small_q && (smallq_mode() == 1 || (smallq_mode() == 0 && fp8))) {
+    // auto: fp8 pools, and 16-bit pools whose mean KV length the host gave as at most 2048 tokens
+    const bool sq_persistent = smallq_mode() == 1 ||
+                               (smallq_mode() == 0 && (fp8 || (a->avg_kv_len_hint > 0 && a->avg_kv_len_hint <= 2048)));
+    if (small_q && sq_persistent) {
       const int items = a->batch * a->num_kv_heads;
       if (fp8)
         err = a->q_dtype == B200ATTN_F16 ? launch_extend_tc_smallq<__half, true>(p, a->head_dim, items, stream)
