@@ -478,17 +478,22 @@ __global__ void __launch_bounds__(kTcThreads, 1) extend_tc_smallq_kernel(const E
             cp_async16_zfill(dst0 + row * 128 + (FP8 ? 0 : ((chunk8 ^ (row & 7)) << 4)), base + (ok ? sl : 0) * sb, ok);
           }
         } else {
+          // two batches of 8 rows: ids of a batch in registers before its copies (an asm volatile copy orders
+          // the next shared load behind it), and half the addresses live at once -- this loop runs at the
+          // kernel's 80-register budget
           const int4* idv = reinterpret_cast<const int4*>(sidt + rbase * 16);
-          const int4 i0 = idv[0], i1 = idv[1], i2 = idv[2], i3 = idv[3];
-          const int32_t ids[16] = {i0.x, i0.y, i0.z, i0.w, i1.x, i1.y, i1.z, i1.w,
-                                   i2.x, i2.y, i2.z, i2.w, i3.x, i3.y, i3.z, i3.w};
-          const uint32_t dst0 = kv_base + slot * kTcSlotBytes + sw_col;
+          // row & 7 == rbase & 7 for every row of this thread: one swizzled column offset
+          const uint32_t dst0 = kv_base + slot * kTcSlotBytes + sw_col + rbase * 128 + (((chunk & 7) ^ (rbase & 7)) << 4);
 #pragma unroll
-          for (int i = 0; i < 16; ++i) {
-            const int row = rbase + 8 * i;
-            const int32_t sl = ids[i];
-            const bool ok = sl >= 0;
-            cp_async16_zfill(dst0 + row * 128 + (((chunk & 7) ^ (row & 7)) << 4), base + (ok ? sl : 0) * sb, ok);
+          for (int hb = 0; hb < 2; ++hb) {
+            const int4 i0 = idv[2 * hb], i1 = idv[2 * hb + 1];
+            const int32_t ids[8] = {i0.x, i0.y, i0.z, i0.w, i1.x, i1.y, i1.z, i1.w};
+#pragma unroll
+            for (int i = 0; i < 8; ++i) {
+              const int32_t sl = ids[i];
+              const bool ok = sl >= 0;
+              cp_async16_zfill(dst0 + (hb * 8 + i) * (8 * 128), base + (ok ? sl : 0) * sb, ok);
+            }
           }
         }
         cp_async_commit();
