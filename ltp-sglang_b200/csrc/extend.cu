@@ -192,6 +192,10 @@ extern "C" __attribute__((visibility("default"))) int b200attn_extend(const b200
   if (!(a->sm_scale > 0.f) || a->logit_cap < 0.f) return B200ATTN_E_INVALID;
   if ((reinterpret_cast<uintptr_t>(a->k_pool) | reinterpret_cast<uintptr_t>(a->v_pool)) & 15) return B200ATTN_E_ALIGN;
   if ((a->k_pool_stride_slot * esz) % 16 != 0 || (a->v_pool_stride_slot * esz) % 16 != 0) return B200ATTN_E_ALIGN;
+  // the loaders form a row address as base + slot (u32) x slot bytes (u32)
+  if (a->k_pool_stride_slot <= 0 || a->v_pool_stride_slot <= 0 || a->k_pool_stride_slot * esz > 0xffffffffll ||
+      a->v_pool_stride_slot * esz > 0xffffffffll)
+    return B200ATTN_E_UNSUPPORTED;
   if ((reinterpret_cast<uintptr_t>(a->q) & 3) || a->q_stride_token % 2 != 0 || a->q_stride_head % 2 != 0)
     return B200ATTN_E_ALIGN;
   if ((reinterpret_cast<uintptr_t>(a->o) & 3) || a->o_stride_token % 2 != 0 || a->o_stride_head % 2 != 0)

@@ -618,7 +618,7 @@ __global__ void __launch_bounds__(kTcThreads, 1) extend_tc_kernel(const ExtendPa
       }
       if (!is_v) named_bar_sync(3, 128);  // slot ids of this tile are visible
       const uint8_t* base = is_v ? v_head : k_head;
-      const int64_t sb = is_v ? p.v_slot_bytes : p.k_slot_bytes;
+      const uint32_t sb = static_cast<uint32_t>(is_v ? p.v_slot_bytes : p.k_slot_bytes);  // < 2^32 (host check): one 32 x 32 -> 64 mad per row address
       if constexpr (NARROW) {
         const int4* idv = reinterpret_cast<const int4*>(sid + (tile & 3) * kTcBN + rb8 * 8);
         const int4 i0 = idv[0], i1 = idv[1];
@@ -631,7 +631,7 @@ __global__ void __launch_bounds__(kTcThreads, 1) extend_tc_kernel(const ExtendPa
           const int32_t sl = ids[i];
           const bool ok = sl >= 0;
           const int row = rb8 + 16 * i;
-          cp_async16_zfill(dst0 + row * 128 + (FP8 ? 0 : ((chunk8 ^ (row & 7)) << 4)), base + (ok ? sl : 0) * sb, ok);
+          cp_async16_zfill(dst0 + row * 128 + (FP8 ? 0 : ((chunk8 ^ (row & 7)) << 4)), base + static_cast<uint64_t>(static_cast<uint32_t>(ok ? sl : 0)) * sb, ok);
         }
       } else {
         const int4* idv = reinterpret_cast<const int4*>(sid + (tile & 3) * kTcBN + rbase * 16);
@@ -644,7 +644,7 @@ __global__ void __launch_bounds__(kTcThreads, 1) extend_tc_kernel(const ExtendPa
           const int row = rbase + 8 * i;
           const int32_t sl = ids[i];
           const bool ok = sl >= 0;
-          cp_async16_zfill(dst0 + row * 128 + (((chunk & 7) ^ (row & 7)) << 4), base + (ok ? sl : 0) * sb, ok);
+          cp_async16_zfill(dst0 + row * 128 + (((chunk & 7) ^ (row & 7)) << 4), base + static_cast<uint64_t>(static_cast<uint32_t>(ok ? sl : 0)) * sb, ok);
         }
       }
       cp_async_commit();

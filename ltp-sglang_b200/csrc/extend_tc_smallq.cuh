@@ -463,7 +463,7 @@ __global__ void __launch_bounds__(kTcThreads, 1) extend_tc_smallq_kernel(const E
           }
         }
         const uint8_t* base = is_v ? v_head : k_head;
-        const int64_t sb = is_v ? p.v_slot_bytes : p.k_slot_bytes;
+        const uint32_t sb = static_cast<uint32_t>(is_v ? p.v_slot_bytes : p.k_slot_bytes);  // < 2^32 (host check): one 32 x 32 -> 64 mad per row address
         const int32_t* sidt = sid + ((vt0 + tile) & 3) * kTcBN;
         if constexpr (NARROW) {
           const int4* idv = reinterpret_cast<const int4*>(sidt + rb8 * 8);
@@ -475,7 +475,7 @@ __global__ void __launch_bounds__(kTcThreads, 1) extend_tc_smallq_kernel(const E
             const int32_t sl = ids[i];
             const bool ok = sl >= 0;
             const int row = rb8 + 16 * i;
-            cp_async16_zfill(dst0 + row * 128 + (FP8 ? 0 : ((chunk8 ^ (row & 7)) << 4)), base + (ok ? sl : 0) * sb, ok);
+            cp_async16_zfill(dst0 + row * 128 + (FP8 ? 0 : ((chunk8 ^ (row & 7)) << 4)), base + static_cast<uint64_t>(static_cast<uint32_t>(ok ? sl : 0)) * sb, ok);
           }
         } else {
           // two batches of 8 rows: ids of a batch in registers before its copies (an asm volatile copy orders
@@ -492,7 +492,7 @@ __global__ void __launch_bounds__(kTcThreads, 1) extend_tc_smallq_kernel(const E
             for (int i = 0; i < 8; ++i) {
               const int32_t sl = ids[i];
               const bool ok = sl >= 0;
-              cp_async16_zfill(dst0 + (hb * 8 + i) * (8 * 128), base + (ok ? sl : 0) * sb, ok);
+              cp_async16_zfill(dst0 + (hb * 8 + i) * (8 * 128), base + static_cast<uint64_t>(static_cast<uint32_t>(ok ? sl : 0)) * sb, ok);
             }
           }
         }
