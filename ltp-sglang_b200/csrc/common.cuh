@@ -57,14 +57,14 @@ struct Geometry {
                      // inside the CTA), 0 = none
 };
 
-// Tuning aids, read once: B200ATTN_CPASYNC_MAX_ROW (default 512: wider rows are faster as bulk copies),
+// Tuning aids, read once: B200ATTN_CPASYNC_MAX_ROW (default and maximum 512: wider rows go as bulk copies),
 // B200ATTN_NO_SWIZZLE=1 (padded rows on the cp.async path), B200ATTN_NO_XCH=1 (token slices always merged
 // through the global workspace).
 inline int cp_async_max_row() {
   static const int v = [] {
     const char* e = getenv("B200ATTN_CPASYNC_MAX_ROW");
     const int x = e ? atoi(e) : 512;
-    return x > kMaxRowBytes ? kMaxRowBytes : x;
+    return x > 512 ? 512 : x;  // one warp instruction covers at most one 512-byte row
   }();
   return v;
 }

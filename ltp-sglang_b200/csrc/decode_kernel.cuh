@@ -191,17 +191,16 @@ __global__ void __launch_bounds__(kThreads, 1) decode_kernel(const DecodeParams 
       // size (4.2 TB/s at 256 B, 2.0 TB/s at 128 B, 6.2 at 512 B, profiles/ r01 tp-sim), so rows are
       // moved as 16-byte cp.async units instead: one warp instruction carries 512 B (6.4 TB/s at 512 B,
       // 6.1-6.5 at 256 B, 4.4 at 128 B = the memory system's own random-row ceiling, tools/gather_roofline.cu).
-      // From 1 KB up the bulk copy is used (its issue costs the SM nothing; measured with
-      // B200ATTN_CPASYNC_MAX_ROW=2048: 1 KB rows 4.98 TB/s as cp.async against 6.75 as bulk copies, 2 KB rows 6.62
-      // against 6.68).  Warp (tensor, half)
+      // From 1 KB up the bulk copy is used (its issue costs the SM nothing).  A variant of this loop that
+      // also covered wider rows (several instructions per row, a run-time inner loop) was measured and dropped:
+      // no gain at 2 KB (6.62 against 6.68 TB/s), and the inner loop cost the 256- / 512-byte shapes 25 %.
+      // Warp (tensor, half)
       // owns tokens [half * T/2, (half + 1) * T/2) of every chunk; lane l holds the slot ids of
       // tokens l and l + 32 of that range (one chunk ahead) and hands them out by shuffle.
       // The issue loop is the producers' whole job and was this path's bound (ncu r01 tp8: ~31 instructions
       // per LDGSTS, producer warps never idle, consumers starved): everything lane-invariant is hoisted, a copy
       // costs one shuffle (slot id), one 32 x 32 -> 64 bit multiply-add (address), the copy, two adds.
-      // rows wider than 512 bytes take `segs` instructions, 512 bytes apart in the row
-      const int ush = p.unit_shift < 5 ? p.unit_shift : 5;  // log2(16-byte units of a row one instruction covers)
-      const int segs = 1 << (p.unit_shift - ush);
+      const int ush = p.unit_shift;  // <= 5: this path serves rows of at most 512 bytes (one warp instruction)
       const int umask = (1 << ush) - 1;
       const int Tw = T >> 1;
       const int tbase = par * Tw;
@@ -261,10 +260,7 @@ __global__ void __launch_bounds__(kThreads, 1) decode_kernel(const DecodeParams 
                 if (j == 4 && cnt == 4) break;
                 const uint32_t sl = static_cast<uint32_t>(__shfl_sync(0xffffffffu, cur, srcl));
                 const uint8_t* src = bl + static_cast<uint64_t>(sl) * sb32;
-                if (!PRED || tl < nvalid) {
-                  cp_async16(dstp + scol[j], src);
-                  for (int sg = 1; sg < segs; ++sg) cp_async16(dstp + scol[j] + sg * 512, src + sg * 512);
-                }
+                if (!PRED || tl < nvalid) cp_async16(dstp + scol[j], src);
                 srcl += rpi;
                 dstp += dstep;
                 if constexpr (PRED) tl += rpi;
