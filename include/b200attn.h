@@ -43,7 +43,7 @@
 extern "C" {
 #endif
 
-#define B200ATTN_ABI_VERSION 4
+#define B200ATTN_ABI_VERSION 5
 
 /* cudaStream_t without pulling in the CUDA headers. */
 typedef void* b200attn_stream_t;
@@ -330,6 +330,38 @@ typedef struct {
 } b200attn_merge_states_args;
 
 int b200attn_merge_states(const b200attn_merge_states_args* args, b200attn_stream_t stream);
+
+/* ------------------------------------------------------------------ */
+/* Multi-step draft decode: kv_indptr / kv_indices of every draft step  */
+/* ------------------------------------------------------------------ */
+/* Replaces the Triton kernel generate_draft_decode_kv_indices
+ * (python/sglang/srt/speculative/eagle_utils.py:844-920) that TritonMultiStepDraftBackend launches once per
+ * draft forward with grid (num_steps, num_seqs, topk) (layers/attention/triton_backend.py:779-809).  Step `it`
+ * (iters = it + 1), sequence s, branch t own the CSR row z = s * topk + t of step it:
+ *   kv_indices[it][sum_{i<s} S_i * topk + s * iters * topk + t * (S_s + iters) + j]
+ *       = req_to_token[req_s, j]                       for j < S_s            (the committed prefix)
+ *       = req_to_token[req_s, ext + j - S_s]           for S_s <= j < S_s + iters (the branch's draft tokens)
+ *     ext = S_s + t * num_steps when page_size == 1 or topk == 1, else
+ *           S_s / P * P + t * ceil((S_s % P + num_steps) / P) * P + S_s % P    (each branch owns whole pages)
+ *   kv_indptr[it][z] = sum(positions[0 .. z)) + z * iters; row 0 writes entry num_seqs * topk (the total), so
+ *                      entry 0 is never written: the caller zero-initialises kv_indptr once.
+ * positions[z] is the position of row z's newest token (= S_s for every branch of sequence s). */
+typedef struct {
+  const void* req_pool_indices;  /* [num_seqs] int32|int64 */
+  const int32_t* req_to_token;   /* [max_reqs, stride] */
+  int64_t req_to_token_stride;
+  const void* seq_lens;          /* [num_seqs] int32|int64 (paged_kernel_lens) */
+  int32_t index_dtype;           /* B200ATTN_I32 | B200ATTN_I64 (req_pool_indices, seq_lens) */
+  int32_t positions_dtype;       /* B200ATTN_I32 | B200ATTN_I64 */
+  const void* positions;         /* [num_seqs * topk] */
+  int32_t* kv_indices;           /* out [num_steps, kv_indices_stride] */
+  int64_t kv_indices_stride;     /* elements between steps */
+  int32_t* kv_indptr;            /* out [num_steps, kv_indptr_stride] */
+  int64_t kv_indptr_stride;
+  int32_t num_steps, num_seqs, topk, page_size;
+} b200attn_draft_kv_indices_args;
+
+int b200attn_draft_kv_indices(const b200attn_draft_kv_indices_args* args, b200attn_stream_t stream);
 
 /* ------------------------------------------------------------------ */
 /* misc                                                                */

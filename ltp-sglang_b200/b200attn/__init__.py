@@ -8,7 +8,7 @@ from . import capi
 capi.lib()
 
 from . import ops  # noqa: E402  (registers torch.ops.b200attn.*)
-from .backend import B200AttnBackend, ExtendMetadata, ForwardMetadata, rope_store_kv, store_kv  # noqa: E402
+from .backend import B200AttnBackend, B200MultiStepDraftBackend, ExtendMetadata, ForwardMetadata, rope_store_kv, store_kv  # noqa: E402
 from .interfaces import (  # noqa: E402
     AttentionBackend,
     AttentionType,
@@ -23,6 +23,7 @@ __all__ = [
     "capi",
     "ops",
     "B200AttnBackend",
+    "B200MultiStepDraftBackend",
     "ForwardMetadata",
     "ExtendMetadata",
     "store_kv",

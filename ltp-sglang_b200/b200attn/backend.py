@@ -28,7 +28,7 @@ from typing import Any, Optional
 import torch
 
 from . import capi, ops
-from .interfaces import AttentionBackend
+from .interfaces import AttentionBackend, ForwardMode
 
 
 def store_kv(k_pool: torch.Tensor, v_pool: torch.Tensor, loc: torch.Tensor, cache_k: torch.Tensor,
@@ -134,10 +134,15 @@ class ExtendMetadata:
 
 
 class B200AttnBackend(AttentionBackend):
-    def __init__(self, model_runner: Any, prefill_backend: Optional[AttentionBackend] = None,
+    def __init__(self, model_runner: Any, skip_prefill: bool = False, kv_indptr_buf: Optional[torch.Tensor] = None,
+                 prefill_backend: Optional[AttentionBackend] = None,
                  materialize_kv_indices: bool = False, max_ctas: int = 0, min_chunks: int = 0,
                  return_lse: bool = False):
+        """``skip_prefill`` / ``kv_indptr_buf``: the two constructor arguments the multi-step draft wrapper
+        passes (triton_backend.py:41-61, 761-769): no extend-side buffers, and a caller-owned ``kv_indptr`` row
+        of ``[max_bs * topk + 1]`` entries."""
         super().__init__()
+        self.skip_prefill = skip_prefill
         capi.lib()  # fail here, loudly, if the CUDA library has not been built
         self.device = torch.device(model_runner.device)
         if self.device.type != "cuda":
@@ -179,41 +184,88 @@ class B200AttnBackend(AttentionBackend):
         self.max_context_len = getattr(mc, "context_len", self.req_to_token.shape[1])
 
         dev = self.device
-        self.plan_buf = torch.zeros(ops.plan_bytes(self.max_bs), dtype=torch.uint8, device=dev)
-        ws = ops.workspace_bytes(self.max_bs, self.num_head, self.num_kv_head, self.head_dim,
+        sa = getattr(model_runner, "server_args", None)
+        self.num_draft_tokens = getattr(sa, "speculative_num_draft_tokens", None)
+        self.speculative_num_steps = getattr(sa, "speculative_num_steps", None)
+        self.speculative = getattr(sa, "speculative_algorithm", None) is not None or kv_indptr_buf is not None
+        # Rows one decode launch may carry: a speculative draft step runs topk branches per request through the
+        # CSR plan (kv_indptr.numel() - 1 = bs * topk rows, triton_backend.py:206-208), so every per-row buffer
+        # is sized for that, not for req_to_token_pool.size alone.
+        topk = int(getattr(sa, "speculative_eagle_topk", None) or 1)
+        self.max_rows = self.max_bs * max(1, topk)
+        if kv_indptr_buf is not None:
+            self.max_rows = max(self.max_rows, kv_indptr_buf.numel() - 1)
+        self.plan_buf = torch.zeros(ops.plan_bytes(self.max_rows), dtype=torch.uint8, device=dev)
+        ws = ops.workspace_bytes(self.max_rows, self.num_head, self.num_kv_head, self.head_dim,
                                  self.v_head_dim, self.kv_dtype)
         self.workspace = torch.empty(ws // 4, dtype=torch.float32, device=dev)
-        self.kv_indptr = torch.zeros(self.max_bs + 1, dtype=torch.int32, device=dev)
+        if kv_indptr_buf is None:
+            self.kv_indptr = torch.zeros(self.max_rows + 1, dtype=torch.int32, device=dev)
+        else:
+            if kv_indptr_buf.dtype != torch.int32 or not kv_indptr_buf.is_contiguous():
+                raise TypeError("kv_indptr_buf must be a contiguous int32 tensor")
+            self.kv_indptr = kv_indptr_buf
         self.window_plan_buf = self.window_kv_indptr = None
         if self.sliding_window_size is not None:   # two sets of buffers, as triton_backend.py:77-90
             self.window_plan_buf = torch.zeros_like(self.plan_buf)
             self.window_kv_indptr = torch.zeros_like(self.kv_indptr)
         self.cuda_graph_window_kv_indices: Optional[torch.Tensor] = None
-        self.lse = torch.empty(self.max_bs * self.num_head, dtype=torch.float32, device=dev) if return_lse else None
+        self.lse = torch.empty(self.max_rows * self.num_head, dtype=torch.float32, device=dev) if return_lse else None
         self.cuda_graph_kv_indices: Optional[torch.Tensor] = None
         self.forward_metadata: Optional[ForwardMetadata] = None
         # extend (prefill) path: index buffers as triton_backend.py:92-99
-        self.qo_indptr = torch.zeros(self.max_bs + 1, dtype=torch.int32, device=dev)
-        self.extend_kv_indptr = torch.zeros(self.max_bs + 1, dtype=torch.int32, device=dev)
-        self.extend_window_kv_indptr = torch.zeros_like(self.extend_kv_indptr) \
-            if self.sliding_window_size is not None else None
-        self.mask_indptr = torch.zeros(self.max_bs + 1, dtype=torch.int64, device=dev)
-        sa = getattr(model_runner, "server_args", None)
-        self.num_draft_tokens = getattr(sa, "speculative_num_draft_tokens", None)
+        self.qo_indptr = self.extend_kv_indptr = self.extend_window_kv_indptr = self.mask_indptr = None
+        if not skip_prefill:
+            self.qo_indptr = torch.zeros(self.max_bs + 1, dtype=torch.int32, device=dev)
+            self.extend_kv_indptr = torch.zeros(self.max_bs + 1, dtype=torch.int32, device=dev)
+            self.extend_window_kv_indptr = torch.zeros_like(self.extend_kv_indptr) \
+                if self.sliding_window_size is not None else None
+            self.mask_indptr = torch.zeros(self.max_bs + 1, dtype=torch.int64, device=dev)
         self.extend_metadata: Optional[ExtendMetadata] = None
+        # CUDA-graph state (init_cuda_graph_state): static copies of everything a captured kernel reads that the
+        # runner hands over afresh on every replay (spec_info tensors, triton_backend.py:445-501, 575-619)
+        self.cuda_graph_custom_mask: Optional[torch.Tensor] = None
+        self.cg_req_pool_indices = self.cg_prefix_lens = self.cg_extend_lens = None
+        self.cg_max_bs = self.cg_max_num_tokens = 0
 
     # ------------------------------------------------------------------ #
     # metadata
     # ------------------------------------------------------------------ #
+    def _ensure_graph_kv_indices(self, need: int = 0) -> None:
+        """``cuda_graph_kv_indices`` (triton_backend.py:357-364).  Decode reads req_to_token in place, so the
+        buffer only exists where something consumes a flat list: materialised indices, or speculative CSR
+        input.  Allocated by init_cuda_graph_state when that is known up front, else by the first capture
+        hook that needs it (the hook runs before the capture begins, cuda_graph_runner.py:618)."""
+        if self.cuda_graph_kv_indices is None:
+            n = max(need, max(self.cg_max_num_tokens, 1) * self.max_context_len)
+            self.cuda_graph_kv_indices = torch.zeros(n, dtype=torch.int32, device=self.device)
+
     def _plan(self, bs: int, req_pool_indices: torch.Tensor, seq_lens: torch.Tensor,
               seq_lens_sum: Optional[int], spec_info: Any, graph: bool) -> None:
         if bs > self.max_bs:
             raise ValueError(f"batch {bs} exceeds req_to_token_pool.size {self.max_bs}")
         if spec_info is not None:
+            # speculative draft decode: the CSR lists come from spec_info (triton_backend.py:206-208)
             kv_indptr, kv_indices = spec_info.kv_indptr, spec_info.kv_indices
+            rows = kv_indptr.numel() - 1
+            if rows > self.max_rows:
+                raise ValueError(f"speculative decode batch of {rows} rows exceeds the {self.max_rows} rows this backend "
+                                 "was sized for (req_to_token_pool.size * speculative_eagle_topk)")
+            if graph:
+                # A captured decode kernel keeps the addresses it was launched with, and CudaGraphRunner hands the
+                # replay hook a fresh spec_info every step (cuda_graph_runner.py:760-768): the lists are copied
+                # into the backend's static buffers, as the reference does (triton_backend.py:574-576).
+                self._ensure_graph_kv_indices(kv_indices.numel())
+                if kv_indices.numel() > self.cuda_graph_kv_indices.numel():
+                    raise ValueError("spec_info.kv_indices is longer than cuda_graph_kv_indices")
+                if kv_indptr.data_ptr() != self.kv_indptr.data_ptr():
+                    self.kv_indptr[: rows + 1].copy_(kv_indptr)
+                if kv_indices.data_ptr() != self.cuda_graph_kv_indices.data_ptr():
+                    self.cuda_graph_kv_indices[: kv_indices.numel()].copy_(kv_indices)
+                kv_indptr, kv_indices = self.kv_indptr[: rows + 1], self.cuda_graph_kv_indices
             torch.ops.b200attn.plan_csr(kv_indptr, self.plan_buf, self.num_head, self.num_kv_head,
                                         self.head_dim, self.kv_dtype, self.max_ctas, self.min_chunks)
-            self.forward_metadata = ForwardMetadata(kv_indptr.numel() - 1, kv_indices, kv_indptr, kv_indices)
+            self.forward_metadata = ForwardMetadata(rows, kv_indices, kv_indptr, kv_indices)
             return
         kv_indices = window_kv_indices = None
         if self.materialize_kv_indices:
@@ -256,10 +308,14 @@ class B200AttnBackend(AttentionBackend):
                               mode, forward_batch.spec_info, forward_batch)
 
     def _plan_extend(self, bs: int, req_pool_indices: torch.Tensor, seq_lens: torch.Tensor, mode,
-                     spec_info: Any, forward_batch: Any = None) -> None:
+                     spec_info: Any, forward_batch: Any = None, graph: Optional[str] = None) -> None:
         """Metadata of the native extend path: what ``TritonAttnBackend.init_forward_metadata`` builds
         for its three extend modes (triton_backend.py:227-318), in one launch and without
-        materialising ``kv_indices`` for the cached prefix."""
+        materialising ``kv_indices`` for the cached prefix.  ``graph`` = "capture" / "replay": every array
+        a captured kernel reads lives in a buffer this backend owns and is refilled here
+        (triton_backend.py:445-501, 579-623)."""
+        if self.skip_prefill:
+            raise RuntimeError("B200AttnBackend was built with skip_prefill=True: no extend path")
         if bs > self.max_bs:
             raise ValueError(f"batch {bs} exceeds req_to_token_pool.size {self.max_bs}")
         if bs == 0:
@@ -271,22 +327,53 @@ class B200AttnBackend(AttentionBackend):
         # has none -- its kernel choice is fixed at capture
         sls = getattr(forward_batch, "seq_lens_sum", None) if forward_batch is not None else None
         avg = int(sls) // bs if sls else 0
+        if graph is not None:
+            if self.cg_req_pool_indices is None or bs > self.cg_req_pool_indices.numel():
+                raise RuntimeError("init_cuda_graph_state was not run (or max_bs was smaller than this batch)")
+            # static int64 copies: copy_ converts the runner's int32 buffers without allocating
+            self.cg_req_pool_indices[:bs].copy_(rpi)
+            self.cg_prefix_lens[:bs].copy_(seq_lens[:bs])
+            rpi, pl_static = self.cg_req_pool_indices[:bs], self.cg_prefix_lens[:bs]
         if mode.is_target_verify():
             # prefix = the whole committed sequence, extend = num_draft_tokens per request, visibility
             # inside the draft tree from spec_info.custom_mask (:227-263)
             n = int(getattr(spec_info, "draft_token_num", None) or self.num_draft_tokens)
-            pl = seq_lens[:bs]
-            if pl.dtype != rpi.dtype:
-                pl = pl.to(rpi.dtype)
+            mask = spec_info.custom_mask
+            if graph is not None:
+                pl = pl_static
+                if mask is not None:
+                    if mask.numel() > self.cuda_graph_custom_mask.numel():
+                        raise ValueError("spec_info.custom_mask is longer than cuda_graph_custom_mask")
+                    self.cuda_graph_custom_mask[: mask.numel()].copy_(mask.reshape(-1))   # :467-468, :602-603
+                    mask = self.cuda_graph_custom_mask
+            else:
+                pl = seq_lens[:bs]
+                if pl.dtype != rpi.dtype:
+                    pl = pl.to(rpi.dtype)
             mi = self.mask_indptr[: bs + 1]
             torch.ops.b200attn.extend_plan(None, pl, qo, kv, mi, n, 0)
-            self.extend_metadata = ExtendMetadata(bs, qo, kv, None, rpi, pl, spec_info.custom_mask, mi, n, None, avg)
+            self.extend_metadata = ExtendMetadata(bs, qo, kv, None, rpi, pl, mask, mi, n, None, avg)
         elif mode.is_draft_extend():
-            kv_indices, kv_indptr, qo_indptr, custom_mask = spec_info.generate_attn_arg_prefill(
-                req_pool_indices, seq_lens, None, self.req_to_token)   # :265-279
-            self.extend_metadata = ExtendMetadata(bs, qo_indptr, kv_indptr, kv_indices, None, None,
-                                                  custom_mask, None, None, None, avg)
+            if graph is None:
+                kv_indices, kv_indptr, qo_indptr, custom_mask = spec_info.generate_attn_arg_prefill(
+                    req_pool_indices, seq_lens, None, self.req_to_token)   # :265-279
+                self.extend_metadata = ExtendMetadata(bs, qo_indptr, kv_indptr, kv_indices, None, None,
+                                                      custom_mask, None, None, None, avg)
+                return
+            # Under a graph generate_attn_arg_prefill cannot be used (it allocates): the same lists are built
+            # into static buffers.  Prefix list = req_to_token[req, :seq_len] read in place (the reference
+            # flattens it into cuda_graph_kv_indices, :486-497, :612-623); extend tokens per request =
+            # speculative_num_steps + 1 at capture (:477-485), spec_info.accept_length at replay (:608-611).
+            per = int(self.speculative_num_steps or 0) + 1
+            if graph == "capture":
+                torch.ops.b200attn.extend_plan(None, pl_static, qo, kv, None, per, 0)
+            else:
+                self.cg_extend_lens[:bs].copy_(spec_info.accept_length[:bs])
+                torch.ops.b200attn.extend_plan(self.cg_extend_lens[:bs], pl_static, qo, kv, None, 0, 0)
+            self.extend_metadata = ExtendMetadata(bs, qo, kv, None, rpi, pl_static, None, None, per, None, avg)
         else:
+            if graph is not None:
+                raise ValueError(f"Invalid forward mode for CUDA graph capture / replay: {mode!r}")   # :504-507
             pl, el = forward_batch.extend_prefix_lens[:bs], forward_batch.extend_seq_lens[:bs]
             if pl.dtype != rpi.dtype:
                 pl = pl.to(rpi.dtype)
@@ -300,13 +387,29 @@ class B200AttnBackend(AttentionBackend):
             self.extend_metadata = ExtendMetadata(bs, qo, kv, None, rpi, pl, None, None,
                                                   max(cpu) if cpu else None, win, avg)
 
-    def init_cuda_graph_state(self, max_bs: int, max_num_tokens: int):
-        if self.materialize_kv_indices:
+    def init_cuda_graph_state(self, max_bs: int, max_num_tokens: int, kv_indices_buf: Optional[torch.Tensor] = None):
+        """Static buffers of the CUDA-graph path (triton_backend.py:338-388).  The decode kernel reads
+        req_to_token in place and its plan / workspace already have fixed addresses, so only the flat index
+        list (speculative CSR input, materialised indices) and the extend-side spec buffers are added."""
+        self.cg_max_bs, self.cg_max_num_tokens = max_bs, max_num_tokens
+        if kv_indices_buf is not None:
+            if kv_indices_buf.dtype != torch.int32 or not kv_indices_buf.is_contiguous():
+                raise TypeError("kv_indices_buf must be a contiguous int32 tensor")
+            self.cuda_graph_kv_indices = kv_indices_buf                       # :363-364
+        elif self.materialize_kv_indices or self.speculative:
             self.cuda_graph_kv_indices = torch.zeros(max_num_tokens * self.max_context_len,
                                                      dtype=torch.int32, device=self.device)
-            if self.sliding_window_size is not None:   # triton_backend.py:373-380
-                self.cuda_graph_window_kv_indices = torch.zeros(
-                    max_num_tokens * (self.sliding_window_size + 1), dtype=torch.int32, device=self.device)
+        if self.materialize_kv_indices and self.sliding_window_size is not None:   # :373-380
+            self.cuda_graph_window_kv_indices = torch.zeros(
+                max_num_tokens * (self.sliding_window_size + 1), dtype=torch.int32, device=self.device)
+        if not self.skip_prefill and self.prefill_backend is None:
+            if self.speculative or self.num_draft_tokens:
+                self.cuda_graph_custom_mask = torch.zeros(max_num_tokens * self.max_context_len,
+                                                          dtype=torch.uint8, device=self.device)    # :366-371
+            n = max(max_bs, 1)
+            self.cg_req_pool_indices = torch.zeros(n, dtype=torch.int64, device=self.device)
+            self.cg_prefix_lens = torch.zeros(n, dtype=torch.int64, device=self.device)
+            self.cg_extend_lens = torch.zeros(n, dtype=torch.int64, device=self.device)
         if self.prefill_backend is not None and hasattr(self.prefill_backend, "init_cuda_graph_state"):
             try:
                 self.prefill_backend.init_cuda_graph_state(max_bs, max_num_tokens)
@@ -321,8 +424,13 @@ class B200AttnBackend(AttentionBackend):
                 return self.prefill_backend.init_forward_metadata_capture_cuda_graph(
                     bs, num_tokens, req_pool_indices, seq_lens, encoder_lens, forward_mode, spec_info)
             if not (forward_mode.is_target_verify() or forward_mode.is_draft_extend()):
-                raise ValueError(f"Invalid forward mode for CUDA graph capture: {forward_mode!r}")  # triton_backend.py:509-511
-            return self._plan_extend(bs, req_pool_indices, seq_lens, forward_mode, spec_info)
+                raise ValueError(f"Invalid forward mode for CUDA graph capture: {forward_mode!r}")  # triton_backend.py:504-507
+            if forward_mode.is_target_verify() and self.cuda_graph_custom_mask is None \
+                    and getattr(spec_info, "custom_mask", None) is not None:
+                # not announced through server_args: allocate now, before the capture begins
+                self.cuda_graph_custom_mask = torch.zeros(max(self.cg_max_num_tokens, num_tokens) * self.max_context_len,
+                                                          dtype=torch.uint8, device=self.device)
+            return self._plan_extend(bs, req_pool_indices, seq_lens, forward_mode, spec_info, graph="capture")
         self._plan(bs, req_pool_indices, seq_lens, None, spec_info, graph=True)
 
     def init_forward_metadata_replay_cuda_graph(self, bs, req_pool_indices, seq_lens, seq_lens_sum,
@@ -332,7 +440,9 @@ class B200AttnBackend(AttentionBackend):
                 return self.prefill_backend.init_forward_metadata_replay_cuda_graph(
                     bs, req_pool_indices, seq_lens, seq_lens_sum, encoder_lens, forward_mode, spec_info,
                     seq_lens_cpu)
-            return self._plan_extend(bs, req_pool_indices, seq_lens, forward_mode, spec_info)
+            if not (forward_mode.is_target_verify() or forward_mode.is_draft_extend()):
+                raise ValueError(f"Invalid forward mode for CUDA graph replay: {forward_mode!r}")   # :624-627
+            return self._plan_extend(bs, req_pool_indices, seq_lens, forward_mode, spec_info, graph="replay")
         self._plan(bs, req_pool_indices, seq_lens, seq_lens_sum, spec_info, graph=True)
 
     def get_cuda_graph_seq_len_fill_value(self):
@@ -456,3 +566,83 @@ class B200AttnBackend(AttentionBackend):
 
     def support_triton(self):
         return True
+
+
+class B200MultiStepDraftBackend:
+    """``speculative_num_steps`` decode backends behind one object, for the consecutive draft-decode steps
+    of EAGLE-style speculative decoding: the drop-in for ``TritonMultiStepDraftBackend``
+    (triton_backend.py:735-872) -- same constructor, same four hooks, same ``attn_backends`` list the
+    draft worker indexes per step.
+
+    All steps share one ``kv_indptr`` ``[steps, max_bs * topk + 1]`` and one ``kv_indices`` ``[steps, n]``
+    buffer, filled by ONE ``draft_kv_indices`` launch per draft forward (the reference launches the Triton
+    kernel ``generate_draft_decode_kv_indices`` with the same grid, eagle_utils.py:844-920); step i's backend
+    then plans over its row through the CSR input mode.
+    """
+
+    def __init__(self, model_runner: Any, topk: int, speculative_num_steps: int, **backend_kwargs):
+        self.topk = int(topk)
+        self.speculative_num_steps = int(speculative_num_steps)
+        self.device = torch.device(model_runner.device)
+        max_bs = model_runner.req_to_token_pool.size * self.topk
+        self.kv_indptr = torch.zeros((self.speculative_num_steps, max_bs + 1), dtype=torch.int32, device=self.device)
+        self.attn_backends = [
+            B200AttnBackend(model_runner, skip_prefill=True, kv_indptr_buf=self.kv_indptr[i], **backend_kwargs)
+            for i in range(self.speculative_num_steps)
+        ]
+        self.max_context_len = self.attn_backends[0].max_context_len
+        self.num_head = self.attn_backends[0].num_head
+        self.pool_len = model_runner.req_to_token_pool.req_to_token.shape[1]
+        sa = getattr(model_runner, "server_args", None)
+        self.page_size = int(getattr(sa, "page_size", None) or getattr(model_runner, "page_size", None) or 1)
+        self.cuda_graph_kv_indices: Optional[torch.Tensor] = None
+
+    def common_template(self, forward_batch, kv_indices_buffer: torch.Tensor, call_fn) -> None:
+        num_seqs = forward_batch.batch_size
+        bs = self.topk * num_seqs
+        seq_lens_sum = forward_batch.seq_lens_sum
+        torch.ops.b200attn.draft_kv_indices(
+            forward_batch.req_pool_indices[:num_seqs], forward_batch.req_to_token_pool.req_to_token,
+            forward_batch.seq_lens[:num_seqs], forward_batch.positions, kv_indices_buffer, self.kv_indptr,
+            self.topk, self.page_size)
+        for i in range(self.speculative_num_steps):
+            forward_batch.spec_info.kv_indptr = self.kv_indptr[i, : bs + 1]
+            # seq_lens_sum is -1 on graph replays (the reference slices with it all the same, :806-808, which
+            # leaves a harmlessly short view); the whole row is handed on instead -- kv_indptr bounds what is read
+            n = seq_lens_sum * self.topk + bs * (i + 1) if seq_lens_sum is not None and seq_lens_sum >= 0 else None
+            forward_batch.spec_info.kv_indices = kv_indices_buffer[i] if n is None else kv_indices_buffer[i][:n]
+            call_fn(i, forward_batch)
+
+    def init_forward_metadata(self, forward_batch) -> None:
+        kv_indices = torch.empty(
+            (self.speculative_num_steps, forward_batch.batch_size * self.topk * self.max_context_len),
+            dtype=torch.int32, device=self.device)
+
+        def call_fn(i, fb):
+            # no clone needed (the reference clones, :822-827): every step owns its row of both buffers
+            self.attn_backends[i].init_forward_metadata(fb)
+
+        self.common_template(forward_batch, kv_indices, call_fn)
+
+    def init_cuda_graph_state(self, max_bs: int, max_num_tokens: int) -> None:
+        self.cuda_graph_kv_indices = torch.zeros(
+            (self.speculative_num_steps, max_num_tokens * self.max_context_len), dtype=torch.int32, device=self.device)
+        for i in range(self.speculative_num_steps):
+            self.attn_backends[i].init_cuda_graph_state(max_bs, max_num_tokens,
+                                                        kv_indices_buf=self.cuda_graph_kv_indices[i])
+
+    def init_forward_metadata_capture_cuda_graph(self, forward_batch) -> None:
+        def call_fn(i, fb):
+            self.attn_backends[i].init_forward_metadata_capture_cuda_graph(
+                fb.batch_size, fb.batch_size * self.topk, fb.req_pool_indices, fb.seq_lens,
+                encoder_lens=None, forward_mode=ForwardMode.DECODE, spec_info=fb.spec_info)
+
+        self.common_template(forward_batch, self.cuda_graph_kv_indices, call_fn)
+
+    def init_forward_metadata_replay_cuda_graph(self, forward_batch, bs: int) -> None:
+        def call_fn(i, fb):
+            self.attn_backends[i].init_forward_metadata_replay_cuda_graph(
+                bs, fb.req_pool_indices, fb.seq_lens, seq_lens_sum=-1, encoder_lens=None,
+                forward_mode=ForwardMode.DECODE, spec_info=fb.spec_info, seq_lens_cpu=None)
+
+        self.common_template(forward_batch, self.cuda_graph_kv_indices, call_fn)

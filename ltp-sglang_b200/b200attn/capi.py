@@ -19,7 +19,7 @@ E_INVALID, E_UNSUPPORTED, E_ALIGN, E_CUDA, E_WORKSPACE = -1, -2, -3, -4, -5
 BF16, F16, FP8_E4M3 = 0, 1, 2
 I32, I64 = 0, 1
 SCALE_NONE, SCALE_TRUE_DIV, SCALE_RECIP_MUL = 0, 1, 2
-ABI_VERSION = 4
+ABI_VERSION = 5
 
 
 class KvStoreArgs(C.Structure):
@@ -202,6 +202,26 @@ class MergeStatesArgs(C.Structure):
     ]
 
 
+class DraftKvIndicesArgs(C.Structure):
+    _fields_ = [
+        ("req_pool_indices", C.c_void_p),
+        ("req_to_token", C.c_void_p),
+        ("req_to_token_stride", C.c_int64),
+        ("seq_lens", C.c_void_p),
+        ("index_dtype", C.c_int32),
+        ("positions_dtype", C.c_int32),
+        ("positions", C.c_void_p),
+        ("kv_indices", C.c_void_p),
+        ("kv_indices_stride", C.c_int64),
+        ("kv_indptr", C.c_void_p),
+        ("kv_indptr_stride", C.c_int64),
+        ("num_steps", C.c_int32),
+        ("num_seqs", C.c_int32),
+        ("topk", C.c_int32),
+        ("page_size", C.c_int32),
+    ]
+
+
 # name -> (restype, argtypes); every symbol include/b200attn.h declares.
 SYMBOLS = {
     "b200attn_kv_store": (C.c_int, [C.POINTER(KvStoreArgs), C.c_void_p]),
@@ -215,6 +235,7 @@ SYMBOLS = {
     "b200attn_decode": (C.c_int, [C.POINTER(DecodeArgs), C.c_void_p]),
     "b200attn_extend": (C.c_int, [C.POINTER(ExtendArgs), C.c_void_p]),
     "b200attn_extend_plan": (C.c_int, [C.POINTER(ExtendPlanArgs), C.c_void_p]),
+    "b200attn_draft_kv_indices": (C.c_int, [C.POINTER(DraftKvIndicesArgs), C.c_void_p]),
     "b200attn_merge_states": (C.c_int, [C.POINTER(MergeStatesArgs), C.c_void_p]),
     "b200attn_abi_version": (C.c_int, []),
     "b200attn_strerror": (C.c_char_p, [C.c_int]),

@@ -63,22 +63,7 @@ def _kv_store(k, v, loc, k_pool, v_pool, k_scale, v_scale, k_scale_t, v_scale_t,
     if k.shape[1] != k_pool.shape[1] or k.shape[2] != k_pool.shape[2] or v.shape[2] != v_pool.shape[2]:
         raise ValueError("kv_store: k/v shape does not match the pool")
     a = capi.KvStoreArgs()
-    a.k, a.v = k.data_ptr(), v.data_ptr()
-    a.k_stride_token, a.k_stride_head = k.stride(0), k.stride(1)
-    a.v_stride_token, a.v_stride_head = v.stride(0), v.stride(1)
-    a.loc = loc.data_ptr()
-    a.k_pool, a.v_pool = k_pool.data_ptr(), v_pool.data_ptr()
-    a.k_pool_stride_slot, a.v_pool_stride_slot = k_pool.stride(0), v_pool.stride(0)
-    a.pool_slots = k_pool.shape[0]
-    a.n_tokens, a.num_kv_heads = k.shape[0], k.shape[1]
-    a.head_dim, a.v_head_dim = k.shape[2], v.shape[2]
-    a.src_dtype = dtype_code(k.dtype)
-    a.pool_dtype = dtype_code(k_pool.dtype)
-    a.scale_mode = scale_mode
-    a.mutate_src = 1
-    a.k_scale = 1.0 if k_scale is None else k_scale
-    a.v_scale = 1.0 if v_scale is None else v_scale
-    a.k_scale_ptr, a.v_scale_ptr = _ptr(k_scale_t), _ptr(v_scale_t)
+    _fill_store_args(a, k, v, loc, k_pool, v_pool, k_scale, v_scale, k_scale_t, v_scale_t, scale_mode)
     with torch.cuda.device(k.device):
         capi.check("b200attn_kv_store", capi.lib().b200attn_kv_store(C.byref(a), _stream(k)))
 
@@ -341,6 +326,39 @@ def _extend_plan(extend_seq_lens, prefix_lens, qo_indptr, kv_indptr, mask_indptr
         capi.check("b200attn_extend_plan", capi.lib().b200attn_extend_plan(C.byref(a), _stream(prefix_lens)))
 
 
+def _draft_kv_indices(req_pool_indices, req_to_token, seq_lens, positions, kv_indices, kv_indptr, topk, page_size):
+    """kv_indptr / kv_indices of all draft-decode steps (``generate_draft_decode_kv_indices``,
+    speculative/eagle_utils.py:844-920).  ``kv_indices`` ``[steps, n]`` and ``kv_indptr``
+    ``[steps, rows + 1]`` int32 are written in place; ``kv_indptr[:, 0]`` is left alone."""
+    _cuda(req_pool_indices, req_to_token, seq_lens, positions, kv_indices, kv_indptr)
+    if req_to_token.dtype != torch.int32 or req_to_token.dim() != 2 or req_to_token.stride(1) != 1:
+        raise TypeError("draft_kv_indices: req_to_token must be int32 [max_reqs, max_context_len]")
+    if req_pool_indices.dtype != seq_lens.dtype or seq_lens.dtype not in _IDX:
+        raise TypeError("draft_kv_indices: req_pool_indices and seq_lens must both be int32 or both int64")
+    if positions.dtype not in _IDX or not positions.is_contiguous():
+        raise TypeError("draft_kv_indices: positions must be contiguous int32/int64")
+    if not (req_pool_indices.is_contiguous() and seq_lens.is_contiguous()):
+        raise ValueError("draft_kv_indices: req_pool_indices / seq_lens must be contiguous")
+    for name, t in (("kv_indices", kv_indices), ("kv_indptr", kv_indptr)):
+        if t.dtype != torch.int32 or t.dim() != 2 or t.stride(1) != 1:
+            raise TypeError(f"draft_kv_indices: {name} must be int32 [steps, n] with a contiguous last dim")
+    num_seqs = seq_lens.numel()
+    if kv_indices.shape[0] != kv_indptr.shape[0]:
+        raise ValueError("draft_kv_indices: kv_indices and kv_indptr disagree on the number of steps")
+    if positions.numel() < num_seqs * topk or kv_indptr.shape[1] < num_seqs * topk + 1:
+        raise ValueError("draft_kv_indices: positions / kv_indptr shorter than num_seqs * topk")
+    a = capi.DraftKvIndicesArgs()
+    a.req_pool_indices, a.seq_lens = req_pool_indices.data_ptr(), seq_lens.data_ptr()
+    a.req_to_token, a.req_to_token_stride = req_to_token.data_ptr(), req_to_token.stride(0)
+    a.index_dtype, a.positions_dtype = _IDX[seq_lens.dtype], _IDX[positions.dtype]
+    a.positions = positions.data_ptr()
+    a.kv_indices, a.kv_indices_stride = kv_indices.data_ptr(), kv_indices.stride(0)
+    a.kv_indptr, a.kv_indptr_stride = kv_indptr.data_ptr(), kv_indptr.stride(0)
+    a.num_steps, a.num_seqs, a.topk, a.page_size = kv_indices.shape[0], num_seqs, topk, page_size
+    with torch.cuda.device(kv_indices.device):
+        capi.check("b200attn_draft_kv_indices", capi.lib().b200attn_draft_kv_indices(C.byref(a), _stream(kv_indices)))
+
+
 def _merge_states(o_a, lse_a, o_b, lse_b, o_out, lse_out):
     _cuda(o_a, lse_a, o_b, lse_b, o_out, lse_out)
     if o_a.dim() != 3 or o_a.shape != o_b.shape or o_out.shape != o_a.shape:
@@ -401,6 +419,11 @@ _LIB.define(
     "merge_states(Tensor o_a, Tensor lse_a, Tensor o_b, Tensor lse_b, Tensor(a!) o_out, "
     "Tensor(b!)? lse_out) -> ()"
 )
+_LIB.define(
+    "draft_kv_indices(Tensor req_pool_indices, Tensor req_to_token, Tensor seq_lens, Tensor positions, "
+    "Tensor(a!) kv_indices, Tensor(b!) kv_indptr, int topk, int page_size) -> ()"
+)
+_LIB.impl("draft_kv_indices", _draft_kv_indices, "CUDA")
 _LIB.impl("kv_store", _kv_store, "CUDA")
 _LIB.impl("rope_kv_store", _rope_kv_store, "CUDA")
 _LIB.impl("plan", _plan, "CUDA")

@@ -262,3 +262,105 @@ extern "C" __attribute__((visibility("default"))) int b200attn_plan(const b200at
   }
   return B200ATTN_OK;
 }
+
+// ---------------------------------------------------------------------------
+// Multi-step draft decode (speculative decoding): kv_indptr / kv_indices of all
+// `num_steps` draft steps in one launch.  Replaces generate_draft_decode_kv_indices
+// (python/sglang/srt/speculative/eagle_utils.py:844-920) as TritonMultiStepDraftBackend
+// launches it (layers/attention/triton_backend.py:779-809), same outputs bit for bit:
+//   step it (iters = it + 1), sequence s, branch t:
+//     kv_indices[it][cum(s) * topk + s * iters * topk + t * (S_s + iters) + j]
+//         = req_to_token[req_s, j]                            j < S_s
+//         = req_to_token[req_s, ext(s, t) + (j - S_s)]        S_s <= j < S_s + iters
+//     kv_indptr[it][z] = sum(positions[0 .. z)) + z * iters    z = s * topk + t, z = 0 writes entry
+//                                                              num_seqs * topk instead (the total)
+//   ext = S_s + t * num_steps (page_size 1 or topk 1), else the branch's own pages:
+//   S_s / P * P + t * ceil((S_s % P + num_steps) / P) * P + S_s % P.
+// ---------------------------------------------------------------------------
+namespace b200attn {
+
+struct DraftIdxParams {
+  const void* req_pool_indices;
+  const int32_t* req_to_token;
+  int64_t r2t_stride;
+  const void* seq_lens;
+  const void* positions;
+  int32_t* kv_indices;
+  int64_t kv_indices_stride;
+  int32_t* kv_indptr;
+  int64_t kv_indptr_stride;
+  int32_t idx64, pos64;
+  int32_t num_steps, num_seqs, topk, page_size;
+};
+
+__global__ void __launch_bounds__(128) draft_kv_indices_kernel(const DraftIdxParams p) {
+  __shared__ long long red[4];
+  const int it = blockIdx.x, s = blockIdx.y, t = blockIdx.z;
+  const int iters = it + 1;
+  const int tid = threadIdx.x;
+  auto block_sum = [&](long long v) -> long long {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+    __syncthreads();
+    if ((tid & 31) == 0) red[tid >> 5] = v;
+    __syncthreads();
+    return red[0] + red[1] + red[2] + red[3];
+  };
+  long long part = 0;
+  for (int i = tid; i < s; i += 128) part += load_idx(p.seq_lens, i, p.idx64);
+  const long long cum = block_sum(part);
+  const long long S = load_idx(p.seq_lens, s, p.idx64);
+  const int32_t* row = p.req_to_token + load_idx(p.req_pool_indices, s, p.idx64) * p.r2t_stride;
+  int32_t* dst = p.kv_indices + p.kv_indices_stride * it + cum * p.topk +
+                 static_cast<long long>(s) * iters * p.topk + static_cast<long long>(t) * (S + iters);
+  for (long long j = tid; j < S; j += 128) dst[j] = row[j];
+  long long ext;
+  if (p.page_size == 1 || p.topk == 1) {
+    ext = S + static_cast<long long>(t) * p.num_steps;
+  } else {
+    const long long last = S % p.page_size;
+    const long long pages = (last + p.num_steps + p.page_size - 1) / p.page_size;
+    ext = S / p.page_size * p.page_size + t * pages * p.page_size + last;
+  }
+  for (int e = tid; e < iters; e += 128) dst[S + e] = row[ext + e];
+
+  int z = s * p.topk + t;
+  if (z == 0) z = p.num_seqs * p.topk;
+  part = 0;
+  for (int i = tid; i < z; i += 128) part += load_idx(p.positions, i, p.pos64);
+  const long long base = block_sum(part);
+  if (tid == 0) p.kv_indptr[p.kv_indptr_stride * it + z] = static_cast<int32_t>(base + static_cast<long long>(z) * iters);
+}
+
+}  // namespace b200attn
+
+extern "C" __attribute__((visibility("default"))) int b200attn_draft_kv_indices(const b200attn_draft_kv_indices_args* a,
+                                                                                b200attn_stream_t stream_) {
+  if (!a || a->num_steps < 0 || a->num_seqs < 0 || a->topk < 0) return B200ATTN_E_INVALID;
+  if (a->num_steps == 0 || a->num_seqs == 0 || a->topk == 0) return B200ATTN_OK;
+  if (!a->req_pool_indices || !a->req_to_token || !a->seq_lens || !a->positions || !a->kv_indices || !a->kv_indptr)
+    return B200ATTN_E_INVALID;
+  if ((a->index_dtype != B200ATTN_I32 && a->index_dtype != B200ATTN_I64) ||
+      (a->positions_dtype != B200ATTN_I32 && a->positions_dtype != B200ATTN_I64) || a->page_size < 1)
+    return B200ATTN_E_INVALID;
+  if (a->num_seqs > 65535 || a->topk > 65535) return B200ATTN_E_UNSUPPORTED;
+  DraftIdxParams p;
+  p.req_pool_indices = a->req_pool_indices;
+  p.req_to_token = a->req_to_token;
+  p.r2t_stride = a->req_to_token_stride;
+  p.seq_lens = a->seq_lens;
+  p.positions = a->positions;
+  p.kv_indices = a->kv_indices;
+  p.kv_indices_stride = a->kv_indices_stride;
+  p.kv_indptr = a->kv_indptr;
+  p.kv_indptr_stride = a->kv_indptr_stride;
+  p.idx64 = a->index_dtype == B200ATTN_I64;
+  p.pos64 = a->positions_dtype == B200ATTN_I64;
+  p.num_steps = a->num_steps;
+  p.num_seqs = a->num_seqs;
+  p.topk = a->topk;
+  p.page_size = a->page_size;
+  draft_kv_indices_kernel<<<dim3(a->num_steps, a->num_seqs, a->topk), 128, 0, static_cast<cudaStream_t>(stream_)>>>(p);
+  count_launch();
+  return cudaGetLastError() == cudaSuccess ? B200ATTN_OK : B200ATTN_E_CUDA;
+}

@@ -181,6 +181,43 @@ def kv_indices(req_to_token: torch.Tensor, req_pool_indices: torch.Tensor,
     return indptr, flat
 
 
+def draft_decode_kv_indices(req_to_token, req_pool_indices, seq_lens, positions, num_steps: int, topk: int,
+                            page_size: int, kv_indices_width: int):
+    """All draft-decode steps' (kv_indptr [steps, bs*topk + 1], kv_indices [steps, width]) -- a loop-level
+    restatement of the Triton kernel ``generate_draft_decode_kv_indices``
+    (python/sglang/srt/speculative/eagle_utils.py:844-920; grid (num_steps, num_seqs, topk)).  Parity
+    UNPINNED: the reference kernel needs Triton on a GPU and holds no golden vectors; this follows its source
+    line by line.  Unwritten entries stay 0 (the caller's zero-initialised buffers)."""
+    r2t = req_to_token.detach().cpu().numpy()
+    rpi = req_pool_indices.detach().cpu().numpy().astype(np.int64)
+    sl = seq_lens.detach().cpu().numpy().astype(np.int64)
+    pos = positions.detach().cpu().numpy().astype(np.int64)
+    n = len(sl)
+    indptr = np.zeros((num_steps, n * topk + 1), dtype=np.int32)
+    indices = np.zeros((num_steps, kv_indices_width), dtype=np.int32)
+    for it in range(num_steps):
+        iters = it + 1
+        for b in range(n):
+            S = int(sl[b])
+            cum = int(sl[:b].sum())
+            row = r2t[rpi[b]]
+            for t in range(topk):
+                off = cum * topk + b * iters * topk + t * (S + iters)
+                indices[it, off: off + S] = row[:S]
+                if page_size == 1 or topk == 1:
+                    ext = S + t * num_steps
+                else:
+                    last = S % page_size
+                    pages = (last + num_steps + page_size - 1) // page_size
+                    ext = S // page_size * page_size + t * pages * page_size + last
+                indices[it, off + S: off + S + iters] = row[ext: ext + iters]
+                z = b * topk + t
+                if z == 0:
+                    z = n * topk
+                indptr[it, z] = int(pos[:z].sum()) + z * iters
+    return indptr, indices
+
+
 # --------------------------------------------------------------------------- #
 # decode attention (float64 SDPA + lse)
 # --------------------------------------------------------------------------- #

@@ -92,13 +92,24 @@ def oracle_step(w_cpu: synth.Workload, logit_cap: float = 0.0, save_kv: bool = T
     return out, lse, kp, vp, k, v
 
 
-def assert_close_out(got: np.ndarray, ref: np.ndarray, atol=2e-2, rtol=1e-2, what="attention output"):
-    """BASELINE.json tolerance: max-abs 2e-2 / rel 1e-2 against the fp32+ oracle."""
-    err = np.abs(got.astype(np.float64) - ref.astype(np.float64))
-    bound = atol + rtol * np.abs(ref)
-    worst = float((err - bound).max())
+def assert_close_out(got: np.ndarray, ref: np.ndarray, atol=2e-2, rtol=1e-2, what="attention output", rel_l2=2e-2):
+    """BASELINE.json tolerance: max-abs 2e-2 / rel 1e-2 against the fp32+ oracle -- and, because |o| is only
+    0.01-0.1 at contexts of a few hundred tokens and more (so that bar alone would pass a wrong V row or a
+    swapped head-dim column), a relative L2 bound per output row (last axis = head_dim):
+    ||got - ref|| <= rel_l2 * ||ref||.  A correct bf16 kernel sits at 2e-3 ... 5e-3."""
+    g = got.astype(np.float64)
+    r = ref.astype(np.float64)
+    err = np.abs(g - r)
+    bound = atol + rtol * np.abs(r)
+    worst = float((err - bound).max()) if err.size else 0.0
     assert worst <= 0, f"{what}: max abs err {err.max():.4e} exceeds atol {atol} + rtol {rtol}"
-    return float(err.max())
+    if rel_l2 is not None and err.size:
+        num = np.sqrt((err ** 2).sum(axis=-1))
+        den = np.sqrt((r ** 2).sum(axis=-1))
+        ok = num <= rel_l2 * den + 1e-6
+        assert ok.all(), (f"{what}: relative L2 error {float((num / np.maximum(den, 1e-30))[~ok].max()):.3e} of a row "
+                          f"exceeds {rel_l2} ({int((~ok).sum())} rows)")
+    return float(err.max()) if err.size else 0.0
 
 
 def canon_e4m3_nan(b: np.ndarray) -> np.ndarray:

@@ -41,7 +41,7 @@ def test_library_exports_every_declared_symbol():
 def test_abi_version_and_strerror():
     from b200attn import capi
 
-    assert capi.lib().b200attn_abi_version() == capi.ABI_VERSION == 4
+    assert capi.lib().b200attn_abi_version() == capi.ABI_VERSION == 5
     for code in (0, -1, -2, -3, -4, -5, -99):
         assert isinstance(capi.strerror(code), str) and capi.strerror(code)
     assert "unsupported" in capi.strerror(capi.E_UNSUPPORTED)

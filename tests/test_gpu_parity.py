@@ -43,10 +43,12 @@ def _check_same_inputs(w_cpu, w_gpu):
 
 
 def _run_case(cfg, logit_cap=0.0, max_ctas=0, min_chunks=0, index_dtype=torch.int64,
-              materialize=False, lse_tol=1e-3):
+              materialize=False, lse_tol=1e-3, q_gain=1.0):
     import b200attn
 
     w_cpu, w = _pair(cfg)
+    if q_gain != 1.0:   # peaked softmax: a few keys carry the row, so P.V errors are not averaged away
+        w_cpu.qkv[:, : cfg.num_q_heads * cfg.head_dim] *= q_gain
     _check_same_inputs(w_cpu, w)
     runner = make_runner(w, DEV)
     backend = b200attn.B200AttnBackend(runner, return_lse=True, max_ctas=max_ctas, min_chunks=min_chunks,
@@ -257,6 +259,17 @@ def test_decode_fp8_tp8_and_wide_group():
 def test_decode_logit_cap(cap):
     cfg = synth.Config("cap", 4, 0, 16, 4, 128, ragged=(10, 600), seed=27)
     _run_case(cfg, logit_cap=cap, max_ctas=6, min_chunks=1)
+
+
+@pytest.mark.parametrize("kv_dtype", ["bf16", "fp8_e4m3"])
+@pytest.mark.parametrize("D", [64, 128])
+def test_decode_peaked_softmax(kv_dtype, D):
+    """q scaled by 6: the softmax of a row is carried by a handful of keys, so a wrong V row, a dropped
+    token or a swapped head-dim column moves the output by far more than the tolerance (with randn q the
+    output is an average of hundreds of V rows, |o| ~ 0.05, and such errors could hide under atol)."""
+    cfg = synth.Config("peak", 6, 0, 32, 8, D, kv_dtype=kv_dtype, ragged=(100, 1500), page_size=4,
+                       k_scale=0.5 if kv_dtype != "bf16" else 1.0, v_scale=2.0 if kv_dtype != "bf16" else 1.0, seed=33)
+    _run_case(cfg, q_gain=6.0, max_ctas=17, min_chunks=1, lse_tol=2e-3)
 
 
 def test_uniform_c1_shape():
