@@ -306,7 +306,7 @@ def measure(R: Rank, args, gcfg, scaling: str, with_clocks: bool = True) -> dict
     import synth
     import b200attn
     from b200attn import capi
-    from tests.harness import make_batch, make_layer, make_runner
+    from bench_harness import make_batch, make_layer, make_runner
 
     torch, world, dev = R.torch, R.world, R.dev
     c = synth.shard(gcfg, world * args.tp_sim)           # this rank's head slice

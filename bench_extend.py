@@ -64,7 +64,7 @@ def main():
     import b200attn
     import synth
     from bench import ClockSampler
-    from tests.harness import make_extend_runner
+    from bench_harness import make_extend_runner
 
     dev = torch.device("cuda:0")
     torch.cuda.set_device(dev)

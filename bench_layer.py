@@ -52,7 +52,7 @@ def main():
     import b200attn
     import synth
     from b200attn import capi
-    from tests.harness import make_batch, make_layer, make_runner
+    from bench_harness import make_batch, make_layer, make_runner
 
     R = bench.Rank(args)
     world, dev = R.world, R.dev

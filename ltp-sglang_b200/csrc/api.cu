@@ -42,6 +42,14 @@ cudaError_t launch_decode<__half, true>(const DecodeParams&, int, bool, int, int
 
 using namespace b200attn;
 
+#ifdef B200ATTN_DEC_TRACE
+// Trace build only (make trace): where decode_kernel drops its per-CTA clock stamps; [148][16] uint64.
+static unsigned long long* g_decode_trace = nullptr;
+extern "C" __attribute__((visibility("default"))) void b200attn_debug_set_decode_trace(void* buf) {
+  g_decode_trace = static_cast<unsigned long long*>(buf);
+}
+#endif
+
 extern "C" __attribute__((visibility("default"))) int b200attn_abi_version(void) { return B200ATTN_ABI_VERSION; }
 
 extern "C" __attribute__((visibility("default"))) uint64_t b200attn_launch_count(void) { return g_launches.load(std::memory_order_relaxed); }
@@ -152,6 +160,9 @@ extern "C" __attribute__((visibility("default"))) int b200attn_decode(const b200
   p.scale_log2 = p.sm_scale_k * kLog2e;
   p.logit_cap = a->logit_cap;
   p.v_scale = a->v_scale;
+#ifdef B200ATTN_DEC_TRACE
+  p.trace = g_decode_trace;
+#endif
 
   cudaStream_t stream = static_cast<cudaStream_t>(stream_);
   const bool rows16 = g.group > 8;

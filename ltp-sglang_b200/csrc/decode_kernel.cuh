@@ -57,7 +57,32 @@ struct DecodeParams {
   float sm_scale_k;              // sm_scale * k_scale
   float logit_cap;
   float v_scale;
+#ifdef B200ATTN_DEC_TRACE
+  unsigned long long* trace;     // [grid][kTraceSlots] clock stamps (tools/trace_decode.py); nullptr = off
+#endif
 };
+
+// -DB200ATTN_DEC_TRACE (make trace -> libb200attn_trace.so): per-CTA timeline of one launch.  Slot 0 / 15 hold
+// %globaltimer (ns, comparable across SMs) at entry / exit, the others clock64 of the CTA's own SM.
+#ifdef B200ATTN_DEC_TRACE
+constexpr int kTraceSlots = 16;
+enum {
+  TR_GT_ENTRY = 0, TR_ENTRY, TR_BARS_READY, TR_P_WALK, TR_P_IDS, TR_P_FIRST_ISSUE, TR_P_LAST_ISSUE, TR_C_Q,
+  TR_C_FIRST_FULL, TR_C_FIRST_DONE, TR_C_LAST_DONE, TR_C_EPILOGUE, TR_C_MERGED, TR_C_EXIT, TR_COUNTS, TR_GT_EXIT
+};
+__device__ __forceinline__ unsigned long long globaltimer_ns() {
+  unsigned long long t;
+  asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t));
+  return t;
+}
+#define B200_TR(slot) do { if (p.trace) p.trace[blockIdx.x * kTraceSlots + (slot)] = clock64(); } while (0)
+#define B200_TR_ONCE(slot, flag) do { if (p.trace && !(flag)) { (flag) = true; p.trace[blockIdx.x * kTraceSlots + (slot)] = clock64(); } } while (0)
+#define B200_TR_GT(slot) do { if (p.trace) p.trace[blockIdx.x * kTraceSlots + (slot)] = globaltimer_ns(); } while (0)
+#else
+#define B200_TR(slot) do { } while (0)
+#define B200_TR_ONCE(slot, flag) do { } while (0)
+#define B200_TR_GT(slot) do { } while (0)
+#endif
 
 constexpr float kLog2e = 1.4426950408889634f;
 constexpr float kLn2 = 0.6931471805599453f;
@@ -139,6 +164,11 @@ __global__ void __launch_bounds__(kThreads, 1) decode_kernel(const DecodeParams 
   const PlanView pv = plan_view(const_cast<void*>(p.plan), p.batch);
   const PlanHeader& H = *pv.hdr;  // read where needed (range transitions), not held in registers
   const int cta = blockIdx.x;
+#ifdef B200ATTN_DEC_TRACE
+  bool tr_a = false, tr_b = false, tr_c = false;
+  unsigned long long tr_chunks = 0, tr_pieces = 0;
+  if (threadIdx.x == 0) { B200_TR_GT(TR_GT_ENTRY); B200_TR(TR_ENTRY); }
+#endif
   if (cta >= H.grid) return;
   const int R = H.n_ranges;
   const int n_dyn = H.n_dynamic, n_grid = H.grid, n_static = H.n_static;
@@ -168,6 +198,7 @@ __global__ void __launch_bounds__(kThreads, 1) decode_kernel(const DecodeParams 
     rq[0] = cta < n_static ? cta : take_ticket();
   }
   __syncthreads();
+  if (threadIdx.x == 0) B200_TR(TR_BARS_READY);
 
   const int T = p.chunk_tokens;
   const uint32_t v_off = T * p.row_stride;  // V rows follow the K rows of a stage
@@ -226,6 +257,7 @@ __global__ void __launch_bounds__(kThreads, 1) decode_kernel(const DecodeParams 
         if (pw == 0 && lane == 0) next_rg = take_ticket();
         PieceWalk walk(pv, H, rg, p.ng);
       while (walk.next(pv, b, hg, lc0, lc1, nchunks, vreq)) {
+        if (pw == 0 && lane == 0) B200_TR_ONCE(TR_P_WALK, tr_a);
         const int S = pv.seq_len[b];
         const int32_t* idx = p.indices + pv.row_off[b];
         const uint8_t* base = pool + static_cast<int64_t>(hg) * p.row_bytes;
@@ -279,6 +311,7 @@ __global__ void __launch_bounds__(kThreads, 1) decode_kernel(const DecodeParams 
             __threadfence_block();
           }
           cp_async_mbar_arrive_noinc(full);
+          if (pw == 0 && lane == 0) { B200_TR_ONCE(TR_P_FIRST_ISSUE, tr_b); B200_TR(TR_P_LAST_ISSUE); }
           if (++stage == p.stages) {
             stage = 0;
             phase ^= 1;
@@ -298,6 +331,7 @@ __global__ void __launch_bounds__(kThreads, 1) decode_kernel(const DecodeParams 
       if (pw == 0 && lane == 0) next_rg = take_ticket();
       PieceWalk walk(pv, H, rg, p.ng);
     while (walk.next(pv, b, hg, lc0, lc1, nchunks, vreq)) {
+      if (pw == 0 && lane == 0) B200_TR_ONCE(TR_P_WALK, tr_a);
       const int S = pv.seq_len[b];
       const int32_t* idx = p.indices + pv.row_off[b];
       const uint8_t* base = pool + static_cast<int64_t>(hg) * p.row_bytes;
@@ -337,6 +371,7 @@ __global__ void __launch_bounds__(kThreads, 1) decode_kernel(const DecodeParams 
             bulk_g2s(dst + i * p.row_stride, base + static_cast<int64_t>(cur[r]) * slot_bytes,
                      p.row_bytes, full);
         }
+        if (pw == 0 && lane == 0) { B200_TR_ONCE(TR_P_FIRST_ISSUE, tr_b); B200_TR(TR_P_LAST_ISSUE); }
         if (++stage == p.stages) {
           stage = 0;
           phase ^= 1;
@@ -451,8 +486,12 @@ __global__ void __launch_bounds__(kThreads, 1) decode_kernel(const DecodeParams 
       for (int e = 0; e < QR; ++e) o[n][e] = 0.f;
     float m0 = -CUDART_INF_F, m1 = -CUDART_INF_F, l0 = 0.f, l1 = 0.f;
 
+#ifdef B200ATTN_DEC_TRACE
+    if (threadIdx.x == 0) { B200_TR_ONCE(TR_C_Q, tr_a); ++tr_pieces; }
+#endif
     for (int lc = lc0; lc < lc1; ++lc) {
       mbar_wait(bar_full + stage * 8, phase);
+      if (threadIdx.x == 0) B200_TR_ONCE(TR_C_FIRST_FULL, tr_b);
       const uint32_t sbase = stage0 + stage * p.stage_bytes;
 
       // ---- S = Q.K^T for 16 tokens (two n8 tiles) ----
@@ -618,6 +657,9 @@ __global__ void __launch_bounds__(kThreads, 1) decode_kernel(const DecodeParams 
       if (tail) pv_mma(std::true_type{}); else pv_mma(std::false_type{});
       __syncwarp();
       if (lane == 0) mbar_arrive(bar_empty + stage * 8);
+#ifdef B200ATTN_DEC_TRACE
+      if (threadIdx.x == 0) { B200_TR_ONCE(TR_C_FIRST_DONE, tr_c); B200_TR(TR_C_LAST_DONE); ++tr_chunks; }
+#endif
       if (++stage == p.stages) {
         stage = 0;
         phase ^= 1;
@@ -752,6 +794,7 @@ __global__ void __launch_bounds__(kThreads, 1) decode_kernel(const DecodeParams 
         }
         named_bar_sync(2, kConsumerWarps * 32);
         if (*merge_flag) {
+          if (threadIdx.x == 0) B200_TR(TR_C_MERGED);
           __threadfence();
           const int np = pv.vreq_pieces[vreq] * p.ts;
           const int64_t prow0 = static_cast<int64_t>(vreq + pv.vreq_rfirst[vreq]) * p.ts * hqv;
@@ -764,10 +807,18 @@ __global__ void __launch_bounds__(kThreads, 1) decode_kernel(const DecodeParams 
         }
       }
     }
+    if (threadIdx.x == 0) B200_TR(TR_C_EPILOGUE);
   }
   ++rn;
   rg = rq[rn & (kRangeRing - 1)];
   }
+#ifdef B200ATTN_DEC_TRACE
+  if (threadIdx.x == 0 && p.trace) {
+    B200_TR(TR_C_EXIT);
+    p.trace[blockIdx.x * kTraceSlots + TR_COUNTS] = tr_chunks | (tr_pieces << 32);
+    B200_TR_GT(TR_GT_EXIT);
+  }
+#endif
 }
 
 template <typename QT, bool FP8>

@@ -8,7 +8,7 @@ ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path[:0] = [ROOT, os.path.join(ROOT, "ltp-sglang_b200")]
 import torch
 import b200attn, synth
-from tests.harness import make_batch, make_layer, make_runner
+from bench_harness import make_batch, make_layer, make_runner
 
 dev = torch.device("cuda:0")
 
