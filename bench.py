@@ -51,6 +51,9 @@ def parse_args():
     ap.add_argument("--page-size", type=int, default=0, help="override the config's page size")
     ap.add_argument("--no-graph", action="store_true", help="time eager launches instead of a CUDA graph")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--sustain", type=float, default=2.0,
+                    help="seconds of back-to-back replays of the step graph after the timed steps (clocks / power "
+                         "under sustained load, reported under 'sustained'); 0 = skip")
     ap.add_argument("--scaling", default="weak", choices=["weak", "strong"],
                     help="N > 1: weak = batch x N with KV heads sharded (per-GPU bytes fixed); strong = fixed batch")
     ap.add_argument("--no-strong", action="store_true", help="N > 1: skip the extra strong-scaling measurement")
@@ -163,11 +166,69 @@ def cpu_reference_run(cfg, sample_requests: int, steps: int, warmup: int):
     for _ in range(steps):
         step()
     dt = (time.perf_counter() - t0) / steps
-    info = {"kind": kind, "cores": torch.get_num_threads(),
+    tn = torch_native_cpu_run(scfg, min(8, n))
+    info = {"kind": kind, "cores": torch.get_num_threads(), "torch_native": tn,
             "sample": f"{n} of {cfg.batch} requests of {cfg.name} at full context ({w.seq_lens_sum} tokens, "
                       f"{w.algorithmic_bytes() / 1e6:.0f} MB algorithmic), {steps} steps; {impl}{note}",
             "gb_per_s": w.algorithmic_bytes() / dt / 1e9}
     return n / dt, dt * 1e3, info
+
+
+def torch_native_cpu_run(scfg, n_req: int, steps: int = 2):
+    """The reference's OTHER CPU path: ``TorchNativeAttnBackend.forward_decode``
+    (layers/attention/torch_native_backend.py:226-267: set_kv_buffer + one SDPA per request on gathered K/V),
+    timed beside the sgl-kernel kernel on a smaller sample.  The reference's own class is used where its tree
+    is mounted (this container); on the GPU box, where it is not, the line is the oracle's restatement of the
+    same loop (``decode_oracle.torch_native_decode``) and says so."""
+    import torch
+
+    import synth
+    from oracle import decode_oracle, ref_loader
+
+    c = replace(scfg, batch=n_req)
+    w = synth.make_workload(c, "cpu")
+    q = w.q.reshape(c.batch, c.num_q_heads, c.head_dim)
+    k = w.k.reshape(c.batch, c.num_kv_heads, c.head_dim)
+    v = w.v.reshape(c.batch, c.num_kv_heads, c.head_dim)
+    kind = "port"
+    step = None
+    if ref_loader.available():
+        try:
+            import types
+
+            ref = ref_loader.load()
+            r2t = ref.ReqToTokenPool(size=w.req_to_token.shape[0], max_context_len=w.req_to_token.shape[1], device="cpu",
+                                     enable_memory_saver=False)
+            r2t.req_to_token.copy_(w.req_to_token)
+            pool = ref.MHATokenToKVPool(size=w.pool_size, page_size=c.page_size, dtype=w.k_pool.dtype, head_num=c.num_kv_heads,
+                                        head_dim=c.head_dim, layer_num=1, device="cpu", enable_memory_saver=False)
+            pool.k_buffer[0].copy_(w.k_pool)
+            pool.v_buffer[0].copy_(w.v_pool)
+            backend = ref.TorchNativeAttnBackend(types.SimpleNamespace(device="cpu"))
+            fb = ref.ForwardBatch(forward_mode=ref.ForwardMode.DECODE, batch_size=c.batch, input_ids=torch.zeros(c.batch, dtype=torch.int64),
+                                  req_pool_indices=w.req_pool_indices, seq_lens=w.seq_lens, out_cache_loc=w.out_cache_loc,
+                                  seq_lens_sum=w.seq_lens_sum, req_to_token_pool=r2t, token_to_kv_pool=pool, attn_backend=backend)
+            layer = ref.RadixAttention(c.num_q_heads, c.head_dim, w.sm_scale, c.num_kv_heads, layer_id=0)
+
+            def step():
+                return layer(w.q.clone(), w.k.clone(), w.v.clone(), fb)
+            step()
+            kind = "reference"
+        except Exception as e:   # constructor signatures drift between reference versions: fall back, say why
+            step = None
+            kind = f"port (reference class not usable here: {str(e)[:60]})"
+    if step is None:
+        def step():
+            decode_oracle.kv_store(w.k_pool, w.v_pool, w.out_cache_loc, k, v)
+            return decode_oracle.torch_native_decode(q, w.k_pool, w.v_pool, w.req_to_token, w.req_pool_indices,
+                                                     w.seq_lens, w.sm_scale)
+        step()
+    t0 = time.perf_counter()
+    for _ in range(steps):
+        step()
+    dt = (time.perf_counter() - t0) / steps
+    return {"value": n_req / dt, "unit": UNIT, "ms_per_step": dt * 1e3, "kind": kind, "cores": torch.get_num_threads(),
+            "sample": f"{n_req} requests of {scfg.name} at full context, {steps} steps; TorchNativeAttnBackend.forward_decode"}
 
 
 def run_reference_arm(args, cfg):
@@ -183,7 +244,7 @@ def run_reference_arm(args, cfg):
         "config": workload_config(replace(cfg, batch=cfg.batch * (args.gpus if args.scaling == "weak" else 1)),
                                   args.gpus, note="reference CPU path on host cores; bounded sample"),
         "cpu_baseline": {"value": tps, "unit": UNIT, "cores": info["cores"], "kind": info["kind"],
-                         "sample": info["sample"]},
+                         "sample": info["sample"], "torch_native": info["torch_native"]},
         "e2e": {"value": tps, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
     }
@@ -381,14 +442,19 @@ def measure(R: Rank, args, gcfg, scaling: str, with_clocks: bool = True) -> dict
              float(layer.scaling), 0.0, c.k_scale if fp8 else 1.0, c.v_scale if fp8 else 1.0, 0)
     for _ in range(3):
         torch.ops.b200attn.decode(*dargs)
+    # K_PER launches per graph replay (a model's decode step is one graph of many kernels, not one graph per
+    # kernel): the average launch duration excludes most of the graph-launch gap.  With an L2 flush in front of
+    # every step only one launch per replay can be timed cold.
+    K_PER = 1 if flush else 4
     kgraph = torch.cuda.CUDAGraph()
     torch.cuda.synchronize()
     with torch.cuda.graph(kgraph):
-        torch.ops.b200attn.decode(*dargs)
+        for _ in range(K_PER):
+            torch.ops.b200attn.decode(*dargs)
     for _ in range(3):
         kgraph.replay()
     torch.cuda.synchronize()
-    k_ms = R.max_over_ranks(R.timed(kgraph.replay, max(10, min(args.steps, 50)), flush))
+    k_ms = R.max_over_ranks(R.timed(kgraph.replay, max(10, min(args.steps, 50)), flush)) / K_PER
     clocks = None
     if sampler:  # sampled from the start of the timed steps to the end of the K2-alone timing
         clocks = sampler.stop()
@@ -399,34 +465,66 @@ def measure(R: Rank, args, gcfg, scaling: str, with_clocks: bool = True) -> dict
     achieved = decode_bytes / (k_ms * 1e-3) / 1e9
     roofline = {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
                 "traffic": _ncu_traffic(gcfg.name, world), "kernel": "decode_kernel (split-KV decode with the LSE merge fused in; one launch), per GPU",
-                "kernel_ms": k_ms, "algorithmic_bytes": decode_bytes, "peak_source": peak_src,
+                "kernel_ms": k_ms, "launches_per_timed_graph": K_PER, "algorithmic_bytes": decode_bytes, "peak_source": peak_src,
                 "frac_of_nominal_8TBs": achieved / 8000.0}
+
+    # ---------------- sustained replay: >= args.sustain seconds of the same step graph ----------------
+    sustained = None
+    if args.sustain > 0 and graph is not None and not flush and world == 1:
+        ssamp = ClockSampler(R.local_rank)
+        reps = max(100, int(args.sustain * 1e3 / ms) + 1)
+        ssamp.start()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(reps):
+            graph.replay()
+        e1.record()
+        torch.cuda.synchronize()
+        sms = e0.elapsed_time(e1) / reps
+        sustained = {"seconds": e0.elapsed_time(e1) / 1e3, "steps": reps, "ms_per_step": sms, "value": B / (sms * 1e-3),
+                     "hbm_gb_per_s": w.algorithmic_bytes() / (sms * 1e-3) / 1e9, "clocks": ssamp.stop()}
+
+    # ---------------- the small kernels of the path: K1 kv_store, K4 rope + store, merge_states ----------------
+    other = small_kernel_rooflines(R, w, c, pool, peak) if world == 1 and args.tp_sim == 1 else None
 
     # ---------------- end to end with host buffers: `e2e` ----------------
     # The call sequence CudaGraphRunner.replay makes every decode step (cuda_graph_runner.py:698-790):
     # copy the step's inputs into the static buffers (here: from pinned HOST memory), re-plan through
     # init_forward_metadata_replay_cuda_graph, replay the captured layer, read the result on the host.
-    host_qkv = torch.empty(w.qkv.shape, dtype=w.qkv.dtype).pin_memory()
-    host_qkv.copy_(qkv0.cpu())
-    host_rpi = w.req_pool_indices.cpu().pin_memory()
-    host_sl = w.seq_lens.cpu().pin_memory()
-    host_loc = w.out_cache_loc.cpu().pin_memory()
+    # One packed pinned staging buffer [qkv | req_pool_indices | seq_lens | out_cache_loc] and one device
+    # mirror: a step's inputs cross PCIe / C2C as ONE copy (four separate copies cost ~4 x 8 us of launch +
+    # DMA set-up for 2.6 MB).
+    def _al(n):
+        return (n + 255) // 256 * 256
+    nb_qkv = w.qkv.numel() * w.qkv.element_size()
+    parts = [("qkv", w.qkv.dtype, tuple(w.qkv.shape), nb_qkv)] + \
+            [(n, torch.int64, (B,), 8 * B) for n in ("rpi", "sl", "loc")]
+    offs, total_b = {}, 0
+    for name, dt, shape, nb in parts:
+        offs[name] = (total_b, nb, dt, shape)
+        total_b = _al(total_b + nb)
+    host_buf = torch.empty(total_b, dtype=torch.uint8).pin_memory()
+    dev_buf = torch.empty(total_b, dtype=torch.uint8, device=dev)
+
+    def _view(buf, name):
+        o, nb, dt, shape = offs[name]
+        return buf[o:o + nb].view(dt).view(shape)
+    _view(host_buf, "qkv").copy_(qkv0.cpu())
+    _view(host_buf, "rpi").copy_(w.req_pool_indices.cpu())
+    _view(host_buf, "sl").copy_(w.seq_lens.cpu())
+    _view(host_buf, "loc").copy_(w.out_cache_loc.cpu())
     host_out = torch.empty((B, c.num_q_heads * c.head_dim), dtype=w.q.dtype).pin_memory()
-    d_qkv = torch.empty_like(w.qkv)
-    d_rpi, d_sl, d_loc = (torch.empty_like(t) for t in (w.req_pool_indices, w.seq_lens, w.out_cache_loc))
+    d_qkv, d_rpi, d_sl, d_loc = (_view(dev_buf, n) for n in ("qkv", "rpi", "sl", "loc"))
     qs, ks, vs = d_qkv.split([c.num_q_heads * c.head_dim, c.num_kv_heads * c.head_dim,
                               c.num_kv_heads * c.head_dim], dim=-1)
     fb2 = make_batch(w, runner, backend)
     fb2.req_pool_indices, fb2.seq_lens, fb2.out_cache_loc = d_rpi, d_sl, d_loc
-    h2d = sum(t.numel() * t.element_size() for t in (host_qkv, host_rpi, host_sl, host_loc))
+    h2d = total_b
     d2h = host_out.numel() * host_out.element_size()
     mode = b200attn.ForwardMode.DECODE
 
     def h2d_copies():
-        d_qkv.copy_(host_qkv, non_blocking=True)
-        d_rpi.copy_(host_rpi, non_blocking=True)
-        d_sl.copy_(host_sl, non_blocking=True)
-        d_loc.copy_(host_loc, non_blocking=True)
+        dev_buf.copy_(host_buf, non_blocking=True)
 
     def e2e_eager():
         h2d_copies()
@@ -514,13 +612,13 @@ def measure(R: Rank, args, gcfg, scaling: str, with_clocks: bool = True) -> dict
         host_out.zero_()
         e2e_ms, e2e_launches = time_e2e(e2e_one_graph)
         variants["one_graph"] = e2e_ms
-        e2e_path = ("one CUDA graph per step = [H2D(qkv, req_pool_indices, seq_lens, out_cache_loc) from pinned host "
-                    "memory -> init_forward_metadata_replay_cuda_graph (plan) -> RadixAttention.forward "
-                    "(kv_store, decode, merge) -> D2H(o) to pinned host memory]; host: graph launch + stream sync")
-        if hook_ms < e2e_ms:   # report the faster of the two graph variants, say which
-            e2e_ms, e2e_launches = hook_ms, hook_launches
-            e2e_path = ("H2D(qkv, req_pool_indices, seq_lens, out_cache_loc) -> init_forward_metadata_replay_cuda_graph "
-                        "(eager) -> CUDA-graph replay of RadixAttention.forward -> D2H(o) -> stream sync")
+        # Headline: the sequence the unmodified CudaGraphRunner drives (replay_prepare runs the backend's replay
+        # hook eagerly, then graph.replay(): cuda_graph_runner.py:760-768, 783-790).  The one-graph form (copies,
+        # plan, layer and D2H as nodes of a single graph) is reported beside it under variants_ms_per_step.
+        e2e_ms, e2e_launches = hook_ms, hook_launches
+        e2e_path = ("ONE packed H2D(qkv | req_pool_indices | seq_lens | out_cache_loc) from pinned host memory -> "
+                    "init_forward_metadata_replay_cuda_graph (eager plan launch) -> CUDA-graph replay of "
+                    "RadixAttention.forward (kv_store, decode + merge) -> D2H(o) -> stream sync")
     else:
         e2e_ms, e2e_launches = eager_ms, eager_launches
         e2e_path = "H2D -> init_forward_metadata -> RadixAttention.forward (eager) -> D2H(o) -> stream sync"
@@ -548,6 +646,17 @@ def measure(R: Rank, args, gcfg, scaling: str, with_clocks: bool = True) -> dict
         "gpu_launches": launches_per_step * args.steps,
         "clocks": clocks,
     }
+    if sustained is not None:
+        res["sustained"] = sustained
+    if other is not None:
+        res["other_kernels"] = other
+    if w.unique_tokens != w.seq_lens_sum:
+        # shared-prefix pages are read once per request that names them (logical bytes) but live in
+        # HBM once: the unique-byte figure is what DRAM must deliver at least, the rest can come from L2
+        ub = w.unique_tokens * c.num_kv_heads * 2 * c.head_dim * e_kv + decode_bytes - kv_bytes
+        res["roofline"]["unique_bytes"] = ub
+        res["roofline"]["achieved_unique"] = ub / (k_ms * 1e-3) / 1e9
+        res["roofline"]["frac_unique"] = ub / (k_ms * 1e-3) / 1e9 / peak
     del graph, kgraph, egraph, wgraph, backend, runner, w, fb, fb2
     torch.cuda.empty_cache()
     return res
@@ -594,9 +703,58 @@ def main():
         if world == 1 and not args.no_cpu_baseline:
             tps, cms, info = cpu_reference_run(cfg, args.cpu_sample_requests, 5, 2)
             line["cpu_baseline"] = {"value": tps, "unit": UNIT, "cores": info["cores"], "kind": info["kind"],
-                                    "sample": info["sample"], "ms_per_step": cms, "gb_per_s": info["gb_per_s"]}
+                                    "sample": info["sample"], "ms_per_step": cms, "gb_per_s": info["gb_per_s"],
+                                    "torch_native": info["torch_native"]}
         print(json.dumps(line), flush=True)
     R.shutdown()
+
+
+def small_kernel_rooflines(R, w, c, pool, peak):
+    """K1 kv_store, K4 rope_kv_store and merge_states at the workload's shape: bytes moved / CUDA-event time of
+    8 launches per graph replay.  MB-sized launches: their time is launch latency, not bandwidth -- the lines
+    exist so that nothing on the path goes unmeasured."""
+    import b200attn
+
+    torch, dev = R.torch, R.dev
+    B, Hq, Hkv, D = c.batch, c.num_q_heads, c.num_kv_heads, c.head_dim
+    fp8 = c.kv_dtype == "fp8_e4m3"
+    e_kv = 1 if fp8 else 2
+    q3, k3, v3 = w.q.view(B, Hq, D), w.k.view(B, Hkv, D), w.v.view(B, Hkv, D)
+    kp, vp = pool.k_buffer[0], pool.v_buffer[0]
+    pos = (w.seq_lens - 1).to(torch.int64)
+    import synth
+    cache = synth.cos_sin_cache(D, int(w.seq_lens_np.max()) + 8).to(dev)
+    ks = c.k_scale if fp8 else None
+    vs = c.v_scale if fp8 else None
+    oa = torch.randn((B, Hq, D), device=dev).to(w.q.dtype)
+    ob = torch.randn((B, Hq, D), device=dev).to(w.q.dtype)
+    la, lb = torch.randn((B, Hq), device=dev), torch.randn((B, Hq), device=dev)
+    oo, lo = torch.empty_like(oa), torch.empty_like(la)
+    cases = [
+        ("kv_store_kernel (K1)", lambda: b200attn.store_kv(kp, vp, w.out_cache_loc, k3, v3, ks, vs),
+         2 * B * Hkv * D * (2 + e_kv) + 8 * B),
+        ("rope_kv_store_kernel (K4)", lambda: b200attn.rope_store_kv(q3, k3, v3, pos, cache, True, w.out_cache_loc, kp, vp, ks, vs),
+         2 * B * Hq * D * 2 + 2 * B * Hkv * D * (2 + e_kv) + B * (8 + 8 + 4 * D)),
+        ("merge_states_kernel (merge_state_v2)", lambda: torch.ops.b200attn.merge_states(oa, la, ob, lb, oo, lo),
+         3 * B * Hq * D * 2 + 3 * B * Hq * 4),
+    ]
+    out = []
+    qkv0 = w.qkv.clone()
+    for name, fn, nbytes in cases:
+        fn()
+        torch.cuda.synchronize()
+        g = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(g):
+            for _ in range(8):
+                fn()
+        for _ in range(3):
+            g.replay()
+        ms = R.timed(g.replay, 20, False) / 8
+        w.qkv.copy_(qkv0)          # RoPE / fp8 div_ rotate and scale q, k, v in place
+        gbs = nbytes / (ms * 1e-3) / 1e9
+        out.append({"kernel": name, "kernel_ms": ms, "algorithmic_bytes": nbytes, "achieved": gbs, "unit": "GB/s",
+                    "frac": gbs / peak, "bound": "hbm (launch-latency dominated at this size)"})
+    return out
 
 
 def _measured_peak():

@@ -61,7 +61,8 @@ enum {
 enum {
   B200ATTN_BF16 = 0,
   B200ATTN_F16 = 1,
-  B200ATTN_FP8_E4M3 = 2 /* torch.float8_e4m3fn, stored as raw bytes (uint8 pool) */
+  B200ATTN_FP8_E4M3 = 2, /* torch.float8_e4m3fn, stored as raw bytes (uint8 pool) */
+  B200ATTN_F32 = 3       /* b200attn_merge_states only */
 };
 
 /* Width of the seq_lens / req_pool_indices arrays (int64 eager, int32 under
@@ -326,7 +327,8 @@ typedef struct {
   void* o_out;                 /* [tokens, heads, head_dim] */
   float* lse_out;              /* optional */
   int32_t tokens, heads, head_dim;
-  int32_t dtype;               /* B200ATTN_BF16 | B200ATTN_F16 */
+  int32_t dtype;               /* B200ATTN_BF16 | B200ATTN_F16 | B200ATTN_F32 (the reference dispatches all
+                                  three, merge_attn_states.cu:111-122); head_dim % (16 / sizeof) == 0 */
 } b200attn_merge_states_args;
 
 int b200attn_merge_states(const b200attn_merge_states_args* args, b200attn_stream_t stream);

@@ -372,7 +372,7 @@ def _merge_states(o_a, lse_a, o_b, lse_b, o_out, lse_out):
     a.o_a, a.lse_a, a.o_b, a.lse_b = o_a.data_ptr(), lse_a.data_ptr(), o_b.data_ptr(), lse_b.data_ptr()
     a.o_out, a.lse_out = o_out.data_ptr(), _ptr(lse_out)
     a.tokens, a.heads, a.head_dim = o_a.shape
-    a.dtype = dtype_code(o_a.dtype)
+    a.dtype = capi.F32 if o_a.dtype == torch.float32 else dtype_code(o_a.dtype)
     with torch.cuda.device(o_a.device):
         capi.check("b200attn_merge_states", capi.lib().b200attn_merge_states(C.byref(a), _stream(o_a)))
 

@@ -76,6 +76,10 @@ inline bool no_swizzle() {
   static const bool v = env_flag("B200ATTN_NO_SWIZZLE");
   return v;
 }
+inline bool no_pdl() {   // B200ATTN_NO_PDL=1: decode_kernel launched without the programmatic-serialization attribute
+  static const bool v = env_flag("B200ATTN_NO_PDL");
+  return v;
+}
 inline bool no_xch() {
   static const bool v = env_flag("B200ATTN_NO_XCH");
   return v;
@@ -165,6 +169,21 @@ __host__ __device__ inline int range_of(const PlanHeader& h, int g) {
   return g < s ? g / h.per_static : h.n_static + (g - s) / h.per_dynamic;
 }
 
+// What a CTA needs to start streaming range r without walking the plan's tables: the range's bounds and the
+// piece it visits first (PieceWalk: the range's LAST virtual request).  Read with one load at kernel entry,
+// next to the header, so the producers' first copy waits on desc -> slot ids -> rows instead of
+// header -> range tables -> chunk prefix -> seq_len / row_off -> slot ids -> rows (each a dependent global
+// round trip of 0.5-0.7 us: tools/trace_decode.py, 3.3 us from CTA entry to the first copy).
+struct __align__(16) RangeDesc {
+  int32_t v_first, v_last;   // first / last virtual request of the range
+  int32_t g0, g1;            // chunk interval [g0, g1) of the range
+  int32_t b, hg;             // the first piece visited: request, head group
+  int32_t lc0, lc1;          // its chunk interval inside the request
+  int32_t nchunks, seq_len;  // of request b
+  int64_t row_off;           // element offset of request b's index row
+};
+static_assert(sizeof(RangeDesc) == 48, "RangeDesc is 48 bytes");
+
 struct PlanView {
   PlanHeader* hdr;
   int32_t* seq_len;       // [batch]
@@ -175,6 +194,7 @@ struct PlanView {
   int32_t* vreq_rfirst;   // [batch * kMaxHeadGroups] first range that touches virtual request v
   int32_t* vreq_pieces;   // [batch * kMaxHeadGroups] ranges that touch v (its partials to merge)
   int32_t* vreq_arrived;  // [batch * kMaxHeadGroups] pieces written so far (self-resetting)
+  RangeDesc* range_desc;  // [kMaxRanges]
 };
 
 __host__ __device__ inline size_t align_up(size_t x, size_t a) { return (x + a - 1) / a * a; }
@@ -186,6 +206,7 @@ __host__ __device__ inline size_t plan_bytes_for(int batch) {
   n += align_up((size_t)batch * 8, 16);        // row_off
   n += 2 * (size_t)kMaxRanges * 4;             // range_vreq, range_vlast
   n += 3 * align_up((size_t)batch * kMaxHeadGroups * 4, 16);
+  n += (size_t)kMaxRanges * sizeof(RangeDesc);
   return n;
 }
 
@@ -210,6 +231,8 @@ __host__ __device__ inline PlanView plan_view(void* base, int batch) {
   v.vreq_pieces = reinterpret_cast<int32_t*>(p);
   p += tbl;
   v.vreq_arrived = reinterpret_cast<int32_t*>(p);
+  p += tbl;
+  v.range_desc = reinterpret_cast<RangeDesc*>(p);
   return v;
 }
 
@@ -351,6 +374,12 @@ __device__ __forceinline__ uint32_t e4m3x2_to_f16x2(uint32_t x) {
       : "r"(x));
   return r;
 }
+
+// Programmatic dependent launch (sm_90+).  launch_dependents: the next kernel on the stream, if it was launched
+// with the programmatic-serialization attribute, may start its CTAs now.  wait: block until the kernels this
+// one depends on have completed and their writes are visible (a no-op for a normally launched kernel).
+__device__ __forceinline__ void pdl_launch_dependents() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+__device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
 
 __device__ __forceinline__ float fast_exp2(float x) {
   float y;

@@ -119,33 +119,55 @@ __device__ __forceinline__ void mma_q(float (&d)[4], const uint32_t (&q)[QR], ui
 // shared with the neighbouring ranges (a request cut by the range boundary); visiting both early
 // means every cut request has all its partials -- and its merge -- done long before the kernel ends,
 // and each CTA finishes on whole requests whose epilogue is a plain store.
+__device__ __forceinline__ RangeDesc load_desc(const RangeDesc* d) {
+  RangeDesc r;
+  const int4* s = reinterpret_cast<const int4*>(d);
+  int4* t = reinterpret_cast<int4*>(&r);
+  t[0] = s[0];
+  t[1] = s[1];
+  t[2] = s[2];
+  return r;
+}
+
 struct PieceWalk {
-  int v_first, v_last, g0, g1, ng;
+  RangeDesc d;
+  int ng;
   int i = 0;
   int left;  // chunks of the range not yet handed out
-  __device__ __forceinline__ PieceWalk(const PlanView& pv, const PlanHeader& H, int rg, int ng_)
-      : v_first(pv.range_vreq[rg]), v_last(pv.range_vlast[rg]), g0(range_begin(H, rg)),
-        g1(range_begin(H, rg + 1)), ng(ng_) {
-    left = g1 - g0;
-  }
+  __device__ __forceinline__ PieceWalk(const RangeDesc& d_, int ng_) : d(d_), ng(ng_) { left = d.g1 - d.g0; }
+  // S / row_off: the request's length and the element offset of its index row
   __device__ __forceinline__ bool next(const PlanView& pv, int& b, int& hg, int& lc0, int& lc1,
-                                       int& nchunks, int& vreq) {
-    const int m = v_last - v_first + 1;
+                                       int& nchunks, int& vreq, int& S, int64_t& row_off) {
+    if (i == 0) {  // the range's last virtual request, straight from the descriptor
+      i = 1;
+      b = d.b;
+      hg = d.hg;
+      lc0 = d.lc0;
+      lc1 = d.lc1;
+      nchunks = d.nchunks;
+      vreq = d.v_last;
+      S = d.seq_len;
+      row_off = d.row_off;
+      return true;
+    }
+    const int m = d.v_last - d.v_first + 1;
     while (i < m) {
-      const int v = i == 0 ? v_last : v_first + i - 1;
+      const int v = d.v_first + i - 1;
       ++i;
       b = v / ng;
       hg = v - b * ng;
       const int cp0 = pv.chunk_prefix[b];
       const int n = pv.chunk_prefix[b + 1] - cp0;
       const int vstart = ng * cp0 + hg * n;
-      const int lo = vstart > g0 ? vstart : g0;
-      const int hi = vstart + n < g1 ? vstart + n : g1;
+      const int lo = vstart > d.g0 ? vstart : d.g0;
+      const int hi = vstart + n < d.g1 ? vstart + n : d.g1;
       if (lo >= hi) continue;  // empty request
       lc0 = lo - vstart;
       lc1 = hi - vstart;
       nchunks = n;
       vreq = v;
+      S = pv.seq_len[b];
+      row_off = pv.row_off[b];
       return true;
     }
     return false;
@@ -161,24 +183,40 @@ __global__ void __launch_bounds__(kThreads, 1) decode_kernel(const DecodeParams 
   constexpr int EB = FP8 ? 1 : 2;      // KV element bytes
 
   extern __shared__ __align__(128) uint8_t smem[];
-  const PlanView pv = plan_view(const_cast<void*>(p.plan), p.batch);
-  const PlanHeader& H = *pv.hdr;  // read where needed (range transitions), not held in registers
   const int cta = blockIdx.x;
-#ifdef B200ATTN_DEC_TRACE
-  bool tr_a = false, tr_b = false, tr_c = false;
-  unsigned long long tr_chunks = 0, tr_pieces = 0;
-  if (threadIdx.x == 0) { B200_TR_GT(TR_GT_ENTRY); B200_TR(TR_ENTRY); }
-#endif
-  if (cta >= H.grid) return;
-  const int R = H.n_ranges;
-  const int n_dyn = H.n_dynamic, n_grid = H.grid, n_static = H.n_static;
-
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const uint32_t bar_full = smem_u32(smem);
   const uint32_t bar_empty = bar_full + kMaxStages * 8;
   const uint32_t stage0 = bar_full + kBarrierBytes;
   volatile int32_t* rq = reinterpret_cast<volatile int32_t*>(smem + kRangeRingOff);   // ring of range ids
   volatile int32_t* merge_flag = reinterpret_cast<volatile int32_t*>(smem + kMergeFlagOff);
-  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+#ifdef B200ATTN_DEC_TRACE
+  bool tr_a = false, tr_b = false, tr_c = false;
+  unsigned long long tr_chunks = 0, tr_pieces = 0;
+  if (threadIdx.x == 0) { B200_TR_GT(TR_GT_ENTRY); B200_TR(TR_ENTRY); }
+#endif
+  // Everything that needs no global data first: under programmatic dependent launch this part (CTA launch,
+  // barrier init) overlaps the tail of the kernel in front (kv_store / RoPE + store), which has released its
+  // dependents at its start.
+  if (threadIdx.x == 0) {
+    for (int s = 0; s < p.stages; ++s) {
+      mbar_init(bar_full + s * 8, p.cp_async ? kProducerWarps * 32 : kProducerWarps);
+      mbar_init(bar_empty + s * 8, kConsumerWarps);
+    }
+    fence_barrier_init();
+  }
+  pdl_wait();  // plan, q and the pool rows of this step are written by kernels in front of this one
+
+  const PlanView pv = plan_view(const_cast<void*>(p.plan), p.batch);
+  const PlanHeader& H = *pv.hdr;  // read where needed (range transitions), not held in registers
+  // this CTA's static range, fetched together with the header (valid when cta < n_static)
+  const RangeDesc d0 = load_desc(pv.range_desc + cta);
+  if (cta >= H.grid) return;
+  // A plan built for another batch, head geometry or chunk size would send the walk through garbage ranges:
+  // do nothing instead (o is left untouched; b200attn_decode documents that plan and call must agree).
+  if (H.magic != kPlanMagic || H.batch != p.batch || H.ng != p.ng || H.chunk_tokens != p.chunk_tokens) return;
+  const int R = H.n_ranges;
+  const int n_dyn = H.n_dynamic, n_grid = H.grid, n_static = H.n_static;
 
   // Dynamic ranges are claimed through a ticket counter in the plan buffer.  Every launch draws
   // exactly n_dynamic + grid tickets (each CTA stops at its first ticket past the dynamic ranges),
@@ -189,20 +227,14 @@ __global__ void __launch_bounds__(kThreads, 1) decode_kernel(const DecodeParams 
     return k < static_cast<unsigned>(n_dyn) ? n_static + static_cast<int>(k) : R;
   };
 
-  if (threadIdx.x == 0) {
-    for (int s = 0; s < p.stages; ++s) {
-      mbar_init(bar_full + s * 8, p.cp_async ? kProducerWarps * 32 : kProducerWarps);
-      mbar_init(bar_empty + s * 8, kConsumerWarps);
-    }
-    fence_barrier_init();
-    rq[0] = cta < n_static ? cta : take_ticket();
-  }
+  if (threadIdx.x == 0) rq[0] = cta < n_static ? cta : take_ticket();
   __syncthreads();
   if (threadIdx.x == 0) B200_TR(TR_BARS_READY);
 
   const int T = p.chunk_tokens;
   const uint32_t v_off = T * p.row_stride;  // V rows follow the K rows of a stage
-  int b, hg, lc0, lc1, nchunks, vreq;
+  int b, hg, lc0, lc1, nchunks, vreq, S;
+  int64_t row_off;
   int stage = 0;
   uint32_t phase = 0;
   int rn = 0;          // ranges done by this CTA
@@ -255,11 +287,10 @@ __global__ void __launch_bounds__(kThreads, 1) decode_kernel(const DecodeParams 
         // chunk is issued, so the atomic's round trip (microseconds under load) hides behind the copies.
         int next_rg = R;
         if (pw == 0 && lane == 0) next_rg = take_ticket();
-        PieceWalk walk(pv, H, rg, p.ng);
-      while (walk.next(pv, b, hg, lc0, lc1, nchunks, vreq)) {
+        PieceWalk walk(rn == 0 && rg == cta ? d0 : load_desc(pv.range_desc + rg), p.ng);
+      while (walk.next(pv, b, hg, lc0, lc1, nchunks, vreq, S, row_off)) {
         if (pw == 0 && lane == 0) B200_TR_ONCE(TR_P_WALK, tr_a);
-        const int S = pv.seq_len[b];
-        const int32_t* idx = p.indices + pv.row_off[b];
+        const int32_t* idx = p.indices + row_off;
         const uint8_t* base = pool + static_cast<int64_t>(hg) * p.row_bytes;
         int32_t nxt[2];
 #pragma unroll
@@ -329,11 +360,10 @@ __global__ void __launch_bounds__(kThreads, 1) decode_kernel(const DecodeParams 
       // chunk is issued, so the atomic's round trip (microseconds under load) hides behind the copies.
       int next_rg = R;
       if (pw == 0 && lane == 0) next_rg = take_ticket();
-      PieceWalk walk(pv, H, rg, p.ng);
-    while (walk.next(pv, b, hg, lc0, lc1, nchunks, vreq)) {
+      PieceWalk walk(rn == 0 && rg == cta ? d0 : load_desc(pv.range_desc + rg), p.ng);
+    while (walk.next(pv, b, hg, lc0, lc1, nchunks, vreq, S, row_off)) {
       if (pw == 0 && lane == 0) B200_TR_ONCE(TR_P_WALK, tr_a);
-      const int S = pv.seq_len[b];
-      const int32_t* idx = p.indices + pv.row_off[b];
+      const int32_t* idx = p.indices + row_off;
       const uint8_t* base = pool + static_cast<int64_t>(hg) * p.row_bytes;
       int32_t nxt[2];
 #pragma unroll
@@ -434,9 +464,8 @@ __global__ void __launch_bounds__(kThreads, 1) decode_kernel(const DecodeParams 
   }
 
   while (rg < R) {
-  PieceWalk walk(pv, H, rg, p.ng);
-  while (walk.next(pv, b, hg, lc0, lc1, nchunks, vreq)) {
-    const int S = pv.seq_len[b];
+  PieceWalk walk(rn == 0 && rg == cta ? d0 : load_desc(pv.range_desc + rg), p.ng);
+  while (walk.next(pv, b, hg, lc0, lc1, nchunks, vreq, S, row_off)) {
     const int hq0 = (hg * p.hc + h) * p.group;
     const bool row0 = gq < p.group;
     const bool row1 = ROWS16 && (gq + 8 < p.group);
@@ -679,13 +708,19 @@ __global__ void __launch_bounds__(kThreads, 1) decode_kernel(const DecodeParams 
       lse1 = l1 > 0.f ? m1 * c * kLn2 + logf(l1) : -CUDART_INF_F;
     }
     const bool full_req = lc0 == 0 && lc1 == nchunks;
-    const bool whole = p.ts == 1 && full_req;
     // column (head-dim index) of accumulator element e (0/1) of tile n
     auto col_of = [&](int n, int e) -> int {
       if constexpr (!FP8) return n * 8 + 2 * jq + e;
       return (n >> 1) * 16 + 4 * jq + 2 * e + (n & 1);
     };
-    if (whole) {
+    const int hqv = p.hc * p.group;
+    // Workspace rows of this piece: ((vreq + rg) * ts + slice) * hqv + head; with the in-CTA slice merge below
+    // only slice 0's rows are used (one partial per piece instead of ts).
+    const int64_t piece_row = static_cast<int64_t>(vreq + rg) * p.ts * hqv;
+    const bool use_xch = !ROWS16 && p.xch_off != 0;   // implies ts > 1 (make_geometry)
+    bool final_written = false;
+    if (p.ts == 1 && full_req) {
+      final_written = true;
       QT* o0 = reinterpret_cast<QT*>(p.o) + b * p.o_sb + (hq0 + gq) * p.o_sh;
       if (row0) {
 #pragma unroll
@@ -706,11 +741,14 @@ __global__ void __launch_bounds__(kThreads, 1) decode_kernel(const DecodeParams 
           if (p.lse && jq == 0) p.lse[static_cast<int64_t>(b) * p.hq + hq0 + gq + 8] = lse1;
         }
       }
-    } else if (!ROWS16 && full_req && p.xch_off != 0) {
-      // A whole request, cut into ts token slices only by this CTA's own warps: the slices meet in shared
-      // memory (unnormalised O, max, sum) and each warp finishes 1 / ts of the head's columns.  Through the
-      // workspace the same merge cost a write -> fence -> atomic -> read-back chain of global round trips
-      // (~3 us per request with the consumers idle: 7 % of a 4096-token request on the 8-way shard shape).
+    } else if (use_xch) {
+      // The ts token slices of this piece meet in shared memory (unnormalised O, max, sum) and each warp
+      // finishes 1 / ts of its head's columns: a whole request goes straight to `o`; a piece of a request cut
+      // by a range boundary leaves ONE normalised partial per head in the workspace instead of ts.  Through
+      // the workspace the slice merge cost a write -> fence -> atomic -> read-back chain of global round trips
+      // per piece with the consumers idle, and ts x the rows for the cross-CTA merge to read back
+      // (tools/trace_decode.py, 8-way shard shape: 6.7 us from the last chunk to the CTA's exit).
+      final_written = full_req;
       const int g4 = p.group * 4;
       float2* xall = reinterpret_cast<float2*>(smem + p.xch_off);
       float2* xml = xall + kXchWarps * NTILES * g4;
@@ -739,7 +777,9 @@ __global__ void __launch_bounds__(kThreads, 1) decode_kernel(const DecodeParams 
           }
         }
         const float inv = L > 0.f ? p.v_scale / L : 0.f;
+        const float lse_all = L > 0.f ? mm * kLn2 + logf(L) : -CUDART_INF_F;
         QT* o0 = reinterpret_cast<QT*>(p.o) + b * p.o_sb + (hq0 + gq) * p.o_sh;
+        float* w0 = p.ws_o + (piece_row + h * p.group + gq) * D;
         for (int n = tsi; n < NTILES; n += p.ts) {
           float a0 = 0.f, a1 = 0.f;
 #pragma unroll
@@ -750,16 +790,24 @@ __global__ void __launch_bounds__(kThreads, 1) decode_kernel(const DecodeParams 
               a1 = fmaf(wgt[s], v.y, a1);
             }
           }
-          store_q(o0 + col_of(n, 0), a0 * inv);
-          store_q(o0 + col_of(n, 1), a1 * inv);
+          if (full_req) {
+            store_q(o0 + col_of(n, 0), a0 * inv);
+            store_q(o0 + col_of(n, 1), a1 * inv);
+          } else {
+            w0[col_of(n, 0)] = a0 * inv;
+            w0[col_of(n, 1)] = a1 * inv;
+          }
         }
-        if (p.lse && jq == 0 && tsi == 0)
-          p.lse[static_cast<int64_t>(b) * p.hq + hq0 + gq] = L > 0.f ? mm * kLn2 + logf(L) : -CUDART_INF_F;
+        if (jq == 0 && tsi == 0) {
+          if (!full_req) p.ws_lse[piece_row + h * p.group + gq] = lse_all;
+          else if (p.lse) p.lse[static_cast<int64_t>(b) * p.hq + hq0 + gq] = lse_all;
+        }
       }
-      named_bar_sync(2, kConsumerWarps * 32);  // the area is free for the next request
+      // the closing barrier (the area is free for the next piece) is the one in front of the arrival counter
+      // below for a partial piece
+      if (full_req || !p.fuse_merge) named_bar_sync(2, kConsumerWarps * 32);
     } else {
-      const int hqv = p.hc * p.group;
-      const int64_t row = (static_cast<int64_t>(vreq + rg) * p.ts + tsi) * hqv + h * p.group + gq;
+      const int64_t row = piece_row + static_cast<int64_t>(tsi) * hqv + h * p.group + gq;
       if (row0) {
         float* w = p.ws_o + row * D;
 #pragma unroll
@@ -780,30 +828,39 @@ __global__ void __launch_bounds__(kThreads, 1) decode_kernel(const DecodeParams 
           if (jq == 0) p.ws_lse[row + 8] = lse1;
         }
       }
-      if (p.fuse_merge) {
-        // Stage 2 without a second launch: the CTA that lands a virtual request's last piece
-        // merges all of them (threadfence + counter, the "last block done" pattern).  The
-        // producers keep streaming the next piece's chunks meanwhile.
+    }
+    if (!final_written && p.fuse_merge) {
+      // Stage 2 without a second launch: the CTA that lands a virtual request's last piece
+      // merges all of them (threadfence + counter, the "last block done" pattern).  The
+      // producers keep streaming the next piece's chunks meanwhile.
+      __threadfence();
+      named_bar_sync(2, kConsumerWarps * 32);
+      if (threadIdx.x == 0) {
+        const int arrived = atomicAdd(&pv.vreq_arrived[vreq], 1) + 1;
+        const int last = arrived == pv.vreq_pieces[vreq];
+        if (last) pv.vreq_arrived[vreq] = 0;  // ready for the next layer's launch
+        *merge_flag = last;
+      }
+      named_bar_sync(2, kConsumerWarps * 32);
+      if (*merge_flag) {
+        if (threadIdx.x == 0) B200_TR(TR_C_MERGED);
         __threadfence();
-        named_bar_sync(2, kConsumerWarps * 32);
-        if (threadIdx.x == 0) {
-          const int arrived = atomicAdd(&pv.vreq_arrived[vreq], 1) + 1;
-          const int last = arrived == pv.vreq_pieces[vreq];
-          if (last) pv.vreq_arrived[vreq] = 0;  // ready for the next layer's launch
-          *merge_flag = last;
-        }
-        named_bar_sync(2, kConsumerWarps * 32);
-        if (*merge_flag) {
-          if (threadIdx.x == 0) B200_TR(TR_C_MERGED);
-          __threadfence();
-          const int np = pv.vreq_pieces[vreq] * p.ts;
-          const int64_t prow0 = static_cast<int64_t>(vreq + pv.vreq_rfirst[vreq]) * p.ts * hqv;
-          for (int hl = warp; hl < hqv; hl += kConsumerWarps) {
-            const int hqi = hg * hqv + hl;
-            merge_rows<QT>(p.ws_o, p.ws_lse, prow0 + hl, hqv, np, D,
-                           reinterpret_cast<QT*>(p.o) + b * p.o_sb + hqi * p.o_sh,
-                           p.lse ? p.lse + static_cast<int64_t>(b) * p.hq + hqi : nullptr, lane);
+        const int nsl = use_xch ? 1 : p.ts;            // partial rows per piece
+        const int np = pv.vreq_pieces[vreq] * nsl;
+        const int64_t step = static_cast<int64_t>(use_xch ? p.ts : 1) * hqv;
+        const int64_t prow0 = static_cast<int64_t>(vreq + pv.vreq_rfirst[vreq]) * p.ts * hqv;
+        QT* ob = reinterpret_cast<QT*>(p.o) + b * p.o_sb + static_cast<int64_t>(hg) * hqv * p.o_sh;
+        float* lb = p.lse ? p.lse + static_cast<int64_t>(b) * p.hq + hg * hqv : nullptr;
+        if (np <= 4 && D <= 128) {
+          // few partials: four heads per warp at once, every load in flight together (one L2 round trip)
+          for (int hl = warp; hl < hqv; hl += 4 * kConsumerWarps) {
+            const int nh = (hqv - hl + kConsumerWarps - 1) / kConsumerWarps;
+            merge_heads4<QT>(p.ws_o, p.ws_lse, prow0 + hl, kConsumerWarps, nh < 4 ? nh : 4, step, np, D,
+                             ob + hl * p.o_sh, kConsumerWarps * p.o_sh, lb ? lb + hl : nullptr, kConsumerWarps, lane);
           }
+        } else {
+          for (int hl = warp; hl < hqv; hl += kConsumerWarps)
+            merge_head<QT>(p.ws_o, p.ws_lse, prow0 + hl, step, np, D, ob + hl * p.o_sh, lb ? lb + hl : nullptr, lane);
         }
       }
     }
@@ -825,18 +882,39 @@ template <typename QT, bool FP8>
 cudaError_t launch_decode(const DecodeParams& p, int head_dim, bool rows16, int grid, int smem,
                           cudaStream_t stream);
 
+// The dynamic shared-memory limit is a per-function, per-device attribute: set on first use, not per launch.
+inline cudaError_t ensure_smem_attr(const void* fn, int smem, int* cache /* [64] */) {
+  int dev = 0;
+  if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) dev = -1;
+  if (dev >= 0 && cache[dev] >= smem) return cudaSuccess;
+  cudaError_t e = cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
+  if (e == cudaSuccess && dev >= 0) cache[dev] = smem;
+  return e;
+}
+
 #define B200ATTN_DEFINE_LAUNCH(QT, FP8)                                                          \
   template <>                                                                                    \
   cudaError_t launch_decode<QT, FP8>(const DecodeParams& p, int head_dim, bool rows16, int grid, \
                                      int smem, cudaStream_t stream) {                            \
+    static int attr_cache[4][64];                                                                \
     void (*fn)(const DecodeParams) = nullptr;                                                    \
-    if (head_dim == 64) fn = rows16 ? decode_kernel<QT, FP8, 64, true> : decode_kernel<QT, FP8, 64, false>;        \
-    else if (head_dim == 128) fn = rows16 ? decode_kernel<QT, FP8, 128, true> : decode_kernel<QT, FP8, 128, false>; \
+    int slot = 0;                                                                                \
+    if (head_dim == 64) { fn = rows16 ? decode_kernel<QT, FP8, 64, true> : decode_kernel<QT, FP8, 64, false>; slot = rows16; }        \
+    else if (head_dim == 128) { fn = rows16 ? decode_kernel<QT, FP8, 128, true> : decode_kernel<QT, FP8, 128, false>; slot = 2 + rows16; } \
     if (!fn) return cudaErrorInvalidValue;                                                       \
-    cudaError_t e = cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, smem); \
+    cudaError_t e = ensure_smem_attr(reinterpret_cast<const void*>(fn), smem, attr_cache[slot]); \
     if (e != cudaSuccess) return e;                                                              \
-    fn<<<grid, kThreads, smem, stream>>>(p);                                                     \
-    return cudaGetLastError();                                                                   \
+    cudaLaunchConfig_t cfg = {};                                                                 \
+    cfg.gridDim = dim3(grid);                                                                    \
+    cfg.blockDim = dim3(kThreads);                                                               \
+    cfg.dynamicSmemBytes = smem;                                                                 \
+    cfg.stream = stream;                                                                         \
+    cudaLaunchAttribute at[1];                                                                   \
+    at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;                               \
+    at[0].val.programmaticStreamSerializationAllowed = 1;                                        \
+    cfg.attrs = at;                                                                              \
+    cfg.numAttrs = no_pdl() ? 0 : 1;                                                             \
+    return cudaLaunchKernelEx(&cfg, fn, p);                                                      \
   }
 
 }  // namespace b200attn

@@ -28,6 +28,7 @@ struct StoreParams {
 
 template <typename T, bool FP8, int VEC>
 __global__ void __launch_bounds__(256) kv_store_kernel(StoreParams p) {
+  pdl_launch_dependents();  // decode_kernel's CTAs may come up and initialise; they wait before reading the pool
   const int vk = p.heads * (p.dim[0] / VEC);
   const int vv = p.heads * (p.dim[1] / VEC);
   const int per_token = vk + vv;

@@ -37,7 +37,7 @@ __global__ void __launch_bounds__(128) merge_kernel(const MergeParams p) {
   }
   if (p.ts == 1 && pieces == 1) return;  // decode_kernel wrote o directly
   const int64_t row0 = static_cast<int64_t>(v + pv.vreq_rfirst[v]) * p.ts * hqv + hl;
-  merge_rows<QT>(p.ws_o, p.ws_lse, row0, hqv, pieces * p.ts, p.dv, out, lse_out, lane);
+  merge_head<QT>(p.ws_o, p.ws_lse, row0, hqv, pieces * p.ts, p.dv, out, lse_out, lane);
 }
 
 template __global__ void merge_kernel<__nv_bfloat16>(const MergeParams);
@@ -51,8 +51,14 @@ cudaError_t launch_merge(const MergeParams& p, bool half, cudaStream_t stream) {
   return cudaGetLastError();
 }
 
-// 2-way merge; one thread per 8-element pack.  +inf lse counts as -inf
-// (merge_attn_states.cu:68-69).
+// 2-way merge; one thread per 128-bit pack (8 half / bf16 elements, 4 floats: the reference dispatches
+// float, half and bf16, merge_attn_states.cu:111-122).  +inf lse counts as -inf (merge_attn_states.cu:68-69).
+__device__ __forceinline__ float ms_to_f32(float x) { return x; }
+__device__ __forceinline__ float ms_to_f32(__half x) { return __half2float(x); }
+__device__ __forceinline__ float ms_to_f32(__nv_bfloat16 x) { return __bfloat162float(x); }
+template <typename QT>
+__device__ __forceinline__ QT ms_from_f32(float x) { return QT(x); }
+
 template <typename QT>
 __global__ void __launch_bounds__(128) merge_states_kernel(const QT* __restrict__ oa,
                                                           const float* __restrict__ la,
@@ -61,7 +67,8 @@ __global__ void __launch_bounds__(128) merge_states_kernel(const QT* __restrict_
                                                           QT* __restrict__ out,
                                                           float* __restrict__ lout, int tokens,
                                                           int heads, int dim) {
-  const int packs = dim / 8;
+  constexpr int PACK = 16 / sizeof(QT);
+  const int packs = dim / PACK;
   const int64_t i = blockIdx.x * static_cast<int64_t>(blockDim.x) + threadIdx.x;
   if (i >= static_cast<int64_t>(tokens) * heads * packs) return;
   const int64_t th = i / packs;
@@ -73,14 +80,23 @@ __global__ void __launch_bounds__(128) merge_states_kernel(const QT* __restrict_
   const float ea = expf(a - mx), eb = expf(b - mx);
   const float se = ea + eb;
   const float wa = ea / se, wb = eb / se;
-  const int64_t off = th * dim + pk * 8;
-  QT xa[8], xb[8], y[8];
+  const int64_t off = th * dim + pk * PACK;
+  QT xa[PACK], xb[PACK], y[PACK];
   *reinterpret_cast<uint4*>(xa) = *reinterpret_cast<const uint4*>(oa + off);
   *reinterpret_cast<uint4*>(xb) = *reinterpret_cast<const uint4*>(ob + off);
 #pragma unroll
-  for (int e = 0; e < 8; ++e) y[e] = QT(float(xa[e]) * wa + float(xb[e]) * wb);
+  for (int e = 0; e < PACK; ++e) y[e] = ms_from_f32<QT>(ms_to_f32(xa[e]) * wa + ms_to_f32(xb[e]) * wb);
   *reinterpret_cast<uint4*>(out + off) = *reinterpret_cast<const uint4*>(y);
   if (lout && pk == 0) lout[th] = logf(se) + mx;
+}
+
+template <typename QT>
+static void launch_merge_states(const b200attn_merge_states_args* a, cudaStream_t s) {
+  const int64_t n = static_cast<int64_t>(a->tokens) * a->heads * (a->head_dim / (16 / sizeof(QT)));
+  const unsigned blocks = static_cast<unsigned>((n + 127) / 128);
+  merge_states_kernel<QT><<<blocks, 128, 0, s>>>(static_cast<const QT*>(a->o_a), a->lse_a, static_cast<const QT*>(a->o_b),
+                                                 a->lse_b, static_cast<QT*>(a->o_out), a->lse_out, a->tokens, a->heads,
+                                                 a->head_dim);
 }
 
 }  // namespace b200attn
@@ -90,23 +106,16 @@ using namespace b200attn;
 extern "C" __attribute__((visibility("default"))) int b200attn_merge_states(const b200attn_merge_states_args* a, b200attn_stream_t s_) {
   if (!a || !a->o_a || !a->o_b || !a->lse_a || !a->lse_b || !a->o_out) return B200ATTN_E_INVALID;
   if (a->tokens < 0 || a->heads <= 0 || a->head_dim <= 0) return B200ATTN_E_INVALID;
-  if (a->head_dim % 8 != 0) return B200ATTN_E_UNSUPPORTED;
-  if (a->dtype != B200ATTN_BF16 && a->dtype != B200ATTN_F16) return B200ATTN_E_UNSUPPORTED;
+  if (a->dtype != B200ATTN_BF16 && a->dtype != B200ATTN_F16 && a->dtype != B200ATTN_F32) return B200ATTN_E_UNSUPPORTED;
+  if (a->head_dim % (a->dtype == B200ATTN_F32 ? 4 : 8) != 0) return B200ATTN_E_UNSUPPORTED;  // 128-bit packs (:185-202)
   if ((reinterpret_cast<uintptr_t>(a->o_a) | reinterpret_cast<uintptr_t>(a->o_b) |
        reinterpret_cast<uintptr_t>(a->o_out)) & 15)
     return B200ATTN_E_ALIGN;
   if (a->tokens == 0) return B200ATTN_OK;
-  const int64_t n = static_cast<int64_t>(a->tokens) * a->heads * (a->head_dim / 8);
-  const unsigned blocks = static_cast<unsigned>((n + 127) / 128);
   cudaStream_t s = static_cast<cudaStream_t>(s_);
-  if (a->dtype == B200ATTN_BF16)
-    merge_states_kernel<__nv_bfloat16><<<blocks, 128, 0, s>>>(
-        static_cast<const __nv_bfloat16*>(a->o_a), a->lse_a, static_cast<const __nv_bfloat16*>(a->o_b),
-        a->lse_b, static_cast<__nv_bfloat16*>(a->o_out), a->lse_out, a->tokens, a->heads, a->head_dim);
-  else
-    merge_states_kernel<__half><<<blocks, 128, 0, s>>>(
-        static_cast<const __half*>(a->o_a), a->lse_a, static_cast<const __half*>(a->o_b), a->lse_b,
-        static_cast<__half*>(a->o_out), a->lse_out, a->tokens, a->heads, a->head_dim);
+  if (a->dtype == B200ATTN_BF16) launch_merge_states<__nv_bfloat16>(a, s);
+  else if (a->dtype == B200ATTN_F16) launch_merge_states<__half>(a, s);
+  else launch_merge_states<float>(a, s);
   count_launch();
   return cudaGetLastError() == cudaSuccess ? B200ATTN_OK : B200ATTN_E_CUDA;
 }

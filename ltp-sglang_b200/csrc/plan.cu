@@ -157,6 +157,26 @@ __global__ void __launch_bounds__(kPlanThreads) plan_kernel(PlanParams p) {
     }
     (last ? pv.range_vlast : pv.range_vreq)[rr] = vq;
   }
+  // Range descriptors: bounds + the first piece the decode kernel's PieceWalk visits (the range's last
+  // virtual request, whose chunk interval holds the range's last chunk and is therefore never empty).
+  __syncthreads();   // range_vreq / range_vlast above were written by other threads of this block
+  for (int r = tid; r < h.n_ranges; r += kPlanThreads) {
+    RangeDesc d;
+    d.v_first = pv.range_vreq[r];
+    d.v_last = pv.range_vlast[r];
+    d.g0 = range_begin(h, r);
+    d.g1 = range_begin(h, r + 1);
+    d.b = d.v_last / p.ng;
+    d.hg = d.v_last - d.b * p.ng;
+    const int cp0 = pv.chunk_prefix[d.b];
+    d.nchunks = pv.chunk_prefix[d.b + 1] - cp0;
+    const int vstart = p.ng * cp0 + d.hg * d.nchunks;
+    d.lc0 = (vstart > d.g0 ? vstart : d.g0) - vstart;
+    d.lc1 = (vstart + d.nchunks < d.g1 ? vstart + d.nchunks : d.g1) - vstart;
+    d.seq_len = pv.seq_len[d.b];
+    d.row_off = pv.row_off[d.b];
+    pv.range_desc[r] = d;
+  }
   // Per virtual request: the ranges that touch it (= its partial pieces) and the arrival counter.
   for (int v = tid; v < p.batch * p.ng; v += kPlanThreads) {
     const int b = v / p.ng, hg = v - b * p.ng;
