@@ -624,9 +624,12 @@ def measure(R: Rank, args, gcfg, scaling: str, with_clocks: bool = True) -> dict
         e2e_path = "H2D -> init_forward_metadata -> RadixAttention.forward (eager) -> D2H(o) -> stream sync"
     torch.cuda.synchronize()
     assert torch.isfinite(host_out.float()).all(), "e2e output is not finite"
-    # the e2e result must be the same attention output the device-resident path produced
+    # the e2e result must be the same attention output the device-resident path produced -- to rounding: every
+    # plan sizes the CTA ranges by the streaming rates recorded so far, so two plans of the same batch may cut the
+    # KV sequence at different places (fp32 reassociation, 1 bf16 ulp at most on |o| <= 0.25)
     if not fp8:
-        assert torch.equal(host_out.to(dev).view(-1), out.view(-1)), "e2e output differs from the device-resident step"
+        diff = (host_out.to(dev).view(-1).float() - out.view(-1).float()).abs().max().item()
+        assert diff <= 4e-3, f"e2e output differs from the device-resident step by {diff}"
 
     total_bytes = w.algorithmic_bytes() * world
     res = {

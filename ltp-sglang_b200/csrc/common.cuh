@@ -80,6 +80,10 @@ inline bool no_pdl() {   // B200ATTN_NO_PDL=1: decode_kernel launched without th
   static const bool v = env_flag("B200ATTN_NO_PDL");
   return v;
 }
+inline bool no_balance() {   // B200ATTN_NO_BALANCE=1: equal static ranges whatever the per-CTA rates say
+  static const bool v = env_flag("B200ATTN_NO_BALANCE");
+  return v;
+}
 inline bool no_xch() {
   static const bool v = env_flag("B200ATTN_NO_XCH");
   return v;
@@ -158,16 +162,19 @@ struct PlanHeader {
 static_assert(sizeof(PlanHeader) == 64, "PlanHeader is 64 bytes");
 constexpr int32_t kPlanMagic = 0x42323031;  // "B201"
 
-// First chunk of range r (r == n_ranges gives total_chunks).
-__host__ __device__ inline int range_begin(const PlanHeader& h, int r) {
-  int g = r <= h.n_static ? r * h.per_static : h.n_static * h.per_static + (r - h.n_static) * h.per_dynamic;
-  return g < h.total_chunks ? g : h.total_chunks;
-}
-// Range that holds chunk g (0 <= g < total_chunks).
-__host__ __device__ inline int range_of(const PlanHeader& h, int g) {
-  const int s = h.n_static * h.per_static;
-  return g < s ? g / h.per_static : h.n_static + (g - s) / h.per_dynamic;
-}
+// Per-CTA streaming rate, kept ACROSS plans at a fixed offset of the plan buffer (so a changing batch size does
+// not move it): decode_kernel folds every launch's steady-state clocks per chunk into an exponential average,
+// and plan_kernel sizes the static ranges in inverse proportion.  Why: one CTA per SM, and the SMs do not stream
+// equally fast -- tools/trace_decode.py on C2 / C4: clocks per chunk spread by +-8 % across SMs, the same SMs
+// slow on every launch (blockIdx -> SM is stable; rank correlation 0.75-0.95 between launches), so with equal
+// ranges the median CTA sat idle for the last 9 % of the kernel.  A buffer that was never zeroed is harmless:
+// entries count only with a valid tag, and weights are clamped to [0.85, 1.18].
+struct CtaStat {
+  float clk_per_chunk;   // exponential average
+  uint32_t tag;          // kStatTag ^ cta when valid
+};
+constexpr uint32_t kStatTag = 0x5ca1ab1eu;
+constexpr int kMaxCtas = kMaxRanges / 2;
 
 // What a CTA needs to start streaming range r without walking the plan's tables: the range's bounds and the
 // piece it visits first (PieceWalk: the range's LAST virtual request).  Read with one load at kernel entry,
@@ -189,6 +196,8 @@ struct PlanView {
   int32_t* seq_len;       // [batch]
   int32_t* chunk_prefix;  // [batch + 1] exclusive prefix of ceil(S_b / T)
   int64_t* row_off;       // [batch] element offset of request b's index row
+  CtaStat* cta_stat;      // [kMaxCtas] fixed offset: survives re-planning with another batch size
+  int32_t* range_start;   // [kMaxRanges + 1] first chunk of range r; entry n_ranges = total_chunks
   int32_t* range_vreq;    // [kMaxRanges] first virtual request of range r
   int32_t* range_vlast;   // [kMaxRanges] last virtual request of range r
   int32_t* vreq_rfirst;   // [batch * kMaxHeadGroups] first range that touches virtual request v
@@ -201,6 +210,8 @@ __host__ __device__ inline size_t align_up(size_t x, size_t a) { return (x + a -
 
 __host__ __device__ inline size_t plan_bytes_for(int batch) {
   size_t n = sizeof(PlanHeader);
+  n += (size_t)kMaxCtas * sizeof(CtaStat);     // cta_stat
+  n += align_up((size_t)(kMaxRanges + 1) * 4, 16);  // range_start
   n += align_up((size_t)batch * 4, 16);        // seq_len
   n += align_up((size_t)(batch + 1) * 4, 16);  // chunk_prefix
   n += align_up((size_t)batch * 8, 16);        // row_off
@@ -215,6 +226,10 @@ __host__ __device__ inline PlanView plan_view(void* base, int batch) {
   char* p = reinterpret_cast<char*>(base);
   v.hdr = reinterpret_cast<PlanHeader*>(p);
   p += sizeof(PlanHeader);
+  v.cta_stat = reinterpret_cast<CtaStat*>(p);
+  p += (size_t)kMaxCtas * sizeof(CtaStat);
+  v.range_start = reinterpret_cast<int32_t*>(p);
+  p += align_up((size_t)(kMaxRanges + 1) * 4, 16);
   v.seq_len = reinterpret_cast<int32_t*>(p);
   p += align_up((size_t)batch * 4, 16);
   v.chunk_prefix = reinterpret_cast<int32_t*>(p);

@@ -193,7 +193,13 @@ __global__ void __launch_bounds__(kThreads, 1) decode_kernel(const DecodeParams 
 #ifdef B200ATTN_DEC_TRACE
   bool tr_a = false, tr_b = false, tr_c = false;
   unsigned long long tr_chunks = 0, tr_pieces = 0;
-  if (threadIdx.x == 0) { B200_TR_GT(TR_GT_ENTRY); B200_TR(TR_ENTRY); }
+  if (threadIdx.x == 0) {
+    B200_TR_GT(TR_GT_ENTRY);
+    B200_TR(TR_ENTRY);
+    unsigned smid;
+    asm volatile("mov.u32 %0, %smid;" : "=r"(smid));
+    if (p.trace) p.trace[blockIdx.x * kTraceSlots + TR_P_IDS] = smid;   // slot reused: which SM ran this CTA
+  }
 #endif
   // Everything that needs no global data first: under programmatic dependent launch this part (CTA launch,
   // barrier init) overlaps the tail of the kernel in front (kv_store / RoPE + store), which has released its
@@ -221,7 +227,10 @@ __global__ void __launch_bounds__(kThreads, 1) decode_kernel(const DecodeParams 
   // Dynamic ranges are claimed through a ticket counter in the plan buffer.  Every launch draws
   // exactly n_dynamic + grid tickets (each CTA stops at its first ticket past the dynamic ranges),
   // so the counter never needs a reset between the layers that share one plan.
+  // Without dynamic ranges (the default plan) there is nothing to claim: no atomic.  (148 CTAs incrementing one
+  // address took ~1 us, and the K producer warp sat on the result before its first copy: tools/trace_decode.py.)
   auto take_ticket = [&]() -> int {
+    if (n_dyn == 0) return R;
     const unsigned long long t = atomicAdd(&pv.hdr->ticket, 1ull);
     const unsigned k = static_cast<unsigned>(t % static_cast<unsigned>(n_dyn + n_grid));
     return k < static_cast<unsigned>(n_dyn) ? n_static + static_cast<int>(k) : R;
@@ -463,12 +472,26 @@ __global__ void __launch_bounds__(kThreads, 1) decode_kernel(const DecodeParams 
     }
   }
 
+  // steady-state streaming rate of this CTA (clocks per chunk, first to last chunk of its static range): folded
+  // into cta_stat so that the next plan can size the ranges by it
+  long long clk_first = 0, clk_last = 0;
+  int n_consumed = 0;
+  int npiece = 0;     // pieces seen by this CTA: parity picks the flag slot
   while (rg < R) {
   PieceWalk walk(rn == 0 && rg == cta ? d0 : load_desc(pv.range_desc + rg), p.ng);
   while (walk.next(pv, b, hg, lc0, lc1, nchunks, vreq, S, row_off)) {
     const int hq0 = (hg * p.hc + h) * p.group;
     const bool row0 = gq < p.group;
     const bool row1 = ROWS16 && (gq + 8 < p.group);
+    const bool full_req = lc0 == 0 && lc1 == nchunks;
+    // merge bookkeeping of a request cut by a range boundary, fetched now so that the epilogue does not wait for it
+    int v_pieces = 1, v_rfirst = rg;   // a whole request is one piece, in this range
+    if (!full_req) {
+      v_pieces = pv.vreq_pieces[vreq];
+      v_rfirst = pv.vreq_rfirst[vreq];
+    }
+    int early_ok = 0;   // thread 0: every other piece of this request had arrived when the last chunk began
+    ++npiece;
 
     // ---- Q fragments (A operand), loaded once per piece ----
     uint32_t qf[KSTEPS][QR];
@@ -519,6 +542,14 @@ __global__ void __launch_bounds__(kThreads, 1) decode_kernel(const DecodeParams 
     if (threadIdx.x == 0) { B200_TR_ONCE(TR_C_Q, tr_a); ++tr_pieces; }
 #endif
     for (int lc = lc0; lc < lc1; ++lc) {
+      if (threadIdx.x == 0 && lc == lc1 - 1 && !full_req && p.fuse_merge && v_pieces <= 4) {
+        // Last-arriver shortcut, decided one chunk early (the load's round trip hides behind the chunk): if
+        // every other piece of the request is already in the workspace, this CTA is the one that merges, so
+        // its own partial never needs to go through global memory (see the epilogue).
+        int arrived;
+        asm volatile("ld.acquire.gpu.global.s32 %0, [%1];" : "=r"(arrived) : "l"(pv.vreq_arrived + vreq) : "memory");
+        early_ok = arrived == v_pieces - 1;
+      }
       mbar_wait(bar_full + stage * 8, phase);
       if (threadIdx.x == 0) B200_TR_ONCE(TR_C_FIRST_FULL, tr_b);
       const uint32_t sbase = stage0 + stage * p.stage_bytes;
@@ -686,6 +717,10 @@ __global__ void __launch_bounds__(kThreads, 1) decode_kernel(const DecodeParams 
       if (tail) pv_mma(std::true_type{}); else pv_mma(std::false_type{});
       __syncwarp();
       if (lane == 0) mbar_arrive(bar_empty + stage * 8);
+      if (threadIdx.x == 0 && rn == 0) {
+        clk_last = clock64();
+        if (n_consumed++ == 0) clk_first = clk_last;
+      }
 #ifdef B200ATTN_DEC_TRACE
       if (threadIdx.x == 0) { B200_TR_ONCE(TR_C_FIRST_DONE, tr_c); B200_TR(TR_C_LAST_DONE); ++tr_chunks; }
 #endif
@@ -707,7 +742,6 @@ __global__ void __launch_bounds__(kThreads, 1) decode_kernel(const DecodeParams 
       inv1 = l1 > 0.f ? p.v_scale / l1 : 0.f;
       lse1 = l1 > 0.f ? m1 * c * kLn2 + logf(l1) : -CUDART_INF_F;
     }
-    const bool full_req = lc0 == 0 && lc1 == nchunks;
     // column (head-dim index) of accumulator element e (0/1) of tile n
     auto col_of = [&](int n, int e) -> int {
       if constexpr (!FP8) return n * 8 + 2 * jq + e;
@@ -718,6 +752,55 @@ __global__ void __launch_bounds__(kThreads, 1) decode_kernel(const DecodeParams 
     // only slice 0's rows are used (one partial per piece instead of ts).
     const int64_t piece_row = static_cast<int64_t>(vreq + rg) * p.ts * hqv;
     const bool use_xch = !ROWS16 && p.xch_off != 0;   // implies ts > 1 (make_geometry)
+
+    // Last-arriver shortcut (partial pieces): when every other piece of the request had already arrived one
+    // chunk ago, this CTA is the one that merges -- so it merges its own partial straight from registers with
+    // the others read from the workspace, instead of write partial -> fence -> atomic -> read everything back
+    // (four dependent global round trips of ~1.5 us each under load at the end of a CTA's range:
+    // tools/trace_decode.py, 6.6 us from the last chunk to the exit on C2).  Same values, same order, same
+    // arithmetic as merge_heads4, so which path ran never shows in the result.
+    const bool can_fast = !ROWS16 && !full_req && p.fuse_merge && (use_xch || p.ts == 1);
+    volatile int32_t* flags = merge_flag + (npiece & 1) * 2;
+    if (can_fast && threadIdx.x == 0) flags[0] = early_ok;
+    if (can_fast && !use_xch) named_bar_sync(2, kConsumerWarps * 32);   // (the slice exchange has its own barrier)
+    const int64_t prow0 = static_cast<int64_t>(vreq + v_rfirst) * p.ts * hqv;   // first piece's rows
+    const int64_t pstep = static_cast<int64_t>(p.ts) * hqv;                      // piece to piece (slice 0 rows)
+    const int me = rg - v_rfirst;                                                // this piece's index
+    float wk[4], inv_s = 0.f, lse_tot = -CUDART_INF_F;
+    auto merge_weights = [&](int rowh, float lse_mine) {
+      float l[4];
+#pragma unroll
+      for (int i = 0; i < 4; ++i)
+        l[i] = i < v_pieces ? (i == me ? lse_mine : __ldcg(p.ws_lse + prow0 + i * pstep + rowh)) : -CUDART_INF_F;
+      const float m = fmaxf(fmaxf(l[0], l[1]), fmaxf(l[2], l[3]));
+      float s = 0.f;
+#pragma unroll
+      for (int i = 0; i < 4; ++i) {
+        wk[i] = m != -CUDART_INF_F ? __expf(l[i] - m) : 0.f;
+        s += wk[i];
+      }
+      inv_s = s > 0.f ? 1.f / s : 0.f;
+      lse_tot = s > 0.f ? m + logf(s) : -CUDART_INF_F;
+    };
+    auto merge_tile = [&](int rowh, int c0, int c1, float x0, float x1, float& y0, float& y1) {
+      float a0 = 0.f, a1 = 0.f;
+#pragma unroll
+      for (int i = 0; i < 4; ++i) {
+        if (i < v_pieces) {
+          float v0 = x0, v1 = x1;
+          if (i != me) {
+            const float* w = p.ws_o + (prow0 + i * pstep + rowh) * D;
+            v0 = __ldcg(w + c0);
+            v1 = __ldcg(w + c1);
+          }
+          a0 = fmaf(wk[i], v0, a0);
+          a1 = fmaf(wk[i], v1, a1);
+        }
+      }
+      y0 = a0 * inv_s;
+      y1 = a1 * inv_s;
+    };
+
     bool final_written = false;
     if (p.ts == 1 && full_req) {
       final_written = true;
@@ -746,9 +829,7 @@ __global__ void __launch_bounds__(kThreads, 1) decode_kernel(const DecodeParams 
       // finishes 1 / ts of its head's columns: a whole request goes straight to `o`; a piece of a request cut
       // by a range boundary leaves ONE normalised partial per head in the workspace instead of ts.  Through
       // the workspace the slice merge cost a write -> fence -> atomic -> read-back chain of global round trips
-      // per piece with the consumers idle, and ts x the rows for the cross-CTA merge to read back
-      // (tools/trace_decode.py, 8-way shard shape: 6.7 us from the last chunk to the CTA's exit).
-      final_written = full_req;
+      // per piece with the consumers idle, and ts x the rows for the cross-CTA merge to read back.
       const int g4 = p.group * 4;
       float2* xall = reinterpret_cast<float2*>(smem + p.xch_off);
       float2* xml = xall + kXchWarps * NTILES * g4;
@@ -760,6 +841,8 @@ __global__ void __launch_bounds__(kThreads, 1) decode_kernel(const DecodeParams 
         if (jq == 0) xml[warp * 8 + gq] = make_float2(l0 > 0.f ? m0 * c : -CUDART_INF_F, l0);
       }
       named_bar_sync(2, kConsumerWarps * 32);
+      const bool fast = can_fast && flags[0] != 0;
+      final_written = full_req || fast;
       if (row0) {
         float wgt[kXchWarps];
         float mm = -CUDART_INF_F;
@@ -778,8 +861,10 @@ __global__ void __launch_bounds__(kThreads, 1) decode_kernel(const DecodeParams 
         }
         const float inv = L > 0.f ? p.v_scale / L : 0.f;
         const float lse_all = L > 0.f ? mm * kLn2 + logf(L) : -CUDART_INF_F;
+        const int rowh = h * p.group + gq;
         QT* o0 = reinterpret_cast<QT*>(p.o) + b * p.o_sb + (hq0 + gq) * p.o_sh;
-        float* w0 = p.ws_o + (piece_row + h * p.group + gq) * D;
+        float* w0 = p.ws_o + (piece_row + rowh) * D;
+        if (fast) merge_weights(rowh, lse_all);
         for (int n = tsi; n < NTILES; n += p.ts) {
           float a0 = 0.f, a1 = 0.f;
 #pragma unroll
@@ -793,19 +878,45 @@ __global__ void __launch_bounds__(kThreads, 1) decode_kernel(const DecodeParams 
           if (full_req) {
             store_q(o0 + col_of(n, 0), a0 * inv);
             store_q(o0 + col_of(n, 1), a1 * inv);
+          } else if (fast) {
+            float y0, y1;
+            merge_tile(rowh, col_of(n, 0), col_of(n, 1), a0 * inv, a1 * inv, y0, y1);
+            store_q(o0 + col_of(n, 0), y0);
+            store_q(o0 + col_of(n, 1), y1);
           } else {
             w0[col_of(n, 0)] = a0 * inv;
             w0[col_of(n, 1)] = a1 * inv;
           }
         }
         if (jq == 0 && tsi == 0) {
-          if (!full_req) p.ws_lse[piece_row + h * p.group + gq] = lse_all;
-          else if (p.lse) p.lse[static_cast<int64_t>(b) * p.hq + hq0 + gq] = lse_all;
+          if (full_req) {
+            if (p.lse) p.lse[static_cast<int64_t>(b) * p.hq + hq0 + gq] = lse_all;
+          } else if (fast) {
+            if (p.lse) p.lse[static_cast<int64_t>(b) * p.hq + hq0 + gq] = lse_tot;
+          } else {
+            p.ws_lse[piece_row + rowh] = lse_all;
+          }
         }
       }
       // the closing barrier (the area is free for the next piece) is the one in front of the arrival counter
-      // below for a partial piece
-      if (full_req || !p.fuse_merge) named_bar_sync(2, kConsumerWarps * 32);
+      // below when the partial goes through the workspace
+      if (final_written || !p.fuse_merge) named_bar_sync(2, kConsumerWarps * 32);
+    } else if (can_fast && flags[0] != 0) {
+      // ts == 1: this warp owns its head's rows outright
+      final_written = true;
+      if (row0) {
+        const int rowh = h * p.group + gq;
+        merge_weights(rowh, lse0);
+        QT* o0 = reinterpret_cast<QT*>(p.o) + b * p.o_sb + (hq0 + gq) * p.o_sh;
+#pragma unroll
+        for (int n = 0; n < NTILES; ++n) {
+          float y0, y1;
+          merge_tile(rowh, col_of(n, 0), col_of(n, 1), o[n][0] * inv0, o[n][1] * inv0, y0, y1);
+          store_q(o0 + col_of(n, 0), y0);
+          store_q(o0 + col_of(n, 1), y1);
+        }
+        if (p.lse && jq == 0) p.lse[static_cast<int64_t>(b) * p.hq + hq0 + gq] = lse_tot;
+      }
     } else {
       const int64_t row = piece_row + static_cast<int64_t>(tsi) * hqv + h * p.group + gq;
       if (row0) {
@@ -829,6 +940,10 @@ __global__ void __launch_bounds__(kThreads, 1) decode_kernel(const DecodeParams 
         }
       }
     }
+    if (final_written && !full_req && threadIdx.x == 0) {
+      pv.vreq_arrived[vreq] = 0;   // shortcut taken: the counter is ready for the next layer's launch
+      B200_TR(TR_C_MERGED);
+    }
     if (!final_written && p.fuse_merge) {
       // Stage 2 without a second launch: the CTA that lands a virtual request's last piece
       // merges all of them (threadfence + counter, the "last block done" pattern).  The
@@ -837,18 +952,17 @@ __global__ void __launch_bounds__(kThreads, 1) decode_kernel(const DecodeParams 
       named_bar_sync(2, kConsumerWarps * 32);
       if (threadIdx.x == 0) {
         const int arrived = atomicAdd(&pv.vreq_arrived[vreq], 1) + 1;
-        const int last = arrived == pv.vreq_pieces[vreq];
+        const int last = arrived == v_pieces;
         if (last) pv.vreq_arrived[vreq] = 0;  // ready for the next layer's launch
-        *merge_flag = last;
+        flags[1] = last;
       }
       named_bar_sync(2, kConsumerWarps * 32);
-      if (*merge_flag) {
+      if (flags[1]) {
         if (threadIdx.x == 0) B200_TR(TR_C_MERGED);
         __threadfence();
         const int nsl = use_xch ? 1 : p.ts;            // partial rows per piece
-        const int np = pv.vreq_pieces[vreq] * nsl;
+        const int np = v_pieces * nsl;
         const int64_t step = static_cast<int64_t>(use_xch ? p.ts : 1) * hqv;
-        const int64_t prow0 = static_cast<int64_t>(vreq + pv.vreq_rfirst[vreq]) * p.ts * hqv;
         QT* ob = reinterpret_cast<QT*>(p.o) + b * p.o_sb + static_cast<int64_t>(hg) * hqv * p.o_sh;
         float* lb = p.lse ? p.lse + static_cast<int64_t>(b) * p.hq + hg * hqv : nullptr;
         if (np <= 4 && D <= 128) {
@@ -868,6 +982,14 @@ __global__ void __launch_bounds__(kThreads, 1) decode_kernel(const DecodeParams 
   }
   ++rn;
   rg = rq[rn & (kRangeRing - 1)];
+  }
+  if (threadIdx.x == 0 && n_consumed >= 16 && cta < kMaxCtas) {
+    const float r = static_cast<float>(clk_last - clk_first) / static_cast<float>(n_consumed - 1);
+    CtaStat st = pv.cta_stat[cta];
+    const bool ok = st.tag == (kStatTag ^ static_cast<uint32_t>(cta)) && st.clk_per_chunk > 0.f;
+    st.clk_per_chunk = ok ? 0.75f * st.clk_per_chunk + 0.25f * r : r;
+    st.tag = kStatTag ^ static_cast<uint32_t>(cta);
+    pv.cta_stat[cta] = st;
   }
 #ifdef B200ATTN_DEC_TRACE
   if (threadIdx.x == 0 && p.trace) {

@@ -30,6 +30,7 @@ struct PlanParams {
   int32_t dyn_pct;      // share of the chunks handed out dynamically, percent
   int32_t dyn_chunks;   // chunks per dynamic range
   int32_t window;       // sliding window W (0 = none): the last min(S, W + 1) tokens
+  int32_t balance;      // 1: size the static ranges by the per-CTA streaming rates decode_kernel has recorded
 };
 
 __global__ void __launch_bounds__(kPlanThreads) plan_kernel(PlanParams p) {
@@ -139,13 +140,71 @@ __global__ void __launch_bounds__(kPlanThreads) plan_kernel(PlanParams p) {
   __syncthreads();
   const PlanHeader h = sh;
 
+  // Range table.  Static range c is CTA c's: equal shares, or -- when every CTA has a share worth balancing and
+  // decode_kernel has left its streaming rates in cta_stat -- shares in inverse proportion to the rate, so that
+  // slow and fast SMs finish together.  Integer weights (4096 = average) keep the split exact and reproducible.
+  {
+    const int G = h.grid;
+    const bool weighted = p.balance && h.n_static == G && h.per_static >= 16;
+    int rate = 0, valid = 0;
+    if (weighted && tid < G) {
+      const CtaStat st = pv.cta_stat[tid];
+      if (st.tag == (kStatTag ^ static_cast<uint32_t>(tid)) && st.clk_per_chunk > 16.f && st.clk_per_chunk < 1.0e6f) {
+        rate = static_cast<int>(st.clk_per_chunk);
+        valid = 1;
+      }
+    }
+    const int rate_sum = block_scan_incl(rate, warp_sums);
+    const int valid_cnt = block_scan_incl(valid, warp_sums);
+    __shared__ int mean_rate_sh;
+    if (tid == kPlanThreads - 1) mean_rate_sh = valid_cnt > 0 ? rate_sum / valid_cnt : 0;
+    __syncthreads();
+    int wgt = 0;
+    if (tid < h.n_static) {
+      wgt = 4096;
+      if (valid && mean_rate_sh > 0) {
+        const long long x = static_cast<long long>(mean_rate_sh) * 4096 / rate;
+        wgt = x < 3482 ? 3482 : (x > 4833 ? 4833 : static_cast<int>(x));   // [0.85, 1.18]
+      }
+    }
+    const int cum = block_scan_incl(wgt, warp_sums);
+    __shared__ int wsum_sh;
+    if (tid == kPlanThreads - 1) wsum_sh = cum;
+    __syncthreads();
+    const int static_chunks = h.n_dynamic > 0 ? h.n_static * h.per_static : h.total_chunks;
+    if (tid < h.n_static) {
+      int g;
+      if (weighted && mean_rate_sh > 0)
+        g = static_cast<int>(static_cast<long long>(static_chunks) * (cum - wgt) / wsum_sh);
+      else
+        g = tid * h.per_static;
+      pv.range_start[tid] = g < h.total_chunks ? g : h.total_chunks;
+    }
+    for (int r = h.n_static + tid; r <= h.n_ranges; r += kPlanThreads) {
+      const long long g = static_cast<long long>(static_chunks) + static_cast<long long>(r - h.n_static) * h.per_dynamic;
+      pv.range_start[r] = g < h.total_chunks ? static_cast<int>(g) : h.total_chunks;
+    }
+    if (h.n_dynamic == 0 && tid == 0) pv.range_start[h.n_ranges] = h.total_chunks;
+  }
+  __threadfence_block();
+  __syncthreads();
+  auto range_begin = [&](int r) -> int { return pv.range_start[r]; };
+  auto range_of = [&](int g) -> int {   // largest r with range_start[r] <= g (empty ranges share a start: take the last)
+    int lo = 0, hi = h.n_ranges;
+    while (hi - lo > 1) {
+      const int mid = (lo + hi) >> 1;
+      if (pv.range_start[mid] <= g) lo = mid; else hi = mid;
+    }
+    return lo;
+  };
+
   // First and last virtual request (b * ng + hg) of every range: the ones whose chunk interval
   // contains the range's first / last chunk.  Virtual request (b, hg) starts at ng * prefix[b] + hg * n_b.
   for (int r = tid; r < 2 * kMaxRanges; r += kPlanThreads) {
     const int rr = r >> 1, last = r & 1;
     int vq = p.batch * p.ng;
     if (rr < h.n_ranges) {
-      const int64_t g0 = last ? range_begin(h, rr + 1) - 1 : range_begin(h, rr);
+      const int64_t g0 = last ? range_begin(rr + 1) - 1 : range_begin(rr);
       int lo = 0, hi = p.batch;  // largest b with ng * prefix[b] <= g0
       while (hi - lo > 1) {
         const int mid = (lo + hi) >> 1;
@@ -164,8 +223,8 @@ __global__ void __launch_bounds__(kPlanThreads) plan_kernel(PlanParams p) {
     RangeDesc d;
     d.v_first = pv.range_vreq[r];
     d.v_last = pv.range_vlast[r];
-    d.g0 = range_begin(h, r);
-    d.g1 = range_begin(h, r + 1);
+    d.g0 = range_begin(r);
+    d.g1 = range_begin(r + 1);
     d.b = d.v_last / p.ng;
     d.hg = d.v_last - d.b * p.ng;
     const int cp0 = pv.chunk_prefix[d.b];
@@ -185,8 +244,8 @@ __global__ void __launch_bounds__(kPlanThreads) plan_kernel(PlanParams p) {
     int rf = 0, np = 0;
     if (n > 0) {
       const int vstart = p.ng * cp0 + hg * n;
-      rf = range_of(h, vstart);
-      np = range_of(h, vstart + n - 1) - rf + 1;
+      rf = range_of(vstart);
+      np = range_of(vstart + n - 1) - rf + 1;
     }
     pv.vreq_rfirst[v] = rf;
     pv.vreq_pieces[v] = np;
@@ -260,6 +319,7 @@ extern "C" __attribute__((visibility("default"))) int b200attn_plan(const b200at
   if (n > kMaxRanges / 2) n = kMaxRanges / 2;
   p.max_ctas = n;
   p.window = a->sliding_window;
+  p.balance = no_balance() ? 0 : 1;
   // Default floor: >= 64 tokens per piece so the partial write-out stays small
   // next to the KV bytes a piece streams.
   p.min_chunks = a->min_chunks_per_cta > 0 ? a->min_chunks_per_cta : (64 + g.chunk_tokens - 1) / g.chunk_tokens;

@@ -38,6 +38,8 @@ def main():
     ap.add_argument("--page-size", type=int, default=0)
     ap.add_argument("--flush", action="store_true", help="flush L2 before the traced launch")
     ap.add_argument("--out", default="")
+    ap.add_argument("--per-cta", action="store_true", help="also dump per-CTA arrays (SM id, steady us / chunk, lifetime)")
+    ap.add_argument("--repeat", type=int, default=1, help="trace this many launches (per-CTA arrays of each are kept)")
     args = ap.parse_args()
 
     import torch
@@ -83,12 +85,22 @@ def main():
     if args.flush:
         flush.zero_()
         flush.sum()
-    lib.b200attn_debug_set_decode_trace(C.c_void_p(trace.data_ptr()))
-    e0.record()
-    torch.ops.b200attn.decode(*dargs)
-    e1.record()
-    torch.cuda.synchronize()
-    lib.b200attn_debug_set_decode_trace(None)
+    per_cta = []
+    for rep_i in range(args.repeat):
+        trace.zero_()
+        if args.flush:
+            flush.zero_()
+            flush.sum()
+        lib.b200attn_debug_set_decode_trace(C.c_void_p(trace.data_ptr()))
+        e0.record()
+        torch.ops.b200attn.decode(*dargs)
+        e1.record()
+        torch.cuda.synchronize()
+        lib.b200attn_debug_set_decode_trace(None)
+        tt = trace.cpu().numpy().astype(np.int64)
+        ch = np.maximum((tt[:, 14] & 0xFFFFFFFF) - 1, 1)
+        per_cta.append({"smid": tt[:, 4].tolist(), "clk_per_chunk": ((tt[:, 10] - tt[:, 9]) / ch).round(1).tolist(),
+                        "lifetime_ns": (tt[:, 15] - tt[:, 0]).tolist(), "start_ns": (tt[:, 0] - tt[:, 0].min()).tolist()})
     t = trace.cpu().numpy().astype(np.int64)
     t = t[t[:, 1] != 0]          # CTAs that ran
     t = t[t[:, 13] != 0]         # ... and had work
@@ -129,7 +141,17 @@ def main():
         "idle_after_exit_us": st((col["gt_exit"].max() - col["gt_exit"]) / 1e3),
         "merging_ctas": int((col["c_merged"] != 0).sum()),
     }
-    print(json.dumps(rep, indent=1))
+    if args.per_cta:
+        rep["per_cta"] = per_cta
+        if len(per_cta) > 1:   # is a slow SM always slow?  rank correlation of clk / chunk by SM id between launches
+            a = dict(zip(per_cta[0]["smid"], per_cta[0]["clk_per_chunk"]))
+            cors = []
+            for other in per_cta[1:]:
+                b = dict(zip(other["smid"], other["clk_per_chunk"]))
+                ks = sorted(set(a) & set(b))
+                cors.append(round(float(np.corrcoef([a[k] for k in ks], [b[k] for k in ks])[0, 1]), 3))
+            rep["steady_rate_correlation_by_sm_vs_first_launch"] = cors
+    print(json.dumps({k: v for k, v in rep.items() if k != "per_cta"}, indent=1))
     if args.out:
         with open(args.out, "w") as f:
             json.dump(rep, f, indent=1)
