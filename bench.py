@@ -390,8 +390,14 @@ def measure(R: Rank, args, gcfg, scaling: str, with_clocks: bool = True) -> dict
                if flush else "per-GPU KV working set (%d MB) far larger than the 126 MB L2; no flush" % (kv_bytes >> 20))
 
     # ---------------- device-resident timing: `value` ----------------
-    backend.init_forward_metadata(fb)
-    out = layer(w.q, w.k, w.v, fb)            # eager warm-up
+    # Eager warm-up the way a server runs: every decode step plans (init_forward_metadata), then runs the layers.
+    # The plan sizes the per-SM ranges by the streaming rates the previous launches left in the plan buffer
+    # (csrc/plan.cu), so a few steps are needed before the ranges are the steady-state ones.
+    for _ in range(10):
+        backend.init_forward_metadata(fb)
+        if refresh:
+            w.qkv.copy_(qkv0)
+        out = layer(w.q, w.k, w.v, fb)
     torch.cuda.synchronize()
     graph = None
     launches_per_step = None

@@ -175,6 +175,7 @@ struct CtaStat {
 };
 constexpr uint32_t kStatTag = 0x5ca1ab1eu;
 constexpr int kMaxCtas = kMaxRanges / 2;
+constexpr int kFirstIds = 128;   // >= the largest chunk (16 * 8 tokens): slot ids of a static range's first chunk
 
 // What a CTA needs to start streaming range r without walking the plan's tables: the range's bounds and the
 // piece it visits first (PieceWalk: the range's LAST virtual request).  Read with one load at kernel entry,
@@ -204,6 +205,7 @@ struct PlanView {
   int32_t* vreq_pieces;   // [batch * kMaxHeadGroups] ranges that touch v (its partials to merge)
   int32_t* vreq_arrived;  // [batch * kMaxHeadGroups] pieces written so far (self-resetting)
   RangeDesc* range_desc;  // [kMaxRanges]
+  int32_t* first_ids;     // [kMaxCtas][kFirstIds] slot ids of the first chunk static range c streams (req_to_token mode)
 };
 
 __host__ __device__ inline size_t align_up(size_t x, size_t a) { return (x + a - 1) / a * a; }
@@ -218,6 +220,7 @@ __host__ __device__ inline size_t plan_bytes_for(int batch) {
   n += 2 * (size_t)kMaxRanges * 4;             // range_vreq, range_vlast
   n += 3 * align_up((size_t)batch * kMaxHeadGroups * 4, 16);
   n += (size_t)kMaxRanges * sizeof(RangeDesc);
+  n += (size_t)kMaxCtas * kFirstIds * 4;
   return n;
 }
 
@@ -248,6 +251,8 @@ __host__ __device__ inline PlanView plan_view(void* base, int batch) {
   v.vreq_arrived = reinterpret_cast<int32_t*>(p);
   p += tbl;
   v.range_desc = reinterpret_cast<RangeDesc*>(p);
+  p += (size_t)kMaxRanges * sizeof(RangeDesc);
+  v.first_ids = reinterpret_cast<int32_t*>(p);
   return v;
 }
 

@@ -217,6 +217,19 @@ __global__ void __launch_bounds__(kThreads, 1) decode_kernel(const DecodeParams 
   const PlanHeader& H = *pv.hdr;  // read where needed (range transitions), not held in registers
   // this CTA's static range, fetched together with the header (valid when cta < n_static)
   const RangeDesc d0 = load_desc(pv.range_desc + cta);
+  // ... and, for the producers, the slot ids of the range's first chunk (plan_kernel copied them next to the
+  // descriptors): issued with the two loads above, so the first copies wait on one round trip, not three.
+  int32_t pre_ids[2] = {0, 0};
+  if (warp >= kConsumerWarps && cta < kMaxCtas) {
+    const int pw_ = warp - kConsumerWarps;
+    const int T_ = p.chunk_tokens;
+#pragma unroll
+    for (int r = 0; r < 2; ++r) {
+      const int i = p.cp_async ? (pw_ >> 1) * (T_ >> 1) + lane + 32 * r : 2 * (lane + 32 * r) + (pw_ >> 1);
+      const bool mine = p.cp_async ? lane + 32 * r < (T_ >> 1) : i < T_;
+      if (mine) pre_ids[r] = __ldg(pv.first_ids + cta * kFirstIds + i);
+    }
+  }
   if (cta >= H.grid) return;
   // A plan built for another batch, head geometry or chunk size would send the walk through garbage ranges:
   // do nothing instead (o is left untouched; b200attn_decode documents that plan and call must agree).
@@ -297,16 +310,22 @@ __global__ void __launch_bounds__(kThreads, 1) decode_kernel(const DecodeParams 
         int next_rg = R;
         if (pw == 0 && lane == 0) next_rg = take_ticket();
         PieceWalk walk(rn == 0 && rg == cta ? d0 : load_desc(pv.range_desc + rg), p.ng);
+        const bool use_pre = rn == 0 && rg == cta && cta < kMaxCtas && !H.csr_mode;
       while (walk.next(pv, b, hg, lc0, lc1, nchunks, vreq, S, row_off)) {
         if (pw == 0 && lane == 0) B200_TR_ONCE(TR_P_WALK, tr_a);
         const int32_t* idx = p.indices + row_off;
         const uint8_t* base = pool + static_cast<int64_t>(hg) * p.row_bytes;
         int32_t nxt[2];
+        if (use_pre && walk.i == 1) {   // the static range's first piece: ids came with the descriptor
+          nxt[0] = pre_ids[0];
+          nxt[1] = pre_ids[1];
+        } else {
 #pragma unroll
-        for (int r = 0; r < 2; ++r) {
-          const int i = lane + 32 * r;
-          const int t = lc0 * T + tbase + i;
-          nxt[r] = (i < Tw && t < S) ? idx[t] : 0;
+          for (int r = 0; r < 2; ++r) {
+            const int i = lane + 32 * r;
+            const int t = lc0 * T + tbase + i;
+            nxt[r] = (i < Tw && t < S) ? idx[t] : 0;
+          }
         }
         for (int lc = lc0; lc < lc1; ++lc) {
           const int32_t cur0 = nxt[0], cur1 = nxt[1];
@@ -370,16 +389,22 @@ __global__ void __launch_bounds__(kThreads, 1) decode_kernel(const DecodeParams 
       int next_rg = R;
       if (pw == 0 && lane == 0) next_rg = take_ticket();
       PieceWalk walk(rn == 0 && rg == cta ? d0 : load_desc(pv.range_desc + rg), p.ng);
+      const bool use_pre = rn == 0 && rg == cta && cta < kMaxCtas && !H.csr_mode;
     while (walk.next(pv, b, hg, lc0, lc1, nchunks, vreq, S, row_off)) {
       if (pw == 0 && lane == 0) B200_TR_ONCE(TR_P_WALK, tr_a);
       const int32_t* idx = p.indices + row_off;
       const uint8_t* base = pool + static_cast<int64_t>(hg) * p.row_bytes;
       int32_t nxt[2];
+      if (use_pre && walk.i == 1) {   // the static range's first piece: ids came with the descriptor
+        nxt[0] = pre_ids[0];
+        nxt[1] = pre_ids[1];
+      } else {
 #pragma unroll
-      for (int r = 0; r < 2; ++r) {
-        const int i = 2 * (lane + 32 * r) + par;
-        const int t = lc0 * T + i;
-        nxt[r] = (i < T && t < S) ? idx[t] : 0;
+        for (int r = 0; r < 2; ++r) {
+          const int i = 2 * (lane + 32 * r) + par;
+          const int t = lc0 * T + i;
+          nxt[r] = (i < T && t < S) ? idx[t] : 0;
+        }
       }
       for (int lc = lc0; lc < lc1; ++lc) {
         int32_t cur[2] = {nxt[0], nxt[1]};
@@ -472,9 +497,12 @@ __global__ void __launch_bounds__(kThreads, 1) decode_kernel(const DecodeParams 
     }
   }
 
-  // steady-state streaming rate of this CTA (clocks per chunk, first to last chunk of its static range): folded
-  // into cta_stat so that the next plan can size the ranges by it
-  long long clk_first = 0, clk_last = 0;
+  // streaming rate of this CTA (clocks per chunk over its static range, pipeline fill included -- what the plan
+  // wants to equalise is when the CTAs END): folded into cta_stat so that the next plan can size the ranges by
+  // it.  Stamped per range, not per chunk: on an fp8 pool the consumers are the bound and warp 0 is on every
+  // chunk's critical path (thread-0 work inside the chunk loop cost C3 10 %, profiles/r02_baseline).
+  const long long clk_first = clock64();
+  long long clk_last = clk_first;
   int n_consumed = 0;
   int npiece = 0;     // pieces seen by this CTA: parity picks the flag slot
   while (rg < R) {
@@ -491,6 +519,7 @@ __global__ void __launch_bounds__(kThreads, 1) decode_kernel(const DecodeParams 
       v_rfirst = pv.vreq_rfirst[vreq];
     }
     int early_ok = 0;   // thread 0: every other piece of this request had arrived when the last chunk began
+    const bool try_early = !full_req && p.fuse_merge && v_pieces <= 4;
     ++npiece;
 
     // ---- Q fragments (A operand), loaded once per piece ----
@@ -542,7 +571,7 @@ __global__ void __launch_bounds__(kThreads, 1) decode_kernel(const DecodeParams 
     if (threadIdx.x == 0) { B200_TR_ONCE(TR_C_Q, tr_a); ++tr_pieces; }
 #endif
     for (int lc = lc0; lc < lc1; ++lc) {
-      if (threadIdx.x == 0 && lc == lc1 - 1 && !full_req && p.fuse_merge && v_pieces <= 4) {
+      if (lc == lc1 - 1 && try_early && threadIdx.x == 0) {   // (warp-uniform tests first: two instructions per chunk)
         // Last-arriver shortcut, decided one chunk early (the load's round trip hides behind the chunk): if
         // every other piece of the request is already in the workspace, this CTA is the one that merges, so
         // its own partial never needs to go through global memory (see the epilogue).
@@ -717,10 +746,6 @@ __global__ void __launch_bounds__(kThreads, 1) decode_kernel(const DecodeParams 
       if (tail) pv_mma(std::true_type{}); else pv_mma(std::false_type{});
       __syncwarp();
       if (lane == 0) mbar_arrive(bar_empty + stage * 8);
-      if (threadIdx.x == 0 && rn == 0) {
-        clk_last = clock64();
-        if (n_consumed++ == 0) clk_first = clk_last;
-      }
 #ifdef B200ATTN_DEC_TRACE
       if (threadIdx.x == 0) { B200_TR_ONCE(TR_C_FIRST_DONE, tr_c); B200_TR(TR_C_LAST_DONE); ++tr_chunks; }
 #endif
@@ -979,12 +1004,14 @@ __global__ void __launch_bounds__(kThreads, 1) decode_kernel(const DecodeParams 
       }
     }
     if (threadIdx.x == 0) B200_TR(TR_C_EPILOGUE);
+    if (rn == 0) n_consumed += lc1 - lc0;
   }
+  if (rn == 0) clk_last = clock64();
   ++rn;
   rg = rq[rn & (kRangeRing - 1)];
   }
   if (threadIdx.x == 0 && n_consumed >= 16 && cta < kMaxCtas) {
-    const float r = static_cast<float>(clk_last - clk_first) / static_cast<float>(n_consumed - 1);
+    const float r = static_cast<float>(clk_last - clk_first) / static_cast<float>(n_consumed);
     CtaStat st = pv.cta_stat[cta];
     const bool ok = st.tag == (kStatTag ^ static_cast<uint32_t>(cta)) && st.clk_per_chunk > 0.f;
     st.clk_per_chunk = ok ? 0.75f * st.clk_per_chunk + 0.25f * r : r;

@@ -236,6 +236,20 @@ __global__ void __launch_bounds__(kPlanThreads) plan_kernel(PlanParams p) {
     d.row_off = pv.row_off[d.b];
     pv.range_desc[r] = d;
   }
+  // Slot ids of the first chunk each static range streams (its first piece's chunk lc0), copied next to the
+  // descriptors: the decode producers' first copies then wait on ONE plan-buffer load instead of
+  // descriptor -> req_to_token row -> pool rows (a dependent DRAM round trip of ~1 us at every launch of every
+  // layer: tools/trace_decode.py).  req_to_token mode only (a CSR index list is not known to the plan).
+  if (!p.csr_indptr) {
+    __syncthreads();   // range_desc written above
+    const int ns = h.n_static < kMaxCtas ? h.n_static : kMaxCtas;
+    for (int i = tid; i < ns * T; i += kPlanThreads) {
+      const int r = i / T, j = i - r * T;
+      const RangeDesc& d = pv.range_desc[r];
+      const int t = d.lc0 * T + j;
+      pv.first_ids[r * kFirstIds + j] = t < d.seq_len ? p.req_to_token[d.row_off + t] : 0;
+    }
+  }
   // Per virtual request: the ranges that touch it (= its partial pieces) and the arrival counter.
   for (int v = tid; v < p.batch * p.ng; v += kPlanThreads) {
     const int b = v / p.ng, hg = v - b * p.ng;

@@ -87,6 +87,7 @@ def main():
         flush.sum()
     per_cta = []
     for rep_i in range(args.repeat):
+        backend.init_forward_metadata(fb)   # a server plans every step: ranges follow the recorded per-SM rates
         trace.zero_()
         if args.flush:
             flush.zero_()
@@ -137,6 +138,8 @@ def main():
         "stream_us_first_to_last_chunk": st(us(col["c_last_done"] - col["c_first_done"])),
         "producer_last_issue_to_consumer_last_done_us": st(us(col["c_last_done"] - col["p_last_issue"])),
         "last_chunk_to_exit_us": st(us(col["c_exit"] - col["c_last_done"])),
+        "last_chunk_to_last_epilogue_us": st(us(col["c_epilogue"] - col["c_last_done"])),
+        "last_epilogue_to_exit_us": st(us(col["c_exit"] - col["c_epilogue"])),
         "cta_lifetime_us": st(span_ns / 1e3),
         "idle_after_exit_us": st((col["gt_exit"].max() - col["gt_exit"]) / 1e3),
         "merging_ctas": int((col["c_merged"] != 0).sum()),
