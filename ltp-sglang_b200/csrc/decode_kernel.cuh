@@ -214,7 +214,19 @@ __global__ void __launch_bounds__(kThreads, 1) decode_kernel(const DecodeParams 
   pdl_wait();  // plan, q and the pool rows of this step are written by kernels in front of this one
 
   const PlanView pv = plan_view(const_cast<void*>(p.plan), p.batch);
-  const PlanHeader& H = *pv.hdr;  // read where needed (range transitions), not held in registers
+  // the header's first 56 bytes (everything but the ticket) in one batch of loads, issued with the descriptor's:
+  // a field read later (csr_mode in the producers, n_empty in the consumers) is then no further round trip
+  PlanHeader H;
+  {
+    const int4* hs = reinterpret_cast<const int4*>(pv.hdr);
+    int4* hd = reinterpret_cast<int4*>(&H);
+    hd[0] = hs[0];
+    hd[1] = hs[1];
+    hd[2] = hs[2];
+    const int2 h3 = *reinterpret_cast<const int2*>(hs + 3);
+    H.total_tokens = h3.x;
+    H.n_empty = h3.y;
+  }
   // this CTA's static range, fetched together with the header (valid when cta < n_static)
   const RangeDesc d0 = load_desc(pv.range_desc + cta);
   // ... and, for the producers, the slot ids of the range's first chunk (plan_kernel copied them next to the
@@ -230,6 +242,9 @@ __global__ void __launch_bounds__(kThreads, 1) decode_kernel(const DecodeParams 
       if (mine) pre_ids[r] = __ldg(pv.first_ids + cta * kFirstIds + i);
     }
   }
+  // the rate this CTA recorded in earlier launches (updated at exit; fetched here so that the exit is a plain store)
+  CtaStat st_prev = {0.f, 0u};
+  if (threadIdx.x == 0 && cta < kMaxCtas) st_prev = pv.cta_stat[cta];
   if (cta >= H.grid) return;
   // A plan built for another batch, head geometry or chunk size would send the walk through garbage ranges:
   // do nothing instead (o is left untouched; b200attn_decode documents that plan and call must agree).
@@ -264,6 +279,9 @@ __global__ void __launch_bounds__(kThreads, 1) decode_kernel(const DecodeParams 
 
   if (warp >= kConsumerWarps) {
     // ------------------------------ producers ------------------------------
+    // The producers (warp group 2) need few registers; they hand theirs to the two consumer warp groups, whose
+    // accumulators + fragments + epilogue state did not fit the 168 registers of a 384-thread CTA without spills.
+    asm volatile("setmaxnreg.dec.sync.aligned.u32 72;");
     // warp pw: tensor = pw & 1 (K / V), tokens of parity pw >> 1.  Lane l, round r owns chunk
     // token 2 * (l + 32 r) + parity.
     const int pw = warp - kConsumerWarps;
@@ -450,6 +468,7 @@ __global__ void __launch_bounds__(kThreads, 1) decode_kernel(const DecodeParams 
   }
 
   // -------------------------------- consumers --------------------------------
+  asm volatile("setmaxnreg.inc.sync.aligned.u32 216;");   // 128 x 72 + 256 x 216 = 64512 = 384 x 168
   const int h = warp % p.hc;
   const int tsi = warp / p.hc;
   const int gq = lane >> 2, jq = lane & 3;     // MMA fragment coordinates
@@ -521,6 +540,16 @@ __global__ void __launch_bounds__(kThreads, 1) decode_kernel(const DecodeParams 
     int early_ok = 0;   // thread 0: every other piece of this request had arrived when the last chunk began
     const bool try_early = !full_req && p.fuse_merge && v_pieces <= 4;
     ++npiece;
+    const int hqv = p.hc * p.group;
+    const int64_t prow0 = static_cast<int64_t>(vreq + v_rfirst) * p.ts * hqv;   // first piece's workspace rows
+    const int64_t pstep = static_cast<int64_t>(p.ts) * hqv;                      // piece to piece (slice 0 rows)
+    const int me = rg - v_rfirst;                                                // this piece's index
+    // A few chunks before the end of a cut request's piece, the other pieces' partial rows of this warp's head are
+    // pulled into L2: the CTA that merges (normally this one: its neighbour finished the other half long ago, and
+    // ~1 GB has gone through L2 since) then reads them in one short round trip instead of a DRAM access queued
+    // behind the KV stream (2 us each under load, tools/trace_decode.py: 7 us from the last chunk to the last
+    // store on C2).  A row that has not been written yet is harmless to prefetch: L2 is the coherence point.
+    const int lc_pf = lc1 - 4 > lc0 ? lc1 - 4 : lc0;
 
     // ---- Q fragments (A operand), loaded once per piece ----
     uint32_t qf[KSTEPS][QR];
@@ -571,6 +600,20 @@ __global__ void __launch_bounds__(kThreads, 1) decode_kernel(const DecodeParams 
     if (threadIdx.x == 0) { B200_TR_ONCE(TR_C_Q, tr_a); ++tr_pieces; }
 #endif
     for (int lc = lc0; lc < lc1; ++lc) {
+      if (lc == lc_pf && try_early) {
+        const int g = lane >> 2, line = lane & 3;
+        if (g < p.group && line * 32 < D) {
+          const int rowh = h * p.group + g;
+#pragma unroll
+          for (int i = 0; i < 4; ++i) {
+            if (i < v_pieces && i != me) {
+              const int64_t row = prow0 + i * pstep + rowh;
+              asm volatile("prefetch.global.L2 [%0];" ::"l"(p.ws_o + row * D + line * 32));
+              if (line == 0) asm volatile("prefetch.global.L2 [%0];" ::"l"(p.ws_lse + row));
+            }
+          }
+        }
+      }
       if (lc == lc1 - 1 && try_early && threadIdx.x == 0) {   // (warp-uniform tests first: two instructions per chunk)
         // Last-arriver shortcut, decided one chunk early (the load's round trip hides behind the chunk): if
         // every other piece of the request is already in the workspace, this CTA is the one that merges, so
@@ -772,7 +815,6 @@ __global__ void __launch_bounds__(kThreads, 1) decode_kernel(const DecodeParams 
       if constexpr (!FP8) return n * 8 + 2 * jq + e;
       return (n >> 1) * 16 + 4 * jq + 2 * e + (n & 1);
     };
-    const int hqv = p.hc * p.group;
     // Workspace rows of this piece: ((vreq + rg) * ts + slice) * hqv + head; with the in-CTA slice merge below
     // only slice 0's rows are used (one partial per piece instead of ts).
     const int64_t piece_row = static_cast<int64_t>(vreq + rg) * p.ts * hqv;
@@ -788,15 +830,17 @@ __global__ void __launch_bounds__(kThreads, 1) decode_kernel(const DecodeParams 
     volatile int32_t* flags = merge_flag + (npiece & 1) * 2;
     if (can_fast && threadIdx.x == 0) flags[0] = early_ok;
     if (can_fast && !use_xch) named_bar_sync(2, kConsumerWarps * 32);   // (the slice exchange has its own barrier)
-    const int64_t prow0 = static_cast<int64_t>(vreq + v_rfirst) * p.ts * hqv;   // first piece's rows
-    const int64_t pstep = static_cast<int64_t>(p.ts) * hqv;                      // piece to piece (slice 0 rows)
-    const int me = rg - v_rfirst;                                                // this piece's index
     float wk[4], inv_s = 0.f, lse_tot = -CUDART_INF_F;
-    auto merge_weights = [&](int rowh, float lse_mine) {
-      float l[4];
+    // The merge's loads go out in ONE batch -- the other pieces' lse and the rows of the first other piece (the
+    // only other piece in all but the rarest plans) -- before anything waits on them: issued one after the other's
+    // result (lse -> weights -> row loads per tile) the shortcut still cost 3-4 dependent round trips.
+    const int i1 = me == 0 ? 1 : 0;   // the first other piece
+    auto merge_lse_load = [&](int rowh, float lse_mine, float (&l)[4]) {
 #pragma unroll
       for (int i = 0; i < 4; ++i)
         l[i] = i < v_pieces ? (i == me ? lse_mine : __ldcg(p.ws_lse + prow0 + i * pstep + rowh)) : -CUDART_INF_F;
+    };
+    auto merge_weights = [&](const float (&l)[4]) {
       const float m = fmaxf(fmaxf(l[0], l[1]), fmaxf(l[2], l[3]));
       float s = 0.f;
 #pragma unroll
@@ -807,16 +851,29 @@ __global__ void __launch_bounds__(kThreads, 1) decode_kernel(const DecodeParams 
       inv_s = s > 0.f ? 1.f / s : 0.f;
       lse_tot = s > 0.f ? m + logf(s) : -CUDART_INF_F;
     };
-    auto merge_tile = [&](int rowh, int c0, int c1, float x0, float x1, float& y0, float& y1) {
+    // columns col_of(n, 0 / 1) of workspace row w
+    auto load_pair = [&](const float* w, int n, float& v0, float& v1) {
+      if constexpr (!FP8) {
+        const float2 t = __ldcg(reinterpret_cast<const float2*>(w + n * 8 + 2 * jq));
+        v0 = t.x;
+        v1 = t.y;
+      } else {
+        v0 = __ldcg(w + col_of(n, 0));
+        v1 = __ldcg(w + col_of(n, 1));
+      }
+    };
+    // x1_0 / x1_1: the first other piece's values of this tile, already in registers
+    auto merge_tile = [&](int rowh, int n, float x0, float x1, float x1_0, float x1_1, float& y0, float& y1) {
       float a0 = 0.f, a1 = 0.f;
 #pragma unroll
       for (int i = 0; i < 4; ++i) {
         if (i < v_pieces) {
           float v0 = x0, v1 = x1;
-          if (i != me) {
-            const float* w = p.ws_o + (prow0 + i * pstep + rowh) * D;
-            v0 = __ldcg(w + c0);
-            v1 = __ldcg(w + c1);
+          if (i == i1) {
+            v0 = x1_0;
+            v1 = x1_1;
+          } else if (i != me) {
+            load_pair(p.ws_o + (prow0 + i * pstep + rowh) * D, n, v0, v1);
           }
           a0 = fmaf(wk[i], v0, a0);
           a1 = fmaf(wk[i], v1, a1);
@@ -889,8 +946,22 @@ __global__ void __launch_bounds__(kThreads, 1) decode_kernel(const DecodeParams 
         const int rowh = h * p.group + gq;
         QT* o0 = reinterpret_cast<QT*>(p.o) + b * p.o_sb + (hq0 + gq) * p.o_sh;
         float* w0 = p.ws_o + (piece_row + rowh) * D;
-        if (fast) merge_weights(rowh, lse_all);
-        for (int n = tsi; n < NTILES; n += p.ts) {
+        // this warp finishes tiles tsi, tsi + ts, ...: at most NTILES / 2 of them (ts >= 2)
+        float x1[NTILES / 2][2];
+        if (fast) {
+          float l[4];
+          merge_lse_load(rowh, lse_all, l);
+          const float* w1 = p.ws_o + (prow0 + i1 * pstep + rowh) * D;
+#pragma unroll
+          for (int k = 0; k < NTILES / 2; ++k) {
+            const int n = tsi + k * p.ts;
+            x1[k][0] = x1[k][1] = 0.f;
+            if (n < NTILES) load_pair(w1, n, x1[k][0], x1[k][1]);
+          }
+          merge_weights(l);
+        }
+        int kt = 0;
+        for (int n = tsi; n < NTILES; n += p.ts, ++kt) {
           float a0 = 0.f, a1 = 0.f;
 #pragma unroll
           for (int s = 0; s < kXchWarps; ++s) {
@@ -905,7 +976,14 @@ __global__ void __launch_bounds__(kThreads, 1) decode_kernel(const DecodeParams 
             store_q(o0 + col_of(n, 1), a1 * inv);
           } else if (fast) {
             float y0, y1;
-            merge_tile(rowh, col_of(n, 0), col_of(n, 1), a0 * inv, a1 * inv, y0, y1);
+            float f0 = 0.f, f1 = 0.f;
+#pragma unroll
+            for (int k = 0; k < NTILES / 2; ++k)   // (a run-time index would send x1 to local memory)
+              if (k == kt) {
+                f0 = x1[k][0];
+                f1 = x1[k][1];
+              }
+            merge_tile(rowh, n, a0 * inv, a1 * inv, f0, f1, y0, y1);
             store_q(o0 + col_of(n, 0), y0);
             store_q(o0 + col_of(n, 1), y1);
           } else {
@@ -931,12 +1009,17 @@ __global__ void __launch_bounds__(kThreads, 1) decode_kernel(const DecodeParams 
       final_written = true;
       if (row0) {
         const int rowh = h * p.group + gq;
-        merge_weights(rowh, lse0);
+        float l[4], x1[NTILES][2];
+        merge_lse_load(rowh, lse0, l);
+        const float* w1 = p.ws_o + (prow0 + i1 * pstep + rowh) * D;
+#pragma unroll
+        for (int n = 0; n < NTILES; ++n) load_pair(w1, n, x1[n][0], x1[n][1]);
+        merge_weights(l);
         QT* o0 = reinterpret_cast<QT*>(p.o) + b * p.o_sb + (hq0 + gq) * p.o_sh;
 #pragma unroll
         for (int n = 0; n < NTILES; ++n) {
           float y0, y1;
-          merge_tile(rowh, col_of(n, 0), col_of(n, 1), o[n][0] * inv0, o[n][1] * inv0, y0, y1);
+          merge_tile(rowh, n, o[n][0] * inv0, o[n][1] * inv0, x1[n][0], x1[n][1], y0, y1);
           store_q(o0 + col_of(n, 0), y0);
           store_q(o0 + col_of(n, 1), y1);
         }
@@ -997,6 +1080,14 @@ __global__ void __launch_bounds__(kThreads, 1) decode_kernel(const DecodeParams 
             merge_heads4<QT>(p.ws_o, p.ws_lse, prow0 + hl, kConsumerWarps, nh < 4 ? nh : 4, step, np, D,
                              ob + hl * p.o_sh, kConsumerWarps * p.o_sh, lb ? lb + hl : nullptr, kConsumerWarps, lane);
           }
+        } else if (D <= 128) {
+          // many partials: one head per lane group (two at D = 64), 16 partials in flight per round
+          constexpr int HPW = 128 / D;   // heads per warp and pass
+          for (int hl = warp; hl < hqv; hl += HPW * kConsumerWarps) {
+            const int nh = (hqv - hl + kConsumerWarps - 1) / kConsumerWarps;
+            merge_rows_wide<QT>(p.ws_o, p.ws_lse, prow0 + hl, kConsumerWarps, nh < HPW ? nh : HPW, step, np, D,
+                                ob + hl * p.o_sh, kConsumerWarps * p.o_sh, lb ? lb + hl : nullptr, kConsumerWarps, lane);
+          }
         } else {
           for (int hl = warp; hl < hqv; hl += kConsumerWarps)
             merge_head<QT>(p.ws_o, p.ws_lse, prow0 + hl, step, np, D, ob + hl * p.o_sh, lb ? lb + hl : nullptr, lane);
@@ -1012,7 +1103,7 @@ __global__ void __launch_bounds__(kThreads, 1) decode_kernel(const DecodeParams 
   }
   if (threadIdx.x == 0 && n_consumed >= 16 && cta < kMaxCtas) {
     const float r = static_cast<float>(clk_last - clk_first) / static_cast<float>(n_consumed);
-    CtaStat st = pv.cta_stat[cta];
+    CtaStat st = st_prev;
     const bool ok = st.tag == (kStatTag ^ static_cast<uint32_t>(cta)) && st.clk_per_chunk > 0.f;
     st.clk_per_chunk = ok ? 0.75f * st.clk_per_chunk + 0.25f * r : r;
     st.tag = kStatTag ^ static_cast<uint32_t>(cta);

@@ -145,6 +145,65 @@ __device__ __forceinline__ void merge_heads4(const float* __restrict__ ws_o, con
   }
 }
 
+// Many partials per head (a request cut across many CTA ranges: small batches such as C1, where every request
+// spans ~10 of the 148 ranges).  The lanes of a warp split into 32 / (dv / 4) groups, one head per group (two
+// heads at dv = 64), and up to R = 16 partials are in flight per round, so a request of <= 16 pieces costs each
+// warp hq / (8 * groups) round trips instead of 2 per head (C1: 2 instead of 8; the merge of the last request
+// ran 12 us past the end of the stream).  Head j of the call: workspace row row0 + j * head_step, output
+// out + j * out_step; heads j >= nheads are skipped.  dv = 64 or 128.
+template <typename QT>
+__device__ __forceinline__ void merge_rows_wide(const float* __restrict__ ws_o, const float* __restrict__ ws_lse,
+                                                int64_t row0, int64_t head_step, int nheads, int64_t row_step, int np,
+                                                int dv, QT* out, int64_t out_step, float* lse_out, int64_t lse_step,
+                                                int lane) {
+  constexpr int R = 16;
+  const int lanes_per_head = dv >> 2;            // 16 or 32
+  const int j = lane / lanes_per_head;           // this lane's head of the call
+  const int d = (lane - j * lanes_per_head) * 4;
+  if (j >= nheads) return;
+  row0 += j * head_step;
+  float m = -CUDART_INF_F, s = 0.f;
+  float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
+  for (int i0 = 0; i0 < np; i0 += R) {
+    float l[R];
+    float4 x[R];
+#pragma unroll
+    for (int k = 0; k < R; ++k) {
+      const bool ok = i0 + k < np;
+      const int64_t row = row0 + static_cast<int64_t>(ok ? i0 + k : i0) * row_step;
+      l[k] = ok ? __ldcg(ws_lse + row) : -CUDART_INF_F;
+      x[k] = ok ? __ldcg(reinterpret_cast<const float4*>(ws_o + row * dv + d)) : make_float4(0.f, 0.f, 0.f, 0.f);
+    }
+    float mn = m;
+#pragma unroll
+    for (int k = 0; k < R; ++k) mn = fmaxf(mn, l[k]);
+    if (mn == -CUDART_INF_F) continue;
+    const float sc = __expf(m - mn);
+    s *= sc;
+    acc.x *= sc;
+    acc.y *= sc;
+    acc.z *= sc;
+    acc.w *= sc;
+#pragma unroll
+    for (int k = 0; k < R; ++k) {
+      const float w = __expf(l[k] - mn);
+      s += w;
+      acc.x = fmaf(w, x[k].x, acc.x);
+      acc.y = fmaf(w, x[k].y, acc.y);
+      acc.z = fmaf(w, x[k].z, acc.z);
+      acc.w = fmaf(w, x[k].w, acc.w);
+    }
+    m = mn;
+  }
+  const float inv = s > 0.f ? 1.f / s : 0.f;
+  QT* o = out + j * out_step + d;
+  o[0] = QT(acc.x * inv);
+  o[1] = QT(acc.y * inv);
+  o[2] = QT(acc.z * inv);
+  o[3] = QT(acc.w * inv);
+  if (lse_out && d == 0) lse_out[j * lse_step] = s > 0.f ? m + logf(s) : -CUDART_INF_F;
+}
+
 // One (request, head) row merged by this warp; picks the unroll against the number of partials.
 template <typename QT>
 __device__ __forceinline__ void merge_head(const float* __restrict__ ws_o, const float* __restrict__ ws_lse,
@@ -155,7 +214,7 @@ __device__ __forceinline__ void merge_head(const float* __restrict__ ws_o, const
   } else if (np <= 4) {
     merge_rows<QT, 4, 1>(ws_o, ws_lse, row0, row_step, np, dv, out, lse_out, lane);
   } else {
-    merge_rows<QT, 8, 1>(ws_o, ws_lse, row0, row_step, np, dv, out, lse_out, lane);
+    merge_rows<QT, 16, 1>(ws_o, ws_lse, row0, row_step, np, dv, out, lse_out, lane);   // rounds of 16, as merge_rows_wide
   }
 }
 #endif
