@@ -43,7 +43,7 @@
 extern "C" {
 #endif
 
-#define B200ATTN_ABI_VERSION 5
+#define B200ATTN_ABI_VERSION 6
 
 /* cudaStream_t without pulling in the CUDA headers. */
 typedef void* b200attn_stream_t;
@@ -378,6 +378,13 @@ uint64_t b200attn_launch_count(void);
  * out[3]=pipeline stages, out[4]=dynamic smem bytes, out[5]=head groups. */
 int b200attn_decode_geometry(int32_t num_q_heads, int32_t num_kv_heads, int32_t head_dim,
                              int32_t kv_dtype, int32_t out[6]);
+/* ABI 6.  The geometry b200attn_plan / b200attn_decode use for a decode batch of `batch` requests: small
+ * batches (fewer than 64 request x head-group pairs) take fewer kv heads per CTA, down to 256-byte row slices,
+ * so that a request is cut across 2-3 CTA ranges instead of ~10 and its partials merge in registers.  Both
+ * calls derive it from (shape, batch): a plan is only valid for the batch size it was built for (it always
+ * was: the plan buffer's layout depends on `batch`).  batch = 0 gives b200attn_decode_geometry's answer. */
+int b200attn_decode_geometry_batch(int32_t batch, int32_t num_q_heads, int32_t num_kv_heads, int32_t head_dim,
+                                   int32_t kv_dtype, int32_t out[6]);
 
 #ifdef __cplusplus
 }

@@ -19,7 +19,7 @@ E_INVALID, E_UNSUPPORTED, E_ALIGN, E_CUDA, E_WORKSPACE = -1, -2, -3, -4, -5
 BF16, F16, FP8_E4M3, F32 = 0, 1, 2, 3
 I32, I64 = 0, 1
 SCALE_NONE, SCALE_TRUE_DIV, SCALE_RECIP_MUL = 0, 1, 2
-ABI_VERSION = 5
+ABI_VERSION = 6
 
 
 class KvStoreArgs(C.Structure):
@@ -244,6 +244,10 @@ SYMBOLS = {
         C.c_int,
         [C.c_int32, C.c_int32, C.c_int32, C.c_int32, C.POINTER(C.c_int32 * 6)],
     ),
+    "b200attn_decode_geometry_batch": (
+        C.c_int,
+        [C.c_int32, C.c_int32, C.c_int32, C.c_int32, C.c_int32, C.POINTER(C.c_int32 * 6)],
+    ),
 }
 
 
@@ -290,11 +294,12 @@ def launch_count() -> int:
     return int(lib().b200attn_launch_count())
 
 
-def decode_geometry(num_q_heads: int, num_kv_heads: int, head_dim: int, kv_dtype: int) -> dict:
+def decode_geometry(num_q_heads: int, num_kv_heads: int, head_dim: int, kv_dtype: int, batch: int = 0) -> dict:
+    """Geometry of the decode kernel for a shape; ``batch`` > 0: the one plan / decode use for that batch size."""
     out = (C.c_int32 * 6)()
     check(
-        "b200attn_decode_geometry",
-        lib().b200attn_decode_geometry(num_q_heads, num_kv_heads, head_dim, kv_dtype, C.byref(out)),
+        "b200attn_decode_geometry_batch",
+        lib().b200attn_decode_geometry_batch(batch, num_q_heads, num_kv_heads, head_dim, kv_dtype, C.byref(out)),
     )
     keys = ("heads_per_cta", "token_slices", "chunk_tokens", "stages", "smem_bytes", "head_groups")
     return dict(zip(keys, list(out)))

@@ -80,6 +80,20 @@ extern "C" __attribute__((visibility("default"))) int b200attn_decode_geometry(i
   return B200ATTN_OK;
 }
 
+extern "C" __attribute__((visibility("default"))) int b200attn_decode_geometry_batch(int32_t batch, int32_t hq, int32_t hkv, int32_t d,
+                                        int32_t kv_dtype, int32_t out[6]) {
+  if (!out || batch < 0) return B200ATTN_E_INVALID;
+  Geometry g;
+  if (!make_geometry(hq, hkv, d, kv_dtype, &g, batch)) return B200ATTN_E_UNSUPPORTED;
+  out[0] = g.hc;
+  out[1] = g.ts;
+  out[2] = g.chunk_tokens;
+  out[3] = g.stages;
+  out[4] = g.smem_bytes;
+  out[5] = g.ng;
+  return B200ATTN_OK;
+}
+
 extern "C" __attribute__((visibility("default"))) size_t b200attn_workspace_bytes(int32_t batch, int32_t hq, int32_t hkv, int32_t d,
                                            int32_t dv, int32_t kv_dtype) {
   Geometry g;
@@ -100,7 +114,7 @@ extern "C" __attribute__((visibility("default"))) int b200attn_decode(const b200
   if (a->v_head_dim != a->head_dim) return B200ATTN_E_UNSUPPORTED;
   if (!(a->sm_scale > 0.f) || !(a->k_scale > 0.f) || a->logit_cap < 0.f) return B200ATTN_E_INVALID;
   Geometry g;
-  if (!make_geometry(a->num_q_heads, a->num_kv_heads, a->head_dim, a->kv_dtype, &g))
+  if (!make_geometry(a->num_q_heads, a->num_kv_heads, a->head_dim, a->kv_dtype, &g, a->batch))
     return B200ATTN_E_UNSUPPORTED;
   const int e = elem_bytes(a->kv_dtype);
   // bulk copies move 16-byte units; q fragments are read as 32-bit pairs

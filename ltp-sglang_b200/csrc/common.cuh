@@ -84,6 +84,10 @@ inline bool no_balance() {   // B200ATTN_NO_BALANCE=1: equal static ranges whate
   static const bool v = env_flag("B200ATTN_NO_BALANCE");
   return v;
 }
+inline bool no_narrow() {   // B200ATTN_NO_NARROW=1: small batches keep the widest rows (the default geometry)
+  static const bool v = env_flag("B200ATTN_NO_NARROW");
+  return v;
+}
 inline bool no_xch() {
   static const bool v = env_flag("B200ATTN_NO_XCH");
   return v;
@@ -95,7 +99,14 @@ inline int xch_bytes(int group, int d) { return kXchWarps * (d / 8) * group * 4 
 __host__ __device__ inline int elem_bytes(int dtype) { return dtype == B200ATTN_FP8_E4M3 ? 1 : 2; }
 
 // Returns false when the shape has no kernel.
-inline bool make_geometry(int hq, int hkv, int d, int kv_dtype, Geometry* g) {
+// `batch` > 0 lets small decode batches trade row width for parallelism: with few (request, head group) pairs
+// every request is cut across many of the 148 CTA ranges (C1: 16 requests x 1 head group = ~10 partials each,
+// merged by one CTA at the very end of the kernel).  Fewer heads per CTA give more, shorter virtual requests
+// (C1 at 2 heads per CTA: 64 of them, 2-3 partials each, merged in registers by the shortcut), as long as a pool
+// row slice stays >= 256 bytes (the cp.async path streams those at the bulk-copy rate).  The plan and the
+// decode call derive the geometry from the same (shape, batch), so they always agree.
+constexpr int kFewVreqs = 64;
+inline bool make_geometry(int hq, int hkv, int d, int kv_dtype, Geometry* g, int batch = 0) {
   if (hq <= 0 || hkv <= 0 || hq % hkv != 0) return false;
   if (d != 64 && d != 128) return false;  // instantiated head dims
   int group = hq / hkv;
@@ -105,6 +116,9 @@ inline bool make_geometry(int hq, int hkv, int d, int kv_dtype, Geometry* g) {
   while (hc > 1 && (hkv % hc != 0 || hc * d * e > kMaxRowBytes)) hc >>= 1;
   if (hc * d * e > kMaxRowBytes) return false;
   if (hkv / hc > kMaxHeadGroups) return false;
+  if (batch > 0 && !no_narrow()) {
+    while (hc > 1 && batch * (hkv / hc) < kFewVreqs && (hc / 2) * d * e >= 256 && hkv / (hc / 2) <= kMaxHeadGroups) hc >>= 1;
+  }
   g->hc = hc;
   g->ts = kConsumerWarps / hc;
   g->ng = hkv / hc;
@@ -260,7 +274,9 @@ __host__ __device__ inline PlanView plan_view(void* base, int batch) {
 // (unique and dense because both only grow along the chunk sequence); each
 // piece holds ts slices of [hq_per_vreq, dv] fp32 plus [hq_per_vreq] lse.
 inline size_t workspace_floats(int batch, int hq, int dv, const Geometry& g, size_t* lse_off) {
+  // (a small batch may run with more head groups than the default geometry: at most 2 * kFewVreqs virtual requests)
   size_t pieces = (size_t)batch * g.ng + kMaxRanges;
+  if (pieces < (size_t)2 * kFewVreqs + kMaxRanges) pieces = (size_t)2 * kFewVreqs + kMaxRanges;
   size_t rows = pieces * g.ts * (size_t)(hq / g.ng);
   if (lse_off) *lse_off = rows * dv;
   return rows * dv + rows;

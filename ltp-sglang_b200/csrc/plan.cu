@@ -313,7 +313,7 @@ extern "C" __attribute__((visibility("default"))) int b200attn_plan(const b200at
   if (reinterpret_cast<uintptr_t>(a->plan) % 16 != 0) return B200ATTN_E_ALIGN;
   if (a->plan_bytes < plan_bytes_for(a->batch)) return B200ATTN_E_WORKSPACE;
   Geometry g;
-  if (!make_geometry(a->num_q_heads, a->num_kv_heads, a->head_dim, a->kv_dtype, &g))
+  if (!make_geometry(a->num_q_heads, a->num_kv_heads, a->head_dim, a->kv_dtype, &g, a->batch))
     return B200ATTN_E_UNSUPPORTED;
 
   PlanParams p;

@@ -41,7 +41,7 @@ def test_library_exports_every_declared_symbol():
 def test_abi_version_and_strerror():
     from b200attn import capi
 
-    assert capi.lib().b200attn_abi_version() == capi.ABI_VERSION == 5
+    assert capi.lib().b200attn_abi_version() == capi.ABI_VERSION == 6
     for code in (0, -1, -2, -3, -4, -5, -99):
         assert isinstance(capi.strerror(code), str) and capi.strerror(code)
     assert "unsupported" in capi.strerror(capi.E_UNSUPPORTED)
@@ -94,6 +94,10 @@ def test_geometry_table():
     assert (g["heads_per_cta"], g["token_slices"], g["chunk_tokens"]) == (1, 8, 128)
     g = capi.decode_geometry(32, 8, 128, capi.FP8_E4M3)   # C3
     assert g["stages"] == 6 and g["smem_bytes"] <= 227 * 1024
+    g = capi.decode_geometry(32, 8, 64, capi.BF16, batch=16)   # C1: few requests -> 2 heads per CTA, 256-byte rows
+    assert (g["heads_per_cta"], g["token_slices"], g["head_groups"], g["chunk_tokens"]) == (2, 4, 4, 64)
+    g = capi.decode_geometry(32, 8, 64, capi.BF16, batch=64)   # enough requests: the wide rows stay
+    assert g["heads_per_cta"] == 8
     g = capi.decode_geometry(32, 32, 128, capi.BF16)      # MHA: four head groups of eight
     assert g["head_groups"] == 4
     for bad in ((32, 8, 80), (32, 8, 256), (33, 8, 128), (64, 2, 128)):  # d80/d256, ragged, group 32

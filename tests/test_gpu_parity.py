@@ -550,8 +550,8 @@ def test_rope_kv_store_fused(kv_dtype, q_dtype, neox):
 # fused merge == separate stages; dynamic ranges; plan reuse across launches
 # ----------------------------------------------------------------------------- #
 @pytest.mark.parametrize("dyn", [-1, 0, 50])
-@pytest.mark.parametrize("tp", [1, 8])
-def test_fused_merge_equals_two_stage(dyn, tp, monkeypatch):
+@pytest.mark.parametrize("tp,batch", [(1, 70), (1, 37), (8, 37)])
+def test_fused_merge_equals_two_stage(dyn, tp, batch, monkeypatch):
     """phases 0 (one launch, in-kernel merge) must equal phases 1 + 2 (K2 then K3) bit for bit, for
     static-only plans, the default dynamic tail and a 50 % dynamic tail; the same plan is then reused
     for several launches (layers) to exercise the self-resetting ticket / arrival counters."""
@@ -559,7 +559,7 @@ def test_fused_merge_equals_two_stage(dyn, tp, monkeypatch):
     from b200attn import capi, ops
     import ctypes as C
 
-    cfg = synth.shard(synth.Config("fm", 37, 0, 32, 8, 128, page_size=1, ragged=(1, 3000), seed=41), tp)
+    cfg = synth.shard(synth.Config("fm", batch, 0, 32, 8, 128, page_size=1, ragged=(1, 3000), seed=41), tp)
     w = synth.make_workload(cfg, DEV)
     runner = make_runner(w, DEV)
     backend = b200attn.B200AttnBackend(runner, return_lse=True)
@@ -580,6 +580,10 @@ def test_fused_merge_equals_two_stage(dyn, tp, monkeypatch):
     stream = C.c_void_p(torch.cuda.current_stream().cuda_stream)
     capi.check("plan", capi.lib().b200attn_plan(C.byref(a), stream))
     q3 = w.q.view(B, Hq, D)
+    # batch 70: 8 heads per CTA, one token slice; batch 37: a small batch takes 4 heads per CTA and two token
+    # slices (ABI 6); tp 8: one head per CTA, eight slices
+    ts = capi.decode_geometry(Hq, cfg.num_kv_heads, D, capi.BF16, batch=B)["token_slices"]
+    assert ts == {(1, 70): 1, (1, 37): 2, (8, 37): 8}[(tp, batch)]
 
     def run(phases, o, lse):
         torch.ops.b200attn.decode(q3, w.k_pool, w.v_pool, o, lse, backend.plan_buf, w.req_to_token,
@@ -595,11 +599,11 @@ def test_fused_merge_equals_two_stage(dyn, tp, monkeypatch):
         l1 = torch.full((B * Hq,), float("nan"), dtype=torch.float32, device=DEV)
         run(0, o1, l1)
         torch.cuda.synchronize()
-        if tp == 1:
+        if ts == 1:
             assert torch.equal(o1, o2), f"launch {it}: fused merge differs from K2 + K3"
             assert torch.equal(l1, l2)
         else:
-            # token slices (ts = 8): in the one-launch form a request that one CTA holds whole is merged in
+            # token slices (ts > 1): in the one-launch form a request that one CTA holds whole is merged in
             # shared memory from the unnormalised slice states, not through the workspace -- the same sum
             # in another order, so equal to rounding (a bf16 ulp is 2^-8), and bit-stable across launches
             torch.testing.assert_close(o1.float(), o2.float(), rtol=1.6e-2, atol=2e-3)

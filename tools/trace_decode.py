@@ -117,7 +117,7 @@ def main():
 
     chunks = col["counts"] & 0xFFFFFFFF
     pieces = col["counts"] >> 32
-    g = backend.geometry
+    g = capi.decode_geometry(c.num_q_heads, c.num_kv_heads, c.head_dim, backend.kv_dtype, batch=B)
     e_kv = 1 if fp8 else 2
     chunk_bytes = 2 * g["chunk_tokens"] * g["heads_per_cta"] * c.head_dim * e_kv
     steady = us(col["c_last_done"] - col["c_first_done"]) / np.maximum(chunks - 1, 1)
