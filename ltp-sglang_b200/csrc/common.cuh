@@ -411,6 +411,30 @@ __device__ __forceinline__ uint32_t e4m3x2_to_f16x2(uint32_t x) {
   return r;
 }
 
+// Four e4m3 bytes -> two f16x2 (bytes 0, 1 -> lo; bytes 2, 3 -> hi), exact.
+__device__ __forceinline__ void e4m3x4_to_f16x2x2(uint32_t x, uint32_t& lo, uint32_t& hi) {
+  asm("{\n\t.reg .b16 a, b;\n\tmov.b32 {a, b}, %2;\n\tcvt.rn.f16x2.e4m3x2 %0, a;\n\tcvt.rn.f16x2.e4m3x2 %1, b;\n\t}"
+      : "=r"(lo), "=r"(hi)
+      : "r"(x));
+}
+
+// 8x8 transpose of 16-bit elements across the warp: lane (g, j) gives row g, columns 2j, 2j+1 and receives
+// column g, rows 2j, 2j+1 (tools/probe_frag.cu).
+__device__ __forceinline__ uint32_t movmatrix_trans(uint32_t x) {
+  uint32_t y;
+  asm volatile("movmatrix.sync.aligned.m8n8.trans.b16 %0, %1;" : "=r"(y) : "r"(x));
+  return y;
+}
+
+// Two 16 x 16 BYTE matrices, transposed (sm_100a; SASS LDSM.8.MT1616): lanes 0-15 / 16-31 give the row addresses
+// of matrix 0 / 1; lane (g, j) receives r[0] = rows 4j..4j+3 of column g, r[1] = the same rows of column g + 8
+// (matrix 0), r[2], r[3] likewise from matrix 1 (tools/probe_frag.cu).
+__device__ __forceinline__ void ldsm8_x2_trans(uint32_t addr, uint32_t (&r)[4]) {
+  asm volatile("ldmatrix.sync.aligned.m16n16.x2.trans.shared.b8 {%0,%1,%2,%3}, [%4];"
+               : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3])
+               : "r"(addr));
+}
+
 // Programmatic dependent launch (sm_90+).  launch_dependents: the next kernel on the stream, if it was launched
 // with the programmatic-serialization attribute, may start its CTAs now.  wait: block until the kernels this
 // one depends on have completed and their writes are visible (a no-op for a normally launched kernel).

@@ -177,9 +177,6 @@ struct PieceWalk {
 template <typename QT, bool FP8, int D, bool ROWS16>
 __global__ void __launch_bounds__(kThreads, 1) decode_kernel(const DecodeParams p) {
   constexpr bool HALF = FP8 || std::is_same<QT, __half>::value;
-  constexpr int KSTEPS = D / 16;       // k16 steps of Q.K^T
-  constexpr int NTILES = D / 8;        // n8 tiles of P.V
-  constexpr int QR = ROWS16 ? 4 : 2;   // A-fragment registers per k-step actually loaded
   constexpr int EB = FP8 ? 1 : 2;      // KV element bytes
 
   extern __shared__ __align__(128) uint8_t smem[];
@@ -469,40 +466,63 @@ __global__ void __launch_bounds__(kThreads, 1) decode_kernel(const DecodeParams 
 
   // -------------------------------- consumers --------------------------------
   asm volatile("setmaxnreg.inc.sync.aligned.u32 216;");   // 128 x 72 + 256 x 216 = 64512 = 384 x 168
+  // Transposed formulation: the TOKENS ride in the M dimension of the MMA and the q heads of the group in N.
+  //   S^T[16 tok, 8 heads] = K[16 tok, D] . Q^T     A = K tile straight from smem (ldmatrix), B = q in registers
+  //   O^T[D, 8 heads]     += V^T[D, 16 tok] . P^T   A = V tile through a transposing ldmatrix, B = P^T
+  // Every accumulator row is a real token / head-dim index, so a group of <= 8 q heads wastes nothing (with the
+  // heads in M, as in the reference's Triton kernel, half of every m16 tile and of its accumulator registers was
+  // padding: 96 HMMA + ~80 zeroing / move instructions per 16 tokens where 16 HMMA do).  P^T becomes the B
+  // operand through movmatrix (8x8 b16 transpose, 2 per 16 tokens).  An fp8 pool costs one cvt.f16x2.e4m3x2 per
+  // fragment register and nothing else: K bytes arrive in A-fragment order through the 16-bit ldmatrix, V bytes
+  // through ldmatrix.m16n16.trans.b8 (tools/probe_frag.cu prints both layouts), with the tokens of a chunk assigned
+  // to MMA rows / k slots by a fixed permutation so that no byte shuffle is needed and every 8-row phase of an
+  // ldmatrix still reads 8 distinct bank groups:
+  //   MMA row R <-> token pi(R) = R ^ ((R & 8) >> 1);   V matrix row i = 4a + 2b + e <-> token (8b + 2a + e) ^ 4b.
+  // G in 9..16 (NH = 2) runs a second n8 tile of heads on the same A fragments.
+  constexpr int NH = ROWS16 ? 2 : 1;   // n8 tiles of q heads
+  constexpr int HPT = 2 * NH;          // heads a thread holds values of: 8 * (k >> 1) + 2 j + (k & 1)
+  constexpr int MT = D / 16;           // m16 tiles of O^T = k16 steps of K . Q^T
   const int h = warp % p.hc;
   const int tsi = warp / p.hc;
-  const int gq = lane >> 2, jq = lane & 3;     // MMA fragment coordinates
-  const int mat = lane >> 3, mr = lane & 7;    // ldmatrix: matrix id, row
+  const int g = lane >> 2, j = lane & 3;
   const bool cap = p.logit_cap > 0.f;
   const float c = cap ? kLog2e : p.scale_log2;
   const float cap_pre = cap ? p.sm_scale_k / p.logit_cap : 0.f;
-
-  // lane-constant parts of the ldmatrix addresses (bytes inside a stage)
-  // Two stage layouts.  Padded (bulk-copy path): row stride = row bytes + 16, so the 8 rows of an ldmatrix
-  // fall into distinct bank groups.  Swizzled (cp.async path): row stride = row bytes and the 16-byte unit u of
-  // row r sits at u ^ (r & 7) -- a quarter warp of LDGSTS then writes one aligned 128-byte line.  (With the
-  // padded rows each quarter warp straddled two lines, L1 split the instruction into ~10 wavefronts instead
-  // of 4 and fetched 1.5x the sectors from L2, with 2x the tag lookups: ncu r01 tp8.)  Every row a lane
-  // addresses has r & 7 == mr, and a head starts on a 128-byte boundary, so the swizzle folds into
-  // lane-constant offsets: K unit (mat + 4 k) ^ mr = (mat ^ (mr & 3)) + 4 ((k & 1) ^ (mr >> 2)) + 8 (k >> 1),
-  // V unit ((mat >> 1) + 2 n) ^ mr = ((mat >> 1) ^ (mr & 1)) + 2 ((n & 3) ^ (mr >> 1)) + 8 (n >> 2).
   const bool swz = p.swizzle != 0;
   const uint32_t head_off = h * D * EB;
-  uint32_t k_lane[2], v_lane;
+
+  // Lane-constant parts of the ldmatrix addresses.  Padded rows (bulk-copy path): stride = row bytes + 16.
+  // Swizzled rows (cp.async path): unit u of row r at u ^ (r & 7); a head starts on a 128-byte boundary, so the
+  // swizzle only touches the low three bits of the unit index: bit 0 folds into the lane constant, bits 1-2 are
+  // xor-ed into the (compile-time) unit-pair offset of each instruction.
+  uint32_t k_base, k_x, v_base, v_x;
   {
-    const uint32_t krow = (tsi * 16 + mr) * p.row_stride + head_off;
-    const uint32_t vrow = (tsi * 16 + (mat & 1) * 8 + mr) * p.row_stride + head_off + v_off;
-    if (swz) {
-      k_lane[0] = krow + 16 * ((mat ^ (mr & 3)) + 4 * (mr >> 2));
-      k_lane[1] = krow + 16 * ((mat ^ (mr & 3)) + 4 * ((mr >> 2) ^ 1));
-      v_lane = vrow + 16 * ((mat >> 1) ^ (mr & 1));
+    const int mi = lane >> 3, rr = lane & 7;
+    const int R = (mi & 1) * 8 + rr;                         // MMA row this lane addresses (matrices 0/2: rows 0-7)
+    const int tokK = FP8 ? (R ^ ((R & 8) >> 1)) : R;
+    const int hiK = mi >> 1;                                 // second 16-byte unit of the pair
+    const int kx = swz ? (tokK & 7) : 0;
+    k_base = (tsi * 16 + tokK) * p.row_stride + head_off + ((hiK ^ (kx & 1)) << 4);
+    k_x = (kx & 6) << 4;
+    int tokV, hiV;
+    if constexpr (FP8) {
+      const int i = lane & 15;
+      const int kap = 8 * ((i >> 1) & 1) + 2 * (i >> 2) + (i & 1);
+      tokV = kap ^ (4 * ((i >> 1) & 1));
+      hiV = lane >> 4;
     } else {
-      k_lane[0] = krow + mat * 16;
-      k_lane[1] = k_lane[0] + 64;
-      v_lane = vrow + (mat >> 1) * 16;
+      tokV = (mi >> 1) * 8 + rr;
+      hiV = mi & 1;
     }
+    const int vx = swz ? (tokV & 7) : 0;
+    v_base = (tsi * 16 + tokV) * p.row_stride + head_off + v_off + ((hiV ^ (vx & 1)) << 4);
+    v_x = (vx & 6) << 4;
   }
-  const uint32_t v_x = swz ? (mr >> 1) * 32 : 0u;
+  // tokens (inside the warp's 16) behind this thread's S^T elements and behind the k slots of its V fragments
+  const int tok_hi = FP8 ? 8 + (g ^ 4) : 8 + g;               // elements 2, 3 (elements 0, 1: token g)
+  const int vt0 = 2 * j, vt1 = 2 * j + 1;                     // k slots 2j, 2j + 1
+  const int vt2 = FP8 ? 8 + ((2 * j) ^ 4) : 8 + 2 * j;        // k slots 2j + 8, 2j + 9
+  const int vt3 = FP8 ? 8 + ((2 * j + 1) ^ 4) : 9 + 2 * j;
 
   if (H.n_empty > 0) {
     // Requests of length 0 have no chunks, so no range reaches them: their rows are defined here
@@ -519,7 +539,7 @@ __global__ void __launch_bounds__(kThreads, 1) decode_kernel(const DecodeParams 
   // streaming rate of this CTA (clocks per chunk over its static range, pipeline fill included -- what the plan
   // wants to equalise is when the CTAs END): folded into cta_stat so that the next plan can size the ranges by
   // it.  Stamped per range, not per chunk: on an fp8 pool the consumers are the bound and warp 0 is on every
-  // chunk's critical path (thread-0 work inside the chunk loop cost C3 10 %, profiles/r02_baseline).
+  // chunk's critical path.
   const long long clk_first = clock64();
   long long clk_last = clk_first;
   int n_consumed = 0;
@@ -528,8 +548,6 @@ __global__ void __launch_bounds__(kThreads, 1) decode_kernel(const DecodeParams 
   PieceWalk walk(rn == 0 && rg == cta ? d0 : load_desc(pv.range_desc + rg), p.ng);
   while (walk.next(pv, b, hg, lc0, lc1, nchunks, vreq, S, row_off)) {
     const int hq0 = (hg * p.hc + h) * p.group;
-    const bool row0 = gq < p.group;
-    const bool row1 = ROWS16 && (gq + 8 < p.group);
     const bool full_req = lc0 == 0 && lc1 == nchunks;
     // merge bookkeeping of a request cut by a range boundary, fetched now so that the epilogue does not wait for it
     int v_pieces = 1, v_rfirst = rg;   // a whole request is one piece, in this range
@@ -544,64 +562,66 @@ __global__ void __launch_bounds__(kThreads, 1) decode_kernel(const DecodeParams 
     const int64_t prow0 = static_cast<int64_t>(vreq + v_rfirst) * p.ts * hqv;   // first piece's workspace rows
     const int64_t pstep = static_cast<int64_t>(p.ts) * hqv;                      // piece to piece (slice 0 rows)
     const int me = rg - v_rfirst;                                                // this piece's index
-    // A few chunks before the end of a cut request's piece, the other pieces' partial rows of this warp's head are
-    // pulled into L2: the CTA that merges (normally this one: its neighbour finished the other half long ago, and
-    // ~1 GB has gone through L2 since) then reads them in one short round trip instead of a DRAM access queued
-    // behind the KV stream (2 us each under load, tools/trace_decode.py: 7 us from the last chunk to the last
-    // store on C2).  A row that has not been written yet is harmless to prefetch: L2 is the coherence point.
-    const int lc_pf = lc1 - 4 > lc0 ? lc1 - 4 : lc0;
+    const int lc_pf = lc1 - 4 > lc0 ? lc1 - 4 : lc0;   // where the other pieces' partial rows are pulled into L2
+    // heads this thread holds values of, and whether they exist in the group
+    int hl[HPT];
+    bool hv[HPT];
+#pragma unroll
+    for (int k = 0; k < HPT; ++k) {
+      hl[k] = 8 * (k >> 1) + 2 * j + (k & 1);
+      hv[k] = hl[k] < p.group;
+    }
 
-    // ---- Q fragments (A operand), loaded once per piece ----
-    uint32_t qf[KSTEPS][QR];
-    {
-      const QT* q0 = reinterpret_cast<const QT*>(p.q) + b * p.q_sb + (hq0 + gq) * p.q_sh;
-      const QT* q1 = q0 + 8 * p.q_sh;
+    // ---- Q^T fragments (B operand), loaded once per piece: lane (g, j) holds head g (+ 8) ----
+    uint32_t qb[NH][MT][2];
 #pragma unroll
-      for (int kk = 0; kk < KSTEPS; ++kk) {
+    for (int nh = 0; nh < NH; ++nh) {
+      const bool qv = 8 * nh + g < p.group;
+      const QT* qp = reinterpret_cast<const QT*>(p.q) + b * p.q_sb + (hq0 + 8 * nh + g) * p.q_sh;
+#pragma unroll
+      for (int ks = 0; ks < MT; ++ks) {
         if constexpr (!FP8) {
-          const int d0 = kk * 16 + 2 * jq;
-          qf[kk][0] = row0 ? *reinterpret_cast<const uint32_t*>(q0 + d0) : 0u;
-          qf[kk][1] = row0 ? *reinterpret_cast<const uint32_t*>(q0 + d0 + 8) : 0u;
-          if constexpr (ROWS16) {
-            qf[kk][2] = row1 ? *reinterpret_cast<const uint32_t*>(q1 + d0) : 0u;
-            qf[kk][3] = row1 ? *reinterpret_cast<const uint32_t*>(q1 + d0 + 8) : 0u;
-          }
+          const int dd = ks * 16 + 2 * j;
+          qb[nh][ks][0] = qv ? *reinterpret_cast<const uint32_t*>(qp + dd) : 0u;
+          qb[nh][ks][1] = qv ? *reinterpret_cast<const uint32_t*>(qp + dd + 8) : 0u;
         } else {
-          // fp8 K: MMA k-slot (2j, 2j+1, 2j+8, 2j+9) of step kk <-> d = 16kk + 4j + (0..3)
-          const int d0 = kk * 16 + 4 * jq;
+          // fp8 K: k slots (2j, 2j+1 | 2j+8, 2j+9) of step ks <-> d = 16 ks + 4j + (0, 1 | 2, 3)
+          const int dd = ks * 16 + 4 * j;
           float f[4] = {0.f, 0.f, 0.f, 0.f};
-          if (row0) {
+          if (qv) {
 #pragma unroll
-            for (int e = 0; e < 4; ++e) f[e] = fminf(fmaxf(q_to_f32(q0[d0 + e]), -65504.f), 65504.f);
+            for (int e = 0; e < 4; ++e) f[e] = fminf(fmaxf(q_to_f32(qp[dd + e]), -65504.f), 65504.f);
           }
-          qf[kk][0] = pack2<true>(f[0], f[1]);
-          qf[kk][1] = pack2<true>(f[2], f[3]);
-          if constexpr (ROWS16) {
-            float f1[4] = {0.f, 0.f, 0.f, 0.f};
-            if (row1) {
-#pragma unroll
-              for (int e = 0; e < 4; ++e) f1[e] = fminf(fmaxf(q_to_f32(q1[d0 + e]), -65504.f), 65504.f);
-            }
-            qf[kk][2] = pack2<true>(f1[0], f1[1]);
-            qf[kk][3] = pack2<true>(f1[2], f1[3]);
-          }
+          qb[nh][ks][0] = pack2<true>(f[0], f[1]);
+          qb[nh][ks][1] = pack2<true>(f[2], f[3]);
         }
       }
     }
 
-    float o[NTILES][QR];
+    float o[NH][MT][4];
 #pragma unroll
-    for (int n = 0; n < NTILES; ++n)
+    for (int nh = 0; nh < NH; ++nh)
 #pragma unroll
-      for (int e = 0; e < QR; ++e) o[n][e] = 0.f;
-    float m0 = -CUDART_INF_F, m1 = -CUDART_INF_F, l0 = 0.f, l1 = 0.f;
+      for (int t = 0; t < MT; ++t)
+#pragma unroll
+        for (int e = 0; e < 4; ++e) o[nh][t][e] = 0.f;
+    float m[HPT], l[HPT];
+#pragma unroll
+    for (int k = 0; k < HPT; ++k) {
+      m[k] = -CUDART_INF_F;
+      l[k] = 0.f;
+    }
 
 #ifdef B200ATTN_DEC_TRACE
     if (threadIdx.x == 0) { B200_TR_ONCE(TR_C_Q, tr_a); ++tr_pieces; }
 #endif
     for (int lc = lc0; lc < lc1; ++lc) {
       if (lc == lc_pf && try_early) {
-        const int g = lane >> 2, line = lane & 3;
+        // A few chunks before the end of a cut request's piece, the other pieces' partial rows of this warp's
+        // head are pulled into L2: the CTA that merges (normally this one: its neighbour finished the other half
+        // long ago, and ~1 GB has gone through L2 since) then reads them in one short round trip instead of a
+        // DRAM access queued behind the KV stream.  A row not written yet is harmless to prefetch.
+        const int line = lane & 3;
         if (g < p.group && line * 32 < D) {
           const int rowh = h * p.group + g;
 #pragma unroll
@@ -626,165 +646,129 @@ __global__ void __launch_bounds__(kThreads, 1) decode_kernel(const DecodeParams 
       if (threadIdx.x == 0) B200_TR_ONCE(TR_C_FIRST_FULL, tr_b);
       const uint32_t sbase = stage0 + stage * p.stage_bytes;
 
-      // ---- S = Q.K^T for 16 tokens (two n8 tiles) ----
-      float s[2][4];
+      // ---- S^T = K . Q^T : 16 tokens x 8 (16) heads ----
+      float s[NH][4];
 #pragma unroll
-      for (int nt = 0; nt < 2; ++nt) {
-        s[nt][0] = s[nt][1] = s[nt][2] = s[nt][3] = 0.f;
-        const uint32_t ka0 = sbase + k_lane[0] + nt * 8 * p.row_stride;
-        const uint32_t ka1 = sbase + k_lane[1] + nt * 8 * p.row_stride;
-        if constexpr (!FP8) {
+      for (int nh = 0; nh < NH; ++nh) s[nh][0] = s[nh][1] = s[nh][2] = s[nh][3] = 0.f;
+      if constexpr (!FP8) {
 #pragma unroll
-          for (int k2 = 0; k2 < KSTEPS / 2; ++k2) {
-            uint32_t kf[4];
-            ldsm_x4(((k2 & 1) ? ka1 : ka0) + (k2 >> 1) * 128, kf);
-            mma_q<HALF, ROWS16, QR>(s[nt], qf[2 * k2], kf[0], kf[1]);
-            mma_q<HALF, ROWS16, QR>(s[nt], qf[2 * k2 + 1], kf[2], kf[3]);
-          }
-        } else {
+        for (int ks = 0; ks < MT; ++ks) {
+          uint32_t a[4];
+          ldsm_x4(sbase + k_base + ((32u * ks) ^ k_x), a);
 #pragma unroll
-          for (int k4 = 0; k4 < KSTEPS / 4; ++k4) {
-            uint32_t kf[4];
-            ldsm_x4(((k4 & 1) ? ka1 : ka0) + (k4 >> 1) * 128, kf);
+          for (int nh = 0; nh < NH; ++nh) mma16816<HALF>(s[nh], a[0], a[1], a[2], a[3], qb[nh][ks][0], qb[nh][ks][1]);
+        }
+      } else {
 #pragma unroll
-            for (int mm = 0; mm < 4; ++mm) {
-              const int kk = 4 * k4 + mm;
-              const uint32_t b0 = e4m3x2_to_f16x2(kf[mm]);
-              const uint32_t b1 = e4m3x2_to_f16x2(kf[mm] >> 16);
-              mma_q<true, ROWS16, QR>(s[nt], qf[kk], b0, b1);
-            }
-          }
+        for (int u2 = 0; u2 < MT / 2; ++u2) {
+          uint32_t kf[4], a[4];
+          ldsm_x4(sbase + k_base + ((32u * u2) ^ k_x), kf);
+          e4m3x4_to_f16x2x2(kf[0], a[0], a[2]);
+          e4m3x4_to_f16x2x2(kf[1], a[1], a[3]);
+#pragma unroll
+          for (int nh = 0; nh < NH; ++nh) mma16816<true>(s[nh], a[0], a[1], a[2], a[3], qb[nh][2 * u2][0], qb[nh][2 * u2][1]);
+          e4m3x4_to_f16x2x2(kf[2], a[0], a[2]);
+          e4m3x4_to_f16x2x2(kf[3], a[1], a[3]);
+#pragma unroll
+          for (int nh = 0; nh < NH; ++nh)
+            mma16816<true>(s[nh], a[0], a[1], a[2], a[3], qb[nh][2 * u2 + 1][0], qb[nh][2 * u2 + 1][1]);
         }
       }
 
       // ---- logit cap, tail mask ----
       if (cap) {
 #pragma unroll
-        for (int nt = 0; nt < 2; ++nt)
+        for (int nh = 0; nh < NH; ++nh)
 #pragma unroll
-          for (int e = 0; e < 4; ++e) s[nt][e] = p.logit_cap * tanhf(s[nt][e] * cap_pre);
+          for (int e = 0; e < 4; ++e) s[nh][e] = p.logit_cap * tanhf(s[nh][e] * cap_pre);
       }
-      const int tok0 = lc * T + tsi * 16 + 2 * jq;  // token of s[0][0]
+      const int t0 = lc * T + tsi * 16;   // token of the warp's row 0
       const bool tail = (lc + 1) * T > S;
       if (tail) {
 #pragma unroll
-        for (int nt = 0; nt < 2; ++nt)
-#pragma unroll
-          for (int e = 0; e < 4; ++e)
-            if (tok0 + nt * 8 + (e & 1) >= S) s[nt][e] = -CUDART_INF_F;
-      }
-
-      // ---- online softmax (rows gq and, for wide groups, gq + 8) ----
-      float mx0 = fmaxf(fmaxf(s[0][0], s[0][1]), fmaxf(s[1][0], s[1][1]));
-      mx0 = fmaxf(mx0, __shfl_xor_sync(0xffffffffu, mx0, 1));
-      mx0 = fmaxf(mx0, __shfl_xor_sync(0xffffffffu, mx0, 2));
-      const float mn0 = fmaxf(m0, mx0);
-      const float mr0 = mn0 == -CUDART_INF_F ? 0.f : mn0;
-      const float corr0 = fast_exp2((m0 - mr0) * c);
-      m0 = mn0;
-      const float mc0 = mr0 * c;
-      float pr[2][4];
-      pr[0][0] = fast_exp2(fmaf(s[0][0], c, -mc0));
-      pr[0][1] = fast_exp2(fmaf(s[0][1], c, -mc0));
-      pr[1][0] = fast_exp2(fmaf(s[1][0], c, -mc0));
-      pr[1][1] = fast_exp2(fmaf(s[1][1], c, -mc0));
-      l0 = fmaf(l0, corr0, (pr[0][0] + pr[0][1]) + (pr[1][0] + pr[1][1]));
-      float corr1 = 1.f;
-      if constexpr (ROWS16) {
-        float mx1 = fmaxf(fmaxf(s[0][2], s[0][3]), fmaxf(s[1][2], s[1][3]));
-        mx1 = fmaxf(mx1, __shfl_xor_sync(0xffffffffu, mx1, 1));
-        mx1 = fmaxf(mx1, __shfl_xor_sync(0xffffffffu, mx1, 2));
-        const float mn1 = fmaxf(m1, mx1);
-        const float mr1 = mn1 == -CUDART_INF_F ? 0.f : mn1;
-        corr1 = fast_exp2((m1 - mr1) * c);
-        m1 = mn1;
-        const float mc1 = mr1 * c;
-        pr[0][2] = fast_exp2(fmaf(s[0][2], c, -mc1));
-        pr[0][3] = fast_exp2(fmaf(s[0][3], c, -mc1));
-        pr[1][2] = fast_exp2(fmaf(s[1][2], c, -mc1));
-        pr[1][3] = fast_exp2(fmaf(s[1][3], c, -mc1));
-        l1 = fmaf(l1, corr1, (pr[0][2] + pr[0][3]) + (pr[1][2] + pr[1][3]));
-      }
-      if (__any_sync(0xffffffffu, corr0 != 1.f || corr1 != 1.f)) {
-#pragma unroll
-        for (int n = 0; n < NTILES; ++n) {
-          o[n][0] *= corr0;
-          o[n][1] *= corr0;
-          if constexpr (ROWS16) {
-            o[n][2] *= corr1;
-            o[n][3] *= corr1;
-          }
+        for (int nh = 0; nh < NH; ++nh) {
+          if (t0 + g >= S) s[nh][0] = s[nh][1] = -CUDART_INF_F;
+          if (t0 + tok_hi >= S) s[nh][2] = s[nh][3] = -CUDART_INF_F;
         }
       }
 
-      // ---- P (A operand) ----
-      const uint32_t pa0 = pack2<HALF>(pr[0][0], pr[0][1]);
-      const uint32_t pa2 = pack2<HALF>(pr[1][0], pr[1][1]);
-      uint32_t pa1 = 0u, pa3 = 0u;
-      if constexpr (ROWS16) {
-        pa1 = pack2<HALF>(pr[0][2], pr[0][3]);
-        pa3 = pack2<HALF>(pr[1][2], pr[1][3]);
+      // ---- online softmax over the token dimension: a head's 16 logits sit in 8 lanes (g) x 2 elements ----
+      float corr[HPT], pr[NH][4];
+      bool resc = false;
+#pragma unroll
+      for (int k = 0; k < HPT; ++k) {
+        const int nh = k >> 1, e = k & 1;
+        float mx = fmaxf(s[nh][e], s[nh][e + 2]);
+        mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, 4));
+        mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, 8));
+        mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, 16));
+        const float mn = fmaxf(m[k], mx);
+        const float mr = mn == -CUDART_INF_F ? 0.f : mn;
+        corr[k] = fast_exp2((m[k] - mr) * c);
+        m[k] = mn;
+        const float mc = mr * c;
+        pr[nh][e] = fast_exp2(fmaf(s[nh][e], c, -mc));
+        pr[nh][e + 2] = fast_exp2(fmaf(s[nh][e + 2], c, -mc));
+        l[k] = fmaf(l[k], corr[k], pr[nh][e] + pr[nh][e + 2]);
+        resc |= corr[k] != 1.f;
       }
-      // V fragments of masked tail tokens are zeroed: the smem rows behind them
-      // hold stale bytes of another request (0 * inf would poison this one).
-      uint32_t vm0 = 0xffffffffu, vm1 = 0xffffffffu;
-      if (tail) {
-        vm0 = (tok0 < S ? 0x0000ffffu : 0u) | (tok0 + 1 < S ? 0xffff0000u : 0u);
-        vm1 = (tok0 + 8 < S ? 0x0000ffffu : 0u) | (tok0 + 9 < S ? 0xffff0000u : 0u);
+      if (__any_sync(0xffffffffu, resc)) {
+#pragma unroll
+        for (int nh = 0; nh < NH; ++nh)
+#pragma unroll
+          for (int t = 0; t < MT; ++t) {
+            o[nh][t][0] *= corr[2 * nh];
+            o[nh][t][1] *= corr[2 * nh + 1];
+            o[nh][t][2] *= corr[2 * nh];
+            o[nh][t][3] *= corr[2 * nh + 1];
+          }
       }
 
-      // ---- O += P.V ----  (the masks cost 32 LOP3 per 16 tokens: only the tail chunk pays them)
+      // ---- P^T (B operand): pack [token row][heads 2j, 2j+1], transpose 8x8 -> [head g][k slots 2j, 2j+1] ----
+      uint32_t pb[NH][2];
+#pragma unroll
+      for (int nh = 0; nh < NH; ++nh) {
+        pb[nh][0] = movmatrix_trans(pack2<HALF>(pr[nh][0], pr[nh][1]));
+        pb[nh][1] = movmatrix_trans(pack2<HALF>(pr[nh][2], pr[nh][3]));
+      }
+      // V fragments of masked tail tokens are zeroed: the smem rows behind them hold stale bytes of another
+      // request (0 * inf would poison this one).  Only the tail chunk pays the masks.
+      uint32_t vm_lo = 0xffffffffu, vm_hi = 0xffffffffu;
+      if (tail) {
+        vm_lo = (t0 + vt0 < S ? 0x0000ffffu : 0u) | (t0 + vt1 < S ? 0xffff0000u : 0u);
+        vm_hi = (t0 + vt2 < S ? 0x0000ffffu : 0u) | (t0 + vt3 < S ? 0xffff0000u : 0u);
+      }
+
+      // ---- O^T += V^T . P^T ----
       auto pv_mma = [&](auto tail_tag) {
         constexpr bool TAIL = decltype(tail_tag)::value;
-        const uint32_t m0 = TAIL ? vm0 : 0xffffffffu, m1 = TAIL ? vm1 : 0xffffffffu;
-        const uint32_t va = sbase + v_lane;
+        const uint32_t mlo = TAIL ? vm_lo : 0xffffffffu, mhi = TAIL ? vm_hi : 0xffffffffu;
         if constexpr (!FP8) {
-  #pragma unroll
-          for (int n2 = 0; n2 < NTILES / 2; ++n2) {
-            uint32_t vf[4];
-            ldsm_x4_trans(va + (((n2 & 3) * 32) ^ v_x) + (n2 >> 2) * 128, vf);
-            if constexpr (ROWS16) {
-              mma16816<HALF>(o[2 * n2], pa0, pa1, pa2, pa3, vf[0] & m0, vf[1] & m1);
-              mma16816<HALF>(o[2 * n2 + 1], pa0, pa1, pa2, pa3, vf[2] & m0, vf[3] & m1);
-            } else {
-              float d0[4] = {o[2 * n2][0], o[2 * n2][1], 0.f, 0.f};
-              mma16816<HALF>(d0, pa0, 0u, pa2, 0u, vf[0] & m0, vf[1] & m1);
-              o[2 * n2][0] = d0[0];
-              o[2 * n2][1] = d0[1];
-              float d1[4] = {o[2 * n2 + 1][0], o[2 * n2 + 1][1], 0.f, 0.f};
-              mma16816<HALF>(d1, pa0, 0u, pa2, 0u, vf[2] & m0, vf[3] & m1);
-              o[2 * n2 + 1][0] = d1[0];
-              o[2 * n2 + 1][1] = d1[1];
-            }
+#pragma unroll
+          for (int t = 0; t < MT; ++t) {
+            uint32_t a[4];
+            ldsm_x4_trans(sbase + v_base + ((32u * t) ^ v_x), a);
+#pragma unroll
+            for (int nh = 0; nh < NH; ++nh)
+              mma16816<HALF>(o[nh][t], a[0] & mlo, a[1] & mlo, a[2] & mhi, a[3] & mhi, pb[nh][0], pb[nh][1]);
           }
         } else {
-          // fp8 V: one x4.trans covers 32 d; a b16 transpose leaves each register
-          // with {tok 2j: d, d+1 | tok 2j+1: d, d+1}; PRMT regroups by d parity.
-  #pragma unroll
-          for (int n4 = 0; n4 < NTILES / 4; ++n4) {
-            uint32_t vf[4];
-            ldsm_x4_trans(va + (((n4 & 3) * 32) ^ v_x) + (n4 >> 2) * 128, vf);
-  #pragma unroll
-            for (int gg = 0; gg < 2; ++gg) {
-  #pragma unroll
-              for (int par = 0; par < 2; ++par) {
-                const uint32_t sel = par ? 0x4431u : 0x4420u;
-                const uint32_t b0 = e4m3x2_to_f16x2(__byte_perm(vf[2 * gg], 0u, sel)) & m0;
-                const uint32_t b1 = e4m3x2_to_f16x2(__byte_perm(vf[2 * gg + 1], 0u, sel)) & m1;
-                const int n = n4 * 4 + gg * 2 + par;
-                if constexpr (ROWS16) {
-                  mma16816<true>(o[n], pa0, pa1, pa2, pa3, b0, b1);
-                } else {
-                  float d0[4] = {o[n][0], o[n][1], 0.f, 0.f};
-                  mma16816<true>(d0, pa0, 0u, pa2, 0u, b0, b1);
-                  o[n][0] = d0[0];
-                  o[n][1] = d0[1];
-                }
-              }
-            }
+#pragma unroll
+          for (int t2 = 0; t2 < MT / 2; ++t2) {
+            uint32_t vf[4], a[4];
+            ldsm8_x2_trans(sbase + v_base + ((32u * t2) ^ v_x), vf);
+            e4m3x4_to_f16x2x2(vf[0], a[0], a[2]);
+            e4m3x4_to_f16x2x2(vf[1], a[1], a[3]);
+#pragma unroll
+            for (int nh = 0; nh < NH; ++nh)
+              mma16816<true>(o[nh][2 * t2], a[0] & mlo, a[1] & mlo, a[2] & mhi, a[3] & mhi, pb[nh][0], pb[nh][1]);
+            e4m3x4_to_f16x2x2(vf[2], a[0], a[2]);
+            e4m3x4_to_f16x2x2(vf[3], a[1], a[3]);
+#pragma unroll
+            for (int nh = 0; nh < NH; ++nh)
+              mma16816<true>(o[nh][2 * t2 + 1], a[0] & mlo, a[1] & mlo, a[2] & mhi, a[3] & mhi, pb[nh][0], pb[nh][1]);
           }
         }
-
       };
       if (tail) pv_mma(std::true_type{}); else pv_mma(std::false_type{});
       __syncwarp();
@@ -799,205 +783,182 @@ __global__ void __launch_bounds__(kThreads, 1) decode_kernel(const DecodeParams 
     }
 
     // ---- epilogue: normalise, write final o or a partial ----
-    l0 += __shfl_xor_sync(0xffffffffu, l0, 1);
-    l0 += __shfl_xor_sync(0xffffffffu, l0, 2);
-    const float inv0 = l0 > 0.f ? p.v_scale / l0 : 0.f;
-    const float lse0 = l0 > 0.f ? m0 * c * kLn2 + logf(l0) : -CUDART_INF_F;
-    float inv1 = 0.f, lse1 = -CUDART_INF_F;
-    if constexpr (ROWS16) {
-      l1 += __shfl_xor_sync(0xffffffffu, l1, 1);
-      l1 += __shfl_xor_sync(0xffffffffu, l1, 2);
-      inv1 = l1 > 0.f ? p.v_scale / l1 : 0.f;
-      lse1 = l1 > 0.f ? m1 * c * kLn2 + logf(l1) : -CUDART_INF_F;
+    // This thread holds, for heads hl[k], the head-dim rows d = 16 t + g + 8 (e >> 1): element (nh, t, e) belongs to
+    // head k = 2 nh + (e & 1).  A head's row sum is spread over the 8 token lanes (g).
+    float inv[HPT], lse[HPT];
+#pragma unroll
+    for (int k = 0; k < HPT; ++k) {
+      l[k] += __shfl_xor_sync(0xffffffffu, l[k], 4);
+      l[k] += __shfl_xor_sync(0xffffffffu, l[k], 8);
+      l[k] += __shfl_xor_sync(0xffffffffu, l[k], 16);
+      inv[k] = l[k] > 0.f ? p.v_scale / l[k] : 0.f;
+      lse[k] = l[k] > 0.f ? m[k] * c * kLn2 + logf(l[k]) : -CUDART_INF_F;
     }
-    // column (head-dim index) of accumulator element e (0/1) of tile n
-    auto col_of = [&](int n, int e) -> int {
-      if constexpr (!FP8) return n * 8 + 2 * jq + e;
-      return (n >> 1) * 16 + 4 * jq + 2 * e + (n & 1);
-    };
     // Workspace rows of this piece: ((vreq + rg) * ts + slice) * hqv + head; with the in-CTA slice merge below
     // only slice 0's rows are used (one partial per piece instead of ts).
     const int64_t piece_row = static_cast<int64_t>(vreq + rg) * p.ts * hqv;
-    const bool use_xch = !ROWS16 && p.xch_off != 0;   // implies ts > 1 (make_geometry)
+    const bool use_xch = NH == 1 && p.xch_off != 0;   // implies ts > 1 (make_geometry)
 
     // Last-arriver shortcut (partial pieces): when every other piece of the request had already arrived one
     // chunk ago, this CTA is the one that merges -- so it merges its own partial straight from registers with
-    // the others read from the workspace, instead of write partial -> fence -> atomic -> read everything back
-    // (four dependent global round trips of ~1.5 us each under load at the end of a CTA's range:
-    // tools/trace_decode.py, 6.6 us from the last chunk to the exit on C2).  Same values, same order, same
-    // arithmetic as merge_heads4, so which path ran never shows in the result.
-    const bool can_fast = !ROWS16 && !full_req && p.fuse_merge && (use_xch || p.ts == 1);
+    // the others read from the workspace, instead of write partial -> fence -> atomic -> read everything back.
+    // Same values, same order, same arithmetic as merge_heads4, so which path ran never shows in the result.
+    const bool can_fast = NH == 1 && !full_req && p.fuse_merge && (use_xch || p.ts == 1);
     volatile int32_t* flags = merge_flag + (npiece & 1) * 2;
     if (can_fast && threadIdx.x == 0) flags[0] = early_ok;
     if (can_fast && !use_xch) named_bar_sync(2, kConsumerWarps * 32);   // (the slice exchange has its own barrier)
-    float wk[4], inv_s = 0.f, lse_tot = -CUDART_INF_F;
     // The merge's loads go out in ONE batch -- the other pieces' lse and the rows of the first other piece (the
-    // only other piece in all but the rarest plans) -- before anything waits on them: issued one after the other's
-    // result (lse -> weights -> row loads per tile) the shortcut still cost 3-4 dependent round trips.
+    // only other piece in all but the rarest plans) -- before anything waits on them.
     const int i1 = me == 0 ? 1 : 0;   // the first other piece
-    auto merge_lse_load = [&](int rowh, float lse_mine, float (&l)[4]) {
+    float wk[2][4], inv_s[2] = {0.f, 0.f}, lse_tot[2] = {-CUDART_INF_F, -CUDART_INF_F};
+    auto merge_lse_load = [&](int rowh, float lse_mine, float (&lv)[4]) {
 #pragma unroll
       for (int i = 0; i < 4; ++i)
-        l[i] = i < v_pieces ? (i == me ? lse_mine : __ldcg(p.ws_lse + prow0 + i * pstep + rowh)) : -CUDART_INF_F;
+        lv[i] = i < v_pieces ? (i == me ? lse_mine : __ldcg(p.ws_lse + prow0 + i * pstep + rowh)) : -CUDART_INF_F;
     };
-    auto merge_weights = [&](const float (&l)[4]) {
-      const float m = fmaxf(fmaxf(l[0], l[1]), fmaxf(l[2], l[3]));
-      float s = 0.f;
+    auto merge_weights = [&](int k, const float (&lv)[4]) {
+      const float mm = fmaxf(fmaxf(lv[0], lv[1]), fmaxf(lv[2], lv[3]));
+      float sum = 0.f;
 #pragma unroll
       for (int i = 0; i < 4; ++i) {
-        wk[i] = m != -CUDART_INF_F ? __expf(l[i] - m) : 0.f;
-        s += wk[i];
+        wk[k][i] = mm != -CUDART_INF_F ? __expf(lv[i] - mm) : 0.f;
+        sum += wk[k][i];
       }
-      inv_s = s > 0.f ? 1.f / s : 0.f;
-      lse_tot = s > 0.f ? m + logf(s) : -CUDART_INF_F;
+      inv_s[k] = sum > 0.f ? 1.f / sum : 0.f;
+      lse_tot[k] = sum > 0.f ? mm + logf(sum) : -CUDART_INF_F;
     };
-    // columns col_of(n, 0 / 1) of workspace row w
-    auto load_pair = [&](const float* w, int n, float& v0, float& v1) {
-      if constexpr (!FP8) {
-        const float2 t = __ldcg(reinterpret_cast<const float2*>(w + n * 8 + 2 * jq));
-        v0 = t.x;
-        v1 = t.y;
-      } else {
-        v0 = __ldcg(w + col_of(n, 0));
-        v1 = __ldcg(w + col_of(n, 1));
-      }
-    };
-    // x1_0 / x1_1: the first other piece's values of this tile, already in registers
-    auto merge_tile = [&](int rowh, int n, float x0, float x1, float x1_0, float x1_1, float& y0, float& y1) {
-      float a0 = 0.f, a1 = 0.f;
+    // own = this piece's normalised value, x1 = the first other piece's (already in a register)
+    auto merge_val = [&](int k, int rowh, int d, float own, float x1) -> float {
+      float a = 0.f;
 #pragma unroll
       for (int i = 0; i < 4; ++i) {
         if (i < v_pieces) {
-          float v0 = x0, v1 = x1;
-          if (i == i1) {
-            v0 = x1_0;
-            v1 = x1_1;
-          } else if (i != me) {
-            load_pair(p.ws_o + (prow0 + i * pstep + rowh) * D, n, v0, v1);
-          }
-          a0 = fmaf(wk[i], v0, a0);
-          a1 = fmaf(wk[i], v1, a1);
+          float v = own;
+          if (i == i1) v = x1;
+          else if (i != me) v = __ldcg(p.ws_o + (prow0 + i * pstep + rowh) * D + d);
+          a = fmaf(wk[k][i], v, a);
         }
       }
-      y0 = a0 * inv_s;
-      y1 = a1 * inv_s;
+      return a * inv_s[k];
     };
+    QT* const obase = reinterpret_cast<QT*>(p.o) + b * p.o_sb + hq0 * p.o_sh;
+    float* const lbase = p.lse ? p.lse + static_cast<int64_t>(b) * p.hq + hq0 : nullptr;
 
     bool final_written = false;
     if (p.ts == 1 && full_req) {
       final_written = true;
-      QT* o0 = reinterpret_cast<QT*>(p.o) + b * p.o_sb + (hq0 + gq) * p.o_sh;
-      if (row0) {
 #pragma unroll
-        for (int n = 0; n < NTILES; ++n) {
-          store_q(o0 + col_of(n, 0), o[n][0] * inv0);
-          store_q(o0 + col_of(n, 1), o[n][1] * inv0);
-        }
-        if (p.lse && jq == 0) p.lse[static_cast<int64_t>(b) * p.hq + hq0 + gq] = lse0;
-      }
-      if constexpr (ROWS16) {
-        if (row1) {
-          QT* o1 = o0 + 8 * p.o_sh;
+      for (int nh = 0; nh < NH; ++nh)
 #pragma unroll
-          for (int n = 0; n < NTILES; ++n) {
-            store_q(o1 + col_of(n, 0), o[n][2] * inv1);
-            store_q(o1 + col_of(n, 1), o[n][3] * inv1);
+        for (int t = 0; t < MT; ++t)
+#pragma unroll
+          for (int e = 0; e < 4; ++e) {
+            const int k = 2 * nh + (e & 1);
+            if (hv[k]) store_q(obase + hl[k] * p.o_sh + 16 * t + g + 8 * (e >> 1), o[nh][t][e] * inv[k]);
           }
-          if (p.lse && jq == 0) p.lse[static_cast<int64_t>(b) * p.hq + hq0 + gq + 8] = lse1;
-        }
+      if (lbase && g == 0) {
+#pragma unroll
+        for (int k = 0; k < HPT; ++k)
+          if (hv[k]) lbase[hl[k]] = lse[k];
       }
     } else if (use_xch) {
       // The ts token slices of this piece meet in shared memory (unnormalised O, max, sum) and each warp
-      // finishes 1 / ts of its head's columns: a whole request goes straight to `o`; a piece of a request cut
-      // by a range boundary leaves ONE normalised partial per head in the workspace instead of ts.  Through
-      // the workspace the slice merge cost a write -> fence -> atomic -> read-back chain of global round trips
-      // per piece with the consumers idle, and ts x the rows for the cross-CTA merge to read back.
-      const int g4 = p.group * 4;
-      float2* xall = reinterpret_cast<float2*>(smem + p.xch_off);
-      float2* xml = xall + kXchWarps * NTILES * g4;
-      const int li = gq * 4 + jq;
-      if (row0) {
-        float2* xo = xall + warp * (NTILES * g4) + li;
+      // finishes the m tiles t = slice, slice + ts, ... of its head: a whole request goes straight to `o`; a piece
+      // of a request cut by a range boundary leaves ONE normalised partial per head in the workspace instead of ts.
+      float* xall = reinterpret_cast<float*>(smem + p.xch_off);                    // [warp][group][D]
+      float2* xml = reinterpret_cast<float2*>(xall + kXchWarps * p.group * D);     // [warp][8] (max * c, sum)
 #pragma unroll
-        for (int n = 0; n < NTILES; ++n) xo[n * g4] = make_float2(o[n][0], o[n][1]);
-        if (jq == 0) xml[warp * 8 + gq] = make_float2(l0 > 0.f ? m0 * c : -CUDART_INF_F, l0);
+      for (int t = 0; t < MT; ++t)
+#pragma unroll
+        for (int e = 0; e < 4; ++e) {
+          const int k = e & 1;
+          if (hv[k]) xall[(warp * p.group + hl[k]) * D + 16 * t + g + 8 * (e >> 1)] = o[0][t][e];
+        }
+      if (g == 0) {
+#pragma unroll
+        for (int k = 0; k < 2; ++k)
+          if (hv[k]) xml[warp * 8 + hl[k]] = make_float2(l[k] > 0.f ? m[k] * c : -CUDART_INF_F, l[k]);
       }
       named_bar_sync(2, kConsumerWarps * 32);
       const bool fast = can_fast && flags[0] != 0;
       final_written = full_req || fast;
-      if (row0) {
-        float wgt[kXchWarps];
-        float mm = -CUDART_INF_F;
+      float wgt[kXchWarps][2], invx[2], lse_all[2];
 #pragma unroll
-        for (int s = 0; s < kXchWarps; ++s)
-          if (s < p.ts) mm = fmaxf(mm, xml[(s * p.hc + h) * 8 + gq].x);
+      for (int k = 0; k < 2; ++k) {
+        float mm = -CUDART_INF_F;
+        const int hk = hv[k] ? hl[k] : 0;
+#pragma unroll
+        for (int sl = 0; sl < kXchWarps; ++sl)
+          if (sl < p.ts) mm = fmaxf(mm, xml[(sl * p.hc + h) * 8 + hk].x);
         float L = 0.f;
 #pragma unroll
-        for (int s = 0; s < kXchWarps; ++s) {
-          wgt[s] = 0.f;
-          if (s < p.ts) {
-            const float2 ml = xml[(s * p.hc + h) * 8 + gq];
-            wgt[s] = ml.y > 0.f ? fast_exp2(ml.x - mm) : 0.f;
-            L = fmaf(wgt[s], ml.y, L);
+        for (int sl = 0; sl < kXchWarps; ++sl) {
+          wgt[sl][k] = 0.f;
+          if (sl < p.ts) {
+            const float2 ml = xml[(sl * p.hc + h) * 8 + hk];
+            wgt[sl][k] = ml.y > 0.f ? fast_exp2(ml.x - mm) : 0.f;
+            L = fmaf(wgt[sl][k], ml.y, L);
           }
         }
-        const float inv = L > 0.f ? p.v_scale / L : 0.f;
-        const float lse_all = L > 0.f ? mm * kLn2 + logf(L) : -CUDART_INF_F;
-        const int rowh = h * p.group + gq;
-        QT* o0 = reinterpret_cast<QT*>(p.o) + b * p.o_sb + (hq0 + gq) * p.o_sh;
-        float* w0 = p.ws_o + (piece_row + rowh) * D;
-        // this warp finishes tiles tsi, tsi + ts, ...: at most NTILES / 2 of them (ts >= 2)
-        float x1[NTILES / 2][2];
-        if (fast) {
-          float l[4];
-          merge_lse_load(rowh, lse_all, l);
-          const float* w1 = p.ws_o + (prow0 + i1 * pstep + rowh) * D;
+        invx[k] = L > 0.f ? p.v_scale / L : 0.f;
+        lse_all[k] = L > 0.f ? mm * kLn2 + logf(L) : -CUDART_INF_F;
+      }
+      int rowh[2];
 #pragma unroll
-          for (int k = 0; k < NTILES / 2; ++k) {
-            const int n = tsi + k * p.ts;
-            x1[k][0] = x1[k][1] = 0.f;
-            if (n < NTILES) load_pair(w1, n, x1[k][0], x1[k][1]);
+      for (int k = 0; k < 2; ++k) rowh[k] = h * p.group + (hv[k] ? hl[k] : 0);
+      // this warp finishes tiles tsi, tsi + ts, ...: at most MT / 2 of them (ts >= 2)
+      float x1[MT / 2][4];
+      if (fast) {
+        float lv[2][4];
+#pragma unroll
+        for (int k = 0; k < 2; ++k) merge_lse_load(rowh[k], lse_all[k], lv[k]);
+#pragma unroll
+        for (int tt = 0; tt < MT / 2; ++tt) {
+          const int t = tsi + tt * p.ts;
+#pragma unroll
+          for (int e = 0; e < 4; ++e) {
+            x1[tt][e] = 0.f;
+            if (t < MT && hv[e & 1])
+              x1[tt][e] = __ldcg(p.ws_o + (prow0 + i1 * pstep + rowh[e & 1]) * D + 16 * t + g + 8 * (e >> 1));
           }
-          merge_weights(l);
         }
-        int kt = 0;
-        for (int n = tsi; n < NTILES; n += p.ts, ++kt) {
-          float a0 = 0.f, a1 = 0.f;
 #pragma unroll
-          for (int s = 0; s < kXchWarps; ++s) {
-            if (s < p.ts) {
-              const float2 v = xall[(s * p.hc + h) * (NTILES * g4) + n * g4 + li];
-              a0 = fmaf(wgt[s], v.x, a0);
-              a1 = fmaf(wgt[s], v.y, a1);
+        for (int k = 0; k < 2; ++k) merge_weights(k, lv[k]);
+      }
+#pragma unroll
+      for (int tt = 0; tt < MT / 2; ++tt) {
+        const int t = tsi + tt * p.ts;
+        if (t < MT) {
+#pragma unroll
+          for (int e = 0; e < 4; ++e) {
+            const int k = e & 1;
+            if (!hv[k]) continue;
+            const int d = 16 * t + g + 8 * (e >> 1);
+            float a = 0.f;
+#pragma unroll
+            for (int sl = 0; sl < kXchWarps; ++sl)
+              if (sl < p.ts) a = fmaf(wgt[sl][k], xall[((sl * p.hc + h) * p.group + hl[k]) * D + d], a);
+            a *= invx[k];
+            if (full_req) {
+              store_q(obase + hl[k] * p.o_sh + d, a);
+            } else if (fast) {
+              store_q(obase + hl[k] * p.o_sh + d, merge_val(k, rowh[k], d, a, x1[tt][e]));
+            } else {
+              p.ws_o[(piece_row + rowh[k]) * D + d] = a;
             }
           }
-          if (full_req) {
-            store_q(o0 + col_of(n, 0), a0 * inv);
-            store_q(o0 + col_of(n, 1), a1 * inv);
-          } else if (fast) {
-            float y0, y1;
-            float f0 = 0.f, f1 = 0.f;
-#pragma unroll
-            for (int k = 0; k < NTILES / 2; ++k)   // (a run-time index would send x1 to local memory)
-              if (k == kt) {
-                f0 = x1[k][0];
-                f1 = x1[k][1];
-              }
-            merge_tile(rowh, n, a0 * inv, a1 * inv, f0, f1, y0, y1);
-            store_q(o0 + col_of(n, 0), y0);
-            store_q(o0 + col_of(n, 1), y1);
-          } else {
-            w0[col_of(n, 0)] = a0 * inv;
-            w0[col_of(n, 1)] = a1 * inv;
-          }
         }
-        if (jq == 0 && tsi == 0) {
+      }
+      if (g == 0 && tsi == 0) {
+#pragma unroll
+        for (int k = 0; k < 2; ++k) {
+          if (!hv[k]) continue;
           if (full_req) {
-            if (p.lse) p.lse[static_cast<int64_t>(b) * p.hq + hq0 + gq] = lse_all;
+            if (lbase) lbase[hl[k]] = lse_all[k];
           } else if (fast) {
-            if (p.lse) p.lse[static_cast<int64_t>(b) * p.hq + hq0 + gq] = lse_tot;
+            if (lbase) lbase[hl[k]] = lse_tot[k];
           } else {
-            p.ws_lse[piece_row + rowh] = lse_all;
+            p.ws_lse[piece_row + rowh[k]] = lse_all[k];
           }
         }
       }
@@ -1007,45 +968,49 @@ __global__ void __launch_bounds__(kThreads, 1) decode_kernel(const DecodeParams 
     } else if (can_fast && flags[0] != 0) {
       // ts == 1: this warp owns its head's rows outright
       final_written = true;
-      if (row0) {
-        const int rowh = h * p.group + gq;
-        float l[4], x1[NTILES][2];
-        merge_lse_load(rowh, lse0, l);
-        const float* w1 = p.ws_o + (prow0 + i1 * pstep + rowh) * D;
+      int rowh[2];
+      float lv[2][4], x1[MT][4];
 #pragma unroll
-        for (int n = 0; n < NTILES; ++n) load_pair(w1, n, x1[n][0], x1[n][1]);
-        merge_weights(l);
-        QT* o0 = reinterpret_cast<QT*>(p.o) + b * p.o_sb + (hq0 + gq) * p.o_sh;
+      for (int k = 0; k < 2; ++k) {
+        rowh[k] = h * p.group + (hv[k] ? hl[k] : 0);
+        merge_lse_load(rowh[k], lse[k], lv[k]);
+      }
 #pragma unroll
-        for (int n = 0; n < NTILES; ++n) {
-          float y0, y1;
-          merge_tile(rowh, n, o[n][0] * inv0, o[n][1] * inv0, x1[n][0], x1[n][1], y0, y1);
-          store_q(o0 + col_of(n, 0), y0);
-          store_q(o0 + col_of(n, 1), y1);
+      for (int t = 0; t < MT; ++t)
+#pragma unroll
+        for (int e = 0; e < 4; ++e)
+          x1[t][e] = hv[e & 1] ? __ldcg(p.ws_o + (prow0 + i1 * pstep + rowh[e & 1]) * D + 16 * t + g + 8 * (e >> 1)) : 0.f;
+#pragma unroll
+      for (int k = 0; k < 2; ++k) merge_weights(k, lv[k]);
+#pragma unroll
+      for (int t = 0; t < MT; ++t)
+#pragma unroll
+        for (int e = 0; e < 4; ++e) {
+          const int k = e & 1;
+          const int d = 16 * t + g + 8 * (e >> 1);
+          if (hv[k]) store_q(obase + hl[k] * p.o_sh + d, merge_val(k, rowh[k], d, o[0][t][e] * inv[k], x1[t][e]));
         }
-        if (p.lse && jq == 0) p.lse[static_cast<int64_t>(b) * p.hq + hq0 + gq] = lse_tot;
+      if (lbase && g == 0) {
+#pragma unroll
+        for (int k = 0; k < 2; ++k)
+          if (hv[k]) lbase[hl[k]] = lse_tot[k];
       }
     } else {
-      const int64_t row = piece_row + static_cast<int64_t>(tsi) * hqv + h * p.group + gq;
-      if (row0) {
-        float* w = p.ws_o + row * D;
 #pragma unroll
-        for (int n = 0; n < NTILES; ++n) {
-          w[col_of(n, 0)] = o[n][0] * inv0;
-          w[col_of(n, 1)] = o[n][1] * inv0;
-        }
-        if (jq == 0) p.ws_lse[row] = lse0;
-      }
-      if constexpr (ROWS16) {
-        if (row1) {
-          float* w = p.ws_o + (row + 8) * D;
+      for (int nh = 0; nh < NH; ++nh)
 #pragma unroll
-          for (int n = 0; n < NTILES; ++n) {
-            w[col_of(n, 0)] = o[n][2] * inv1;
-            w[col_of(n, 1)] = o[n][3] * inv1;
+        for (int t = 0; t < MT; ++t)
+#pragma unroll
+          for (int e = 0; e < 4; ++e) {
+            const int k = 2 * nh + (e & 1);
+            if (hv[k])
+              p.ws_o[(piece_row + static_cast<int64_t>(tsi) * hqv + h * p.group + hl[k]) * D + 16 * t + g + 8 * (e >> 1)] =
+                  o[nh][t][e] * inv[k];
           }
-          if (jq == 0) p.ws_lse[row + 8] = lse1;
-        }
+      if (g == 0) {
+#pragma unroll
+        for (int k = 0; k < HPT; ++k)
+          if (hv[k]) p.ws_lse[piece_row + static_cast<int64_t>(tsi) * hqv + h * p.group + hl[k]] = lse[k];
       }
     }
     if (final_written && !full_req && threadIdx.x == 0) {
