@@ -65,11 +65,21 @@ struct DecodeParams {
 // -DB200ATTN_DEC_TRACE (make trace -> libb200attn_trace.so): per-CTA timeline of one launch.  Slot 0 / 15 hold
 // %globaltimer (ns, comparable across SMs) at entry / exit, the others clock64 of the CTA's own SM.
 #ifdef B200ATTN_DEC_TRACE
-constexpr int kTraceSlots = 16;
+constexpr int kTraceSlots = 24;
 enum {
   TR_GT_ENTRY = 0, TR_ENTRY, TR_BARS_READY, TR_P_WALK, TR_P_IDS, TR_P_FIRST_ISSUE, TR_P_LAST_ISSUE, TR_C_Q,
-  TR_C_FIRST_FULL, TR_C_FIRST_DONE, TR_C_LAST_DONE, TR_C_EPILOGUE, TR_C_MERGED, TR_C_EXIT, TR_COUNTS, TR_GT_EXIT
+  TR_C_FIRST_FULL, TR_C_FIRST_DONE, TR_C_LAST_DONE, TR_C_EPILOGUE, TR_C_MERGED, TR_C_EXIT, TR_COUNTS, TR_GT_EXIT,
+  // one steady-state chunk (the 65th this CTA consumes) of consumer warp 0, each stamp taken after an instruction
+  // that needs the phase's result: wait begins, stage full, S^T done, softmax done (P^T in registers), O^T updated
+  TR_K_WAIT, TR_K_FULL, TR_K_QK, TR_K_SOFTMAX, TR_K_PV, TR_K_END, TR_K_WAIT2
 };
+// clock64 read after `val` is available (the compare stalls on the producing instruction's scoreboard; warps issue in order)
+__device__ __forceinline__ unsigned long long clock_after(float val) {
+  unsigned long long t;
+  asm volatile("{\n\t.reg .pred p;\n\tsetp.eq.f32 p, %1, 0f7fc00001;\n\tmov.u64 %0, %%clock64;\n\t@p add.u64 %0, %0, 1;\n\t}" : "=l"(t) : "f"(val));
+  return t;
+}
+#define B200_TR_DEP(slot, val) do { if (p.trace && threadIdx.x == 0 && tr_chunks == 64) p.trace[blockIdx.x * kTraceSlots + (slot)] = clock_after(val); } while (0)
 __device__ __forceinline__ unsigned long long globaltimer_ns() {
   unsigned long long t;
   asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t));
@@ -82,6 +92,7 @@ __device__ __forceinline__ unsigned long long globaltimer_ns() {
 #define B200_TR(slot) do { } while (0)
 #define B200_TR_ONCE(slot, flag) do { } while (0)
 #define B200_TR_GT(slot) do { } while (0)
+#define B200_TR_DEP(slot, val) do { } while (0)
 #endif
 
 constexpr float kLog2e = 1.4426950408889634f;
@@ -182,7 +193,10 @@ __global__ void __launch_bounds__(kThreads, 1) decode_kernel(const DecodeParams 
   extern __shared__ __align__(128) uint8_t smem[];
   const int cta = blockIdx.x;
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const uint32_t bar_full = smem_u32(smem);
+  uint32_t bar_full = smem_u32(smem);
+  // kept in a register: left to the compiler the address was rebuilt from %cluster_ctaid (an S2R of tens of
+  // clocks) in front of every barrier wait of the consumers' chunk loop
+  asm volatile("" : "+r"(bar_full));
   const uint32_t bar_empty = bar_full + kMaxStages * 8;
   const uint32_t stage0 = bar_full + kBarrierBytes;
   volatile int32_t* rq = reinterpret_cast<volatile int32_t*>(smem + kRangeRingOff);   // ring of range ids
@@ -605,10 +619,11 @@ __global__ void __launch_bounds__(kThreads, 1) decode_kernel(const DecodeParams 
       for (int t = 0; t < MT; ++t)
 #pragma unroll
         for (int e = 0; e < 4; ++e) o[nh][t][e] = 0.f;
-    float m[HPT], l[HPT];
+    float m[HPT], mc[HPT], l[HPT];   // reference (a running maximum, in logit units), the same times c, row sum
 #pragma unroll
     for (int k = 0; k < HPT; ++k) {
       m[k] = -CUDART_INF_F;
+      mc[k] = 0.f;
       l[k] = 0.f;
     }
 
@@ -642,21 +657,31 @@ __global__ void __launch_bounds__(kThreads, 1) decode_kernel(const DecodeParams 
         asm volatile("ld.acquire.gpu.global.s32 %0, [%1];" : "=r"(arrived) : "l"(pv.vreq_arrived + vreq) : "memory");
         early_ok = arrived == v_pieces - 1;
       }
+      B200_TR_DEP(TR_K_WAIT, 0.f);
+#ifdef B200ATTN_DEC_TRACE
+      if (p.trace && threadIdx.x == 0 && tr_chunks == 65) p.trace[blockIdx.x * kTraceSlots + TR_K_WAIT2] = clock64();
+#endif
       mbar_wait(bar_full + stage * 8, phase);
       if (threadIdx.x == 0) B200_TR_ONCE(TR_C_FIRST_FULL, tr_b);
+      B200_TR_DEP(TR_K_FULL, 0.f);
       const uint32_t sbase = stage0 + stage * p.stage_bytes;
 
       // ---- S^T = K . Q^T : 16 tokens x 8 (16) heads ----
-      float s[NH][4];
+      // (two accumulators per tile, even / odd k steps: the dependent HMMA chain is half as long)
+      float s[NH][4], sb[NH][4];
 #pragma unroll
-      for (int nh = 0; nh < NH; ++nh) s[nh][0] = s[nh][1] = s[nh][2] = s[nh][3] = 0.f;
+      for (int nh = 0; nh < NH; ++nh) {
+        s[nh][0] = s[nh][1] = s[nh][2] = s[nh][3] = 0.f;
+        sb[nh][0] = sb[nh][1] = sb[nh][2] = sb[nh][3] = 0.f;
+      }
       if constexpr (!FP8) {
 #pragma unroll
         for (int ks = 0; ks < MT; ++ks) {
           uint32_t a[4];
           ldsm_x4(sbase + k_base + ((32u * ks) ^ k_x), a);
 #pragma unroll
-          for (int nh = 0; nh < NH; ++nh) mma16816<HALF>(s[nh], a[0], a[1], a[2], a[3], qb[nh][ks][0], qb[nh][ks][1]);
+          for (int nh = 0; nh < NH; ++nh)
+            mma16816<HALF>((ks & 1) ? sb[nh] : s[nh], a[0], a[1], a[2], a[3], qb[nh][ks][0], qb[nh][ks][1]);
         }
       } else {
 #pragma unroll
@@ -671,10 +696,15 @@ __global__ void __launch_bounds__(kThreads, 1) decode_kernel(const DecodeParams 
           e4m3x4_to_f16x2x2(kf[3], a[1], a[3]);
 #pragma unroll
           for (int nh = 0; nh < NH; ++nh)
-            mma16816<true>(s[nh], a[0], a[1], a[2], a[3], qb[nh][2 * u2 + 1][0], qb[nh][2 * u2 + 1][1]);
+            mma16816<true>(sb[nh], a[0], a[1], a[2], a[3], qb[nh][2 * u2 + 1][0], qb[nh][2 * u2 + 1][1]);
         }
       }
+#pragma unroll
+      for (int nh = 0; nh < NH; ++nh)
+#pragma unroll
+        for (int e = 0; e < 4; ++e) s[nh][e] += sb[nh][e];
 
+      B200_TR_DEP(TR_K_QK, s[0][0]);
       // ---- logit cap, tail mask ----
       if (cap) {
 #pragma unroll
@@ -692,36 +722,50 @@ __global__ void __launch_bounds__(kThreads, 1) decode_kernel(const DecodeParams 
         }
       }
 
-      // ---- online softmax over the token dimension: a head's 16 logits sit in 8 lanes (g) x 2 elements ----
-      float corr[HPT], pr[NH][4];
-      bool resc = false;
+      // ---- online softmax over the token dimension, with a lazily updated reference ----
+      // P = exp2(s c - ref) against the reference the piece already has; the true running maximum (three
+      // dependent shuffle rounds per head, then the rescale factors -- 400 of the 1250 clocks a warp spent on a
+      // chunk, tools/trace_decode.py) is only taken on a piece's first chunk and when some logit rises more than
+      // 2^8 above the reference (P <= 256 fits f16 / bf16 with the same relative precision; l and O are fp32).
+      // Which path ran does not change the mathematics: o = sum P v / sum P and lse = ref + log sum P for any ref.
+      float pr[NH][4];
+      bool far = lc == lc0;
+#pragma unroll
+      for (int nh = 0; nh < NH; ++nh)
+#pragma unroll
+        for (int e = 0; e < 4; ++e) {
+          pr[nh][e] = fmaf(s[nh][e], c, -mc[2 * nh + (e & 1)]);
+          far |= pr[nh][e] > 8.f;
+        }
+      if (__any_sync(0xffffffffu, far)) {
+#pragma unroll
+        for (int k = 0; k < HPT; ++k) {
+          const int nh = k >> 1, e = k & 1;
+          float mx = fmaxf(s[nh][e], s[nh][e + 2]);
+          mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, 4));
+          mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, 8));
+          mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, 16));
+          const float mn = fmaxf(m[k], mx);
+          const float mr = mn == -CUDART_INF_F ? 0.f : mn;
+          const float corr = fast_exp2((m[k] - mr) * c);
+          m[k] = mn;
+          mc[k] = mr * c;
+          l[k] *= corr;
+          pr[nh][e] = fmaf(s[nh][e], c, -mc[k]);
+          pr[nh][e + 2] = fmaf(s[nh][e + 2], c, -mc[k]);
+#pragma unroll
+          for (int t = 0; t < MT; ++t) {
+            o[nh][t][e] *= corr;
+            o[nh][t][e + 2] *= corr;
+          }
+        }
+      }
 #pragma unroll
       for (int k = 0; k < HPT; ++k) {
         const int nh = k >> 1, e = k & 1;
-        float mx = fmaxf(s[nh][e], s[nh][e + 2]);
-        mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, 4));
-        mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, 8));
-        mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, 16));
-        const float mn = fmaxf(m[k], mx);
-        const float mr = mn == -CUDART_INF_F ? 0.f : mn;
-        corr[k] = fast_exp2((m[k] - mr) * c);
-        m[k] = mn;
-        const float mc = mr * c;
-        pr[nh][e] = fast_exp2(fmaf(s[nh][e], c, -mc));
-        pr[nh][e + 2] = fast_exp2(fmaf(s[nh][e + 2], c, -mc));
-        l[k] = fmaf(l[k], corr[k], pr[nh][e] + pr[nh][e + 2]);
-        resc |= corr[k] != 1.f;
-      }
-      if (__any_sync(0xffffffffu, resc)) {
-#pragma unroll
-        for (int nh = 0; nh < NH; ++nh)
-#pragma unroll
-          for (int t = 0; t < MT; ++t) {
-            o[nh][t][0] *= corr[2 * nh];
-            o[nh][t][1] *= corr[2 * nh + 1];
-            o[nh][t][2] *= corr[2 * nh];
-            o[nh][t][3] *= corr[2 * nh + 1];
-          }
+        pr[nh][e] = fast_exp2(pr[nh][e]);
+        pr[nh][e + 2] = fast_exp2(pr[nh][e + 2]);
+        l[k] += pr[nh][e] + pr[nh][e + 2];
       }
 
       // ---- P^T (B operand): pack [token row][heads 2j, 2j+1], transpose 8x8 -> [head g][k slots 2j, 2j+1] ----
@@ -731,6 +775,7 @@ __global__ void __launch_bounds__(kThreads, 1) decode_kernel(const DecodeParams 
         pb[nh][0] = movmatrix_trans(pack2<HALF>(pr[nh][0], pr[nh][1]));
         pb[nh][1] = movmatrix_trans(pack2<HALF>(pr[nh][2], pr[nh][3]));
       }
+      B200_TR_DEP(TR_K_SOFTMAX, __uint_as_float(pb[0][1]));
       // V fragments of masked tail tokens are zeroed: the smem rows behind them hold stale bytes of another
       // request (0 * inf would poison this one).  Only the tail chunk pays the masks.
       uint32_t vm_lo = 0xffffffffu, vm_hi = 0xffffffffu;
@@ -771,8 +816,10 @@ __global__ void __launch_bounds__(kThreads, 1) decode_kernel(const DecodeParams 
         }
       };
       if (tail) pv_mma(std::true_type{}); else pv_mma(std::false_type{});
+      B200_TR_DEP(TR_K_PV, o[0][MT - 1][0]);
       __syncwarp();
       if (lane == 0) mbar_arrive(bar_empty + stage * 8);
+      B200_TR_DEP(TR_K_END, 0.f);
 #ifdef B200ATTN_DEC_TRACE
       if (threadIdx.x == 0) { B200_TR_ONCE(TR_C_FIRST_DONE, tr_c); B200_TR(TR_C_LAST_DONE); ++tr_chunks; }
 #endif

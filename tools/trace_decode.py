@@ -79,7 +79,7 @@ def main():
         torch.ops.b200attn.decode(*dargs)
     torch.cuda.synchronize()
     n_sm = torch.cuda.get_device_properties(dev).multi_processor_count
-    trace = torch.zeros((n_sm, 16), dtype=torch.int64, device=dev)
+    trace = torch.zeros((n_sm, 24), dtype=torch.int64, device=dev)
     flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     if args.flush:
@@ -144,6 +144,13 @@ def main():
         "idle_after_exit_us": st((col["gt_exit"].max() - col["gt_exit"]) / 1e3),
         "merging_ctas": int((col["c_merged"] != 0).sum()),
     }
+    # one steady-state chunk of consumer warp 0 (slots 16-20), CTAs that consumed more than 64 chunks
+    tk = t[t[:, 20] != 0]
+    if len(tk):
+        rep["chunk65_clk"] = {
+            "wait_full": st(tk[:, 17] - tk[:, 16]), "qk": st(tk[:, 18] - tk[:, 17]), "softmax": st(tk[:, 19] - tk[:, 18]),
+            "pv": st(tk[:, 20] - tk[:, 19]), "arrive": st(tk[:, 21] - tk[:, 20]), "to_next_wait": st(tk[:, 22] - tk[:, 21]),
+            "total": st(tk[:, 22] - tk[:, 16])}
     if args.per_cta:
         rep["per_cta"] = per_cta
         if len(per_cta) > 1:   # is a slow SM always slow?  rank correlation of clk / chunk by SM id between launches
