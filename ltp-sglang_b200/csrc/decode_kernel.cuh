@@ -79,7 +79,7 @@ __device__ __forceinline__ unsigned long long clock_after(float val) {
   asm volatile("{\n\t.reg .pred p;\n\tsetp.eq.f32 p, %1, 0f7fc00001;\n\tmov.u64 %0, %%clock64;\n\t@p add.u64 %0, %0, 1;\n\t}" : "=l"(t) : "f"(val));
   return t;
 }
-#define B200_TR_DEP(slot, val) do { if (p.trace && threadIdx.x == 0 && tr_chunks == 64) p.trace[blockIdx.x * kTraceSlots + (slot)] = clock_after(val); } while (0)
+#define B200_TR_DEP(slot, val) do { if (p.trace && tid == 0 && tr_chunks == 64) p.trace[blockIdx.x * kTraceSlots + (slot)] = clock_after(val); } while (0)
 __device__ __forceinline__ unsigned long long globaltimer_ns() {
   unsigned long long t;
   asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t));
@@ -192,7 +192,11 @@ __global__ void __launch_bounds__(kThreads, 1) decode_kernel(const DecodeParams 
 
   extern __shared__ __align__(128) uint8_t smem[];
   const int cta = blockIdx.x;
-  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  // %tid.x read once into a register the compiler cannot rematerialise: every `tid == 0` test in the chunk
+  // loops was otherwise a fresh S2R (tens of clocks each, on the consumers' critical path)
+  int tid;
+  asm volatile("mov.u32 %0, %%tid.x;" : "=r"(tid));
+  const int warp = tid >> 5, lane = tid & 31;
   uint32_t bar_full = smem_u32(smem);
   // kept in a register: left to the compiler the address was rebuilt from %cluster_ctaid (an S2R of tens of
   // clocks) in front of every barrier wait of the consumers' chunk loop
@@ -203,8 +207,8 @@ __global__ void __launch_bounds__(kThreads, 1) decode_kernel(const DecodeParams 
   volatile int32_t* merge_flag = reinterpret_cast<volatile int32_t*>(smem + kMergeFlagOff);
 #ifdef B200ATTN_DEC_TRACE
   bool tr_a = false, tr_b = false, tr_c = false;
-  unsigned long long tr_chunks = 0, tr_pieces = 0;
-  if (threadIdx.x == 0) {
+  unsigned long long tr_chunks = 0, tr_pieces = 0, tr_last = 0;
+  if (tid == 0) {
     B200_TR_GT(TR_GT_ENTRY);
     B200_TR(TR_ENTRY);
     unsigned smid;
@@ -215,7 +219,7 @@ __global__ void __launch_bounds__(kThreads, 1) decode_kernel(const DecodeParams 
   // Everything that needs no global data first: under programmatic dependent launch this part (CTA launch,
   // barrier init) overlaps the tail of the kernel in front (kv_store / RoPE + store), which has released its
   // dependents at its start.
-  if (threadIdx.x == 0) {
+  if (tid == 0) {
     for (int s = 0; s < p.stages; ++s) {
       mbar_init(bar_full + s * 8, p.cp_async ? kProducerWarps * 32 : kProducerWarps);
       mbar_init(bar_empty + s * 8, kConsumerWarps);
@@ -255,7 +259,7 @@ __global__ void __launch_bounds__(kThreads, 1) decode_kernel(const DecodeParams 
   }
   // the rate this CTA recorded in earlier launches (updated at exit; fetched here so that the exit is a plain store)
   CtaStat st_prev = {0.f, 0u};
-  if (threadIdx.x == 0 && cta < kMaxCtas) st_prev = pv.cta_stat[cta];
+  if (tid == 0 && cta < kMaxCtas) st_prev = pv.cta_stat[cta];
   if (cta >= H.grid) return;
   // A plan built for another batch, head geometry or chunk size would send the walk through garbage ranges:
   // do nothing instead (o is left untouched; b200attn_decode documents that plan and call must agree).
@@ -275,9 +279,9 @@ __global__ void __launch_bounds__(kThreads, 1) decode_kernel(const DecodeParams 
     return k < static_cast<unsigned>(n_dyn) ? n_static + static_cast<int>(k) : R;
   };
 
-  if (threadIdx.x == 0) rq[0] = cta < n_static ? cta : take_ticket();
+  if (tid == 0) rq[0] = cta < n_static ? cta : take_ticket();
   __syncthreads();
-  if (threadIdx.x == 0) B200_TR(TR_BARS_READY);
+  if (tid == 0) B200_TR(TR_BARS_READY);
 
   const int T = p.chunk_tokens;
   const uint32_t v_off = T * p.row_stride;  // V rows follow the K rows of a stage
@@ -628,7 +632,7 @@ __global__ void __launch_bounds__(kThreads, 1) decode_kernel(const DecodeParams 
     }
 
 #ifdef B200ATTN_DEC_TRACE
-    if (threadIdx.x == 0) { B200_TR_ONCE(TR_C_Q, tr_a); ++tr_pieces; }
+    if (tid == 0) { B200_TR_ONCE(TR_C_Q, tr_a); ++tr_pieces; }
 #endif
     for (int lc = lc0; lc < lc1; ++lc) {
       if (lc == lc_pf && try_early) {
@@ -649,7 +653,7 @@ __global__ void __launch_bounds__(kThreads, 1) decode_kernel(const DecodeParams 
           }
         }
       }
-      if (lc == lc1 - 1 && try_early && threadIdx.x == 0) {   // (warp-uniform tests first: two instructions per chunk)
+      if (lc == lc1 - 1 && try_early && tid == 0) {   // (warp-uniform tests first: two instructions per chunk)
         // Last-arriver shortcut, decided one chunk early (the load's round trip hides behind the chunk): if
         // every other piece of the request is already in the workspace, this CTA is the one that merges, so
         // its own partial never needs to go through global memory (see the epilogue).
@@ -659,10 +663,10 @@ __global__ void __launch_bounds__(kThreads, 1) decode_kernel(const DecodeParams 
       }
       B200_TR_DEP(TR_K_WAIT, 0.f);
 #ifdef B200ATTN_DEC_TRACE
-      if (p.trace && threadIdx.x == 0 && tr_chunks == 65) p.trace[blockIdx.x * kTraceSlots + TR_K_WAIT2] = clock64();
+      if (p.trace && tid == 0 && tr_chunks == 65) p.trace[blockIdx.x * kTraceSlots + TR_K_WAIT2] = clock64();
 #endif
       mbar_wait(bar_full + stage * 8, phase);
-      if (threadIdx.x == 0) B200_TR_ONCE(TR_C_FIRST_FULL, tr_b);
+      if (tid == 0) B200_TR_ONCE(TR_C_FIRST_FULL, tr_b);
       B200_TR_DEP(TR_K_FULL, 0.f);
       const uint32_t sbase = stage0 + stage * p.stage_bytes;
 
@@ -821,7 +825,9 @@ __global__ void __launch_bounds__(kThreads, 1) decode_kernel(const DecodeParams 
       if (lane == 0) mbar_arrive(bar_empty + stage * 8);
       B200_TR_DEP(TR_K_END, 0.f);
 #ifdef B200ATTN_DEC_TRACE
-      if (threadIdx.x == 0) { B200_TR_ONCE(TR_C_FIRST_DONE, tr_c); B200_TR(TR_C_LAST_DONE); ++tr_chunks; }
+      // (the last chunk's stamp stays in a register until the piece ends: a global store per chunk cost the traced
+      // kernel 600 clocks per chunk on the consumer-bound shapes)
+      if (tid == 0) { B200_TR_ONCE(TR_C_FIRST_DONE, tr_c); tr_last = clock64(); ++tr_chunks; }
 #endif
       if (++stage == p.stages) {
         stage = 0;
@@ -829,6 +835,9 @@ __global__ void __launch_bounds__(kThreads, 1) decode_kernel(const DecodeParams 
       }
     }
 
+#ifdef B200ATTN_DEC_TRACE
+    if (tid == 0 && p.trace) p.trace[blockIdx.x * kTraceSlots + TR_C_LAST_DONE] = tr_last;
+#endif
     // ---- epilogue: normalise, write final o or a partial ----
     // This thread holds, for heads hl[k], the head-dim rows d = 16 t + g + 8 (e >> 1): element (nh, t, e) belongs to
     // head k = 2 nh + (e & 1).  A head's row sum is spread over the 8 token lanes (g).
@@ -852,7 +861,7 @@ __global__ void __launch_bounds__(kThreads, 1) decode_kernel(const DecodeParams 
     // Same values, same order, same arithmetic as merge_heads4, so which path ran never shows in the result.
     const bool can_fast = NH == 1 && !full_req && p.fuse_merge && (use_xch || p.ts == 1);
     volatile int32_t* flags = merge_flag + (npiece & 1) * 2;
-    if (can_fast && threadIdx.x == 0) flags[0] = early_ok;
+    if (can_fast && tid == 0) flags[0] = early_ok;
     if (can_fast && !use_xch) named_bar_sync(2, kConsumerWarps * 32);   // (the slice exchange has its own barrier)
     // The merge's loads go out in ONE batch -- the other pieces' lse and the rows of the first other piece (the
     // only other piece in all but the rarest plans) -- before anything waits on them.
@@ -1060,7 +1069,7 @@ __global__ void __launch_bounds__(kThreads, 1) decode_kernel(const DecodeParams 
           if (hv[k]) p.ws_lse[piece_row + static_cast<int64_t>(tsi) * hqv + h * p.group + hl[k]] = lse[k];
       }
     }
-    if (final_written && !full_req && threadIdx.x == 0) {
+    if (final_written && !full_req && tid == 0) {
       pv.vreq_arrived[vreq] = 0;   // shortcut taken: the counter is ready for the next layer's launch
       B200_TR(TR_C_MERGED);
     }
@@ -1070,7 +1079,7 @@ __global__ void __launch_bounds__(kThreads, 1) decode_kernel(const DecodeParams 
       // producers keep streaming the next piece's chunks meanwhile.
       __threadfence();
       named_bar_sync(2, kConsumerWarps * 32);
-      if (threadIdx.x == 0) {
+      if (tid == 0) {
         const int arrived = atomicAdd(&pv.vreq_arrived[vreq], 1) + 1;
         const int last = arrived == v_pieces;
         if (last) pv.vreq_arrived[vreq] = 0;  // ready for the next layer's launch
@@ -1078,7 +1087,7 @@ __global__ void __launch_bounds__(kThreads, 1) decode_kernel(const DecodeParams 
       }
       named_bar_sync(2, kConsumerWarps * 32);
       if (flags[1]) {
-        if (threadIdx.x == 0) B200_TR(TR_C_MERGED);
+        if (tid == 0) B200_TR(TR_C_MERGED);
         __threadfence();
         const int nsl = use_xch ? 1 : p.ts;            // partial rows per piece
         const int np = v_pieces * nsl;
@@ -1106,14 +1115,14 @@ __global__ void __launch_bounds__(kThreads, 1) decode_kernel(const DecodeParams 
         }
       }
     }
-    if (threadIdx.x == 0) B200_TR(TR_C_EPILOGUE);
+    if (tid == 0) B200_TR(TR_C_EPILOGUE);
     if (rn == 0) n_consumed += lc1 - lc0;
   }
   if (rn == 0) clk_last = clock64();
   ++rn;
   rg = rq[rn & (kRangeRing - 1)];
   }
-  if (threadIdx.x == 0 && n_consumed >= 16 && cta < kMaxCtas) {
+  if (tid == 0 && n_consumed >= 16 && cta < kMaxCtas) {
     const float r = static_cast<float>(clk_last - clk_first) / static_cast<float>(n_consumed);
     CtaStat st = st_prev;
     const bool ok = st.tag == (kStatTag ^ static_cast<uint32_t>(cta)) && st.clk_per_chunk > 0.f;
@@ -1122,7 +1131,7 @@ __global__ void __launch_bounds__(kThreads, 1) decode_kernel(const DecodeParams 
     pv.cta_stat[cta] = st;
   }
 #ifdef B200ATTN_DEC_TRACE
-  if (threadIdx.x == 0 && p.trace) {
+  if (tid == 0 && p.trace) {
     B200_TR(TR_C_EXIT);
     p.trace[blockIdx.x * kTraceSlots + TR_COUNTS] = tr_chunks | (tr_pieces << 32);
     B200_TR_GT(TR_GT_EXIT);
