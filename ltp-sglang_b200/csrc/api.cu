@@ -29,15 +29,6 @@ int sm_count() {
   return n;
 }
 
-template <>
-cudaError_t launch_decode<__nv_bfloat16, false>(const DecodeParams&, int, bool, int, int, cudaStream_t);
-template <>
-cudaError_t launch_decode<__nv_bfloat16, true>(const DecodeParams&, int, bool, int, int, cudaStream_t);
-template <>
-cudaError_t launch_decode<__half, false>(const DecodeParams&, int, bool, int, int, cudaStream_t);
-template <>
-cudaError_t launch_decode<__half, true>(const DecodeParams&, int, bool, int, int, cudaStream_t);
-
 }  // namespace b200attn
 
 using namespace b200attn;
@@ -167,6 +158,7 @@ extern "C" __attribute__((visibility("default"))) int b200attn_decode(const b200
   p.fuse_merge = a->phases == 0;
   p.cp_async = g.cp_async;
   p.swizzle = g.swizzle;
+  p.kv_split = g.kv_split;
   p.xch_off = a->phases == 0 ? g.xch_off : 0;  // K2 + K3 as separate launches keep every slice in the workspace
   p.unit_shift = 0;
   while ((16 << p.unit_shift) < g.row_bytes) ++p.unit_shift;

@@ -55,6 +55,8 @@ struct Geometry {
   int swizzle;       // cp.async path: unpadded rows, 16-byte unit u of row r at u ^ (r & 7)
   int xch_off;       // byte offset of the slice-exchange area (whole requests merge their ts token slices
                      // inside the CTA), 0 = none
+  int kv_split;      // 1: a pipeline slot holds the K rows OR the V rows of a chunk (slots alternate K, V, K, ...):
+                     // head_dim 256 on a 16-bit pool, where a K + V stage is 129 KB and only one would fit
 };
 
 // Tuning aids, read once: B200ATTN_CPASYNC_MAX_ROW (default and maximum 512: wider rows go as bulk copies),
@@ -108,10 +110,11 @@ __host__ __device__ inline int elem_bytes(int dtype) { return dtype == B200ATTN_
 constexpr int kFewVreqs = 64;
 inline bool make_geometry(int hq, int hkv, int d, int kv_dtype, Geometry* g, int batch = 0) {
   if (hq <= 0 || hkv <= 0 || hq % hkv != 0) return false;
-  if (d != 64 && d != 128) return false;  // instantiated head dims
+  if (d != 64 && d != 80 && d != 96 && d != 128 && d != 256) return false;  // instantiated head dims
   int group = hq / hkv;
   if (group > 16) return false;
   int e = elem_bytes(kv_dtype);
+  if (e == 1 && d != 64 && d != 128 && d != 256) return false;  // fp8 pools: the instantiated head dims
   int hc = 8;
   while (hc > 1 && (hkv % hc != 0 || hc * d * e > kMaxRowBytes)) hc >>= 1;
   if (hc * d * e > kMaxRowBytes) return false;
@@ -125,11 +128,18 @@ inline bool make_geometry(int hq, int hkv, int d, int kv_dtype, Geometry* g, int
   g->group = group;
   g->chunk_tokens = 16 * g->ts;
   g->row_bytes = hc * d * e;
-  g->cp_async = g->row_bytes <= cp_async_max_row();
+  // (the cp.async issue loop addresses 16-byte units by shifts: power-of-two rows only; 96- / 80-wide heads go as bulk copies)
+  g->cp_async = g->row_bytes <= cp_async_max_row() && (g->row_bytes & (g->row_bytes - 1)) == 0;
   g->swizzle = g->cp_async && (d * e) % 128 == 0 && !no_swizzle();  // heads start on 128-byte lines
   g->row_stride = g->swizzle ? g->row_bytes : g->row_bytes + kRowPad;
   g->stage_bytes = 2 * g->chunk_tokens * g->row_stride;
+  g->kv_split = 0;
   int stages = (kMaxSmem - kBarrierBytes) / g->stage_bytes;
+  if (stages < 2) {   // K and V of a chunk in separate slots
+    g->kv_split = 1;
+    g->stage_bytes = g->chunk_tokens * g->row_stride;
+    stages = (kMaxSmem - kBarrierBytes) / g->stage_bytes;
+  }
   if (stages > kMaxStages) stages = kMaxStages;
   if (stages < 2) return false;
   g->xch_off = 0;

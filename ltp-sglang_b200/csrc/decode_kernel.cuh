@@ -53,6 +53,7 @@ struct DecodeParams {
   int32_t unit_shift;            // log2(row_bytes / 16)
   int32_t swizzle;               // 1: stage rows unpadded, 16-byte unit u of row r at u ^ (r & 7) (cp.async path)
   int32_t xch_off;               // smem offset of the slice-exchange area (0 = none): whole requests merge in the CTA
+  int32_t kv_split;              // 1: pipeline slots alternate K rows / V rows of a chunk (stage_bytes = one tensor)
   float scale_log2;              // sm_scale * k_scale * log2(e)
   float sm_scale_k;              // sm_scale * k_scale
   float logit_cap;
@@ -221,7 +222,9 @@ __global__ void __launch_bounds__(kThreads, 1) decode_kernel(const DecodeParams 
   // dependents at its start.
   if (tid == 0) {
     for (int s = 0; s < p.stages; ++s) {
-      mbar_init(bar_full + s * 8, p.cp_async ? kProducerWarps * 32 : kProducerWarps);
+      // arrivals on a slot's `full`: every producer thread (cp.async path) or warp (bulk path) that fills it --
+      // all four producer warps, or the two of one tensor when slots alternate K / V
+      mbar_init(bar_full + s * 8, (p.cp_async ? kProducerWarps * 32 : kProducerWarps) >> p.kv_split);
       mbar_init(bar_empty + s * 8, kConsumerWarps);
     }
     fence_barrier_init();
@@ -284,7 +287,8 @@ __global__ void __launch_bounds__(kThreads, 1) decode_kernel(const DecodeParams 
   if (tid == 0) B200_TR(TR_BARS_READY);
 
   const int T = p.chunk_tokens;
-  const uint32_t v_off = T * p.row_stride;  // V rows follow the K rows of a stage
+  const uint32_t v_off = p.kv_split ? 0u : T * p.row_stride;  // V rows follow the K rows of a stage (or own the next slot)
+  const int stage_step = 1 + p.kv_split;                      // producers: slots per chunk
   int b, hg, lc0, lc1, nchunks, vreq, S;
   int64_t row_off;
   int stage = 0;
@@ -302,6 +306,7 @@ __global__ void __launch_bounds__(kThreads, 1) decode_kernel(const DecodeParams 
     const int pw = warp - kConsumerWarps;
     const int which = pw & 1;
     const int par = pw >> 1;
+    if (p.kv_split && which) stage = 1;   // K rows of chunk n in slot 2n, V rows in slot 2n + 1 (mod stages)
     const uint8_t* pool = which ? p.v_pool : p.k_pool;
     const int64_t slot_bytes = which ? p.v_slot_bytes : p.k_slot_bytes;
     if (p.cp_async) {
@@ -404,8 +409,9 @@ __global__ void __launch_bounds__(kThreads, 1) decode_kernel(const DecodeParams 
           }
           cp_async_mbar_arrive_noinc(full);
           if (pw == 0 && lane == 0) { B200_TR_ONCE(TR_P_FIRST_ISSUE, tr_b); B200_TR(TR_P_LAST_ISSUE); }
-          if (++stage == p.stages) {
-            stage = 0;
+          stage += stage_step;
+          if (stage >= p.stages) {
+            stage -= p.stages;
             phase ^= 1;
           }
         }
@@ -469,8 +475,9 @@ __global__ void __launch_bounds__(kThreads, 1) decode_kernel(const DecodeParams 
                      p.row_bytes, full);
         }
         if (pw == 0 && lane == 0) { B200_TR_ONCE(TR_P_FIRST_ISSUE, tr_b); B200_TR(TR_P_LAST_ISSUE); }
-        if (++stage == p.stages) {
-          stage = 0;
+        stage += stage_step;
+        if (stage >= p.stages) {
+          stage -= p.stages;
           phase ^= 1;
         }
       }
@@ -788,6 +795,20 @@ __global__ void __launch_bounds__(kThreads, 1) decode_kernel(const DecodeParams 
         vm_hi = (t0 + vt2 < S ? 0x0000ffffu : 0u) | (t0 + vt3 < S ? 0xffff0000u : 0u);
       }
 
+      // K and V in separate slots: the K slot is done with (its fragments are in registers), the V rows of the
+      // chunk are in the next slot
+      uint32_t sbase_v = sbase;
+      if (p.kv_split) {
+        __syncwarp();
+        if (lane == 0) mbar_arrive(bar_empty + stage * 8);
+        if (++stage == p.stages) {
+          stage = 0;
+          phase ^= 1;
+        }
+        mbar_wait(bar_full + stage * 8, phase);
+        sbase_v = stage0 + stage * p.stage_bytes;
+      }
+
       // ---- O^T += V^T . P^T ----
       auto pv_mma = [&](auto tail_tag) {
         constexpr bool TAIL = decltype(tail_tag)::value;
@@ -796,7 +817,7 @@ __global__ void __launch_bounds__(kThreads, 1) decode_kernel(const DecodeParams 
 #pragma unroll
           for (int t = 0; t < MT; ++t) {
             uint32_t a[4];
-            ldsm_x4_trans(sbase + v_base + ((32u * t) ^ v_x), a);
+            ldsm_x4_trans(sbase_v + v_base + ((32u * t) ^ v_x), a);
 #pragma unroll
             for (int nh = 0; nh < NH; ++nh)
               mma16816<HALF>(o[nh][t], a[0] & mlo, a[1] & mlo, a[2] & mhi, a[3] & mhi, pb[nh][0], pb[nh][1]);
@@ -805,7 +826,7 @@ __global__ void __launch_bounds__(kThreads, 1) decode_kernel(const DecodeParams 
 #pragma unroll
           for (int t2 = 0; t2 < MT / 2; ++t2) {
             uint32_t vf[4], a[4];
-            ldsm8_x2_trans(sbase + v_base + ((32u * t2) ^ v_x), vf);
+            ldsm8_x2_trans(sbase_v + v_base + ((32u * t2) ^ v_x), vf);
             e4m3x4_to_f16x2x2(vf[0], a[0], a[2]);
             e4m3x4_to_f16x2x2(vf[1], a[1], a[3]);
 #pragma unroll
@@ -962,14 +983,14 @@ __global__ void __launch_bounds__(kThreads, 1) decode_kernel(const DecodeParams 
       int rowh[2];
 #pragma unroll
       for (int k = 0; k < 2; ++k) rowh[k] = h * p.group + (hv[k] ? hl[k] : 0);
-      // this warp finishes tiles tsi, tsi + ts, ...: at most MT / 2 of them (ts >= 2)
-      float x1[MT / 2][4];
+      // this warp finishes tiles tsi, tsi + ts, ...: at most ceil(MT / 2) of them (ts >= 2)
+      float x1[(MT + 1) / 2][4];
       if (fast) {
         float lv[2][4];
 #pragma unroll
         for (int k = 0; k < 2; ++k) merge_lse_load(rowh[k], lse_all[k], lv[k]);
 #pragma unroll
-        for (int tt = 0; tt < MT / 2; ++tt) {
+        for (int tt = 0; tt < (MT + 1) / 2; ++tt) {
           const int t = tsi + tt * p.ts;
 #pragma unroll
           for (int e = 0; e < 4; ++e) {
@@ -982,7 +1003,7 @@ __global__ void __launch_bounds__(kThreads, 1) decode_kernel(const DecodeParams 
         for (int k = 0; k < 2; ++k) merge_weights(k, lv[k]);
       }
 #pragma unroll
-      for (int tt = 0; tt < MT / 2; ++tt) {
+      for (int tt = 0; tt < (MT + 1) / 2; ++tt) {
         const int t = tsi + tt * p.ts;
         if (t < MT) {
 #pragma unroll
@@ -1139,9 +1160,40 @@ __global__ void __launch_bounds__(kThreads, 1) decode_kernel(const DecodeParams 
 #endif
 }
 
+// One translation unit per (q dtype, fp8 KV, head dim) -- decode_inst.cu -- defines launch_decode_d for its
+// triple; launch_decode (api.cu) picks by head dim.  fp8 pools: head dims 64 / 128 / 256; 16-bit: also 80 / 96.
+template <typename QT, bool FP8, int D>
+cudaError_t launch_decode_d(const DecodeParams& p, bool rows16, int grid, int smem, cudaStream_t stream);
+
+#define B200ATTN_DECLARE_LAUNCH_D(QT, FP8, D) \
+  template <>                                 \
+  cudaError_t launch_decode_d<QT, FP8, D>(const DecodeParams& p, bool rows16, int grid, int smem, cudaStream_t stream);
+#define B200ATTN_DECLARE_LAUNCH_QT(QT)       \
+  B200ATTN_DECLARE_LAUNCH_D(QT, false, 64)   \
+  B200ATTN_DECLARE_LAUNCH_D(QT, false, 80)   \
+  B200ATTN_DECLARE_LAUNCH_D(QT, false, 96)   \
+  B200ATTN_DECLARE_LAUNCH_D(QT, false, 128)  \
+  B200ATTN_DECLARE_LAUNCH_D(QT, false, 256)  \
+  B200ATTN_DECLARE_LAUNCH_D(QT, true, 64)    \
+  B200ATTN_DECLARE_LAUNCH_D(QT, true, 128)   \
+  B200ATTN_DECLARE_LAUNCH_D(QT, true, 256)
+B200ATTN_DECLARE_LAUNCH_QT(__nv_bfloat16)
+B200ATTN_DECLARE_LAUNCH_QT(__half)
+
 template <typename QT, bool FP8>
-cudaError_t launch_decode(const DecodeParams& p, int head_dim, bool rows16, int grid, int smem,
-                          cudaStream_t stream);
+inline cudaError_t launch_decode(const DecodeParams& p, int head_dim, bool rows16, int grid, int smem, cudaStream_t stream) {
+  switch (head_dim) {
+    case 64: return launch_decode_d<QT, FP8, 64>(p, rows16, grid, smem, stream);
+    case 128: return launch_decode_d<QT, FP8, 128>(p, rows16, grid, smem, stream);
+    case 256: return launch_decode_d<QT, FP8, 256>(p, rows16, grid, smem, stream);
+    default: break;
+  }
+  if constexpr (!FP8) {
+    if (head_dim == 80) return launch_decode_d<QT, FP8, 80>(p, rows16, grid, smem, stream);
+    if (head_dim == 96) return launch_decode_d<QT, FP8, 96>(p, rows16, grid, smem, stream);
+  }
+  return cudaErrorInvalidValue;
+}
 
 // The dynamic shared-memory limit is a per-function, per-device attribute: set on first use, not per launch.
 inline cudaError_t ensure_smem_attr(const void* fn, int smem, int* cache /* [64] */) {
@@ -1153,29 +1205,25 @@ inline cudaError_t ensure_smem_attr(const void* fn, int smem, int* cache /* [64]
   return e;
 }
 
-#define B200ATTN_DEFINE_LAUNCH(QT, FP8)                                                          \
-  template <>                                                                                    \
-  cudaError_t launch_decode<QT, FP8>(const DecodeParams& p, int head_dim, bool rows16, int grid, \
-                                     int smem, cudaStream_t stream) {                            \
-    static int attr_cache[4][64];                                                                \
-    void (*fn)(const DecodeParams) = nullptr;                                                    \
-    int slot = 0;                                                                                \
-    if (head_dim == 64) { fn = rows16 ? decode_kernel<QT, FP8, 64, true> : decode_kernel<QT, FP8, 64, false>; slot = rows16; }        \
-    else if (head_dim == 128) { fn = rows16 ? decode_kernel<QT, FP8, 128, true> : decode_kernel<QT, FP8, 128, false>; slot = 2 + rows16; } \
-    if (!fn) return cudaErrorInvalidValue;                                                       \
-    cudaError_t e = ensure_smem_attr(reinterpret_cast<const void*>(fn), smem, attr_cache[slot]); \
-    if (e != cudaSuccess) return e;                                                              \
-    cudaLaunchConfig_t cfg = {};                                                                 \
-    cfg.gridDim = dim3(grid);                                                                    \
-    cfg.blockDim = dim3(kThreads);                                                               \
-    cfg.dynamicSmemBytes = smem;                                                                 \
-    cfg.stream = stream;                                                                         \
-    cudaLaunchAttribute at[1];                                                                   \
-    at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;                               \
-    at[0].val.programmaticStreamSerializationAllowed = 1;                                        \
-    cfg.attrs = at;                                                                              \
-    cfg.numAttrs = no_pdl() ? 0 : 1;                                                             \
-    return cudaLaunchKernelEx(&cfg, fn, p);                                                      \
+#define B200ATTN_DEFINE_LAUNCH_D(QT, FP8, D)                                                               \
+  template <>                                                                                              \
+  cudaError_t launch_decode_d<QT, FP8, D>(const DecodeParams& p, bool rows16, int grid, int smem,          \
+                                          cudaStream_t stream) {                                           \
+    static int attr_cache[2][64];                                                                          \
+    void (*fn)(const DecodeParams) = rows16 ? decode_kernel<QT, FP8, D, true> : decode_kernel<QT, FP8, D, false>; \
+    cudaError_t e = ensure_smem_attr(reinterpret_cast<const void*>(fn), smem, attr_cache[rows16]);         \
+    if (e != cudaSuccess) return e;                                                                        \
+    cudaLaunchConfig_t cfg = {};                                                                           \
+    cfg.gridDim = dim3(grid);                                                                              \
+    cfg.blockDim = dim3(kThreads);                                                                         \
+    cfg.dynamicSmemBytes = smem;                                                                           \
+    cfg.stream = stream;                                                                                   \
+    cudaLaunchAttribute at[1];                                                                             \
+    at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;                                         \
+    at[0].val.programmaticStreamSerializationAllowed = 1;                                                  \
+    cfg.attrs = at;                                                                                        \
+    cfg.numAttrs = no_pdl() ? 0 : 1;                                                                       \
+    return cudaLaunchKernelEx(&cfg, fn, p);                                                                \
   }
 
 }  // namespace b200attn

@@ -6,7 +6,17 @@ n = int(sys.argv[2]) if len(sys.argv) > 2 else 40
 hdr = rows[1]
 ws, src, ex = hdr.index("Warp Stall Sampling (All Samples)"), hdr.index("Source"), hdr.index("Instructions Executed")
 stall_cols = [i for i, h in enumerate(hdr) if h.startswith("stall_") and "Not Issued" not in h]
-body = [r for r in rows[2:] if len(r) == len(hdr)]
+body = []
+for r in rows[2:]:          # a report with several launches repeats the header block: keep the first launch
+    if len(r) != len(hdr):
+        if body:
+            break
+        continue
+    if r[ws] == hdr[ws]:
+        if body:
+            break
+        continue
+    body.append(r)
 tot = sum(float(r[ws]) for r in body)
 print("total samples", tot)
 for idx, r in sorted(enumerate(body), key=lambda t: -float(t[1][ws]))[:n]:

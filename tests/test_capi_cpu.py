@@ -100,7 +100,10 @@ def test_geometry_table():
     assert g["heads_per_cta"] == 8
     g = capi.decode_geometry(32, 32, 128, capi.BF16)      # MHA: four head groups of eight
     assert g["head_groups"] == 4
-    for bad in ((32, 8, 80), (32, 8, 256), (33, 8, 128), (64, 2, 128)):  # d80/d256, ragged, group 32
+    g = capi.decode_geometry(8, 4, 256, capi.BF16)        # Gemma-shaped: K and V of a chunk in separate pipeline slots
+    assert (g["heads_per_cta"], g["token_slices"], g["stages"]) == (4, 2, 3)
+    assert capi.decode_geometry(32, 8, 80, capi.BF16)["heads_per_cta"] == 8 and capi.decode_geometry(32, 8, 96, capi.BF16)["stages"] == 4
+    for bad in ((32, 8, 72), (32, 8, 512), (33, 8, 128), (64, 2, 128)):  # head dims without a kernel, ragged, group 32
         with pytest.raises(capi.B200AttnError) as e:
             capi.decode_geometry(*bad, capi.BF16)
         assert e.value.code == capi.E_UNSUPPORTED
@@ -137,7 +140,7 @@ def test_argument_errors_need_no_gpu():
     assert capi.launch_count() == n0
     assert lib.b200attn_plan_bytes(128) > 0 and lib.b200attn_plan_bytes(-1) == 0
     assert lib.b200attn_workspace_bytes(128, 32, 8, 128, 128, capi.BF16) > 0
-    assert lib.b200attn_workspace_bytes(128, 32, 8, 80, 80, capi.BF16) == 0
+    assert lib.b200attn_workspace_bytes(128, 32, 8, 72, 72, capi.BF16) == 0
 
 
 def test_ops_refuse_cpu_tensors():

@@ -213,6 +213,19 @@ SHAPES = [
     ("hkv3", 3, 12, 3, 64, 1, (30, 500)),
     ("gqa4_d64_tp8", 5, 4, 1, 64, 1, (1, 900)),      # 128-byte rows: swizzled cp.async stage, 4 rows per copy
     ("gqa8_d64_hkv2", 4, 16, 2, 64, 16, (100, 777)),  # two 128-byte heads per 256-byte row
+    # head dims beyond 64 / 128 (the reference kernel takes any Lk: triton_ops/decode_attention.py:205, 425-430;
+    # its own shape list has D = 80: test/srt/test_triton_attention_kernels.py:375-388)
+    ("gemma_d256", 5, 8, 4, 256, 1, (1, 900)),        # K and V of a chunk in separate pipeline slots
+    ("gemma_d256_b70", 70, 16, 8, 256, 16, (1, 300)), # enough requests for the widest rows (4 heads per CTA)
+    ("mha_d256", 3, 8, 8, 256, 1, (50, 400)),
+    ("gqa8_d256_tp", 4, 8, 1, 256, 1, (30, 1200)),
+    ("gqa16_d256", 2, 16, 1, 256, 1, (30, 500)),      # two n8 tiles of heads
+    ("phi_d96", 6, 32, 8, 96, 1, (1, 800)),
+    ("phi_d96_b80", 80, 32, 8, 96, 4, (1, 200)),
+    ("d96_tp8", 5, 4, 1, 96, 1, (10, 700)),           # 192-byte rows: bulk copies (not a power of two)
+    ("ref_d80", 3, 32, 8, 80, 1, (1, 600)),
+    ("ref_d80_b70", 70, 32, 4, 80, 1, (1, 150)),
+    ("d80_hkv1", 4, 6, 1, 80, 16, (17, 500)),
 ]
 
 
@@ -241,7 +254,7 @@ def test_decode_f16():
 
 
 @pytest.mark.parametrize("q_dtype", ["bf16", "f16"])
-@pytest.mark.parametrize("D", [64, 128])
+@pytest.mark.parametrize("D", [64, 128, 256])
 def test_decode_fp8(q_dtype, D):
     cfg = synth.Config("fp8", 5, 0, 32, 8, D, kv_dtype="fp8_e4m3", q_dtype=q_dtype, page_size=16,
                        ragged=(10, 1100), k_scale=0.5, v_scale=2.0, seed=24)
@@ -262,7 +275,7 @@ def test_decode_logit_cap(cap):
 
 
 @pytest.mark.parametrize("kv_dtype", ["bf16", "fp8_e4m3"])
-@pytest.mark.parametrize("D", [64, 128])
+@pytest.mark.parametrize("D", [64, 128, 256])
 def test_decode_peaked_softmax(kv_dtype, D):
     """q scaled by 6: the softmax of a row is carried by a handful of keys, so a wrong V row, a dropped
     token or a swapped head-dim column moves the output by far more than the tolerance (with randn q the
@@ -394,9 +407,12 @@ def test_errors_are_loud():
                                         torch.zeros(1, 1, 8, dtype=torch.bfloat16), torch.zeros(1, 1),
                                         torch.zeros(1, 1, 8, dtype=torch.bfloat16), None)
     # head dims without an instantiated kernel are refused, not silently mis-served
-    for d in (80, 96, 256):
+    for d in (13, 72, 512):
         with pytest.raises(capi.B200AttnError):
             capi.decode_geometry(32, 8, d, capi.BF16)
+    for d in (80, 96):   # fp8 fragments come in pairs of 16-byte units: head dims 64 / 128 / 256
+        with pytest.raises(capi.B200AttnError):
+            capi.decode_geometry(32, 8, d, capi.FP8_E4M3)
 
 
 # ----------------------------------------------------------------------------- #
@@ -624,14 +640,15 @@ def test_fused_merge_equals_two_stage(dyn, tp, batch, monkeypatch):
 # ----------------------------------------------------------------------------- #
 # sliding-window layers (interleaved with full-attention layers)
 # ----------------------------------------------------------------------------- #
-@pytest.mark.parametrize("window", [1, 16, 127, 4096])
-def test_sliding_window_layers(window):
+@pytest.mark.parametrize("window,D,heads", [(1, 128, (16, 4)), (16, 128, (16, 4)), (127, 128, (16, 4)), (4096, 128, (16, 4)),
+                                            (64, 256, (8, 4)), (511, 256, (16, 8))])   # the last two: Gemma-shaped
+def test_sliding_window_layers(window, D, heads):
     """A window layer attends to the last min(S, W + 1) tokens (triton_backend.py:927-956), a full layer
     of the same forward to everything; window_kv_indptr / window_kv_indices are bit-exact."""
     import b200attn
     from oracle import decode_oracle as oracle
 
-    cfg = synth.Config("swa", 9, 0, 16, 4, 128, page_size=4, ragged=(1, 700), seed=51)
+    cfg = synth.Config("swa", 9, 0, heads[0], heads[1], D, page_size=4, ragged=(1, 700), seed=51)
     w_cpu, w = _pair(cfg)
     _check_same_inputs(w_cpu, w)
     runner = make_runner(w, DEV)
