@@ -108,6 +108,8 @@ SHAPES = [
     ("mha_d64_tile_edges", 2, 2, 64, 16, (0, 0, 127, 128, 129), (128, 129, 1, 256, 257)),
     ("tile_edges", 8, 2, 128, 1, (0, 0, 0, 0, 63, 64, 65), (32, 33, 64, 65, 1, 1, 1)),
     ("many_short", 8, 2, 64, 1, tuple(range(0, 24)), tuple(1 + (i * 7) % 13 for i in range(24))),
+    ("gemma_d256", 8, 4, 256, 1, (0, 33, 300), (130, 64, 1)),         # head_dim 256: the mma.sync kernel
+    ("gemma_d256_gqa8", 16, 2, 256, 16, (100, 0), (257, 70)),
 ]
 
 
@@ -131,6 +133,7 @@ FP8_SHAPES = [
     ("fp8_f16q_d128", 8, 2, 128, 1, "f16", (20, 0), (70, 133), 2.0, 0.25),
     ("fp8_f16q_d64", 32, 2, 64, 4, "f16", (10, 90), (33, 8), 1.0, 1.0),
     ("fp8_tile_edges", 8, 2, 128, 1, "bf16", (0, 0, 127, 128, 129), (128, 129, 1, 1, 1), 0.5, 2.0),
+    ("fp8_gemma_d256", 8, 4, 256, 1, "bf16", (40, 0, 200), (90, 65, 2), 0.5, 2.0),
 ]
 
 
