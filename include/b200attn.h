@@ -219,6 +219,12 @@ typedef struct {
                                   without the merge (K2 alone); 2 = stand-alone merge kernel (K3).
                                   1 followed by 2 equals 0; they exist so each stage can be timed and
                                   tested alone. */
+  const int64_t* slot_map;     /* ABI 6, optional (NULL = none): every slot id read from `indices` goes through
+                                  slot_map[id] before it addresses the pool.  For the hybrid SWAKVPool
+                                  (mem_cache/memory_pool.py:420-553): sliding-window layers live in a smaller pool
+                                  whose slots are full_to_swa_index_mapping[full slot]
+                                  (translate_loc_from_full_to_swa, :515-517; flashinfer_backend.py:754, 1001
+                                  translate a materialised kv_indices list -- here the list is never built). */
 } b200attn_decode_args;
 
 /* Bytes of split-KV workspace (partial o + lse) for up to `batch` requests. */

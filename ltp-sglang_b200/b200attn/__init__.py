@@ -17,6 +17,7 @@ from .interfaces import (  # noqa: E402
     ForwardMode,
     MHATokenToKVPool,
     ReqToTokenPool,
+    SWAKVPool,
 )
 
 __all__ = [
@@ -35,4 +36,5 @@ __all__ = [
     "ForwardMode",
     "MHATokenToKVPool",
     "ReqToTokenPool",
+    "SWAKVPool",
 ]

@@ -168,8 +168,9 @@ class B200AttnBackend(AttentionBackend):
         self.kv_dtype = ops.dtype_code(k0.dtype)
         sw = getattr(model_runner, "sliding_window_size", None)
         self.sliding_window_size = int(sw) if sw is not None and sw > 0 else None
-        if type(self.token_to_kv_pool).__name__ == "SWAKVPool":
-            raise NotImplementedError("B200AttnBackend: the hybrid SWAKVPool (full -> swa slot translation) is not supported yet")
+        # hybrid pool of sliding-window models (SWAKVPool, memory_pool.py:420-553): window layers read and write
+        # the swa pool through full_to_swa_index_mapping (see _layer_pools)
+        self.is_swa_pool = hasattr(self.token_to_kv_pool, "full_to_swa_index_mapping")
         if getattr(mc, "is_encoder_decoder", False):
             raise NotImplementedError("B200AttnBackend: cross attention is not supported yet")
         if self.head_dim != self.v_head_dim:
@@ -466,12 +467,12 @@ class B200AttnBackend(AttentionBackend):
 
         q = q.reshape(-1, layer.tp_q_head_num * layer.qk_head_dim)
         o = torch.empty_like(q)
-        pool = forward_batch.token_to_kv_pool
-        start = getattr(pool, "start_layer", 0) or 0
-        k_pool = pool.k_buffer[layer.layer_id - start]
-        v_pool = pool.v_buffer[layer.layer_id - start]
+        k_pool, v_pool, slot_map = self._layer_pools(forward_batch.token_to_kv_pool, layer)
         if save_kv_cache and k is not None:
-            store_kv(k_pool, v_pool, forward_batch.out_cache_loc,
+            loc = forward_batch.out_cache_loc
+            if slot_map is not None:
+                loc = slot_map[loc]                       # translate_loc_from_full_to_swa (memory_pool.py:531-533)
+            store_kv(k_pool, v_pool, loc,
                      k.view(-1, layer.tp_k_head_num, layer.qk_head_dim),
                      v.view(-1, layer.tp_v_head_num, layer.v_head_dim),
                      getattr(layer, "k_scale", None), getattr(layer, "v_scale", None))
@@ -492,8 +493,23 @@ class B200AttnBackend(AttentionBackend):
             md.indices, self.workspace, float(layer.scaling),
             float(getattr(layer, "logit_cap", 0.0) or 0.0),
             float(k_scale) if (fp8 and k_scale is not None) else 1.0,
-            float(v_scale) if (fp8 and v_scale is not None) else 1.0)
+            float(v_scale) if (fp8 and v_scale is not None) else 1.0, 0, slot_map)
         return o
+
+    def _layer_pools(self, pool, layer):
+        """(k_pool, v_pool, slot_map) of a layer.  ``MHATokenToKVPool``: the layer's buffers, no map.
+        ``SWAKVPool``: a sliding-window layer lives in ``swa_kv_pool`` and every full-pool slot id -- the ones in
+        ``req_to_token`` and ``out_cache_loc`` -- goes through ``full_to_swa_index_mapping`` first (the reference
+        translates a materialised ``kv_indices`` list, flashinfer_backend.py:754, 1001; the decode kernel applies
+        the map to the ids it reads in place instead)."""
+        if not self.is_swa_pool:
+            start = getattr(pool, "start_layer", 0) or 0
+            return pool.k_buffer[layer.layer_id - start], pool.v_buffer[layer.layer_id - start], None
+        pid, is_swa = pool.layers_mapping[layer.layer_id]
+        sub = pool.swa_kv_pool if is_swa else pool.full_kv_pool
+        start = getattr(sub, "start_layer", 0) or 0
+        smap = pool.full_to_swa_index_mapping if is_swa else None
+        return sub.k_buffer[pid - start], sub.v_buffer[pid - start], smap
 
     def last_lse(self, bs: int) -> torch.Tensor:
         """ln sum exp(scaled logits) of the most recent forward_decode, ``[bs, heads]``."""
@@ -514,13 +530,12 @@ class B200AttnBackend(AttentionBackend):
         fp8 = self.kv_dtype == capi.FP8_E4M3
         q = q.reshape(-1, layer.tp_q_head_num * layer.qk_head_dim)
         o = torch.empty_like(q)
-        pool = forward_batch.token_to_kv_pool
-        start = getattr(pool, "start_layer", 0) or 0
-        k_pool = pool.k_buffer[layer.layer_id - start]
-        v_pool = pool.v_buffer[layer.layer_id - start]
+        k_pool, v_pool, slot_map = self._layer_pools(forward_batch.token_to_kv_pool, layer)
         loc = forward_batch.out_cache_loc
         if loc.dtype != torch.int64:
             loc = loc.to(torch.int64)
+        if slot_map is not None:
+            loc = slot_map[loc]
         if save_kv_cache and k is not None:
             store_kv(k_pool, v_pool, loc, k.view(-1, layer.tp_k_head_num, layer.qk_head_dim),
                      v.view(-1, layer.tp_v_head_num, layer.v_head_dim),
@@ -540,6 +555,11 @@ class B200AttnBackend(AttentionBackend):
                 raise NotImplementedError("B200AttnBackend: sliding-window layers need model_runner.sliding_window_size "
                                           "and a plain EXTEND batch")
             kv_indptr = md.window_kv_indptr
+        kv_indices = md.kv_indices
+        if slot_map is not None:
+            # SWAKVPool: the prefix list of a window layer as swa-pool slots (eager prefill only: one host sync for
+            # the list length, as the reference's own extend metadata does, triton_backend.py:283-300)
+            kv_indices = self._swa_prefix_indices(md, kv_indptr, slot_map, windowed)
         max_len = tokens if md.max_extend_len is None else min(md.max_extend_len, tokens)
         k_scale = getattr(layer, "k_scale_float", None)
         v_scale = getattr(layer, "v_scale_float", None)
@@ -547,14 +567,30 @@ class B200AttnBackend(AttentionBackend):
             q.view(tokens, layer.tp_q_head_num, layer.qk_head_dim),
             o.view(tokens, layer.tp_q_head_num, layer.v_head_dim),
             self.lse_extend(tokens) if self.return_lse else None,
-            k_pool, v_pool, md.qo_indptr, kv_indptr, md.kv_indices,
-            self.req_to_token if md.kv_indices is None else None, md.req_pool_indices, md.prefix_lens,
+            k_pool, v_pool, md.qo_indptr, kv_indptr, kv_indices,
+            self.req_to_token if kv_indices is None else None, md.req_pool_indices, md.prefix_lens,
             loc, md.custom_mask, md.mask_indptr, int(max_len), causal,
             int(sw) if windowed else -1, True, float(layer.scaling),
             float(getattr(layer, "logit_cap", 0.0) or 0.0),
             float(k_scale) if (fp8 and k_scale is not None) else 1.0,
             float(v_scale) if (fp8 and v_scale is not None) else 1.0, int(md.avg_kv_len))
         return o
+
+    def _swa_prefix_indices(self, md, kv_indptr: torch.Tensor, slot_map: torch.Tensor, windowed: bool) -> torch.Tensor:
+        """Flat prefix slot list of the batch (request b: entries kv_indptr[b] .. kv_indptr[b + 1]) translated to
+        swa-pool slots.  Window layers keep the LAST kv_indptr[b+1] - kv_indptr[b] prefix tokens of a request."""
+        if md.kv_indices is not None:
+            return slot_map[md.kv_indices.long()].to(torch.int32)
+        if md.req_pool_indices is None or md.prefix_lens is None:
+            raise NotImplementedError("B200AttnBackend: SWAKVPool with this extend metadata")
+        lens = (kv_indptr[1:] - kv_indptr[:-1]).long()
+        total = int(kv_indptr[-1].item())
+        if total == 0:
+            return torch.zeros(1, dtype=torch.int32, device=self.device)
+        first = md.prefix_lens.long() - lens if windowed else torch.zeros_like(lens)
+        pos = torch.arange(total, device=self.device) - torch.repeat_interleave(kv_indptr[:-1].long() - first, lens)
+        rows = torch.repeat_interleave(md.req_pool_indices.long(), lens)
+        return slot_map[self.req_to_token[rows, pos].long()].to(torch.int32)
 
     def lse_extend(self, tokens: int) -> torch.Tensor:
         """fp32 ``[tokens, heads]`` buffer the extend kernel writes ln sum exp(scaled logits) into."""

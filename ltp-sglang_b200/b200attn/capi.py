@@ -125,6 +125,7 @@ class DecodeArgs(C.Structure):
         ("k_scale", C.c_float),
         ("v_scale", C.c_float),
         ("phases", C.c_int32),
+        ("slot_map", C.c_void_p),
     ]
 
 

@@ -141,6 +141,55 @@ class MHATokenToKVPool:
                  loc, cache_k, cache_v, k_scale, v_scale)
 
 
+class SWAKVPool:
+    """Hybrid pool of sliding-window models (``SWAKVPool``, mem_cache/memory_pool.py:420-553): full-attention
+    layers live in ``full_kv_pool``, sliding-window layers in the smaller ``swa_kv_pool`` whose slot of a token
+    is ``full_to_swa_index_mapping[full slot]`` (filled by the allocator, mem_cache/allocator.py).  Same
+    attribute and method names as the reference class."""
+
+    def __init__(self, size: int, size_swa: int, dtype: torch.dtype, head_num: int, head_dim: int,
+                 swa_attention_layer_ids, full_attention_layer_ids, enable_kvcache_transpose: bool = False,
+                 device: Union[str, torch.device] = "cuda"):
+        assert not enable_kvcache_transpose
+        self.size, self.size_swa, self.dtype, self.device = size, size_swa, dtype, device
+        self.page_size = 1
+        self.swa_layer_nums, self.full_layer_nums = len(swa_attention_layer_ids), len(full_attention_layer_ids)
+        self.swa_kv_pool = MHATokenToKVPool(size_swa, 1, dtype, head_num, head_dim, self.swa_layer_nums, device)
+        self.full_kv_pool = MHATokenToKVPool(size, 1, dtype, head_num, head_dim, self.full_layer_nums, device)
+        self.layers_mapping = {}
+        for i, gid in enumerate(full_attention_layer_ids):
+            self.layers_mapping[gid] = (i, False)
+        for i, gid in enumerate(swa_attention_layer_ids):
+            self.layers_mapping[gid] = (i, True)
+        self.full_to_swa_index_mapping: Optional[torch.Tensor] = None
+
+    def _pool(self, layer_id: int):
+        pid, is_swa = self.layers_mapping[layer_id]
+        return (self.swa_kv_pool if is_swa else self.full_kv_pool), pid
+
+    def get_key_buffer(self, layer_id: int):
+        pool, pid = self._pool(layer_id)
+        return pool.get_key_buffer(pid)
+
+    def get_value_buffer(self, layer_id: int):
+        pool, pid = self._pool(layer_id)
+        return pool.get_value_buffer(pid)
+
+    def get_kv_buffer(self, layer_id: int):
+        return self.get_key_buffer(layer_id), self.get_value_buffer(layer_id)
+
+    def translate_loc_from_full_to_swa(self, kv_indices: torch.Tensor):
+        assert self.full_to_swa_index_mapping is not None
+        return self.full_to_swa_index_mapping[kv_indices].to(torch.int32)
+
+    def set_kv_buffer(self, layer, loc: torch.Tensor, cache_k: torch.Tensor, cache_v: torch.Tensor,
+                      k_scale=None, v_scale=None):
+        pool, pid = self._pool(layer.layer_id)
+        if self.layers_mapping[layer.layer_id][1] and self.full_to_swa_index_mapping is not None:
+            loc = self.translate_loc_from_full_to_swa(loc)
+        pool.set_kv_buffer(None, loc, cache_k, cache_v, k_scale, v_scale, layer_id_override=pid)
+
+
 class AttnLayer:
     """The attributes of ``RadixAttention`` the attention backends read."""
 

@@ -186,8 +186,10 @@ def _plan_csr(csr_indptr, plan_buf, num_q_heads, num_kv_heads, head_dim, kv_dtyp
 
 
 def _decode(q, k_pool, v_pool, o, lse, plan_buf, indices, workspace, sm_scale, logit_cap, k_scale, v_scale,
-            phases=0):
-    _cuda(q, k_pool, v_pool, o, lse, plan_buf, indices, workspace)
+            phases=0, slot_map=None):
+    _cuda(q, k_pool, v_pool, o, lse, plan_buf, indices, workspace, slot_map)
+    if slot_map is not None and (slot_map.dtype != torch.int64 or not slot_map.is_contiguous()):
+        raise TypeError("decode: slot_map (SWAKVPool.full_to_swa_index_mapping) must be a contiguous int64 tensor")
     if q.dim() != 3 or o.dim() != 3 or k_pool.dim() != 3 or v_pool.dim() != 3:
         raise ValueError("decode: q/o must be [batch, heads, dim]; pools [slots, kv_heads, dim]")
     if q.stride(2) != 1 or o.stride(2) != 1 or k_pool.stride(2) != 1 or v_pool.stride(2) != 1:
@@ -222,6 +224,7 @@ def _decode(q, k_pool, v_pool, o, lse, plan_buf, indices, workspace, sm_scale, l
     a.kv_dtype = dtype_code(k_pool.dtype)
     a.sm_scale, a.logit_cap, a.k_scale, a.v_scale = sm_scale, logit_cap, k_scale, v_scale
     a.phases = phases
+    a.slot_map = _ptr(slot_map)
     with torch.cuda.device(q.device):
         capi.check("b200attn_decode", capi.lib().b200attn_decode(C.byref(a), _stream(q)))
 
@@ -402,7 +405,7 @@ _LIB.define(
 _LIB.define(
     "decode(Tensor q, Tensor k_pool, Tensor v_pool, Tensor(a!) o, Tensor(b!)? lse, Tensor plan_buf, "
     "Tensor indices, Tensor(c!) workspace, float sm_scale, float logit_cap, float k_scale, "
-    "float v_scale, int phases=0) -> ()"
+    "float v_scale, int phases=0, Tensor? slot_map=None) -> ()"
 )
 _LIB.define(
     "extend(Tensor q, Tensor(a!) o, Tensor(b!)? lse, Tensor k_pool, Tensor v_pool, Tensor qo_indptr, "

@@ -142,6 +142,7 @@ extern "C" __attribute__((visibility("default"))) int b200attn_decode(const b200
   p.lse = a->lse;
   p.plan = a->plan;
   p.indices = a->indices;
+  p.slot_map = a->slot_map;
   p.ws_o = a->ws_o;
   p.ws_lse = a->ws_o + lse_off;
   p.batch = a->batch;

@@ -43,6 +43,7 @@ struct DecodeParams {
   float* lse;                    // optional [batch, hq]
   const void* plan;
   const int32_t* indices;
+  const int64_t* slot_map;       // optional full -> swa slot translation (SWAKVPool), applied to every id read
   float* ws_o;
   float* ws_lse;
   int32_t batch, hq;
@@ -259,6 +260,10 @@ __global__ void __launch_bounds__(kThreads, 1) decode_kernel(const DecodeParams 
       const bool mine = p.cp_async ? lane + 32 * r < (T_ >> 1) : i < T_;
       if (mine) pre_ids[r] = __ldg(pv.first_ids + cta * kFirstIds + i);
     }
+    if (p.slot_map) {
+#pragma unroll
+      for (int r = 0; r < 2; ++r) pre_ids[r] = static_cast<int32_t>(p.slot_map[pre_ids[r]]);
+    }
   }
   // the rate this CTA recorded in earlier launches (updated at exit; fetched here so that the exit is a plain store)
   CtaStat st_prev = {0.f, 0u};
@@ -363,6 +368,7 @@ __global__ void __launch_bounds__(kThreads, 1) decode_kernel(const DecodeParams 
             const int i = lane + 32 * r;
             const int t = lc0 * T + tbase + i;
             nxt[r] = (i < Tw && t < S) ? idx[t] : 0;
+            if (p.slot_map) nxt[r] = static_cast<int32_t>(p.slot_map[nxt[r]]);
           }
         }
         for (int lc = lc0; lc < lc1; ++lc) {
@@ -373,6 +379,7 @@ __global__ void __launch_bounds__(kThreads, 1) decode_kernel(const DecodeParams 
               const int i = lane + 32 * r;
               const int t = (lc + 1) * T + tbase + i;
               nxt[r] = (i < Tw && t < S) ? idx[t] : 0;
+              if (p.slot_map) nxt[r] = static_cast<int32_t>(p.slot_map[nxt[r]]);
             }
           }
           const int nvalid = S - lc * T - tbase;  // valid tokens of this warp's range (may be <= 0)
@@ -443,6 +450,7 @@ __global__ void __launch_bounds__(kThreads, 1) decode_kernel(const DecodeParams 
           const int i = 2 * (lane + 32 * r) + par;
           const int t = lc0 * T + i;
           nxt[r] = (i < T && t < S) ? idx[t] : 0;
+          if (p.slot_map) nxt[r] = static_cast<int32_t>(p.slot_map[nxt[r]]);
         }
       }
       for (int lc = lc0; lc < lc1; ++lc) {
@@ -453,6 +461,7 @@ __global__ void __launch_bounds__(kThreads, 1) decode_kernel(const DecodeParams 
             const int i = 2 * (lane + 32 * r) + par;
             const int t = (lc + 1) * T + i;
             nxt[r] = (i < T && t < S) ? idx[t] : 0;
+            if (p.slot_map) nxt[r] = static_cast<int32_t>(p.slot_map[nxt[r]]);
           }
         }
         const int t0 = lc * T;

@@ -673,3 +673,61 @@ def test_sliding_window_layers(window, D, heads):
     indptr, indices = oracle.kv_indices(w_cpu.req_to_token, w_cpu.req_pool_indices, w_cpu.seq_lens)
     assert np.array_equal(md.kv_indptr.cpu().numpy(), indptr)
     assert np.array_equal(md.kv_indices.cpu().numpy(), indices)
+
+
+# ----------------------------------------------------------------------------- #
+# hybrid SWAKVPool: window layers live in a second pool behind full_to_swa_index_mapping
+# ----------------------------------------------------------------------------- #
+@pytest.mark.parametrize("kv_dtype,D", [("bf16", 128), ("fp8_e4m3", 128), ("bf16", 256)])
+def test_swa_kv_pool_decode(kv_dtype, D):
+    """``SWAKVPool`` (memory_pool.py:420-553): layer 0 is a full-attention layer in ``full_kv_pool``, layer 1 a
+    sliding-window layer in ``swa_kv_pool``, whose slot of a token is ``full_to_swa_index_mapping[full slot]``.
+    The new token's K/V must land at the translated slot of the swa pool only, and the window layer must attend
+    over the translated slots (the reference translates a materialised kv_indices list,
+    flashinfer_backend.py:754, 1001; here the decode kernel maps the ids it reads from req_to_token)."""
+    import b200attn
+    from oracle import decode_oracle as oracle
+
+    W = 200
+    fp8 = kv_dtype != "bf16"
+    cfg = synth.Config("swapool", 9, 0, 8, 4, D, kv_dtype=kv_dtype, ragged=(1, 700), seed=77,
+                       k_scale=0.5 if fp8 else 1.0, v_scale=2.0 if fp8 else 1.0)
+    w_cpu, w = _pair(cfg)
+    _check_same_inputs(w_cpu, w)
+    c = cfg
+    runner = make_runner(w, DEV)
+    n = w.pool_size
+    pool = b200attn.SWAKVPool(n, n, runner.token_to_kv_pool.dtype, c.num_kv_heads, D, [1], [0], False, DEV)
+    gen = torch.Generator().manual_seed(5)
+    perm = torch.randperm(n + 1, generator=gen)                       # a slot of the swa pool for every full slot
+    pool.full_to_swa_index_mapping = perm.to(DEV)
+    pool.full_kv_pool.k_buffer[0], pool.full_kv_pool.v_buffer[0] = w.k_pool.clone(), w.v_pool.clone()
+    pool.swa_kv_pool.k_buffer[0][perm.to(DEV)] = w.k_pool
+    pool.swa_kv_pool.v_buffer[0][perm.to(DEV)] = w.v_pool
+    runner.token_to_kv_pool = pool
+    runner.sliding_window_size = W
+    backend = b200attn.B200AttnBackend(runner, return_lse=True, max_ctas=9)
+    qc = w_cpu.q.reshape(c.batch, c.num_q_heads, D)
+    kp, vp = w_cpu.k_pool.clone(), w_cpu.v_pool.clone()
+    oracle.kv_store(kp, vp, w_cpu.out_cache_loc, w_cpu.k.reshape(c.batch, c.num_kv_heads, D).clone(),
+                    w_cpu.v.reshape(c.batch, c.num_kv_heads, D).clone(), c.k_scale if fp8 else None,
+                    c.v_scale if fp8 else None)
+    loc = w.out_cache_loc.long()
+    for layer_id, window in ((1, W), (0, -1)):
+        layer = make_layer(w)
+        layer.layer_id = layer_id
+        layer.sliding_window_size = window
+        qkv0 = w.qkv.clone()
+        out = run_decode(backend, runner, w, layer=layer, save_kv_cache=True)
+        torch.cuda.synchronize()
+        w.qkv.copy_(qkv0)    # an fp8 store divides k / v in place
+        ref, ref_lse = oracle.decode_attention(qc, kp, vp, w_cpu.req_to_token, w_cpu.req_pool_indices, w_cpu.seq_lens,
+                                               w_cpu.sm_scale, k_scale=c.k_scale if fp8 else 1.0,
+                                               v_scale=c.v_scale if fp8 else 1.0, sliding_window=max(window, 0))
+        assert_close_out(out.float().cpu().numpy().reshape(ref.shape), ref)
+        assert np.abs(backend.last_lse(c.batch).cpu().numpy() - ref_lse).max() <= 1e-3
+        # the new token's rows: bit-exact, in the right pool at the right slot
+        sub = pool.swa_kv_pool if layer_id == 1 else pool.full_kv_pool
+        at = pool.full_to_swa_index_mapping[loc] if layer_id == 1 else loc
+        assert torch.equal(sub.k_buffer[0][at].cpu().view(torch.uint8), kp[w_cpu.out_cache_loc.long()].view(torch.uint8))
+        assert torch.equal(sub.v_buffer[0][at].cpu().view(torch.uint8), vp[w_cpu.out_cache_loc.long()].view(torch.uint8))
