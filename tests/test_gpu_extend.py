@@ -343,3 +343,37 @@ def test_small_q_kernels_forced(mode):
                        env=env, capture_output=True, text=True, timeout=600)
     assert r.returncode == 0, r.stdout[-3000:] + r.stderr[-2000:]
     assert " passed" in r.stdout
+
+
+@pytest.mark.parametrize("window", [40, 300])
+def test_swa_kv_pool_extend(window):
+    """``SWAKVPool`` prefill: a sliding-window layer reads its cached prefix and its new tokens from the swa pool
+    through ``full_to_swa_index_mapping`` (translate_loc_from_full_to_swa, memory_pool.py:515-517), a full layer
+    of the same forward from the full pool; both against the extend oracle on the untranslated layout."""
+    import b200attn
+
+    cfg = synth.Config("swaext", 3, 0, 8, 4, 128, page_size=1, seed=88)
+    pl, el = (0, 150, 700), (90, 33, 5)
+    w_cpu, w = _pair(cfg, pl, el)
+    runner = make_extend_runner(w, DEV, sliding_window_size=window)
+    n = w.pool_size
+    pool = b200attn.SWAKVPool(n, n, runner.token_to_kv_pool.dtype, cfg.num_kv_heads, cfg.head_dim, [1], [0], False, DEV)
+    perm = torch.randperm(n + 1, generator=torch.Generator().manual_seed(9)).to(DEV)
+    pool.full_to_swa_index_mapping = perm
+    pool.full_kv_pool.k_buffer[0], pool.full_kv_pool.v_buffer[0] = w.k_pool.clone(), w.v_pool.clone()
+    pool.swa_kv_pool.k_buffer[0][perm] = w.k_pool
+    pool.swa_kv_pool.v_buffer[0][perm] = w.v_pool
+    runner.token_to_kv_pool = pool
+    backend = b200attn.B200AttnBackend(runner, return_lse=True)
+    for layer_id, win in ((1, window), (0, -1)):
+        layer = _layer(w, True, 0.0, win)
+        layer.layer_id = layer_id
+        out = run_extend(backend, runner, w, layer)
+        torch.cuda.synchronize()
+        ref, ref_lse, kp, vp = oracle_extend(w_cpu, causal=True, sliding_window=win)
+        assert_close_out(out.float().cpu().numpy().reshape(ref.shape), ref)
+        sub = pool.swa_kv_pool if layer_id == 1 else pool.full_kv_pool
+        loc = w.out_cache_loc.long()
+        at = perm[loc] if layer_id == 1 else loc
+        assert torch.equal(sub.k_buffer[0][at].cpu(), kp[w_cpu.out_cache_loc.long()])
+        assert torch.equal(sub.v_buffer[0][at].cpu(), vp[w_cpu.out_cache_loc.long()])
