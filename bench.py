@@ -387,7 +387,9 @@ def measure(R: Rank, args, gcfg, scaling: str, with_clocks: bool = True) -> dict
     # (one 0.5-3 MB device copy inside the timed region) instead of letting k drift to inf.
     qkv0 = w.qkv.clone()
     refresh = fp8
-    l2_note = ("L2 flushed (252 MB memset, then a 252 MB read so no dirty lines remain) before every timed step; each step timed by its own event pair"
+    l2_note = ("L2 flushed (252 MB memset, then a 252 MB read so no dirty lines remain) before every timed step; step time = "
+               "(graph of 4 x [flush, step] - graph of 4 x [flush]) / 4 by CUDA events (ms_per_step_single_replay: event pair "
+               "around one replay of a one-step graph, graph launch included)"
                if flush else "per-GPU KV working set (%d MB) far larger than the 126 MB L2; no flush" % (kv_bytes >> 20))
 
     # ---------------- device-resident timing: `value` ----------------
@@ -438,6 +440,36 @@ def measure(R: Rank, args, gcfg, scaling: str, with_clocks: bool = True) -> dict
     ms = R.timed(step, args.steps, flush)
     R.barrier()
     n_timed = len(sampler.samples) if sampler else 0
+    ms_single = None
+    if flush and graph is not None:
+        # Flushed configs (KV working set < 4 x L2): a step is 25-60 us, and an event pair around ONE replay of a
+        # one-step graph also holds the graph launch (5-9 us) -- which a decode step inside a model's graph of
+        # hundreds of kernels does not pay.  So the step is timed inside a graph: A = 4 x [L2 flush, step],
+        # B = 4 x [L2 flush]; step = (A - B) / 4.  The single-replay figure is reported beside it.
+        ms_single = R.max_over_ranks(ms)
+
+        def _flush_step_graph(with_step: bool):
+            g = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(g):
+                for _ in range(4):
+                    R.flush_l2()
+                    if with_step:
+                        if refresh:
+                            w.qkv.copy_(qkv0)
+                        layer(w.q, w.k, w.v, fb)
+            for _ in range(2):
+                g.replay()
+            torch.cuda.synchronize()
+            return g
+        R.flush_l2()
+        torch.cuda.synchronize()
+        ga, gb = _flush_step_graph(True), _flush_step_graph(False)
+        reps = max(10, min(args.steps, 30))
+        ta = min(R.timed(ga.replay, reps, False) for _ in range(3))
+        tb = min(R.timed(gb.replay, reps, False) for _ in range(3))
+        ms = (ta - tb) / 4
+        del ga, gb
+        R.barrier()
     ms_max = R.max_over_ranks(ms)
 
     # ---------------- decode kernel alone: roofline ----------------
@@ -679,6 +711,7 @@ def measure(R: Rank, args, gcfg, scaling: str, with_clocks: bool = True) -> dict
         "tokens_per_s_model_equiv": B / (ms_max * 1e-3) / gcfg.layers_equiv,
         "layers_equiv": gcfg.layers_equiv,
         "launch_mode": "cuda_graph" if graph is not None else "eager",
+        "ms_per_step_single_replay": ms_single,
         "roofline": roofline,
         "e2e": {"value": B / (e2e_ms * 1e-3), "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
                 "ms_per_step": e2e_ms, "launches": e2e_launches, "path": e2e_path,

@@ -39,7 +39,11 @@ for name in (sys.argv[1:] or ["C2"]):
     fb = make_batch(w, runner, backend)
     backend.init_forward_metadata(fb)
     B, Hq, Hkv, D = c.batch, c.num_q_heads, c.num_kv_heads, c.head_dim
-    ours = layer(w.q, w.k, w.v, fb).view(B, Hq, D).clone()
+    # outputs are compared on the SAME pool state: no KV store here (a store divides k / v in place on an fp8 pool,
+    # so every later call writes another new-token row: round 1's 0.10 "gap" on C3 was exactly that, see
+    # tools/fp8_vs_flashinfer.py and profiles/r02_fp8_vs_flashinfer.jsonl)
+    ours = layer(w.q, w.k, w.v, fb, save_kv_cache=False).view(B, Hq, D).clone()
+    pool_k0, pool_v0 = w.k_pool[w.out_cache_loc.long()].clone(), w.v_pool[w.out_cache_loc.long()].clone()
     e = 1 if c.kv_dtype == "fp8_e4m3" else 2
     kv_bytes = w.seq_lens_sum * Hkv * 2 * D * e
     rec = {"config": name, "kv_bytes": kv_bytes, "page_size": c.page_size}
@@ -60,6 +64,8 @@ for name in (sys.argv[1:] or ["C2"]):
     md = backend.forward_metadata
     kv_indptr, kv_indices = md.kv_indptr[: B + 1], md.kv_indices
     fp8 = c.kv_dtype == "fp8_e4m3"
+    w.k_pool[w.out_cache_loc.long()] = pool_k0   # the timed replays stored new-token rows: back to the compared state
+    w.v_pool[w.out_cache_loc.long()] = pool_v0
     if c.page_size == 1:
         try:
             import flashinfer
