@@ -397,6 +397,32 @@ def test_merge_states_golden():
         assert np.abs(lse.cpu().numpy()[fin] - g["lse"][fin]).max() <= 1e-3
 
 
+def test_merge_states_fp32():
+    """float32 states (merge_attn_states.cu:111-122 dispatches float too): the bf16 golden's inputs widened to fp32,
+    against the float64 merge of the same values (`merge_state_torch`'s formula, test_merge_state_v2.py:30-60)."""
+    g = np.load(os.path.join(GOLDEN_DIR, "g8_merge_bf16.npz"))
+    oa = torch.from_numpy(g["o_a"].view(np.int16)).view(torch.bfloat16).float().to(DEV)
+    ob = torch.from_numpy(g["o_b"].view(np.int16)).view(torch.bfloat16).float().to(DEV)
+    la, lb = torch.from_numpy(g["lse_a"]).to(DEV), torch.from_numpy(g["lse_b"]).to(DEV)
+    out, lse = torch.empty_like(oa), torch.empty_like(la)
+    torch.ops.b200attn.merge_states(oa, la, ob, lb, out, lse)
+    torch.cuda.synchronize()
+    a64, b64 = oa.double().cpu().numpy(), ob.double().cpu().numpy()
+    la64, lb64 = la.double().cpu().numpy(), lb.double().cpu().numpy()
+    la64 = np.where(np.isinf(la64), -np.inf, la64)
+    lb64 = np.where(np.isinf(lb64), -np.inf, lb64)
+    m = np.maximum(la64, lb64)
+    with np.errstate(invalid="ignore"):
+        wa, wb = np.exp(la64 - m), np.exp(lb64 - m)
+    wa, wb = np.nan_to_num(wa), np.nan_to_num(wb)
+    den = wa + wb
+    ok = den > 0
+    ref = np.where(ok[..., None], (wa[..., None] * a64 + wb[..., None] * b64) / np.where(ok, den, 1.0)[..., None], 0.0)
+    got = out.double().cpu().numpy()
+    assert np.abs(got[ok] - ref[ok]).max() <= 1e-5
+    assert np.abs(lse.double().cpu().numpy()[ok] - (m + np.log(den))[ok]).max() <= 1e-5
+
+
 def test_errors_are_loud():
     import b200attn
     from b200attn import capi
