@@ -225,6 +225,10 @@ typedef struct {
                                   whose slots are full_to_swa_index_mapping[full slot]
                                   (translate_loc_from_full_to_swa, :515-517; flashinfer_backend.py:754, 1001
                                   translate a materialised kv_indices list -- here the list is never built). */
+  int64_t pool_slots;          /* ABI 6, optional (0 = unknown): rows of k_pool / v_pool.  Only read by the debug build
+                                  (make -C csrc debug, -DB200ATTN_DEBUG), whose producers trap on a slot id outside
+                                  [0, pool_slots) instead of gathering out of bounds (compute-sanitizer is not
+                                  available on every pool). */
 } b200attn_decode_args;
 
 /* Bytes of split-KV workspace (partial o + lse) for up to `batch` requests. */

@@ -126,6 +126,7 @@ class DecodeArgs(C.Structure):
         ("v_scale", C.c_float),
         ("phases", C.c_int32),
         ("slot_map", C.c_void_p),
+        ("pool_slots", C.c_int64),
     ]
 
 

@@ -225,6 +225,7 @@ def _decode(q, k_pool, v_pool, o, lse, plan_buf, indices, workspace, sm_scale, l
     a.sm_scale, a.logit_cap, a.k_scale, a.v_scale = sm_scale, logit_cap, k_scale, v_scale
     a.phases = phases
     a.slot_map = _ptr(slot_map)
+    a.pool_slots = min(k_pool.shape[0], v_pool.shape[0])
     with torch.cuda.device(q.device):
         capi.check("b200attn_decode", capi.lib().b200attn_decode(C.byref(a), _stream(q)))
 

@@ -143,6 +143,7 @@ extern "C" __attribute__((visibility("default"))) int b200attn_decode(const b200
   p.plan = a->plan;
   p.indices = a->indices;
   p.slot_map = a->slot_map;
+  p.pool_slots = a->pool_slots;
   p.ws_o = a->ws_o;
   p.ws_lse = a->ws_o + lse_off;
   p.batch = a->batch;

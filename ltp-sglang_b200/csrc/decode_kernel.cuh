@@ -44,6 +44,7 @@ struct DecodeParams {
   const void* plan;
   const int32_t* indices;
   const int64_t* slot_map;       // optional full -> swa slot translation (SWAKVPool), applied to every id read
+  int64_t pool_slots;            // rows of the pools (0 = unknown); checked by the -DB200ATTN_DEBUG build only
   float* ws_o;
   float* ws_lse;
   int32_t batch, hq;
@@ -95,6 +96,14 @@ __device__ __forceinline__ unsigned long long globaltimer_ns() {
 #define B200_TR_ONCE(slot, flag) do { } while (0)
 #define B200_TR_GT(slot) do { } while (0)
 #define B200_TR_DEP(slot, val) do { } while (0)
+#endif
+
+// -DB200ATTN_DEBUG (make debug -> libb200attn_debug.so): a slot id outside the pool traps instead of gathering
+// out of bounds; the stage offsets of the consumers are checked against the dynamic smem size at entry.
+#ifdef B200ATTN_DEBUG
+#define B200_CHECK_SLOT(id) do { if (p.pool_slots > 0 && static_cast<uint64_t>(static_cast<int64_t>(id)) >= static_cast<uint64_t>(p.pool_slots)) __trap(); } while (0)
+#else
+#define B200_CHECK_SLOT(id) do { } while (0)
 #endif
 
 constexpr float kLog2e = 1.4426950408889634f;
@@ -230,6 +239,14 @@ __global__ void __launch_bounds__(kThreads, 1) decode_kernel(const DecodeParams 
     }
     fence_barrier_init();
   }
+#ifdef B200ATTN_DEBUG
+  {
+    uint32_t dyn;
+    asm volatile("mov.u32 %0, %%dynamic_smem_size;" : "=r"(dyn));
+    const uint32_t need = kBarrierBytes + p.stages * p.stage_bytes;
+    if (need > dyn || (p.xch_off != 0 && static_cast<uint32_t>(p.xch_off) < need)) __trap();
+  }
+#endif
   pdl_wait();  // plan, q and the pool rows of this step are written by kernels in front of this one
 
   const PlanView pv = plan_view(const_cast<void*>(p.plan), p.batch);
@@ -264,6 +281,8 @@ __global__ void __launch_bounds__(kThreads, 1) decode_kernel(const DecodeParams 
 #pragma unroll
       for (int r = 0; r < 2; ++r) pre_ids[r] = static_cast<int32_t>(p.slot_map[pre_ids[r]]);
     }
+    B200_CHECK_SLOT(pre_ids[0]);
+    B200_CHECK_SLOT(pre_ids[1]);
   }
   // the rate this CTA recorded in earlier launches (updated at exit; fetched here so that the exit is a plain store)
   CtaStat st_prev = {0.f, 0u};
@@ -369,6 +388,7 @@ __global__ void __launch_bounds__(kThreads, 1) decode_kernel(const DecodeParams 
             const int t = lc0 * T + tbase + i;
             nxt[r] = (i < Tw && t < S) ? idx[t] : 0;
             if (p.slot_map) nxt[r] = static_cast<int32_t>(p.slot_map[nxt[r]]);
+            B200_CHECK_SLOT(nxt[r]);
           }
         }
         for (int lc = lc0; lc < lc1; ++lc) {
@@ -380,6 +400,7 @@ __global__ void __launch_bounds__(kThreads, 1) decode_kernel(const DecodeParams 
               const int t = (lc + 1) * T + tbase + i;
               nxt[r] = (i < Tw && t < S) ? idx[t] : 0;
               if (p.slot_map) nxt[r] = static_cast<int32_t>(p.slot_map[nxt[r]]);
+            B200_CHECK_SLOT(nxt[r]);
             }
           }
           const int nvalid = S - lc * T - tbase;  // valid tokens of this warp's range (may be <= 0)
@@ -451,6 +472,7 @@ __global__ void __launch_bounds__(kThreads, 1) decode_kernel(const DecodeParams 
           const int t = lc0 * T + i;
           nxt[r] = (i < T && t < S) ? idx[t] : 0;
           if (p.slot_map) nxt[r] = static_cast<int32_t>(p.slot_map[nxt[r]]);
+            B200_CHECK_SLOT(nxt[r]);
         }
       }
       for (int lc = lc0; lc < lc1; ++lc) {
@@ -462,6 +484,7 @@ __global__ void __launch_bounds__(kThreads, 1) decode_kernel(const DecodeParams 
             const int t = (lc + 1) * T + i;
             nxt[r] = (i < T && t < S) ? idx[t] : 0;
             if (p.slot_map) nxt[r] = static_cast<int32_t>(p.slot_map[nxt[r]]);
+            B200_CHECK_SLOT(nxt[r]);
           }
         }
         const int t0 = lc * T;
