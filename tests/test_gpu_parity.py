@@ -625,7 +625,8 @@ def test_fused_merge_equals_two_stage(dyn, tp, batch, monkeypatch):
     # batch 70: 8 heads per CTA, one token slice; batch 37: a small batch takes 4 heads per CTA and two token
     # slices (ABI 6); tp 8: one head per CTA, eight slices
     ts = capi.decode_geometry(Hq, cfg.num_kv_heads, D, capi.BF16, batch=B)["token_slices"]
-    assert ts == {(1, 70): 1, (1, 37): 2, (8, 37): 8}[(tp, batch)]
+    if os.environ.get("B200ATTN_NO_NARROW") != "1":   # (the switch keeps the widest rows for every batch size)
+        assert ts == {(1, 70): 1, (1, 37): 2, (8, 37): 8}[(tp, batch)]
 
     def run(phases, o, lse):
         torch.ops.b200attn.decode(q3, w.k_pool, w.v_pool, o, lse, backend.plan_buf, w.req_to_token,
