@@ -56,6 +56,9 @@ def main():
     ap.add_argument("--steps", type=int, default=20)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--sdpa", action="store_true")
+    ap.add_argument("--flashinfer", action="store_true",
+                    help="also time flashinfer's BatchPrefillWithPagedKVCacheWrapper on the same paged pool (the reference's "
+                         "prefill route on sm_100, flashinfer_backend.py:155-160, 450-532); a competitor, not an oracle")
     args = ap.parse_args()
 
     import numpy as np
@@ -168,6 +171,63 @@ def main():
                                            "note": "torch SDPA on contiguous K/V (no paging, no KV store)"}
             except Exception as e:  # noqa: BLE001
                 line["sdpa_contiguous"] = {"error": repr(e)[:200]}
+        if args.flashinfer and not fp8:
+            # the same requests through flashinfer's paged prefill: kv list = the request's prefix + new slots
+            # (req_to_token[req, :prefix + extend], the new tokens stored by the step above), causal, page_size 1
+            try:
+                import flashinfer
+
+                sl = (w.extend_prefix_lens + w.extend_seq_lens).to(torch.int64)
+                kv_indptr = torch.zeros(B + 1, dtype=torch.int32, device=dev)
+                kv_indptr[1:] = torch.cumsum(sl, 0)
+                rows = torch.repeat_interleave(w.req_pool_indices.to(torch.int64), sl)
+                pos = torch.arange(int(sl.sum()), device=dev) - torch.repeat_interleave(kv_indptr[:-1].to(torch.int64), sl)
+                kv_indices = runner.req_to_token_pool.req_to_token[rows, pos].to(torch.int32)
+                qo_indptr = torch.zeros(B + 1, dtype=torch.int32, device=dev)
+                qo_indptr[1:] = torch.cumsum(w.extend_seq_lens.to(torch.int64), 0)
+                q3 = w.q.view(w.tokens, 32, D).contiguous()
+                kc, vc = w.k_pool.unsqueeze(1), w.v_pool.unsqueeze(1)
+                ours = kernel_only().view(w.tokens, 32, D).float()
+                res = {}
+                for be in ("cutlass", "auto"):
+                    try:
+                        ws = torch.empty(512 << 20, dtype=torch.uint8, device=dev)
+                        fw = flashinfer.BatchPrefillWithPagedKVCacheWrapper(ws, "NHD", backend=be)
+                        fw.plan(qo_indptr, kv_indptr, kv_indices, torch.ones(B, dtype=torch.int32, device=dev), 32, 8, D, 1,
+                                causal=True, sm_scale=w.sm_scale, q_data_type=w.q.dtype, kv_data_type=w.k_pool.dtype)
+                        o = fw.run(q3, (kc, vc))
+                        torch.cuda.synchronize()
+                        for _ in range(3):
+                            fw.run(q3, (kc, vc))
+                        fms = timed(lambda: fw.run(q3, (kc, vc)), args.steps)
+                        res[be] = {"ms": fms, "tflops": flops / (fms * 1e-3) / 1e12,
+                                   "max_abs_diff_vs_b200attn": float((o.float() - ours).abs().max())}
+                    except Exception as e:  # noqa: BLE001 -- a backend that does not run here is recorded
+                        res[be] = {"error": repr(e)[:200]}
+                if int(w.extend_prefix_lens.sum()) == 0:
+                    # no cached prefix: the reference's sm_100 route for the extend part is the RAGGED wrapper with
+                    # backend="cutlass" (flashinfer_backend.py:155-160) on contiguous k / v of the new tokens
+                    k3 = w.k.view(w.tokens, 8, D).contiguous()
+                    v3 = w.v.view(w.tokens, 8, D).contiguous()
+                    for be in ("cutlass", "auto"):
+                        try:
+                            ws = torch.empty(512 << 20, dtype=torch.uint8, device=dev)
+                            rw = flashinfer.BatchPrefillWithRaggedKVCacheWrapper(ws, "NHD", backend=be)
+                            rw.plan(qo_indptr, qo_indptr, 32, 8, D, causal=True, sm_scale=w.sm_scale,
+                                    q_data_type=w.q.dtype, kv_data_type=w.q.dtype)
+                            o = rw.run(q3, k3, v3)
+                            torch.cuda.synchronize()
+                            for _ in range(3):
+                                rw.run(q3, k3, v3)
+                            fms = timed(lambda: rw.run(q3, k3, v3), args.steps)
+                            res["ragged_" + be] = {"ms": fms, "tflops": flops / (fms * 1e-3) / 1e12,
+                                                   "max_abs_diff_vs_b200attn": float((o.float() - ours).abs().max())}
+                        except Exception as e:  # noqa: BLE001
+                            res["ragged_" + be] = {"error": repr(e)[:200]}
+                line["flashinfer_paged_prefill"] = {"version": flashinfer.__version__, "backends": res,
+                                                    "note": "run() only (no KV store), plan() outside the timed region, page_size 1"}
+            except Exception as e:  # noqa: BLE001
+                line["flashinfer_paged_prefill"] = {"error": repr(e)[:200]}
         print(json.dumps(line), flush=True)
         del w, runner, backend
         torch.cuda.empty_cache()
