@@ -161,6 +161,7 @@ extern "C" __attribute__((visibility("default"))) int b200attn_decode(const b200
   p.cp_async = g.cp_async;
   p.swizzle = g.swizzle;
   p.kv_split = g.kv_split;
+  p.subs = g.subs;
   p.xch_off = a->phases == 0 ? g.xch_off : 0;  // K2 + K3 as separate launches keep every slice in the workspace
   p.unit_shift = 0;
   while ((16 << p.unit_shift) < g.row_bytes) ++p.unit_shift;

@@ -55,6 +55,8 @@ struct Geometry {
   int swizzle;       // cp.async path: unpadded rows, 16-byte unit u of row r at u ^ (r & 7)
   int xch_off;       // byte offset of the slice-exchange area (whole requests merge their ts token slices
                      // inside the CTA), 0 = none
+  int subs;          // 16-token sub-chunks per consumer warp and chunk: 2 for fp8 pools with <= 4 token slices (a slot
+                     // then carries the bytes of a 16-bit one and the per-slot costs halve), else 1
   int kv_split;      // 1: a pipeline slot holds the K rows OR the V rows of a chunk (slots alternate K, V, K, ...):
                      // head_dim 256 on a 16-bit pool, where a K + V stage is 129 KB and only one would fit
 };
@@ -88,6 +90,10 @@ inline bool no_balance() {   // B200ATTN_NO_BALANCE=1: equal static ranges whate
 }
 inline bool no_narrow() {   // B200ATTN_NO_NARROW=1: small batches keep the widest rows (the default geometry)
   static const bool v = env_flag("B200ATTN_NO_NARROW");
+  return v;
+}
+inline bool no_subs() {   // B200ATTN_NO_SUBS=1: fp8 chunks keep one 16-token sub-chunk per warp
+  static const bool v = env_flag("B200ATTN_NO_SUBS");
   return v;
 }
 inline bool no_xch() {
@@ -126,7 +132,8 @@ inline bool make_geometry(int hq, int hkv, int d, int kv_dtype, Geometry* g, int
   g->ts = kConsumerWarps / hc;
   g->ng = hkv / hc;
   g->group = group;
-  g->chunk_tokens = 16 * g->ts;
+  g->subs = (e == 1 && 32 * g->ts <= 128 && !no_subs()) ? 2 : 1;   // (chunks hold at most 128 tokens)
+  g->chunk_tokens = 16 * g->ts * g->subs;
   g->row_bytes = hc * d * e;
   // (the cp.async issue loop addresses 16-byte units by shifts: power-of-two rows only; 96- / 80-wide heads go as bulk copies)
   g->cp_async = g->row_bytes <= cp_async_max_row() && (g->row_bytes & (g->row_bytes - 1)) == 0;

@@ -56,6 +56,7 @@ struct DecodeParams {
   int32_t swizzle;               // 1: stage rows unpadded, 16-byte unit u of row r at u ^ (r & 7) (cp.async path)
   int32_t xch_off;               // smem offset of the slice-exchange area (0 = none): whole requests merge in the CTA
   int32_t kv_split;              // 1: pipeline slots alternate K rows / V rows of a chunk (stage_bytes = one tensor)
+  int32_t subs;                  // 16-token sub-chunks per warp and chunk (chunk_tokens = 16 * ts * subs)
   float scale_log2;              // sm_scale * k_scale * log2(e)
   float sm_scale_k;              // sm_scale * k_scale
   float logit_cap;
@@ -709,60 +710,81 @@ __global__ void __launch_bounds__(kThreads, 1) decode_kernel(const DecodeParams 
       B200_TR_DEP(TR_K_FULL, 0.f);
       const uint32_t sbase = stage0 + stage * p.stage_bytes;
 
-      // ---- S^T = K . Q^T : 16 tokens x 8 (16) heads ----
-      // (two accumulators per tile, even / odd k steps: the dependent HMMA chain is half as long)
-      float s[NH][4], sb[NH][4];
-#pragma unroll
-      for (int nh = 0; nh < NH; ++nh) {
-        s[nh][0] = s[nh][1] = s[nh][2] = s[nh][3] = 0.f;
-        sb[nh][0] = sb[nh][1] = sb[nh][2] = sb[nh][3] = 0.f;
-      }
-      if constexpr (!FP8) {
-#pragma unroll
-        for (int ks = 0; ks < MT; ++ks) {
-          uint32_t a[4];
-          ldsm_x4(sbase + k_base + ((32u * ks) ^ k_x), a);
-#pragma unroll
-          for (int nh = 0; nh < NH; ++nh)
-            mma16816<HALF>((ks & 1) ? sb[nh] : s[nh], a[0], a[1], a[2], a[3], qb[nh][ks][0], qb[nh][ks][1]);
-        }
-      } else {
-#pragma unroll
-        for (int u2 = 0; u2 < MT / 2; ++u2) {
-          uint32_t kf[4], a[4];
-          ldsm_x4(sbase + k_base + ((32u * u2) ^ k_x), kf);
-          e4m3x4_to_f16x2x2(kf[0], a[0], a[2]);
-          e4m3x4_to_f16x2x2(kf[1], a[1], a[3]);
-#pragma unroll
-          for (int nh = 0; nh < NH; ++nh) mma16816<true>(s[nh], a[0], a[1], a[2], a[3], qb[nh][2 * u2][0], qb[nh][2 * u2][1]);
-          e4m3x4_to_f16x2x2(kf[2], a[0], a[2]);
-          e4m3x4_to_f16x2x2(kf[3], a[1], a[3]);
-#pragma unroll
-          for (int nh = 0; nh < NH; ++nh)
-            mma16816<true>(sb[nh], a[0], a[1], a[2], a[3], qb[nh][2 * u2 + 1][0], qb[nh][2 * u2 + 1][1]);
-        }
-      }
-#pragma unroll
-      for (int nh = 0; nh < NH; ++nh)
-#pragma unroll
-        for (int e = 0; e < 4; ++e) s[nh][e] += sb[nh][e];
+      // A chunk holds SUBS sub-chunks of 16 tokens per warp (fp8 pools with <= 4 token slices: 2, so that a slot
+      // is as many BYTES as a 16-bit one and the per-slot costs -- barrier wait, arrive, index loads -- are paid
+      // once per 64 KB, and the two sub-chunks' S / softmax / P.V chains interleave in one basic block).
+      // Sub-chunk u of warp (h, slice): stage rows (u * ts + slice) * 16 ...
+      auto chunk_body = [&](auto subs_tag) {
+      constexpr int SUBS = decltype(subs_tag)::value;
+      const uint32_t sub_stride = static_cast<uint32_t>(p.ts) * 16u * p.row_stride;
 
-      B200_TR_DEP(TR_K_QK, s[0][0]);
-      // ---- logit cap, tail mask ----
-      if (cap) {
+      // ---- S^T = K . Q^T : 16 tokens x 8 (16) heads per sub-chunk ----
+      // (two accumulators per tile, even / odd k steps: the dependent HMMA chain is half as long)
+      float s[SUBS][NH][4], sb[SUBS][NH][4];
+#pragma unroll
+      for (int u = 0; u < SUBS; ++u)
+#pragma unroll
+        for (int nh = 0; nh < NH; ++nh) {
+          s[u][nh][0] = s[u][nh][1] = s[u][nh][2] = s[u][nh][3] = 0.f;
+          sb[u][nh][0] = sb[u][nh][1] = sb[u][nh][2] = sb[u][nh][3] = 0.f;
+        }
+#pragma unroll
+      for (int u = 0; u < SUBS; ++u) {
+        const uint32_t kb = sbase + k_base + u * sub_stride;
+        if constexpr (!FP8) {
+#pragma unroll
+          for (int ks = 0; ks < MT; ++ks) {
+            uint32_t a[4];
+            ldsm_x4(kb + ((32u * ks) ^ k_x), a);
+#pragma unroll
+            for (int nh = 0; nh < NH; ++nh)
+              mma16816<HALF>((ks & 1) ? sb[u][nh] : s[u][nh], a[0], a[1], a[2], a[3], qb[nh][ks][0], qb[nh][ks][1]);
+          }
+        } else {
+#pragma unroll
+          for (int u2 = 0; u2 < MT / 2; ++u2) {
+            uint32_t kf[4], a[4];
+            ldsm_x4(kb + ((32u * u2) ^ k_x), kf);
+            e4m3x4_to_f16x2x2(kf[0], a[0], a[2]);
+            e4m3x4_to_f16x2x2(kf[1], a[1], a[3]);
+#pragma unroll
+            for (int nh = 0; nh < NH; ++nh)
+              mma16816<true>(s[u][nh], a[0], a[1], a[2], a[3], qb[nh][2 * u2][0], qb[nh][2 * u2][1]);
+            e4m3x4_to_f16x2x2(kf[2], a[0], a[2]);
+            e4m3x4_to_f16x2x2(kf[3], a[1], a[3]);
+#pragma unroll
+            for (int nh = 0; nh < NH; ++nh)
+              mma16816<true>(sb[u][nh], a[0], a[1], a[2], a[3], qb[nh][2 * u2 + 1][0], qb[nh][2 * u2 + 1][1]);
+          }
+        }
+      }
+#pragma unroll
+      for (int u = 0; u < SUBS; ++u)
 #pragma unroll
         for (int nh = 0; nh < NH; ++nh)
 #pragma unroll
-          for (int e = 0; e < 4; ++e) s[nh][e] = p.logit_cap * tanhf(s[nh][e] * cap_pre);
+          for (int e = 0; e < 4; ++e) s[u][nh][e] += sb[u][nh][e];
+
+      B200_TR_DEP(TR_K_QK, s[0][0][0]);
+      // ---- logit cap, tail mask ----
+      if (cap) {
+#pragma unroll
+        for (int u = 0; u < SUBS; ++u)
+#pragma unroll
+          for (int nh = 0; nh < NH; ++nh)
+#pragma unroll
+            for (int e = 0; e < 4; ++e) s[u][nh][e] = p.logit_cap * tanhf(s[u][nh][e] * cap_pre);
       }
-      const int t0 = lc * T + tsi * 16;   // token of the warp's row 0
+      const int t0 = lc * T + tsi * 16;   // token of the warp's row 0 in sub-chunk 0 (sub-chunk u: + u * ts * 16)
       const bool tail = (lc + 1) * T > S;
       if (tail) {
 #pragma unroll
-        for (int nh = 0; nh < NH; ++nh) {
-          if (t0 + g >= S) s[nh][0] = s[nh][1] = -CUDART_INF_F;
-          if (t0 + tok_hi >= S) s[nh][2] = s[nh][3] = -CUDART_INF_F;
-        }
+        for (int u = 0; u < SUBS; ++u)
+#pragma unroll
+          for (int nh = 0; nh < NH; ++nh) {
+            if (t0 + u * p.ts * 16 + g >= S) s[u][nh][0] = s[u][nh][1] = -CUDART_INF_F;
+            if (t0 + u * p.ts * 16 + tok_hi >= S) s[u][nh][2] = s[u][nh][3] = -CUDART_INF_F;
+          }
       }
 
       // ---- online softmax over the token dimension, with a lazily updated reference ----
@@ -771,20 +793,24 @@ __global__ void __launch_bounds__(kThreads, 1) decode_kernel(const DecodeParams 
       // chunk, tools/trace_decode.py) is only taken on a piece's first chunk and when some logit rises more than
       // 2^8 above the reference (P <= 256 fits f16 / bf16 with the same relative precision; l and O are fp32).
       // Which path ran does not change the mathematics: o = sum P v / sum P and lse = ref + log sum P for any ref.
-      float pr[NH][4];
+      float pr[SUBS][NH][4];
       bool far = lc == lc0;
 #pragma unroll
-      for (int nh = 0; nh < NH; ++nh)
+      for (int u = 0; u < SUBS; ++u)
 #pragma unroll
-        for (int e = 0; e < 4; ++e) {
-          pr[nh][e] = fmaf(s[nh][e], c, -mc[2 * nh + (e & 1)]);
-          far |= pr[nh][e] > 8.f;
-        }
+        for (int nh = 0; nh < NH; ++nh)
+#pragma unroll
+          for (int e = 0; e < 4; ++e) {
+            pr[u][nh][e] = fmaf(s[u][nh][e], c, -mc[2 * nh + (e & 1)]);
+            far |= pr[u][nh][e] > 8.f;
+          }
       if (__any_sync(0xffffffffu, far)) {
 #pragma unroll
         for (int k = 0; k < HPT; ++k) {
           const int nh = k >> 1, e = k & 1;
-          float mx = fmaxf(s[nh][e], s[nh][e + 2]);
+          float mx = fmaxf(s[0][nh][e], s[0][nh][e + 2]);
+#pragma unroll
+          for (int u = 1; u < SUBS; ++u) mx = fmaxf(mx, fmaxf(s[u][nh][e], s[u][nh][e + 2]));
           mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, 4));
           mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, 8));
           mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, 16));
@@ -794,8 +820,11 @@ __global__ void __launch_bounds__(kThreads, 1) decode_kernel(const DecodeParams 
           m[k] = mn;
           mc[k] = mr * c;
           l[k] *= corr;
-          pr[nh][e] = fmaf(s[nh][e], c, -mc[k]);
-          pr[nh][e + 2] = fmaf(s[nh][e + 2], c, -mc[k]);
+#pragma unroll
+          for (int u = 0; u < SUBS; ++u) {
+            pr[u][nh][e] = fmaf(s[u][nh][e], c, -mc[k]);
+            pr[u][nh][e + 2] = fmaf(s[u][nh][e + 2], c, -mc[k]);
+          }
 #pragma unroll
           for (int t = 0; t < MT; ++t) {
             o[nh][t][e] *= corr;
@@ -804,27 +833,36 @@ __global__ void __launch_bounds__(kThreads, 1) decode_kernel(const DecodeParams 
         }
       }
 #pragma unroll
-      for (int k = 0; k < HPT; ++k) {
-        const int nh = k >> 1, e = k & 1;
-        pr[nh][e] = fast_exp2(pr[nh][e]);
-        pr[nh][e + 2] = fast_exp2(pr[nh][e + 2]);
-        l[k] += pr[nh][e] + pr[nh][e + 2];
-      }
+      for (int u = 0; u < SUBS; ++u)
+#pragma unroll
+        for (int k = 0; k < HPT; ++k) {
+          const int nh = k >> 1, e = k & 1;
+          pr[u][nh][e] = fast_exp2(pr[u][nh][e]);
+          pr[u][nh][e + 2] = fast_exp2(pr[u][nh][e + 2]);
+          l[k] += pr[u][nh][e] + pr[u][nh][e + 2];
+        }
 
       // ---- P^T (B operand): pack [token row][heads 2j, 2j+1], transpose 8x8 -> [head g][k slots 2j, 2j+1] ----
-      uint32_t pb[NH][2];
+      uint32_t pb[SUBS][NH][2];
 #pragma unroll
-      for (int nh = 0; nh < NH; ++nh) {
-        pb[nh][0] = movmatrix_trans(pack2<HALF>(pr[nh][0], pr[nh][1]));
-        pb[nh][1] = movmatrix_trans(pack2<HALF>(pr[nh][2], pr[nh][3]));
-      }
-      B200_TR_DEP(TR_K_SOFTMAX, __uint_as_float(pb[0][1]));
+      for (int u = 0; u < SUBS; ++u)
+#pragma unroll
+        for (int nh = 0; nh < NH; ++nh) {
+          pb[u][nh][0] = movmatrix_trans(pack2<HALF>(pr[u][nh][0], pr[u][nh][1]));
+          pb[u][nh][1] = movmatrix_trans(pack2<HALF>(pr[u][nh][2], pr[u][nh][3]));
+        }
+      B200_TR_DEP(TR_K_SOFTMAX, __uint_as_float(pb[0][0][1]));
       // V fragments of masked tail tokens are zeroed: the smem rows behind them hold stale bytes of another
       // request (0 * inf would poison this one).  Only the tail chunk pays the masks.
-      uint32_t vm_lo = 0xffffffffu, vm_hi = 0xffffffffu;
-      if (tail) {
-        vm_lo = (t0 + vt0 < S ? 0x0000ffffu : 0u) | (t0 + vt1 < S ? 0xffff0000u : 0u);
-        vm_hi = (t0 + vt2 < S ? 0x0000ffffu : 0u) | (t0 + vt3 < S ? 0xffff0000u : 0u);
+      uint32_t vm_lo[SUBS], vm_hi[SUBS];
+#pragma unroll
+      for (int u = 0; u < SUBS; ++u) {
+        vm_lo[u] = vm_hi[u] = 0xffffffffu;
+        if (tail) {
+          const int tu = t0 + u * p.ts * 16;
+          vm_lo[u] = (tu + vt0 < S ? 0x0000ffffu : 0u) | (tu + vt1 < S ? 0xffff0000u : 0u);
+          vm_hi[u] = (tu + vt2 < S ? 0x0000ffffu : 0u) | (tu + vt3 < S ? 0xffff0000u : 0u);
+        }
       }
 
       // K and V in separate slots: the K slot is done with (its fragments are in registers), the V rows of the
@@ -844,36 +882,47 @@ __global__ void __launch_bounds__(kThreads, 1) decode_kernel(const DecodeParams 
       // ---- O^T += V^T . P^T ----
       auto pv_mma = [&](auto tail_tag) {
         constexpr bool TAIL = decltype(tail_tag)::value;
-        const uint32_t mlo = TAIL ? vm_lo : 0xffffffffu, mhi = TAIL ? vm_hi : 0xffffffffu;
-        if constexpr (!FP8) {
 #pragma unroll
-          for (int t = 0; t < MT; ++t) {
-            uint32_t a[4];
-            ldsm_x4_trans(sbase_v + v_base + ((32u * t) ^ v_x), a);
+        for (int u = 0; u < SUBS; ++u) {
+          const uint32_t mlo = TAIL ? vm_lo[u] : 0xffffffffu, mhi = TAIL ? vm_hi[u] : 0xffffffffu;
+          const uint32_t vb = sbase_v + v_base + u * sub_stride;
+          if constexpr (!FP8) {
 #pragma unroll
-            for (int nh = 0; nh < NH; ++nh)
-              mma16816<HALF>(o[nh][t], a[0] & mlo, a[1] & mlo, a[2] & mhi, a[3] & mhi, pb[nh][0], pb[nh][1]);
-          }
-        } else {
+            for (int t = 0; t < MT; ++t) {
+              uint32_t a[4];
+              ldsm_x4_trans(vb + ((32u * t) ^ v_x), a);
 #pragma unroll
-          for (int t2 = 0; t2 < MT / 2; ++t2) {
-            uint32_t vf[4], a[4];
-            ldsm8_x2_trans(sbase_v + v_base + ((32u * t2) ^ v_x), vf);
-            e4m3x4_to_f16x2x2(vf[0], a[0], a[2]);
-            e4m3x4_to_f16x2x2(vf[1], a[1], a[3]);
+              for (int nh = 0; nh < NH; ++nh)
+                mma16816<HALF>(o[nh][t], a[0] & mlo, a[1] & mlo, a[2] & mhi, a[3] & mhi, pb[u][nh][0], pb[u][nh][1]);
+            }
+          } else {
 #pragma unroll
-            for (int nh = 0; nh < NH; ++nh)
-              mma16816<true>(o[nh][2 * t2], a[0] & mlo, a[1] & mlo, a[2] & mhi, a[3] & mhi, pb[nh][0], pb[nh][1]);
-            e4m3x4_to_f16x2x2(vf[2], a[0], a[2]);
-            e4m3x4_to_f16x2x2(vf[3], a[1], a[3]);
+            for (int t2 = 0; t2 < MT / 2; ++t2) {
+              uint32_t vf[4], a[4];
+              ldsm8_x2_trans(vb + ((32u * t2) ^ v_x), vf);
+              e4m3x4_to_f16x2x2(vf[0], a[0], a[2]);
+              e4m3x4_to_f16x2x2(vf[1], a[1], a[3]);
 #pragma unroll
-            for (int nh = 0; nh < NH; ++nh)
-              mma16816<true>(o[nh][2 * t2 + 1], a[0] & mlo, a[1] & mlo, a[2] & mhi, a[3] & mhi, pb[nh][0], pb[nh][1]);
+              for (int nh = 0; nh < NH; ++nh)
+                mma16816<true>(o[nh][2 * t2], a[0] & mlo, a[1] & mlo, a[2] & mhi, a[3] & mhi, pb[u][nh][0], pb[u][nh][1]);
+              e4m3x4_to_f16x2x2(vf[2], a[0], a[2]);
+              e4m3x4_to_f16x2x2(vf[3], a[1], a[3]);
+#pragma unroll
+              for (int nh = 0; nh < NH; ++nh)
+                mma16816<true>(o[nh][2 * t2 + 1], a[0] & mlo, a[1] & mlo, a[2] & mhi, a[3] & mhi, pb[u][nh][0], pb[u][nh][1]);
+            }
           }
         }
       };
       if (tail) pv_mma(std::true_type{}); else pv_mma(std::false_type{});
       B200_TR_DEP(TR_K_PV, o[0][MT - 1][0]);
+      };   // chunk_body
+      if constexpr (FP8) {
+        if (p.subs == 2) chunk_body(std::integral_constant<int, 2>{});
+        else chunk_body(std::integral_constant<int, 1>{});
+      } else {
+        chunk_body(std::integral_constant<int, 1>{});
+      }
       __syncwarp();
       if (lane == 0) mbar_arrive(bar_empty + stage * 8);
       B200_TR_DEP(TR_K_END, 0.f);

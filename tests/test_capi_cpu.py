@@ -93,7 +93,8 @@ def test_geometry_table():
     g = capi.decode_geometry(8, 1, 128, capi.BF16)        # C4 at TP8: one kv head per rank
     assert (g["heads_per_cta"], g["token_slices"], g["chunk_tokens"]) == (1, 8, 128)
     g = capi.decode_geometry(32, 8, 128, capi.FP8_E4M3)   # C3
-    assert g["stages"] == 6 and g["smem_bytes"] <= 227 * 1024
+    # fp8: two 16-token sub-chunks per warp and chunk, so a slot carries the bytes of a 16-bit one
+    assert g["chunk_tokens"] == 32 and g["stages"] == 3 and g["smem_bytes"] <= 227 * 1024
     g = capi.decode_geometry(32, 8, 64, capi.BF16, batch=16)   # C1: few requests -> 2 heads per CTA, 256-byte rows
     assert (g["heads_per_cta"], g["token_slices"], g["head_groups"], g["chunk_tokens"]) == (2, 4, 4, 64)
     g = capi.decode_geometry(32, 8, 64, capi.BF16, batch=64)   # enough requests: the wide rows stay
