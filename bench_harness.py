@@ -11,7 +11,8 @@ import torch
 
 import synth
 
-_TORCH_KV = {"bf16": torch.bfloat16, "f16": torch.float16, "fp8_e4m3": torch.float8_e4m3fn}
+_TORCH_KV = {"bf16": torch.bfloat16, "f16": torch.float16, "fp8_e4m3": torch.float8_e4m3fn,
+             "fp8_e5m2": torch.float8_e5m2}
 
 
 def make_runner(w: synth.Workload, device, tp_size: int = 1):
@@ -40,7 +41,7 @@ def make_layer(w: synth.Workload, logit_cap: float = 0.0, with_scales: bool = Tr
     c = w.cfg
     layer = b200attn.AttnLayer(c.num_q_heads, c.head_dim, w.sm_scale, c.num_kv_heads, layer_id=0,
                                logit_cap=logit_cap)
-    if c.kv_dtype == "fp8_e4m3" and with_scales:
+    if c.kv_dtype.startswith("fp8") and with_scales:
         dev = w.k_pool.device
         layer.k_scale = torch.tensor(c.k_scale, dtype=torch.float32, device=dev)
         layer.v_scale = torch.tensor(c.v_scale, dtype=torch.float32, device=dev)

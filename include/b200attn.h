@@ -62,7 +62,9 @@ enum {
   B200ATTN_BF16 = 0,
   B200ATTN_F16 = 1,
   B200ATTN_FP8_E4M3 = 2, /* torch.float8_e4m3fn, stored as raw bytes (uint8 pool) */
-  B200ATTN_F32 = 3       /* b200attn_merge_states only */
+  B200ATTN_F32 = 3,      /* b200attn_merge_states only */
+  B200ATTN_FP8_E5M2 = 4  /* ABI 6: torch.float8_e5m2 (--kv-cache-dtype fp8_e5m2, server_args.py:828-833), raw bytes;
+                            KV store and decode; extend returns B200ATTN_E_UNSUPPORTED */
 };
 
 /* Width of the seq_lens / req_pool_indices arrays (int64 eager, int32 under
@@ -102,7 +104,7 @@ typedef struct {
   int32_t head_dim;            /* K head dim */
   int32_t v_head_dim;          /* V head dim */
   int32_t src_dtype;           /* B200ATTN_BF16 | B200ATTN_F16 */
-  int32_t pool_dtype;          /* same as src, or B200ATTN_FP8_E4M3 */
+  int32_t pool_dtype;          /* same as src, or B200ATTN_FP8_E4M3 / B200ATTN_FP8_E5M2 */
   int32_t scale_mode;          /* B200ATTN_SCALE_*; ignored unless pool is fp8 */
   int32_t mutate_src;          /* 1: write x/scale back into k/v (div_ is in place) */
   float k_scale, v_scale;      /* host scales (used when *_scale_ptr is NULL) */
@@ -209,7 +211,7 @@ typedef struct {
   int32_t head_dim;
   int32_t v_head_dim;
   int32_t q_dtype;             /* B200ATTN_BF16 | B200ATTN_F16 */
-  int32_t kv_dtype;            /* q_dtype or B200ATTN_FP8_E4M3 */
+  int32_t kv_dtype;            /* q_dtype, B200ATTN_FP8_E4M3 or B200ATTN_FP8_E5M2 */
   float sm_scale;              /* layer.scaling */
   float logit_cap;             /* 0 disables; cap * tanh(x / cap) otherwise */
   float k_scale;               /* fp8 dequant: K = fp8 * k_scale (1.0 for 16-bit pools) */

@@ -45,7 +45,7 @@ def store_kv(k_pool: torch.Tensor, v_pool: torch.Tensor, loc: torch.Tensor, cach
     """
     if loc.dtype != torch.int64:
         loc = loc.to(torch.int64)
-    fp8 = k_pool.dtype in (torch.uint8, torch.float8_e4m3fn)
+    fp8 = k_pool.dtype in (torch.uint8, torch.float8_e4m3fn, torch.float8_e5m2)
     ks = vs = kt = vt = None
     mode = capi.SCALE_NONE
     if fp8 and (k_scale is not None or v_scale is not None):
@@ -79,7 +79,7 @@ def rope_store_kv(q: torch.Tensor, k: torch.Tensor, v: Optional[torch.Tensor], p
     if loc is not None:
         if loc.dtype != torch.int64:
             loc = loc.to(torch.int64)
-        fp8 = k_pool.dtype in (torch.uint8, torch.float8_e4m3fn)
+        fp8 = k_pool.dtype in (torch.uint8, torch.float8_e4m3fn, torch.float8_e5m2)
         if fp8 and (k_scale is not None or v_scale is not None):
             tensors = isinstance(k_scale, torch.Tensor) or isinstance(v_scale, torch.Tensor)
             mode = capi.SCALE_TRUE_DIV if tensors else capi.SCALE_RECIP_MUL
@@ -484,7 +484,7 @@ class B200AttnBackend(AttentionBackend):
             raise RuntimeError("B200AttnBackend.forward_decode: init_forward_metadata was not run for this batch")
         k_scale = getattr(layer, "k_scale_float", None)
         v_scale = getattr(layer, "v_scale_float", None)
-        fp8 = self.kv_dtype == capi.FP8_E4M3
+        fp8 = self.kv_dtype in (capi.FP8_E4M3, capi.FP8_E5M2)
         torch.ops.b200attn.decode(
             q.view(bs, layer.tp_q_head_num, layer.qk_head_dim), k_pool, v_pool,
             o.view(bs, layer.tp_q_head_num, layer.v_head_dim),
@@ -502,14 +502,20 @@ class B200AttnBackend(AttentionBackend):
         ``req_to_token`` and ``out_cache_loc`` -- goes through ``full_to_swa_index_mapping`` first (the reference
         translates a materialised ``kv_indices`` list, flashinfer_backend.py:754, 1001; the decode kernel applies
         the map to the ids it reads in place instead)."""
+        smap = None
         if not self.is_swa_pool:
             start = getattr(pool, "start_layer", 0) or 0
-            return pool.k_buffer[layer.layer_id - start], pool.v_buffer[layer.layer_id - start], None
-        pid, is_swa = pool.layers_mapping[layer.layer_id]
-        sub = pool.swa_kv_pool if is_swa else pool.full_kv_pool
-        start = getattr(sub, "start_layer", 0) or 0
-        smap = pool.full_to_swa_index_mapping if is_swa else None
-        return sub.k_buffer[pid - start], sub.v_buffer[pid - start], smap
+            kb, vb = pool.k_buffer[layer.layer_id - start], pool.v_buffer[layer.layer_id - start]
+        else:
+            pid, is_swa = pool.layers_mapping[layer.layer_id]
+            sub = pool.swa_kv_pool if is_swa else pool.full_kv_pool
+            start = getattr(sub, "start_layer", 0) or 0
+            smap = pool.full_to_swa_index_mapping if is_swa else None
+            kb, vb = sub.k_buffer[pid - start], sub.v_buffer[pid - start]
+        if self.kv_dtype == capi.FP8_E5M2 and kb.dtype == torch.uint8:
+            # fp8 pools are stored as uint8 (memory_pool.py:114-118): the e5m2 kind travels with the view
+            kb, vb = kb.view(torch.float8_e5m2), vb.view(torch.float8_e5m2)
+        return kb, vb, smap
 
     def last_lse(self, bs: int) -> torch.Tensor:
         """ln sum exp(scaled logits) of the most recent forward_decode, ``[bs, heads]``."""
@@ -527,6 +533,9 @@ class B200AttnBackend(AttentionBackend):
             raise NotImplementedError("B200AttnBackend: cross attention is not supported")
         if layer.qk_head_dim != layer.v_head_dim:
             raise NotImplementedError("B200AttnBackend: qk_head_dim != v_head_dim is not supported")
+        if self.kv_dtype == capi.FP8_E5M2:
+            raise NotImplementedError("B200AttnBackend: extend over an fp8_e5m2 pool is not implemented (KV store and "
+                                      "decode are): construct the backend with prefill_backend=")
         fp8 = self.kv_dtype == capi.FP8_E4M3
         q = q.reshape(-1, layer.tp_q_head_num * layer.qk_head_dim)
         o = torch.empty_like(q)

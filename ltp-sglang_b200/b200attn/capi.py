@@ -16,7 +16,7 @@ LIB_PATH = Path(os.environ.get("B200ATTN_LIB", _HERE / "libb200attn.so"))
 # enums (include/b200attn.h)
 OK = 0
 E_INVALID, E_UNSUPPORTED, E_ALIGN, E_CUDA, E_WORKSPACE = -1, -2, -3, -4, -5
-BF16, F16, FP8_E4M3, F32 = 0, 1, 2, 3
+BF16, F16, FP8_E4M3, F32, FP8_E5M2 = 0, 1, 2, 3, 4
 I32, I64 = 0, 1
 SCALE_NONE, SCALE_TRUE_DIV, SCALE_RECIP_MUL = 0, 1, 2
 ABI_VERSION = 6

@@ -106,8 +106,6 @@ class MHATokenToKVPool:
         self.dtype = dtype
         self.device = device
         self.store_dtype = torch.uint8 if dtype in (torch.float8_e5m2, torch.float8_e4m3fn) else dtype
-        if dtype == torch.float8_e5m2:
-            raise NotImplementedError("b200attn: fp8_e5m2 KV cache is not supported (e4m3 only)")
         self.layer_num = layer_num
         self.start_layer = start_layer or 0
         self.head_num = head_num
@@ -137,8 +135,10 @@ class MHATokenToKVPool:
         from .backend import store_kv  # local import: the ops need the built library
 
         layer_id = layer_id_override if layer_id_override is not None else layer.layer_id
-        store_kv(self.k_buffer[layer_id - self.start_layer], self.v_buffer[layer_id - self.start_layer],
-                 loc, cache_k, cache_v, k_scale, v_scale)
+        kb, vb = self.k_buffer[layer_id - self.start_layer], self.v_buffer[layer_id - self.start_layer]
+        if self.dtype == torch.float8_e5m2:
+            kb, vb = kb.view(self.dtype), vb.view(self.dtype)
+        store_kv(kb, vb, loc, cache_k, cache_v, k_scale, v_scale)
 
 
 class SWAKVPool:

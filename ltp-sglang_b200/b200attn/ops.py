@@ -19,7 +19,9 @@ _DT = {
     torch.bfloat16: capi.BF16,
     torch.float16: capi.F16,
     torch.float8_e4m3fn: capi.FP8_E4M3,
-    torch.uint8: capi.FP8_E4M3,  # fp8 pools are stored as uint8 (memory_pool.py:114-118)
+    torch.uint8: capi.FP8_E4M3,  # fp8 pools are stored as uint8 (memory_pool.py:114-118); an e5m2 pool must be
+    #                              passed viewed as torch.float8_e5m2 (the backend does)
+    torch.float8_e5m2: capi.FP8_E5M2,
 }
 _IDX = {torch.int32: capi.I32, torch.int64: capi.I64}
 

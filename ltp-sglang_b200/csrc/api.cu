@@ -100,7 +100,7 @@ extern "C" __attribute__((visibility("default"))) int b200attn_decode(const b200
   if (!a->q || !a->k_pool || !a->v_pool || !a->o || !a->plan || !a->indices || !a->ws_o)
     return B200ATTN_E_INVALID;
   if (a->q_dtype != B200ATTN_BF16 && a->q_dtype != B200ATTN_F16) return B200ATTN_E_UNSUPPORTED;
-  const bool fp8 = a->kv_dtype == B200ATTN_FP8_E4M3;
+  const bool fp8 = is_fp8(a->kv_dtype);
   if (!fp8 && a->kv_dtype != a->q_dtype) return B200ATTN_E_UNSUPPORTED;
   if (a->v_head_dim != a->head_dim) return B200ATTN_E_UNSUPPORTED;
   if (!(a->sm_scale > 0.f) || !(a->k_scale > 0.f) || a->logit_cap < 0.f) return B200ATTN_E_INVALID;
@@ -162,6 +162,7 @@ extern "C" __attribute__((visibility("default"))) int b200attn_decode(const b200
   p.swizzle = g.swizzle;
   p.kv_split = g.kv_split;
   p.subs = g.subs;
+  p.e5m2 = a->kv_dtype == B200ATTN_FP8_E5M2;
   p.xch_off = a->phases == 0 ? g.xch_off : 0;  // K2 + K3 as separate launches keep every slice in the workspace
   p.unit_shift = 0;
   while ((16 << p.unit_shift) < g.row_bytes) ++p.unit_shift;

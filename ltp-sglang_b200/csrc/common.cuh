@@ -104,7 +104,8 @@ inline bool no_xch() {
 // [8 warps][8 rows] float2 (max in log2 units, sum).
 inline int xch_bytes(int group, int d) { return kXchWarps * (d / 8) * group * 4 * 8 + kXchWarps * 8 * 8; }
 
-__host__ __device__ inline int elem_bytes(int dtype) { return dtype == B200ATTN_FP8_E4M3 ? 1 : 2; }
+__host__ __device__ inline bool is_fp8(int dtype) { return dtype == B200ATTN_FP8_E4M3 || dtype == B200ATTN_FP8_E5M2; }
+__host__ __device__ inline int elem_bytes(int dtype) { return is_fp8(dtype) ? 1 : 2; }
 
 // Returns false when the shape has no kernel.
 // `batch` > 0 lets small decode batches trade row width for parallelism: with few (request, head group) pairs
@@ -433,6 +434,17 @@ __device__ __forceinline__ void e4m3x4_to_f16x2x2(uint32_t x, uint32_t& lo, uint
   asm("{\n\t.reg .b16 a, b;\n\tmov.b32 {a, b}, %2;\n\tcvt.rn.f16x2.e4m3x2 %0, a;\n\tcvt.rn.f16x2.e4m3x2 %1, b;\n\t}"
       : "=r"(lo), "=r"(hi)
       : "r"(x));
+}
+
+// Four fp8 bytes -> two f16x2, exact.  e5m2 is the upper byte of an f16: a byte permute places it (PRMT).
+template <bool E5M2>
+__device__ __forceinline__ void fp8x4_to_f16x2x2(uint32_t x, uint32_t& lo, uint32_t& hi) {
+  if constexpr (E5M2) {
+    lo = __byte_perm(x, 0u, 0x1404);   // bytes (0, b0, 0, b1)
+    hi = __byte_perm(x, 0u, 0x3424);   // bytes (0, b2, 0, b3)
+  } else {
+    e4m3x4_to_f16x2x2(x, lo, hi);
+  }
 }
 
 // 8x8 transpose of 16-bit elements across the warp: lane (g, j) gives row g, columns 2j, 2j+1 and receives

@@ -57,6 +57,7 @@ struct DecodeParams {
   int32_t xch_off;               // smem offset of the slice-exchange area (0 = none): whole requests merge in the CTA
   int32_t kv_split;              // 1: pipeline slots alternate K rows / V rows of a chunk (stage_bytes = one tensor)
   int32_t subs;                  // 16-token sub-chunks per warp and chunk (chunk_tokens = 16 * ts * subs)
+  int32_t e5m2;                  // fp8 pools: 1 = float8_e5m2 bytes, 0 = float8_e4m3fn
   float scale_log2;              // sm_scale * k_scale * log2(e)
   float sm_scale_k;              // sm_scale * k_scale
   float logit_cap;
@@ -714,8 +715,9 @@ __global__ void __launch_bounds__(kThreads, 1) decode_kernel(const DecodeParams 
       // is as many BYTES as a 16-bit one and the per-slot costs -- barrier wait, arrive, index loads -- are paid
       // once per 64 KB, and the two sub-chunks' S / softmax / P.V chains interleave in one basic block).
       // Sub-chunk u of warp (h, slice): stage rows (u * ts + slice) * 16 ...
-      auto chunk_body = [&](auto subs_tag) {
+      auto chunk_body = [&](auto subs_tag, auto e5_tag) {
       constexpr int SUBS = decltype(subs_tag)::value;
+      constexpr bool E5M2 = decltype(e5_tag)::value;   // (fp8 pools only)
       const uint32_t sub_stride = static_cast<uint32_t>(p.ts) * 16u * p.row_stride;
 
       // ---- S^T = K . Q^T : 16 tokens x 8 (16) heads per sub-chunk ----
@@ -745,13 +747,13 @@ __global__ void __launch_bounds__(kThreads, 1) decode_kernel(const DecodeParams 
           for (int u2 = 0; u2 < MT / 2; ++u2) {
             uint32_t kf[4], a[4];
             ldsm_x4(kb + ((32u * u2) ^ k_x), kf);
-            e4m3x4_to_f16x2x2(kf[0], a[0], a[2]);
-            e4m3x4_to_f16x2x2(kf[1], a[1], a[3]);
+            fp8x4_to_f16x2x2<E5M2>(kf[0], a[0], a[2]);
+            fp8x4_to_f16x2x2<E5M2>(kf[1], a[1], a[3]);
 #pragma unroll
             for (int nh = 0; nh < NH; ++nh)
               mma16816<true>(s[u][nh], a[0], a[1], a[2], a[3], qb[nh][2 * u2][0], qb[nh][2 * u2][1]);
-            e4m3x4_to_f16x2x2(kf[2], a[0], a[2]);
-            e4m3x4_to_f16x2x2(kf[3], a[1], a[3]);
+            fp8x4_to_f16x2x2<E5M2>(kf[2], a[0], a[2]);
+            fp8x4_to_f16x2x2<E5M2>(kf[3], a[1], a[3]);
 #pragma unroll
             for (int nh = 0; nh < NH; ++nh)
               mma16816<true>(sb[u][nh], a[0], a[1], a[2], a[3], qb[nh][2 * u2 + 1][0], qb[nh][2 * u2 + 1][1]);
@@ -900,13 +902,13 @@ __global__ void __launch_bounds__(kThreads, 1) decode_kernel(const DecodeParams 
             for (int t2 = 0; t2 < MT / 2; ++t2) {
               uint32_t vf[4], a[4];
               ldsm8_x2_trans(vb + ((32u * t2) ^ v_x), vf);
-              e4m3x4_to_f16x2x2(vf[0], a[0], a[2]);
-              e4m3x4_to_f16x2x2(vf[1], a[1], a[3]);
+              fp8x4_to_f16x2x2<E5M2>(vf[0], a[0], a[2]);
+              fp8x4_to_f16x2x2<E5M2>(vf[1], a[1], a[3]);
 #pragma unroll
               for (int nh = 0; nh < NH; ++nh)
                 mma16816<true>(o[nh][2 * t2], a[0] & mlo, a[1] & mlo, a[2] & mhi, a[3] & mhi, pb[u][nh][0], pb[u][nh][1]);
-              e4m3x4_to_f16x2x2(vf[2], a[0], a[2]);
-              e4m3x4_to_f16x2x2(vf[3], a[1], a[3]);
+              fp8x4_to_f16x2x2<E5M2>(vf[2], a[0], a[2]);
+              fp8x4_to_f16x2x2<E5M2>(vf[3], a[1], a[3]);
 #pragma unroll
               for (int nh = 0; nh < NH; ++nh)
                 mma16816<true>(o[nh][2 * t2 + 1], a[0] & mlo, a[1] & mlo, a[2] & mhi, a[3] & mhi, pb[u][nh][0], pb[u][nh][1]);
@@ -918,10 +920,15 @@ __global__ void __launch_bounds__(kThreads, 1) decode_kernel(const DecodeParams 
       B200_TR_DEP(TR_K_PV, o[0][MT - 1][0]);
       };   // chunk_body
       if constexpr (FP8) {
-        if (p.subs == 2) chunk_body(std::integral_constant<int, 2>{});
-        else chunk_body(std::integral_constant<int, 1>{});
+        if (p.e5m2) {
+          if (p.subs == 2) chunk_body(std::integral_constant<int, 2>{}, std::true_type{});
+          else chunk_body(std::integral_constant<int, 1>{}, std::true_type{});
+        } else {
+          if (p.subs == 2) chunk_body(std::integral_constant<int, 2>{}, std::false_type{});
+          else chunk_body(std::integral_constant<int, 1>{}, std::false_type{});
+        }
       } else {
-        chunk_body(std::integral_constant<int, 1>{});
+        chunk_body(std::integral_constant<int, 1>{}, std::false_type{});
       }
       __syncwarp();
       if (lane == 0) mbar_arrive(bar_empty + stage * 8);

@@ -24,6 +24,7 @@ struct StoreParams {
   int32_t mutate;
   float scale[2];
   const float* scale_ptr[2];
+  int32_t e5m2;          // fp8 pools: 1 = float8_e5m2, 0 = float8_e4m3fn
 };
 
 template <typename T, bool FP8, int VEC>
@@ -79,7 +80,7 @@ __global__ void __launch_bounds__(256) kv_store_kernel(StoreParams p) {
                      head * p.dim[which] + col;
       uint8_t y[VEC];
 #pragma unroll
-      for (int e = 0; e < VEC; ++e) y[e] = f32_to_e4m3fn(to_f32<T>(x[e]));
+      for (int e = 0; e < VEC; ++e) y[e] = f32_to_fp8(to_f32<T>(x[e]), p.e5m2 != 0);
       if constexpr (VEC == 8) {
         *reinterpret_cast<uint2*>(dst) = *reinterpret_cast<const uint2*>(y);
       } else {
@@ -111,7 +112,7 @@ extern "C" __attribute__((visibility("default"))) int b200attn_kv_store(const b2
   if (a->n_tokens == 0) return B200ATTN_OK;
   if (!a->k || !a->v || !a->loc || !a->k_pool || !a->v_pool) return B200ATTN_E_INVALID;
   if (a->src_dtype != B200ATTN_BF16 && a->src_dtype != B200ATTN_F16) return B200ATTN_E_UNSUPPORTED;
-  const bool fp8 = a->pool_dtype == B200ATTN_FP8_E4M3;
+  const bool fp8 = a->pool_dtype == B200ATTN_FP8_E4M3 || a->pool_dtype == B200ATTN_FP8_E5M2;
   if (!fp8 && a->pool_dtype != a->src_dtype) return B200ATTN_E_UNSUPPORTED;
   if (fp8 && (a->scale_mode < B200ATTN_SCALE_NONE || a->scale_mode > B200ATTN_SCALE_RECIP_MUL))
     return B200ATTN_E_INVALID;
@@ -139,6 +140,7 @@ extern "C" __attribute__((visibility("default"))) int b200attn_kv_store(const b2
   p.scale[1] = a->v_scale;
   p.scale_ptr[0] = a->k_scale_ptr;
   p.scale_ptr[1] = a->v_scale_ptr;
+  p.e5m2 = a->pool_dtype == B200ATTN_FP8_E5M2;
 
   // 16-byte vectors need 8-element granularity everywhere; otherwise go scalar.
   bool vec = a->head_dim % 8 == 0 && a->v_head_dim % 8 == 0 && aligned16(a->k) &&

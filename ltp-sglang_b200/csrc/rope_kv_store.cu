@@ -31,6 +31,7 @@ struct RopeParams {
   int32_t scale_mode, mutate;
   float scale[2];
   const float* scale_ptr[2];
+  int32_t e5m2;          // fp8 pools: 1 = float8_e5m2
 };
 
 template <typename T>
@@ -63,7 +64,7 @@ __device__ __forceinline__ void pool_store8(const RopeParams& p, int which, T (&
     uint8_t* dst = reinterpret_cast<uint8_t*>(p.pool[which]) + slot * p.pool_stride[which] + head * p.dim + col;
     uint8_t y[8];
 #pragma unroll
-    for (int e = 0; e < 8; ++e) y[e] = f32_to_e4m3fn(to_f32<T>(x[e]));
+    for (int e = 0; e < 8; ++e) y[e] = f32_to_fp8(to_f32<T>(x[e]), p.e5m2 != 0);
     *reinterpret_cast<uint2*>(dst) = *reinterpret_cast<const uint2*>(y);
   } else {
     T* dst = reinterpret_cast<T*>(p.pool[which]) + slot * p.pool_stride[which] + head * p.dim + col;
@@ -177,7 +178,7 @@ extern "C" __attribute__((visibility("default"))) int b200attn_rope_kv_store(con
   if (a->pos_dtype != B200ATTN_I32 && a->pos_dtype != B200ATTN_I64) return B200ATTN_E_INVALID;
   if (s.src_dtype != B200ATTN_BF16 && s.src_dtype != B200ATTN_F16) return B200ATTN_E_UNSUPPORTED;
   const bool save = a->save_kv != 0;
-  const bool fp8 = save && s.pool_dtype == B200ATTN_FP8_E4M3;
+  const bool fp8 = save && (s.pool_dtype == B200ATTN_FP8_E4M3 || s.pool_dtype == B200ATTN_FP8_E5M2);
   if (save) {
     if (!s.v || !s.loc || !s.k_pool || !s.v_pool) return B200ATTN_E_INVALID;
     if (!fp8 && s.pool_dtype != s.src_dtype) return B200ATTN_E_UNSUPPORTED;
@@ -228,6 +229,7 @@ extern "C" __attribute__((visibility("default"))) int b200attn_rope_kv_store(con
   p.neox = a->is_neox != 0;
   p.save_kv = save;
   p.scale_mode = fp8 ? s.scale_mode : B200ATTN_SCALE_NONE;
+  p.e5m2 = save && s.pool_dtype == B200ATTN_FP8_E5M2;
   p.mutate = s.mutate_src;
   p.scale[0] = s.k_scale;
   p.scale[1] = s.v_scale;

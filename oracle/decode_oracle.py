@@ -85,6 +85,38 @@ def f32_to_e4m3fn_bits(x: np.ndarray) -> np.ndarray:
     return out | (sign >> np.uint32(24)).astype(np.uint8)
 
 
+def f32_to_e5m2_bits(x: np.ndarray) -> np.ndarray:
+    """float32 -> float8_e5m2 bits the way torch casts (c10/util/Float8_e5m2.h, what
+    ``MHATokenToKVPool.set_kv_buffer`` runs for ``--kv-cache-dtype fp8_e5m2``, memory_pool.py:385-391): RNE,
+    NOT saturating -- |x| >= 61440 rounds into infinity (0x7C), NaN -> 0x7F, subnormals kept.  Checked against
+    torch on all 65 536 bf16 patterns by tests/test_oracle.py."""
+    x = np.ascontiguousarray(x, dtype=np.float32)
+    bits = x.view(np.uint32).copy()
+    sign = bits & np.uint32(0x80000000)
+    bits ^= sign
+    out = np.zeros(bits.shape, dtype=np.uint8)
+    over = bits >= np.uint32(143 << 23)
+    sub = (~over) & (bits < np.uint32(113 << 23))
+    norm = ~(over | sub)
+    out[over] = np.where(bits[over] > np.uint32(255 << 23), 0x7F, 0x7C).astype(np.uint8)
+    magic = np.uint32(134 << 23)
+    if sub.any():
+        a = bits[sub].view(np.float32) + np.array([magic], dtype=np.uint32).view(np.float32)[0]
+        out[sub] = (a.astype(np.float32).view(np.uint32) - magic).astype(np.uint8)
+    if norm.any():
+        nb = bits[norm].astype(np.uint64)
+        odd = (nb >> 21) & 1
+        nb = (nb + np.uint64(((15 - 127) << 23) & 0xFFFFFFFF) + np.uint64(0xFFFFF) + odd) & np.uint64(0xFFFFFFFF)
+        out[norm] = (nb >> 21).astype(np.uint8)
+    return out | (sign >> np.uint32(24)).astype(np.uint8)
+
+
+def e5m2_bits_to_f32(b: np.ndarray) -> np.ndarray:
+    """float8_e5m2 bits -> float32: the byte is the upper half of an IEEE half (exact)."""
+    h = (np.ascontiguousarray(b, dtype=np.uint8).astype(np.uint16) << np.uint16(8)).view(np.float16)
+    return h.astype(np.float32)
+
+
 _E4M3_TABLE: Optional[np.ndarray] = None
 
 
@@ -142,7 +174,7 @@ def kv_store(k_pool: torch.Tensor, v_pool: torch.Tensor, loc: torch.Tensor, cach
     """
     loc_np = loc.detach().cpu().numpy().astype(np.int64)
     for pool, cache, scale in ((k_pool, cache_k, k_scale), (v_pool, cache_v, v_scale)):
-        if pool.dtype == torch.uint8:
+        if pool.dtype in (torch.uint8, torch.float8_e4m3fn, torch.float8_e5m2):   # (uint8 = e4m3 bytes)
             x = _to_f32(cache)
             if scale is not None and scale_mode != SCALE_NONE:
                 s = np.float32(scale)
@@ -154,8 +186,8 @@ def kv_store(k_pool: torch.Tensor, v_pool: torch.Tensor, loc: torch.Tensor, cach
                     x = x / s
                 x = _round_to(x.astype(np.float32), cache.dtype)
                 cache.copy_(torch.from_numpy(x).to(cache.dtype))
-            bits = f32_to_e4m3fn_bits(x)
-            pool_np = pool.numpy()
+            bits = f32_to_e5m2_bits(x) if pool.dtype == torch.float8_e5m2 else f32_to_e4m3fn_bits(x)
+            pool_np = pool.view(torch.uint8).numpy()
             pool_np[loc_np] = bits  # last write wins for duplicate slots, like index_put
         else:
             assert pool.dtype == cache.dtype
@@ -222,6 +254,8 @@ def draft_decode_kv_indices(req_to_token, req_pool_indices, seq_lens, positions,
 # decode attention (float64 SDPA + lse)
 # --------------------------------------------------------------------------- #
 def pool_to_f32(pool: torch.Tensor) -> np.ndarray:
+    if pool.dtype == torch.float8_e5m2:
+        return e5m2_bits_to_f32(pool.view(torch.uint8).cpu().numpy())
     if pool.dtype in (torch.uint8, torch.float8_e4m3fn):
         return e4m3fn_bits_to_f32(pool.view(torch.uint8).cpu().numpy())
     return _to_f32(pool)

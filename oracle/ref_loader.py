@@ -52,7 +52,7 @@ def load():
     try:
         from sglang.srt.layers.attention.torch_native_backend import TorchNativeAttnBackend
         from sglang.srt.layers.radix_attention import RadixAttention
-        from sglang.srt.mem_cache.memory_pool import MHATokenToKVPool, ReqToTokenPool
+        from sglang.srt.mem_cache.memory_pool import MHATokenToKVPool, ReqToTokenPool, SWAKVPool
         from sglang.srt.model_executor.forward_batch_info import ForwardBatch, ForwardMode
     finally:
         sys.path.pop(0)
@@ -63,6 +63,6 @@ def load():
         sys.modules[name] = cg
     _cache = types.SimpleNamespace(
         TorchNativeAttnBackend=TorchNativeAttnBackend, RadixAttention=RadixAttention,
-        MHATokenToKVPool=MHATokenToKVPool, ReqToTokenPool=ReqToTokenPool,
+        MHATokenToKVPool=MHATokenToKVPool, ReqToTokenPool=ReqToTokenPool, SWAKVPool=SWAKVPool,
         ForwardBatch=ForwardBatch, ForwardMode=ForwardMode)
     return _cache

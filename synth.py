@@ -32,7 +32,7 @@ class Config:
     num_q_heads: int
     num_kv_heads: int
     head_dim: int
-    kv_dtype: str = "bf16"        # "bf16" | "f16" | "fp8_e4m3"
+    kv_dtype: str = "bf16"        # "bf16" | "f16" | "fp8_e4m3" | "fp8_e5m2" (fp8 pools are uint8 byte tensors)
     q_dtype: str = "bf16"
     page_size: int = 1
     ragged: Optional[tuple] = None  # (min_len, max_len): log-uniform lengths
@@ -59,6 +59,7 @@ CONFIGS: Dict[str, Config] = {
 }
 
 _TORCH_DT = {"bf16": torch.bfloat16, "f16": torch.float16}
+_FP8_DT = {"fp8_e4m3": torch.float8_e4m3fn, "fp8_e5m2": torch.float8_e5m2}
 
 
 def shard(cfg: Config, tp_size: int) -> Config:
@@ -104,7 +105,7 @@ class Workload:
     def algorithmic_bytes(self, save_kv: bool = True) -> int:
         """KV read + q + o + (store: read new k/v, write pool rows) + index words."""
         c = self.cfg
-        e_kv = 1 if c.kv_dtype == "fp8_e4m3" else 2
+        e_kv = 1 if c.kv_dtype.startswith("fp8") else 2
         total = self.seq_lens_sum * c.num_kv_heads * 2 * c.head_dim * e_kv
         total += 2 * c.batch * c.num_q_heads * c.head_dim * 2
         if save_kv:
@@ -166,7 +167,7 @@ def make_workload(cfg: Config, device="cpu", max_reqs: Optional[int] = None, sla
     q, k, v = qkv.split([Hq * D, Hkv * D, Hkv * D], dim=-1)
 
     def fill(scale: float) -> torch.Tensor:
-        if cfg.kv_dtype == "fp8_e4m3":
+        if cfg.kv_dtype.startswith("fp8"):
             out = torch.empty((rows, Hkv, D), dtype=torch.uint8, device=dev)
         else:
             out = torch.empty((rows, Hkv, D), dtype=_TORCH_DT[cfg.kv_dtype], device=dev)
@@ -177,8 +178,8 @@ def make_workload(cfg: Config, device="cpu", max_reqs: Optional[int] = None, sla
                 x = torch.zeros((r1 - r0, Hkv, D), device=dev, dtype=torch.float32)
             else:
                 x = torch.randn((r1 - r0, Hkv, D), generator=gen, device=dev, dtype=torch.float32)
-            if cfg.kv_dtype == "fp8_e4m3":
-                out[r0:r1] = (x / scale).to(torch.bfloat16).to(torch.float8_e4m3fn).view(torch.uint8)
+            if cfg.kv_dtype.startswith("fp8"):
+                out[r0:r1] = (x / scale).to(torch.bfloat16).to(_FP8_DT[cfg.kv_dtype]).view(torch.uint8)
             else:
                 out[r0:r1] = x.to(out.dtype)
         return out
@@ -304,7 +305,7 @@ def make_extend_workload(cfg: Config, prefix_lens, extend_lens, device="cpu", ma
     T = int(el.sum())
     qkv = torch.randn((T, (Hq + 2 * Hkv) * D), generator=gen, device=dev, dtype=torch.float32).to(qdt)
     q, k, v = qkv.split([Hq * D, Hkv * D, Hkv * D], dim=-1)
-    fp8 = cfg.kv_dtype == "fp8_e4m3"
+    fp8 = cfg.kv_dtype.startswith("fp8")
     kvdt = torch.uint8 if fp8 else _TORCH_DT[cfg.kv_dtype]   # fp8 pools are stored as raw bytes
     k_pool = torch.empty((rows, Hkv, D), dtype=kvdt, device=dev)
     v_pool = torch.empty((rows, Hkv, D), dtype=kvdt, device=dev)
@@ -314,7 +315,7 @@ def make_extend_workload(cfg: Config, prefix_lens, extend_lens, device="cpu", ma
             r1 = min(rows, r0 + step)
             x = torch.randn((r1 - r0, Hkv, D), generator=gen, device=dev, dtype=torch.float32)
             if fp8:
-                t[r0:r1] = (x / scale).to(torch.bfloat16).to(torch.float8_e4m3fn).view(torch.uint8)
+                t[r0:r1] = (x / scale).to(torch.bfloat16).to(_FP8_DT[cfg.kv_dtype]).view(torch.uint8)
             else:
                 t[r0:r1] = x.to(kvdt)
     return ExtendWorkload(

@@ -30,9 +30,11 @@ def oracle_step(w_cpu: synth.Workload, logit_cap: float = 0.0, save_kv: bool = T
 
     c = w_cpu.cfg
     kp, vp = w_cpu.k_pool.clone(), w_cpu.v_pool.clone()
+    if c.kv_dtype == "fp8_e5m2":   # fp8 pools are byte tensors; the oracle tells the kind by the view (uint8 = e4m3)
+        kp, vp = kp.view(torch.float8_e5m2), vp.view(torch.float8_e5m2)
     k = w_cpu.k.reshape(c.batch, c.num_kv_heads, c.head_dim).clone()
     v = w_cpu.v.reshape(c.batch, c.num_kv_heads, c.head_dim).clone()
-    fp8 = c.kv_dtype == "fp8_e4m3"
+    fp8 = c.kv_dtype.startswith("fp8")
     if save_kv:
         oracle.kv_store(kp, vp, w_cpu.out_cache_loc, k, v, c.k_scale if fp8 else None,
                         c.v_scale if fp8 else None,
@@ -102,7 +104,7 @@ def oracle_extend(w_cpu, causal=True, logit_cap=0.0, custom_mask=None, sliding_w
     c = w_cpu.cfg
     kp, vp = w_cpu.k_pool.clone(), w_cpu.v_pool.clone()
     T = w_cpu.tokens
-    fp8 = c.kv_dtype == "fp8_e4m3"
+    fp8 = c.kv_dtype.startswith("fp8")
     decode_oracle.kv_store(kp, vp, w_cpu.out_cache_loc, w_cpu.k.reshape(T, c.num_kv_heads, c.head_dim).clone(),
                            w_cpu.v.reshape(T, c.num_kv_heads, c.head_dim).clone(),
                            c.k_scale if fp8 else None, c.v_scale if fp8 else None)

@@ -77,9 +77,16 @@ def test_every_attribute_the_backend_reads_exists_in_the_reference(ref):
     missing = {a for a in reads["layer"] if f"self.{a}" not in radix_src and a not in optional}
     assert not missing, f"RadixAttention.__init__ sets no {sorted(missing)}"
     # MHATokenToKVPool: k_buffer / v_buffer / start_layer (memory_pool.py:164-258)
+    # ... and, for the hybrid pool, SWAKVPool's members (memory_pool.py:420-553)
     pool_src = inspect.getsource(ref.MHATokenToKVPool) + inspect.getsource(ref.MHATokenToKVPool.__mro__[1])
-    missing = {a for a in reads["pool"] if f"self.{a}" not in pool_src and not hasattr(ref.MHATokenToKVPool, a)}
-    assert not missing, f"MHATokenToKVPool has no {sorted(missing)}"
+    swa_src = inspect.getsource(ref.SWAKVPool)
+    missing = {a for a in reads["pool"] if f"self.{a}" not in pool_src and not hasattr(ref.MHATokenToKVPool, a)
+               and f"self.{a}" not in swa_src and not hasattr(ref.SWAKVPool, a)}
+    assert not missing, f"neither MHATokenToKVPool nor SWAKVPool has {sorted(missing)}"
+    import b200attn
+    for name in ("get_key_buffer", "get_value_buffer", "get_kv_buffer", "translate_loc_from_full_to_swa", "set_kv_buffer"):
+        assert _params(getattr(ref.SWAKVPool, name))[:2] == _params(getattr(b200attn.SWAKVPool, name))[:2], name
+    assert _params(ref.SWAKVPool.__init__) == _params(b200attn.SWAKVPool.__init__)
 
 
 def test_mirror_classes_cover_the_reference_surface(ref):

@@ -26,7 +26,7 @@ def _bits(t: torch.Tensor) -> np.ndarray:
     t = t.detach().cpu().contiguous()
     if t.dtype in (torch.bfloat16, torch.float16):
         return t.view(torch.int16).numpy().view(np.uint16)
-    if t.dtype in (torch.uint8, torch.float8_e4m3fn):
+    if t.dtype in (torch.uint8, torch.float8_e4m3fn, torch.float8_e5m2):
         return t.view(torch.uint8).numpy()
     return t.numpy()
 
@@ -101,7 +101,7 @@ def test_golden_decode(name, forced_split):
     backend = b200attn.B200AttnBackend(runner, materialize_kv_indices=True, **kw)
     # the reference golden for fp8 is scale-free (dequantised copy, scales 1)
     layer = make_layer(w, with_scales=False)
-    fp8 = cfg.kv_dtype == "fp8_e4m3"
+    fp8 = cfg.kv_dtype.startswith("fp8")
     out = run_decode(backend, runner, w, layer=layer, save_kv_cache=not fp8)
     torch.cuda.synchronize()
     c = cfg
@@ -259,6 +259,34 @@ def test_decode_fp8(q_dtype, D):
     cfg = synth.Config("fp8", 5, 0, 32, 8, D, kv_dtype="fp8_e4m3", q_dtype=q_dtype, page_size=16,
                        ragged=(10, 1100), k_scale=0.5, v_scale=2.0, seed=24)
     _run_case(cfg, max_ctas=9, min_chunks=2)
+
+
+@pytest.mark.parametrize("D,heads,ragged", [(128, (32, 8), (10, 1100)), (64, (32, 8), (1, 600)), (256, (8, 4), (10, 700)),
+                                            (128, (8, 1), (10, 1500)), (128, (32, 2), (10, 500))])
+def test_decode_fp8_e5m2(D, heads, ragged):
+    """``--kv-cache-dtype fp8_e5m2`` (server_args.py:828-833): the store casts like torch's ``.to(float8_e5m2)``
+    (pool bytes bit-exact, RNE, overflow to infinity), decode reads the byte as the upper half of an f16."""
+    cfg = synth.Config("e5m2", 5, 0, heads[0], heads[1], D, kv_dtype="fp8_e5m2", page_size=4, ragged=ragged,
+                       k_scale=0.5, v_scale=2.0, seed=29)
+    _run_case(cfg, max_ctas=9, min_chunks=2)
+
+
+def test_fp8_e5m2_store_matches_torch_cuda():
+    """The e5m2 cast against torch-CUDA's own ``.to(torch.float8_e5m2)`` on every bf16 bit pattern (the arithmetic
+    ``set_kv_buffer`` runs on the GPU, memory_pool.py:385-391)."""
+    import b200attn
+
+    bits = torch.arange(65536, dtype=torch.int32, device=DEV).to(torch.int16)
+    x = bits.view(torch.bfloat16).reshape(1024, 1, 64)
+    ok = ~torch.isnan(x.float())
+    kp = torch.zeros((1024, 1, 64), dtype=torch.uint8, device=DEV).view(torch.float8_e5m2)
+    vp = torch.zeros_like(kp)
+    loc = torch.arange(1024, device=DEV, dtype=torch.int64)
+    b200attn.store_kv(kp, vp, loc, x.clone(), x.clone(), None, None)
+    torch.cuda.synchronize()
+    ref = x.to(torch.float8_e5m2).view(torch.uint8)
+    assert torch.equal(kp.view(torch.uint8)[ok], ref[ok]) and torch.equal(vp.view(torch.uint8)[ok], ref[ok])
+    assert bool(((kp.view(torch.uint8)[~ok] & 0x7F) == 0x7F).all())   # NaN stays NaN
 
 
 def test_decode_fp8_tp8_and_wide_group():

@@ -247,3 +247,17 @@ def test_extend_oracle_mask_properties():
     assert np.abs(win - base).max() > 1e-3   # request 2 (prefix 40 > W + 1) changes
     qo, kv, _ = extend_oracle.extend_indptrs(w.prefix_lens_np, w.extend_lens_np, W)
     assert list(np.diff(kv)) == [min(p, W + 1) for p in pl] and list(np.diff(qo)) == list(el)
+
+
+def test_e5m2_cast_matches_torch_exhaustively():
+    """The oracle's float8_e5m2 cast and dequantisation against torch on all 65 536 bf16 and f16 bit patterns."""
+    b = np.arange(65536, dtype=np.uint16)
+    for x in (oracle.bf16_bits_to_f32(b), b.view(np.float16).astype(np.float32)):
+        ok = ~np.isnan(x)
+        ref = torch.from_numpy(x.copy()).to(torch.float8_e5m2).view(torch.uint8).numpy()
+        got = oracle.f32_to_e5m2_bits(x)
+        assert np.array_equal(ref[ok], got[ok])
+        assert ((got[~ok] & 0x7F) == 0x7F).all()
+    bb = np.arange(256, dtype=np.uint8)
+    ref = torch.from_numpy(bb.copy()).view(torch.float8_e5m2).float().numpy()
+    assert np.array_equal(np.nan_to_num(oracle.e5m2_bits_to_f32(bb), nan=7.0), np.nan_to_num(ref, nan=7.0))
