@@ -63,8 +63,7 @@ enum {
   B200ATTN_F16 = 1,
   B200ATTN_FP8_E4M3 = 2, /* torch.float8_e4m3fn, stored as raw bytes (uint8 pool) */
   B200ATTN_F32 = 3,      /* b200attn_merge_states only */
-  B200ATTN_FP8_E5M2 = 4  /* ABI 6: torch.float8_e5m2 (--kv-cache-dtype fp8_e5m2, server_args.py:828-833), raw bytes;
-                            KV store and decode; extend returns B200ATTN_E_UNSUPPORTED */
+  B200ATTN_FP8_E5M2 = 4  /* ABI 6: torch.float8_e5m2 (--kv-cache-dtype fp8_e5m2, server_args.py:828-833), raw bytes */
 };
 
 /* Width of the seq_lens / req_pool_indices arrays (int64 eager, int32 under
@@ -292,7 +291,7 @@ typedef struct {
   int32_t head_dim;
   int32_t v_head_dim;
   int32_t q_dtype;              /* B200ATTN_BF16 | B200ATTN_F16 */
-  int32_t kv_dtype;             /* == q_dtype, or B200ATTN_FP8_E4M3 (raw bytes; strides then count bytes) */
+  int32_t kv_dtype;             /* == q_dtype, or B200ATTN_FP8_E4M3 / _E5M2 (raw bytes; strides then count bytes) */
   int32_t causal;               /* 1: extend token i sees extend tokens j <= i */
   int32_t sliding_window;       /* <= 0: off */
   int32_t skip_prefix_custom_mask; /* 1 (the reference's default): custom_mask covers the extend part only */

@@ -533,10 +533,7 @@ class B200AttnBackend(AttentionBackend):
             raise NotImplementedError("B200AttnBackend: cross attention is not supported")
         if layer.qk_head_dim != layer.v_head_dim:
             raise NotImplementedError("B200AttnBackend: qk_head_dim != v_head_dim is not supported")
-        if self.kv_dtype == capi.FP8_E5M2:
-            raise NotImplementedError("B200AttnBackend: extend over an fp8_e5m2 pool is not implemented (KV store and "
-                                      "decode are): construct the backend with prefill_backend=")
-        fp8 = self.kv_dtype == capi.FP8_E4M3
+        fp8 = self.kv_dtype in (capi.FP8_E4M3, capi.FP8_E5M2)
         q = q.reshape(-1, layer.tp_q_head_num * layer.qk_head_dim)
         o = torch.empty_like(q)
         k_pool, v_pool, slot_map = self._layer_pools(forward_batch.token_to_kv_pool, layer)

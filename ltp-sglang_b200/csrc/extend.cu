@@ -178,7 +178,7 @@ extern "C" __attribute__((visibility("default"))) int b200attn_extend(const b200
       (a->mask_indptr_dtype != B200ATTN_I32 && a->mask_indptr_dtype != B200ATTN_I64))
     return B200ATTN_E_INVALID;
   if (a->q_dtype != B200ATTN_BF16 && a->q_dtype != B200ATTN_F16) return B200ATTN_E_UNSUPPORTED;
-  const bool fp8 = a->kv_dtype == B200ATTN_FP8_E4M3;
+  const bool fp8 = is_fp8(a->kv_dtype);
   if (!fp8 && a->kv_dtype != a->q_dtype) return B200ATTN_E_UNSUPPORTED;
   const int esz = fp8 ? 1 : 2;
   const float k_scale = fp8 ? a->k_scale : 1.f, v_scale = fp8 ? a->v_scale : 1.f;
@@ -237,6 +237,7 @@ extern "C" __attribute__((visibility("default"))) int b200attn_extend(const b200
   p.scale_log2 = p.sm_scale * kLog2e;
   p.logit_cap = a->logit_cap;
   p.v_scale = v_scale;
+  p.e5m2 = a->kv_dtype == B200ATTN_FP8_E5M2;
   p.batch = a->batch;
 
   cudaStream_t stream = static_cast<cudaStream_t>(stream_);

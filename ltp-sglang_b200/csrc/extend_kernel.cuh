@@ -54,14 +54,26 @@ struct ExtendParams {
   float logit_cap;
   float v_scale;
   int32_t batch;
+  int32_t e5m2;      // fp8 pools: 1 = float8_e5m2 bytes (the byte is the upper half of an f16), 0 = e4m3fn
 };
 
 __host__ __device__ inline int extend_smem_bytes(int d) {
   return kExtStages * 2 * kExtBN * (d * 2 + kRowPad);
 }
 
-// 16 e4m3 bytes -> 16 f16 values (exact), in element order.
-__device__ __forceinline__ void e4m3x16_to_f16(const uint4& r, uint4& lo, uint4& hi) {
+// 16 fp8 bytes -> 16 f16 values (exact), in element order; e5m2 (uniform flag): byte permutes instead of cvt.
+__device__ __forceinline__ void e4m3x16_to_f16(const uint4& r, uint4& lo, uint4& hi, bool e5m2 = false) {
+  if (e5m2) {
+    lo.x = __byte_perm(r.x, 0u, 0x1404);
+    lo.y = __byte_perm(r.x, 0u, 0x3424);
+    lo.z = __byte_perm(r.y, 0u, 0x1404);
+    lo.w = __byte_perm(r.y, 0u, 0x3424);
+    hi.x = __byte_perm(r.z, 0u, 0x1404);
+    hi.y = __byte_perm(r.z, 0u, 0x3424);
+    hi.z = __byte_perm(r.w, 0u, 0x1404);
+    hi.w = __byte_perm(r.w, 0u, 0x3424);
+    return;
+  }
   lo.x = e4m3x2_to_f16x2(r.x);
   lo.y = e4m3x2_to_f16x2(r.x >> 16);
   lo.z = e4m3x2_to_f16x2(r.y);
@@ -253,7 +265,7 @@ __global__ void __launch_bounds__(kExtThreads, 1) extend_kernel(const ExtendPara
 #pragma unroll
         for (int kv = 0; kv < 2; ++kv) {
           uint4 lo, hi;
-          e4m3x16_to_f16(raw[i][kv], lo, hi);
+          e4m3x16_to_f16(raw[i][kv], lo, hi, p.e5m2 != 0);
           sts128(dst + i * RPP * RS + kv * TENSOR_BYTES, lo);
           sts128(dst + i * RPP * RS + kv * TENSOR_BYTES + 16, hi);
         }

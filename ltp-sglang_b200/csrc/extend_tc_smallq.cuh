@@ -351,7 +351,7 @@ __global__ void __launch_bounds__(kTcThreads, 1) extend_tc_smallq_kernel(const E
         for (int i = 0; i < 8; ++i) {
           const int row = rb8 + 16 * i;
           uint4 lo, hi;
-          e4m3x16_to_f16(raw[i], lo, hi);
+          e4m3x16_to_f16(raw[i], lo, hi, p.e5m2 != 0);
           const uint32_t rowa = dslab + row * 128;
           sts128(rowa + ((((2 * chunk8) & 7) ^ (row & 7)) << 4), lo);
           sts128(rowa + ((((2 * chunk8 + 1) & 7) ^ (row & 7)) << 4), hi);

@@ -103,6 +103,8 @@ def oracle_extend(w_cpu, causal=True, logit_cap=0.0, custom_mask=None, sliding_w
 
     c = w_cpu.cfg
     kp, vp = w_cpu.k_pool.clone(), w_cpu.v_pool.clone()
+    if c.kv_dtype == "fp8_e5m2":
+        kp, vp = kp.view(torch.float8_e5m2), vp.view(torch.float8_e5m2)
     T = w_cpu.tokens
     fp8 = c.kv_dtype.startswith("fp8")
     decode_oracle.kv_store(kp, vp, w_cpu.out_cache_loc, w_cpu.k.reshape(T, c.num_kv_heads, c.head_dim).clone(),

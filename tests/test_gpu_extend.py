@@ -44,7 +44,7 @@ def _layer(w, causal=True, logit_cap=0.0, window=-1):
     at = b200attn.AttentionType.DECODER if causal else b200attn.AttentionType.ENCODER_ONLY
     layer = b200attn.AttnLayer(c.num_q_heads, c.head_dim, w.sm_scale, c.num_kv_heads, layer_id=0,
                                logit_cap=logit_cap, sliding_window_size=window, attn_type=at)
-    if c.kv_dtype == "fp8_e4m3":   # per-tensor scales the way RadixAttention carries them (radix_attention.py:61-82)
+    if c.kv_dtype.startswith("fp8"):   # per-tensor scales the way RadixAttention carries them (radix_attention.py:61-82)
         dev = w.k_pool.device
         layer.k_scale = torch.tensor(c.k_scale, dtype=torch.float32, device=dev)
         layer.v_scale = torch.tensor(c.v_scale, dtype=torch.float32, device=dev)
@@ -64,6 +64,8 @@ def _run(cfg, pl, el, causal=True, logit_cap=0.0, window=-1, index_dtype=torch.i
     c = cfg
     if check_pool:
         pool = runner.token_to_kv_pool
+        if kp.dtype == torch.float8_e5m2:   # (the oracle tells the fp8 kind by the view; the pool stores bytes)
+            kp, vp = kp.view(torch.uint8), vp.view(torch.uint8)
         assert torch.equal(pool.k_buffer[0].cpu(), kp) and torch.equal(pool.v_buffer[0].cpu(), vp), \
             "kv_store: pool bytes differ from the oracle"
     got = out.float().cpu().numpy().reshape(ref.shape)
@@ -143,6 +145,21 @@ def test_extend_fp8_pool(shape):
     cfg = synth.Config(name, len(pl), 0, hq, hkv, d, kv_dtype="fp8_e4m3", q_dtype=qdt, page_size=page,
                        k_scale=ks, v_scale=vs, seed=601)
     _run(cfg, pl, el)
+
+
+@pytest.mark.parametrize("shape", [FP8_SHAPES[1], FP8_SHAPES[2], FP8_SHAPES[4], FP8_SHAPES[6]], ids=lambda s: s[0])
+def test_extend_fp8_e5m2_pool(shape):
+    """The same shapes over a float8_e5m2 pool (tcgen05 kernels d128, mma.sync kernel d64 / d256)."""
+    name, hq, hkv, d, page, qdt, pl, el, ks, vs = shape
+    cfg = synth.Config(name + "_e5m2", len(pl), 0, hq, hkv, d, kv_dtype="fp8_e5m2", q_dtype=qdt, page_size=page,
+                       k_scale=ks, v_scale=vs, seed=611)
+    _run(cfg, pl, el)
+
+
+def test_extend_fp8_e5m2_verify_smallq():
+    """TARGET_VERIFY-shaped batch (small-q kernels) over an e5m2 pool."""
+    cfg = synth.Config("e5m2_verify", 6, 0, 32, 8, 128, kv_dtype="fp8_e5m2", k_scale=0.5, v_scale=2.0, seed=612)
+    _run(cfg, (700, 300, 1200, 64, 129, 511), (8, 8, 8, 8, 8, 8))
 
 
 def test_extend_fp8_window_and_cap():
