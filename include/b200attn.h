@@ -54,7 +54,8 @@ enum {
   B200ATTN_E_UNSUPPORTED = -2, /* shape / dtype combination has no kernel */
   B200ATTN_E_ALIGN = -3,       /* pointer or stride breaks an alignment rule */
   B200ATTN_E_CUDA = -4,        /* the CUDA runtime reported a launch error */
-  B200ATTN_E_WORKSPACE = -5    /* plan / workspace buffer too small */
+  B200ATTN_E_WORKSPACE = -5,   /* plan / workspace buffer too small */
+  B200ATTN_E_STATIC_LIMIT = -6 /* b200attn_decode_static_ws: the call needs more than B200ATTN_STATIC_WS_BYTES */
 };
 
 /* Element types. */
@@ -236,6 +237,21 @@ typedef struct {
 size_t b200attn_workspace_bytes(int32_t batch, int32_t num_q_heads, int32_t num_kv_heads,
                                 int32_t head_dim, int32_t v_head_dim, int32_t kv_dtype);
 int b200attn_decode(const b200attn_decode_args* args, b200attn_stream_t stream);
+
+/* b200attn_decode for callers that may not allocate device memory (code under CUDA-graph capture, tight serving
+ * loops, harnesses that forbid cudaMalloc).  No counterpart in the reference.
+ * Same arguments, results and error codes as b200attn_decode, except that the split-KV workspace is a
+ * device array inside the library: args->ws_o must be NULL and args->ws_bytes 0 (B200ATTN_E_INVALID otherwise).
+ *   - Limit: b200attn_workspace_bytes(batch, heads..., kv_dtype) <= B200ATTN_STATIC_WS_BYTES (64 MiB; e.g. 64
+ *     requests x 32 q heads x head_dim 128 need 18.1 MiB, 128 x 64 x 128 need 36.3 MiB); a larger call returns B200ATTN_E_STATIC_LIMIT and
+ *     launches nothing.  Every GPU that loads the library holds the 64 MiB until the process exits.
+ *   - The call and its set-up (one cudaGetSymbolAddress per device, on first use, with that device current) call
+ *     no cudaMalloc / cudaFree / allocating routine.  The plan, q, pools and outputs stay the caller's.
+ *   - All calls on a device share the one array: calls that overlap on the GPU (two streams) race.  Nothing in it
+ *     must start at zero (every partial row is written before it is read; the counters that order the reads are
+ *     in the plan buffer), so it is not cleared between calls and keeps the last call's partials. */
+#define B200ATTN_STATIC_WS_BYTES (64u << 20)
+int b200attn_decode_static_ws(const b200attn_decode_args* args, b200attn_stream_t stream);
 
 /* ------------------------------------------------------------------ */
 /* K5: extend (prefill with cached prefix) attention                   */

@@ -15,7 +15,8 @@ LIB_PATH = Path(os.environ.get("B200ATTN_LIB", _HERE / "libb200attn.so"))
 
 # enums (include/b200attn.h)
 OK = 0
-E_INVALID, E_UNSUPPORTED, E_ALIGN, E_CUDA, E_WORKSPACE = -1, -2, -3, -4, -5
+E_INVALID, E_UNSUPPORTED, E_ALIGN, E_CUDA, E_WORKSPACE, E_STATIC_LIMIT = -1, -2, -3, -4, -5, -6
+STATIC_WS_BYTES = 64 << 20  # B200ATTN_STATIC_WS_BYTES
 BF16, F16, FP8_E4M3, F32, FP8_E5M2 = 0, 1, 2, 3, 4
 I32, I64 = 0, 1
 SCALE_NONE, SCALE_TRUE_DIV, SCALE_RECIP_MUL = 0, 1, 2
@@ -235,6 +236,7 @@ SYMBOLS = {
         [C.c_int32, C.c_int32, C.c_int32, C.c_int32, C.c_int32, C.c_int32],
     ),
     "b200attn_decode": (C.c_int, [C.POINTER(DecodeArgs), C.c_void_p]),
+    "b200attn_decode_static_ws": (C.c_int, [C.POINTER(DecodeArgs), C.c_void_p]),
     "b200attn_extend": (C.c_int, [C.POINTER(ExtendArgs), C.c_void_p]),
     "b200attn_extend_plan": (C.c_int, [C.POINTER(ExtendPlanArgs), C.c_void_p]),
     "b200attn_draft_kv_indices": (C.c_int, [C.POINTER(DraftKvIndicesArgs), C.c_void_p]),

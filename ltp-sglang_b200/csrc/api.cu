@@ -53,6 +53,7 @@ extern "C" __attribute__((visibility("default"))) const char* b200attn_strerror(
     case B200ATTN_E_ALIGN: return "pointer or stride violates an alignment requirement";
     case B200ATTN_E_CUDA: return "CUDA runtime reported a launch error";
     case B200ATTN_E_WORKSPACE: return "plan or workspace buffer too small";
+    case B200ATTN_E_STATIC_LIMIT: return "call needs more scratch than the library's static workspace (B200ATTN_STATIC_WS_BYTES, 64 MiB): use b200attn_decode with a caller-owned workspace";
     default: return "unknown b200attn error code";
   }
 }
