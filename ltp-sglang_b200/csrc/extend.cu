@@ -41,7 +41,7 @@ cudaError_t launch_extend_tc(const ExtendParams& p, int d, dim3 grid, bool small
   }
   cudaError_t e = cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, kTcSmemBytes);
   if (e != cudaSuccess) return e;
-  fn<<<grid, kTcThreads, kTcSmemBytes, stream>>>(p);
+  fn<<<grid, kTcLaunchThreads, kTcSmemBytes, stream>>>(p);
   return cudaGetLastError();
 }
 

@@ -49,6 +49,21 @@ constexpr int kTcLag = B200ATTN_TC_LAG;  // cp.async groups a loader thread keep
 constexpr int kTcBarBytes = 9216;    // mbarriers, TMEM base, row max / row sum exchange, 4 slot-id buffers
 constexpr int kTcSmemBytes = kTcQBytes + kTcSlots * kTcSlotBytes + kTcBarBytes + 1024;  // + alignment slack
 constexpr float kTcRescaleLog2 = 8.f;  // lazy rescale threshold (log2 units)
+#ifdef B200ATTN_TC_TWO_PASS
+constexpr bool kTcSinglePass = false;   // A/B build: the general kernel keeps the two-pass softmax body
+#else
+constexpr bool kTcSinglePass = true;
+#endif
+#ifndef B200ATTN_TC_REGS
+#define B200ATTN_TC_REGS 96, 64, 32
+#endif
+constexpr int kTcRegs[3] = {B200ATTN_TC_REGS};  // softmax / loader / MMA warps after setmaxnreg
+constexpr int kTcSoftmaxRegs = kTcRegs[0], kTcLoaderRegs = kTcRegs[1], kTcMmaRegs = kTcRegs[2];
+// setmaxnreg moves registers inside what the launch allocated: 80 per warp (the compiler's cap for a 6-warp
+// sub-partition).  The general kernel is launched with three idle warps (21-23) so that EVERY sub-partition holds
+// 6 x 80 = 480: 4 softmax + 1 loader + the MMA warp or an idle one (24 registers).
+constexpr int kTcLaunchThreads = 24 * 32;
+static_assert(4 * kTcSoftmaxRegs + kTcLoaderRegs + kTcMmaRegs <= 480, "registers of sub-partition 0");
 
 // ---- tcgen05 wrappers ----
 // The MMA / commit wrappers are executed by a WHOLE warp (uniform control flow) and elect one lane
@@ -177,7 +192,7 @@ __device__ __forceinline__ void setmaxnreg_dec() {
 // D: head_dim 128 or 64.  64 keeps the 128-wide geometry (ring slots, O columns) and uses its first slab /
 // first 64 O columns: rows are one 128-byte swizzle atom wide, Q.K^T takes 4 k-steps, P.V has N = 64.
 template <typename QT, int D, bool FP8, bool ALT, bool CAP>
-__global__ void __launch_bounds__(kTcThreads, 1) extend_tc_kernel(const ExtendParams p) {
+__global__ void __launch_bounds__(kTcLaunchThreads, 1) extend_tc_kernel(const ExtendParams p) {
   static_assert(D == 128 || (D == 64 && !FP8), "head_dim 128, or 64 over a 16-bit pool");
   constexpr bool NARROW = FP8 || D == 64;  // a pool row (one head) is 128 bytes: 8 chunks, 8 rows per loader thread
   constexpr int OH = D / 2;                // O columns per thread (two threads per row)
@@ -285,6 +300,9 @@ __global__ void __launch_bounds__(kTcThreads, 1) extend_tc_kernel(const ExtendPa
 
   if (warp < kTcSoftmaxWarps) {
     // =============================== softmax warps ===============================
+    // (registers: the launch gives every warp 80 -- one sub-partition holds 6 of the 21 warps -- the loaders and
+    //  the MMA warp hand back what they do not need and the softmax warps take it: 4 x 96 + 64 + 32 = 480)
+    setmaxnreg_inc<kTcSoftmaxRegs>();
     // Two threads per row: warp w serves sub-tile w / 8, column half (w / 4) & 1, TMEM lane quarter w & 3
     // (a warp reaches only the 32 lanes of quarter warp_id % 4).  The halves exchange their row max
     // through shared memory (one named barrier per tile) and their row sum once at the end.
@@ -436,8 +454,99 @@ __global__ void __launch_bounds__(kTcThreads, 1) extend_tc_kernel(const ExtendPa
         mbar_arrive(bar_p_full + 8 * sub);
         TC_TR(sub * 3 + 2, n);
         };
-        if (need_mask) tile_body(std::true_type{});
-        else tile_body(std::false_type{});
+        // General kernel: the thread's 64 S columns are read ONCE (two loads in flight, one wait) and stay in
+        // registers across the row-max exchange -- the two-pass body above pays four load round trips per tile on
+        // a chain (S -> softmax -> P.V -> next S) that is latency-bound; 104 registers make room for it.
+        auto tile_body1 = [&](auto masked_tag) {
+          constexpr bool MASKED = decltype(masked_tag)::value;
+          float s[64];
+          tmem_ld32<0>(tS, s);
+          tmem_ld32<32>(tS + 32, s);
+          tmem_wait_ld();
+          if constexpr (cap) {
+#pragma unroll
+            for (int j = 0; j < 64; ++j) s[j] = p.logit_cap * tanhf(s[j] * cap_pre);
+          }
+          if constexpr (MASKED) {
+            const int hi = !rv ? 0 : ((p.causal && !use_mask) ? min(Ltot, Lp + itok + 1) : Ltot);
+            const int lo = p.window > 0 ? min(max(itok - p.window, 0), Lp) : 0;
+            const unsigned span = hi > lo ? static_cast<unsigned>(hi - lo) : 0u;
+            const int mask_from = !use_mask ? 0x7fffffff : (p.skip_prefix_mask ? Lp : 0);
+            const int jb = j0 + half * 64;
+#pragma unroll
+            for (int jj = 0; jj < 64; ++jj)
+              s[jj] = static_cast<unsigned>(jb + jj - lo) < span ? s[jj] : -CUDART_INF_F;
+            if (jb + 64 > mask_from) {
+#pragma unroll
+              for (int jj = 0; jj < 64; ++jj) {
+                const int j = jb + jj;
+                if (j >= mask_from && j < hi && mrow[j] == 0) s[jj] = -CUDART_INF_F;
+              }
+            }
+          }
+          float mx0 = -CUDART_INF_F, mx1 = -CUDART_INF_F, mx2 = -CUDART_INF_F, mx3 = -CUDART_INF_F;
+#pragma unroll
+          for (int j = 0; j < 64; j += 4) {
+            mx0 = fmaxf(mx0, s[j]);
+            mx1 = fmaxf(mx1, s[j + 1]);
+            mx2 = fmaxf(mx2, s[j + 2]);
+            mx3 = fmaxf(mx3, s[j + 3]);
+          }
+          TC_TR(sub * 3 + 1, n);
+          float mx = fmaxf(fmaxf(mx0, mx1), fmaxf(mx2, mx3));
+          const int par = (it & 1) * (2 * 2 * kTcBM);
+          xmine[par] = mx;
+          named_bar_sync(1 + sub, 256);
+          mx = fmaxf(mx, xother[par]);
+          const bool grow = mx > m && (m == -CUDART_INF_F || (mx - m) * c > kTcRescaleLog2);
+          if (__any_sync(0xffffffffu, grow)) {
+            float corr = 1.f;
+            if (grow) {
+              corr = fast_exp2((m - mx) * c);  // m = -inf -> 0
+              m = mx;
+              l *= corr;
+            }
+            if (it > 0) {
+#pragma unroll
+              for (int cc = 0; cc < OH; cc += 16) {   // 16 columns at a time: s[64] is live
+                float o[16];
+                tmem_ld16(tO + cc, o);
+                tmem_wait_ld();
+                uint32_t ou[16];
+#pragma unroll
+                for (int j = 0; j < 16; ++j) ou[j] = __float_as_uint(o[j] * corr);
+                tmem_st16(tO + cc, ou);
+              }
+            }
+          }
+          const float mc = (m == -CUDART_INF_F ? 0.f : m) * c;
+          float sum0 = 0.f, sum1 = 0.f;
+#pragma unroll
+          for (int cc = 0; cc < 64; cc += 32) {
+            uint32_t pk[16];
+#pragma unroll
+            for (int j = 0; j < 32; j += 2) {
+              const float p0 = fast_exp2(fmaf(s[cc + j], c, -mc));
+              const float p1 = fast_exp2(fmaf(s[cc + j + 1], c, -mc));
+              sum0 += p0;
+              sum1 += p1;
+              pk[j >> 1] = pack2<HALF>(p0, p1);
+            }
+            tmem_st16(tS + (cc >> 1), pk);
+          }
+          l += sum0 + sum1;
+          tmem_wait_st();
+          tc_fence_before();
+          mbar_arrive(bar_p_full + 8 * sub);
+          TC_TR(sub * 3 + 2, n);
+        };
+        if constexpr (ALT || !kTcSinglePass) {
+          if (need_mask) tile_body(std::true_type{});
+          else tile_body(std::false_type{});
+        } else {
+          if (need_mask) tile_body1(std::true_type{});
+          else tile_body1(std::false_type{});
+        }
       }
 
       // ---- epilogue: row sum over both halves, then this thread's 64 columns of O / l -> global ----
@@ -511,6 +620,7 @@ __global__ void __launch_bounds__(kTcThreads, 1) extend_tc_kernel(const ExtendPa
   } else {
   if (warp < kTcMmaWarp) {
     // =============================== loaders (4 warps) ===============================
+    setmaxnreg_dec<kTcLoaderRegs>();
     const int tid = threadIdx.x - kTcLoaderWarp0 * 32;  // 0..127
     const int chunk = tid & 15, rbase = tid >> 4;       // 256-byte rows: row = rbase + 8 * i
     const uint32_t sw_col = static_cast<uint32_t>(chunk >> 3) * kTcSlab;
@@ -662,6 +772,7 @@ __global__ void __launch_bounds__(kTcThreads, 1) extend_tc_kernel(const ExtendPa
     TC_TR(13, 252);  // loader done
   } else if (warp == kTcMmaWarp) {
     // =============================== MMA issuer (warp 20) ===============================
+    setmaxnreg_dec<kTcMmaRegs>();
     {
 #ifdef B200ATTN_TC_TRACE
       tr = (blockIdx.x == 0 && blockIdx.y == 0 && blockIdx.z == 0 && lane == 0) ? reinterpret_cast<long long*>(p.lse) : nullptr;
@@ -768,6 +879,8 @@ __global__ void __launch_bounds__(kTcThreads, 1) extend_tc_kernel(const ExtendPa
       TC_TR(13, 253);  // last MMA committed
       tc_fence_before();
     }
+  } else {
+    setmaxnreg_dec<24>();   // warps 21-23 only lend their registers
   }
   }
   __syncthreads();

@@ -112,8 +112,11 @@ __device__ __forceinline__ uint32_t time_variant(uint32_t tmem, uint8_t* sA, uin
 constexpr int M = 128, N = 128, K = 128;
 
 // A, B: [128][K] row-major bf16 (K-major).  P: [128][K].  V: [K tokens][N d] row-major.
-__global__ void __launch_bounds__(128) probe(const __nv_bfloat16* A, const __nv_bfloat16* B, const __nv_bfloat16* P,
-                                             const __nv_bfloat16* V, float* D1, float* D2) {
+// mode (timing section only): warps 4-15 interfere while warp 0 times the MMAs -- bit 0: tcgen05.ld x32 loops on
+// the S columns (what the softmax warps do), bit 1: 16-byte shared-memory stores (what the loaders' cp.async does),
+// bit 2: MUFU.EX2 loops
+__global__ void __launch_bounds__(512) probe(const __nv_bfloat16* A, const __nv_bfloat16* B, const __nv_bfloat16* P,
+                                             const __nv_bfloat16* V, float* D1, float* D2, int mode) {
   extern __shared__ __align__(1024) uint8_t smem_raw[];
   uint8_t* smem = (uint8_t*)(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
   uint8_t* sA = smem;                 // 2 slabs
@@ -121,7 +124,37 @@ __global__ void __launch_bounds__(128) probe(const __nv_bfloat16* A, const __nv_
   uint8_t* sV = smem + 4 * SLAB;      // 2 slabs (d 0-63, d 64-127), rows = tokens
   __shared__ uint64_t bar;
   __shared__ uint32_t tmem_base_s;
+  __shared__ volatile int done_flag;
+  __shared__ uint4 scratch[512];
   const int t = threadIdx.x, warp = t >> 5;
+  if (t == 0) done_flag = 0;
+  if (t >= 128) {
+    // interferers: wait for the set-up, then run until warp 0 has finished timing
+    asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+    __syncthreads();   // matches the set-up barrier below
+    __syncthreads();   // test 2 staging barrier
+    __syncthreads();   // timing start
+    asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+    const uint32_t tm = tmem_base_s + ((uint32_t)((warp & 3) * 32) << 16);
+    uint32_t acc = 0;
+    float f = (float)t;
+    while (mode && !done_flag) {
+      if (mode & 1) {
+        uint32_t r[32];
+        tmem_ld32(tm + (warp & 4 ? 32 : 0), r);
+        for (int j = 0; j < 32; ++j) acc ^= r[j];
+      }
+      if (mode & 2) {
+        for (int j = 0; j < 8; ++j) scratch[(t + 32 * j) & 511] = make_uint4(acc, t, j, 0);
+      }
+      if (mode & 4) {
+        for (int j = 0; j < 32; ++j) f = exp2f(f * 0.001f);
+      }
+    }
+    if (acc == 0x12345 || f == 3.f) D1[0] = 1.f;
+    __syncthreads();   // end
+    return;
+  }
 
   // K-major swizzled fill: row r, 16-byte chunk c (0..15): slab c / 8, chunk (c % 8) ^ (r % 8)
   for (int i = t; i < 128 * 16; i += 128) {
@@ -201,6 +234,7 @@ __global__ void __launch_bounds__(128) probe(const __nv_bfloat16* A, const __nv_
     par = time_variant<5>(tmem, sA, sB, sV, &bar, par, D2, t);
     par = time_variant<6>(tmem, sA, sB, sV, &bar, par, D2, t);
     par = time_variant<7>(tmem, sA, sB, sV, &bar, par, D2, t);
+    done_flag = 1;
   }
   asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
   __syncthreads();
@@ -225,8 +259,17 @@ int main() {
   cudaMemcpy(dV, V.data(), V.size() * 2, cudaMemcpyHostToDevice);
   const int smem = 6 * SLAB + 1024;
   cudaFuncSetAttribute(probe, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
-  probe<<<1, 128, smem>>>(dA, dB, dP, dV, d1, d2);
-  cudaError_t e = cudaDeviceSynchronize();
+  cudaError_t e = cudaSuccess;
+  for (int mode = 0; mode < 8 && e == cudaSuccess; ++mode) {
+    probe<<<1, 512, smem>>>(dA, dB, dP, dV, d1, d2, mode);
+    e = cudaDeviceSynchronize();
+    float tm[16];
+    cudaMemcpy(tm, d2 + M * N, sizeof(tm), cudaMemcpyDeviceToHost);
+    printf("interference mode %d (1 = tcgen05.ld, 2 = st.shared, 4 = MUFU): clk / MMA  SS K-major %.1f | TS MN-major %.1f | SS N=64 %.1f | SS N=256 %.1f\n",
+           mode, tm[1] / 64, tm[7] / 64, tm[15] / 64, tm[13] / 64);
+  }
+  probe<<<1, 512, smem>>>(dA, dB, dP, dV, d1, d2, 0);
+  e = cudaDeviceSynchronize();
   printf("kernel: %s\n", cudaGetErrorString(e));
   if (e != cudaSuccess) return 1;
   std::vector<float> h1(M * N), h2(M * N);
