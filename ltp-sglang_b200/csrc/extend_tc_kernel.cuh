@@ -54,6 +54,11 @@ constexpr bool kTcSinglePass = false;   // A/B build: the general kernel keeps t
 #else
 constexpr bool kTcSinglePass = true;
 #endif
+#ifdef B200ATTN_TC_NO_EARLY_P
+constexpr bool kTcEarlyP = false;
+#else
+constexpr bool kTcEarlyP = kTcSinglePass;   // (the two-pass body publishes P once per tile)
+#endif
 #ifndef B200ATTN_TC_REGS
 #define B200ATTN_TC_REGS 96, 64, 32
 #endif
@@ -212,7 +217,8 @@ __global__ void __launch_bounds__(kTcLaunchThreads, 1) extend_tc_kernel(const Ex
   const uint32_t bar_s_full = bar_q_full + 8;             // [2]
   const uint32_t bar_p_full = bar_s_full + 16;            // [2]
   const uint32_t bar_o_full = bar_p_full + 16;
-  const uint32_t tmem_slot = bar_o_full + 8;
+  const uint32_t bar_p_half = bar_o_full + 8;             // [2] general kernel: P of every thread's first 32 tokens is in TMEM
+  const uint32_t tmem_slot = bar_p_half + 16;
   // row max [parity][sub][half][row] and row sum [sub][half][row] exchanged between the two threads of a row
   float* xch = reinterpret_cast<float*>(smem_raw + (bars + 1024 - smem_u32(smem_raw)));
   float* lxch = xch + 2 * 2 * 2 * kTcBM;
@@ -284,6 +290,7 @@ __global__ void __launch_bounds__(kTcLaunchThreads, 1) extend_tc_kernel(const Ex
     for (int i = 0; i < 2; ++i) {
       mbar_init(bar_s_full + 8 * i, 1);
       mbar_init(bar_p_full + 8 * i, 256);
+      mbar_init(bar_p_half + 8 * i, 256);
     }
     mbar_init(bar_o_full, 1);
     fence_barrier_init();
@@ -496,8 +503,15 @@ __global__ void __launch_bounds__(kTcLaunchThreads, 1) extend_tc_kernel(const Ex
           float mx = fmaxf(fmaxf(mx0, mx1), fmaxf(mx2, mx3));
           const int par = (it & 1) * (2 * 2 * kTcBM);
           xmine[par] = mx;
+          // only the two warps that share these 32 rows meet (barriers 6..13): a barrier over all eight warps
+          // of the sub-tile waits for the slowest of them every tile
+#ifdef B200ATTN_TC_WIDE_XCH
           named_bar_sync(1 + sub, 256);
+#else
+          named_bar_sync(6 + sub * 4 + (warp & 3), 64);
+#endif
           mx = fmaxf(mx, xother[par]);
+          if (sub == 0) TC_TR(14, n);
           const bool grow = mx > m && (m == -CUDART_INF_F || (mx - m) * c > kTcRescaleLog2);
           if (__any_sync(0xffffffffu, grow)) {
             float corr = 1.f;
@@ -533,8 +547,15 @@ __global__ void __launch_bounds__(kTcLaunchThreads, 1) extend_tc_kernel(const Ex
               pk[j >> 1] = pack2<HALF>(p0, p1);
             }
             tmem_st16(tS + (cc >> 1), pk);
+            if (kTcEarlyP && cc == 0) {
+              // publish the first 32 tokens' P now: the MMA warp runs their half of P.V under the other 32 exps
+              tmem_wait_st();
+              tc_fence_before();
+              mbar_arrive(bar_p_half + 8 * sub);
+            }
           }
           l += sum0 + sum1;
+          if (sub == 0) TC_TR(15, n);
           tmem_wait_st();
           tc_fence_before();
           mbar_arrive(bar_p_full + 8 * sub);
@@ -800,6 +821,35 @@ __global__ void __launch_bounds__(kTcLaunchThreads, 1) extend_tc_kernel(const Ex
         for (int k = 1; k < kTcBN / 16; ++k)  // P: columns [0, 32) hold tokens 0-63, [64, 96) tokens 64-127
           umma_ts(d, a + k * 8 + (k >= 4 ? 32 : 0), v0 + k * (2048 >> 4), IDESC_PV, 1u);
       };
+      // P.V of the k-steps whose 16 tokens lie in every thread's first (which = 0) / second 32-token chunk:
+      // half h of a row holds tokens 64 h .., so chunk c is k-steps 4 h + 2 c, 4 h + 2 c + 1
+      auto issue_pv_part = [&](int sub, int slot, int which, bool acc) {
+        const uint64_t v0 = dv + static_cast<uint32_t>(slot * (kTcSlotBytes >> 4));
+        const uint32_t d = tmem + 2 * kTcBN + sub * kTcD, a = tmem + sub * kTcBN;
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+          const int k = (i >> 1) * 4 + which * 2 + (i & 1);
+          umma_ts(d, a + k * 8 + (k >= 4 ? 32 : 0), v0 + k * (2048 >> 4), IDESC_PV, (acc || i > 0) ? 1u : 0u);
+        }
+      };
+      auto issue_pv_tile = [&](int sub, int slot, int n) {
+        if constexpr (kTcEarlyP && !ALT) {
+          mbar_wait_wd(bar_p_half + 8 * sub, n & 1);
+          tc_fence_after();
+          issue_pv_part(sub, slot, 0, n > 0);
+          mbar_wait_wd(bar_p_full + 8 * sub, n & 1);
+          tc_fence_after();
+          if (sub == 0) TC_TR(7, n);
+          else TC_TR(9, n);
+          issue_pv_part(sub, slot, 1, true);
+        } else {
+          mbar_wait_wd(bar_p_full + 8 * sub, n & 1);
+          tc_fence_after();
+          if (sub == 0) TC_TR(7, n);
+          else TC_TR(9, n);
+          issue_pv(sub, slot, n > 0);
+        }
+      };
       auto full_wait = [&](int st) {
         mbar_wait_wd(bar_kv_full + 8 * (st % kTcSlots), static_cast<uint32_t>(st / kTcSlots) & 1u);
       };
@@ -848,10 +898,7 @@ __global__ void __launch_bounds__(kTcLaunchThreads, 1) extend_tc_kernel(const Ex
         const bool more = n + 1 < N;
         full_wait(vst);
         TC_TR(6, n);
-        mbar_wait_wd(bar_p_full, n & 1);
-        tc_fence_after();
-        TC_TR(7, n);
-        issue_pv(0, vslot, n > 0);
+        issue_pv_tile(0, vslot, n);
         if (more) {
           full_wait(kst);
           tc_fence_after();
@@ -859,12 +906,7 @@ __global__ void __launch_bounds__(kTcLaunchThreads, 1) extend_tc_kernel(const Ex
           issue_qk(0, kslot);
           umma_commit(bar_s_full);
         }
-        if (nsub == 2) {
-          mbar_wait_wd(bar_p_full + 8, n & 1);
-          tc_fence_after();
-          TC_TR(9, n);
-          issue_pv(1, vslot, n > 0);
-        }
+        if (nsub == 2) issue_pv_tile(1, vslot, n);
         umma_commit(bar_kv_empty + 8 * vslot);
         if (more) {
           if (nsub == 2) {

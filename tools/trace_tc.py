@@ -21,7 +21,7 @@ for _ in range(2):
     torch.ops.b200attn.extend(q, o, lse, w.k_pool, w.v_pool, qo, kv, None, w.req_to_token, w.req_pool_indices,
                               w.extend_prefix_lens, w.out_cache_loc, None, None, L, True, -1, True, w.sm_scale, 0.0)
 torch.cuda.synchronize()
-t = lse.view(torch.int64)[: 14 * 256].cpu().numpy().reshape(14, 256)
+t = lse.view(torch.int64)[: 16 * 256].cpu().numpy().reshape(16, 256)
 N = (L + 127) // 128
 t0 = t[0, 0]
 np.set_printoptions(linewidth=200)
@@ -36,3 +36,11 @@ for st in list(range(0, 8)) + list(range(60, 66)):
 d = np.diff(t[0, 8:N-2]).astype(float)
 print("steady period per tile (clk): mean %.0f" % d.mean(), " softmax0 busy (s->p): %.0f" % (t[2, 8:N-2] - t[0, 8:N-2]).mean(),
       " ld: %.0f" % (t[1, 8:N-2] - t[0, 8:N-2]).mean(), " p0->next s0: %.0f" % (t[0, 9:N-1] - t[2, 8:N-2]).mean())
+
+if t[14, 8] and t[15, 8]:
+    # single-pass body: kind 14 = row max exchanged (after the named barrier), 15 = exps + P stores issued (before wait::st)
+    a = t[:, 8:N-2].astype(float)
+    print("softmax0 per tile: s_full -> max %.0f | exchange + barrier %.0f | rescale vote + exps + st issue %.0f | wait::st + fence + arrive %.0f" % (
+        (a[1]-a[0]).mean(), (a[14]-a[1]).mean(), (a[15]-a[14]).mean(), (a[2]-a[15]).mean()))
+    print("mma: p0 published -> seen %.0f | PV0 issue (+ K wait) %.0f | p1 published -> seen %.0f | s1 commit -> softmax1 sees s_full(n+1): %.0f after loop top" % (
+        (a[7]-a[2]).mean(), (a[8]-a[7]).mean(), (a[9]-a[5]).mean(), (t[3, 9:N-1]-t[6, 9:N-1]).mean()))
