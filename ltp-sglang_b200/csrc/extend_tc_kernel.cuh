@@ -5,20 +5,24 @@
 //
 // One CTA = (request, kv head, q tile of 256 MMA rows) = two 128-row sub-tiles that share every
 // K/V tile.  A row is a (token, q head of the kv head's group) pair, so GQA packs G heads into M.
-//   warps 0-3 / 4-7   softmax warpgroup of sub-tile 0 / 1: thread r owns row r = TMEM lane r.  Reads
-//                     its S row from TMEM (tcgen05.ld 32x32b), masks, keeps the running max / sum
-//                     (no shuffles: one thread, one row), writes P as packed 16-bit pairs back into
-//                     the columns S occupied (tcgen05.st), rescales its O row in TMEM only when the
-//                     max grew by more than 2^8 (lazy rescale), and writes the final O row.
-//   warps 8-11        loaders: gather K / V rows of the paged pool (prefix through the index list,
+//   warps 0-7 / 8-15  softmax warps of sub-tile 0 / 1, two threads per row (column halves; warp w serves TMEM
+//                     lane quarter w & 3).  General kernel: the thread's 64 S columns are read ONCE from TMEM
+//                     (two tcgen05.ld in flight), masked, the row max is exchanged with the other half's warp
+//                     (pairwise named barrier), P goes back as packed 16-bit pairs into the columns S occupied
+//                     (tcgen05.st) -- the first 32 tokens' P is published early so that half of P.V runs under
+//                     the remaining exps -- and O is rescaled in TMEM only when the max grew by more than 2^8.
+//                     (Small-q instantiation, ALT: the older two-pass body on 32-column chunks.)
+//   warps 16-19       loaders: gather K / V rows of the paged pool (prefix through the index list,
 //                     new tokens through out_cache_loc) with 16-byte cp.async straight into the
 //                     128-byte-swizzled K-major layout tcgen05 reads (row r, chunk c -> c ^ (r & 7)),
 //                     ring of kSlots 32 KB slots, full / empty mbarriers; also the Q tile.
-//   warp 12           one elected thread issues every MMA:  S_i = Q_i . K^T   (SS, both K-major)
+//   warp 20           issues every MMA (warp-uniform, elect inside): S_i = Q_i . K^T   (SS, both K-major)
 //                                                           O_i += P_i . V     (TS: P from TMEM,
 //                                                           V MN-major = the same row layout)
 //                     in the order PV0(n) S0(n+1) PV1(n) S1(n+1), so the softmax of one sub-tile
 //                     overlaps the MMAs of the other; tcgen05.commit signals the mbarriers.
+//   warps 21-23       idle: they exist so that every SM sub-partition holds 6 x 80 launch registers, which
+//                     setmaxnreg then moves to the softmax warps (96) from loaders (64), MMA (32), idle (24).
 // TMEM (512 columns): S0 [0,128) S1 [128,256) O0 [256,384) O1 [384,512); P_i aliases S_i [0,32) + [64,96).
 // The descriptor encodings are pinned by tools/probe_umma.cu.
 #pragma once
@@ -161,6 +165,8 @@ __device__ __forceinline__ void tmem_st16(uint32_t taddr, const uint32_t (&u)[16
 }
 
 // mbarrier wait with a watchdog: a protocol bug traps instead of hanging the GPU.
+// (Measured and dropped, profiles/r02_extend2: a suspend-time hint on try_wait -- the softmax warps' s_full spin is
+//  45 % of the executed instructions, yet parking them changed nothing -- and a pure test_wait poll.)
 __device__ __forceinline__ void mbar_wait_wd(uint32_t bar, uint32_t parity) {
   uint32_t spins = 0;
   while (!mbar_try_wait(bar, parity)) {
@@ -467,6 +473,12 @@ __global__ void __launch_bounds__(kTcLaunchThreads, 1) extend_tc_kernel(const Ex
         auto tile_body1 = [&](auto masked_tag) {
           constexpr bool MASKED = decltype(masked_tag)::value;
           float s[64];
+#ifdef B200ATTN_TC_TRACE
+          // per-warp skew: lane 0 of every softmax warp of CTA 0 stamps s_full seen / P published (kinds 32 + 2 warp, + 1)
+          long long* trw = (blockIdx.x == 0 && blockIdx.y == 0 && blockIdx.z == 0 && lane == 0 && n < 256)
+                               ? reinterpret_cast<long long*>(p.lse) + (32 + 2 * warp) * 256 + n : nullptr;
+          if (trw) trw[0] = clock64();
+#endif
           tmem_ld32<0>(tS, s);
           tmem_ld32<32>(tS + 32, s);
           tmem_wait_ld();
@@ -559,6 +571,9 @@ __global__ void __launch_bounds__(kTcLaunchThreads, 1) extend_tc_kernel(const Ex
           tmem_wait_st();
           tc_fence_before();
           mbar_arrive(bar_p_full + 8 * sub);
+#ifdef B200ATTN_TC_TRACE
+          if (trw) trw[256] = clock64();
+#endif
           TC_TR(sub * 3 + 2, n);
         };
         if constexpr (ALT || !kTcSinglePass) {

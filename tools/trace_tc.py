@@ -44,3 +44,14 @@ if t[14, 8] and t[15, 8]:
         (a[1]-a[0]).mean(), (a[14]-a[1]).mean(), (a[15]-a[14]).mean(), (a[2]-a[15]).mean()))
     print("mma: p0 published -> seen %.0f | PV0 issue (+ K wait) %.0f | p1 published -> seen %.0f | s1 commit -> softmax1 sees s_full(n+1): %.0f after loop top" % (
         (a[7]-a[2]).mean(), (a[8]-a[7]).mean(), (a[9]-a[5]).mean(), (t[3, 9:N-1]-t[6, 9:N-1]).mean()))
+
+tw = lse.view(torch.int64)[32 * 256: 64 * 256].cpu().numpy().reshape(16, 2, 256)
+if tw[0, 0, 8]:
+    print("per-warp (relative to warp 0's s_full of the tile): s_full seen / P published")
+    for n in (30, 31):
+        base = tw[0, 0, n]
+        print(f" n={n}: " + "  ".join(f"w{w}:{int(tw[w,0,n]-base)}/{int(tw[w,1,n]-base)}" for w in range(16)))
+    busy = (tw[:, 1, 8:N-2] - tw[:, 0, 8:N-2]).mean(axis=1)
+    print(" mean busy per warp:", " ".join(f"{b:.0f}" for b in busy))
+    first = tw[:8, 1, 8:N-2].min(axis=0); last = tw[:8, 1, 8:N-2].max(axis=0)
+    print(" sub-tile 0: first warp's P -> last warp's P: mean %.0f clk; s_full skew %.0f" % ((last - first).mean(), (tw[:8, 0, 8:N-2].max(axis=0) - tw[:8, 0, 8:N-2].min(axis=0)).mean()))
