@@ -15,6 +15,10 @@ cudaError_t launch_extend(const ExtendParams& p, int d, dim3 grid, cudaStream_t 
   if (d == 64) fn = cap ? extend_kernel<QT, 64, FP8, true> : extend_kernel<QT, 64, FP8, false>;
   else if (d == 128) fn = cap ? extend_kernel<QT, 128, FP8, true> : extend_kernel<QT, 128, FP8, false>;
   else if (d == 256) fn = cap ? extend_kernel<QT, 256, FP8, true> : extend_kernel<QT, 256, FP8, false>;   // Gemma-sized heads
+  if constexpr (!FP8) {   // head dims 80 / 96 (16-bit pools, as in the decode kernel)
+    if (d == 80) fn = cap ? extend_kernel<QT, 80, false, true> : extend_kernel<QT, 80, false, false>;
+    else if (d == 96) fn = cap ? extend_kernel<QT, 96, false, true> : extend_kernel<QT, 96, false, false>;
+  }
   if (!fn) return cudaErrorInvalidValue;
   const int smem = extend_smem_bytes(d);
   cudaError_t e = cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
@@ -184,7 +188,9 @@ extern "C" __attribute__((visibility("default"))) int b200attn_extend(const b200
   const float k_scale = fp8 ? a->k_scale : 1.f, v_scale = fp8 ? a->v_scale : 1.f;
   if (fp8 && (!(k_scale > 0.f) || !(v_scale > 0.f))) return B200ATTN_E_INVALID;
   if (a->v_head_dim != a->head_dim) return B200ATTN_E_UNSUPPORTED;
-  if (a->head_dim != 64 && a->head_dim != 128 && a->head_dim != 256) return B200ATTN_E_UNSUPPORTED;
+  if (a->head_dim != 64 && a->head_dim != 128 && a->head_dim != 256 &&
+      !(!fp8 && (a->head_dim == 80 || a->head_dim == 96)))   // the decode kernel's head dims
+    return B200ATTN_E_UNSUPPORTED;
   if (a->num_q_heads <= 0 || a->num_kv_heads <= 0 || a->num_q_heads % a->num_kv_heads != 0)
     return B200ATTN_E_INVALID;
   const int group = a->num_q_heads / a->num_kv_heads;

@@ -123,7 +123,11 @@ __global__ void __launch_bounds__(kExtThreads, 1) extend_kernel(const ExtendPara
   constexpr int CH = D * ESZ / 16;           // 16-byte chunks per pool row
   constexpr int RAW_OFF = FP8 ? D : 0;       // fp8 bytes land in the upper half of the row
   constexpr int RPP = kExtThreads / CH;      // rows per loader pass
-  constexpr int PASSES = kExtBN / RPP;
+  constexpr int PASSES = (kExtBN + RPP - 1) / RPP;
+  // head_dim 80 / 96 (10 / 12 chunks per row): the threads past RPP * CH idle and the last pass is ragged
+  constexpr bool EXACT = kExtThreads % CH == 0 && kExtBN % RPP == 0;
+  static_assert(D % 16 == 0 && (D / 8) % 2 == 0, "head_dim: whole k-steps, n8 tiles in pairs");
+  static_assert(!FP8 || EXACT, "fp8 pools: head dims 64 / 128 / 256");
   constexpr int TENSOR_BYTES = kExtBN * RS;
   constexpr int STAGE_BYTES = 2 * TENSOR_BYTES;
   constexpr int NT = kExtBN / 8;             // n8 tiles of S per stage
@@ -179,10 +183,13 @@ __global__ void __launch_bounds__(kExtThreads, 1) extend_kernel(const ExtendPara
       nslot[i] = s;
     }
   };
+  // (ragged loader only) this thread copies row ld_row + i * RPP of a stage
+  auto ld_active = [&](int i) { return EXACT || (ld_row < RPP && ld_row + i * RPP < kExtBN); };
   auto issue = [&](int stage) {
     const uint32_t dst = stage0 + stage * STAGE_BYTES + ld_row * RS + RAW_OFF + ld_chunk * 16;
 #pragma unroll
     for (int i = 0; i < PASSES; ++i) {
+      if (!ld_active(i)) continue;
       const bool ok = nslot[i] >= 0;
       const int64_t s = ok ? nslot[i] : 0;
       cp_async16_zfill(dst + i * RPP * RS, k_head + s * p.k_slot_bytes, ok);
@@ -280,12 +287,13 @@ __global__ void __launch_bounds__(kExtThreads, 1) extend_kernel(const ExtendPara
       s[nt][0] = s[nt][1] = s[nt][2] = s[nt][3] = 0.f;
       const uint32_t ka = sbase + k_lane + nt * 8 * RS;
 #pragma unroll
-      for (int k2 = 0; k2 < KSTEPS / 2; ++k2) {
+      for (int k2 = 0; k2 < (KSTEPS + 1) / 2; ++k2) {
         uint32_t kf[4];
-        ldsm_x4(ka + k2 * 64, kf);
+        ldsm_x4(ka + k2 * 64, kf);   // (head_dim 80: the last load's upper two matrices read the row pad; unused)
         mma16816<HALF>(s[nt], qf[2 * k2][0], qf[2 * k2][2], qf[2 * k2][1], qf[2 * k2][3], kf[0], kf[1]);
-        mma16816<HALF>(s[nt], qf[2 * k2 + 1][0], qf[2 * k2 + 1][2], qf[2 * k2 + 1][1], qf[2 * k2 + 1][3],
-                       kf[2], kf[3]);
+        if (2 * k2 + 1 < KSTEPS)
+          mma16816<HALF>(s[nt], qf[2 * k2 + 1][0], qf[2 * k2 + 1][2], qf[2 * k2 + 1][1], qf[2 * k2 + 1][3],
+                         kf[2], kf[3]);
       }
     }
     if constexpr (cap) {

@@ -112,6 +112,12 @@ SHAPES = [
     ("many_short", 8, 2, 64, 1, tuple(range(0, 24)), tuple(1 + (i * 7) % 13 for i in range(24))),
     ("gemma_d256", 8, 4, 256, 1, (0, 33, 300), (130, 64, 1)),         # head_dim 256: the mma.sync kernel
     ("gemma_d256_gqa8", 16, 2, 256, 16, (100, 0), (257, 70)),
+    # head dims 80 / 96 (the decode kernel takes them too; test/srt/test_triton_attention_kernels.py:283-291 lists
+    # D = 80): 10 / 12 chunks per pool row, ragged loader passes, odd k-step count at 80
+    ("phi_d96_gqa3", 12, 4, 96, 1, (0, 33, 300), (130, 64, 1)),
+    ("phi_d96_mha_long", 4, 4, 96, 16, (700, 0), (257, 129)),
+    ("d80_gqa4", 16, 4, 80, 1, (0, 65, 1500), (129, 64, 3)),
+    ("d80_mha_tile_edges", 2, 2, 80, 1, (0, 0, 63, 64, 65), (64, 65, 1, 127, 128)),
 ]
 
 
@@ -119,6 +125,15 @@ SHAPES = [
 def test_extend_shapes(shape):
     name, hq, hkv, d, page, pl, el = shape
     _run(synth.Config(name, len(pl), 0, hq, hkv, d, page_size=page, seed=101), pl, el)
+
+
+@pytest.mark.parametrize("d", [80, 96])
+def test_extend_d80_d96_options(d):
+    """head dims 80 / 96 through the options of the path: logit cap, sliding window, non-causal, f16."""
+    _run(synth.Config(f"d{d}_cap", 2, 0, 8, 2, d, seed=131), (100, 0), (70, 129), logit_cap=30.0)
+    _run(synth.Config(f"d{d}_win", 2, 0, 8, 4, d, seed=132), (300, 20), (64, 90), window=64)
+    _run(synth.Config(f"d{d}_noncausal_f16", 2, 0, 4, 4, d, kv_dtype="f16", q_dtype="f16", seed=133), (10, 0), (33, 65),
+         causal=False)
 
 
 def test_extend_f16_and_int32_indices():
