@@ -27,25 +27,40 @@ cudaError_t launch_extend(const ExtendParams& p, int d, dim3 grid, cudaStream_t 
   return cudaGetLastError();
 }
 
+// The general kernel runs one thread per row (WIDE, 16 warps); B200ATTN_TC_LAYOUT=two picks the older
+// two-threads-per-row instantiation (24 warps) for A/B runs and the tests.  The small-q mode always has two.
+static bool tc_wide() {
+  static const bool wide = [] {
+    const char* e = std::getenv("B200ATTN_TC_LAYOUT");
+    return !(e && e[0] == 't');
+  }();
+  return wide;
+}
+
 template <typename QT, bool FP8>
 cudaError_t launch_extend_tc(const ExtendParams& p, int d, dim3 grid, bool small_q, cudaStream_t stream) {
   void (*fn)(const ExtendParams);
+  const bool wide = !small_q && !FP8 && tc_wide();   // (fp8 pools: measured a shade slower, P2f 775 against 789 TFLOP/s)
+#define B200_TC_PICK(DD, F8, CP)                                                                      \
+  (small_q ? extend_tc_kernel<QT, DD, F8, true, CP, false>                                            \
+           : (wide ? extend_tc_kernel<QT, DD, F8, false, CP, true> : extend_tc_kernel<QT, DD, F8, false, CP, false>))
   if constexpr (!FP8) {
     if (d == 64) {  // head_dim 64: 16-bit pools without a logit cap (the caller checked)
-      fn = small_q ? extend_tc_kernel<QT, 64, false, true, false> : extend_tc_kernel<QT, 64, false, false, false>;
+      fn = B200_TC_PICK(64, false, false);
     } else if (p.logit_cap > 0.f) {
-      fn = small_q ? extend_tc_kernel<QT, 128, false, true, true> : extend_tc_kernel<QT, 128, false, false, true>;
+      fn = B200_TC_PICK(128, false, true);
     } else {
-      fn = small_q ? extend_tc_kernel<QT, 128, false, true, false> : extend_tc_kernel<QT, 128, false, false, false>;
+      fn = B200_TC_PICK(128, false, false);
     }
   } else if (p.logit_cap > 0.f) {
-    fn = small_q ? extend_tc_kernel<QT, 128, true, true, true> : extend_tc_kernel<QT, 128, true, false, true>;
+    fn = B200_TC_PICK(128, true, true);
   } else {
-    fn = small_q ? extend_tc_kernel<QT, 128, true, true, false> : extend_tc_kernel<QT, 128, true, false, false>;
+    fn = B200_TC_PICK(128, true, false);
   }
+#undef B200_TC_PICK
   cudaError_t e = cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, kTcSmemBytes);
   if (e != cudaSuccess) return e;
-  fn<<<grid, kTcLaunchThreads, kTcSmemBytes, stream>>>(p);
+  fn<<<grid, wide ? kTcWideThreads : kTcLaunchThreads, kTcSmemBytes, stream>>>(p);
   return cudaGetLastError();
 }
 

@@ -72,6 +72,7 @@ constexpr int kTcSoftmaxRegs = kTcRegs[0], kTcLoaderRegs = kTcRegs[1], kTcMmaReg
 // sub-partition).  The general kernel is launched with three idle warps (21-23) so that EVERY sub-partition holds
 // 6 x 80 = 480: 4 softmax + 1 loader + the MMA warp or an idle one (24 registers).
 constexpr int kTcLaunchThreads = 24 * 32;
+constexpr int kTcWideThreads = 16 * 32;   // WIDE: 8 softmax + 4 loader + 1 MMA + 3 idle warps, 128 registers at launch
 static_assert(4 * kTcSoftmaxRegs + kTcLoaderRegs + kTcMmaRegs <= 480, "registers of sub-partition 0");
 
 // ---- tcgen05 wrappers ----
@@ -202,8 +203,18 @@ __device__ __forceinline__ void setmaxnreg_dec() {
 // MUFU ops per element on a loop that is issue-bound -- although no Llama-class model sets a cap.
 // D: head_dim 128 or 64.  64 keeps the 128-wide geometry (ring slots, O columns) and uses its first slab /
 // first 64 O columns: rows are one 128-byte swizzle atom wide, Q.K^T takes 4 k-steps, P.V has N = 64.
-template <typename QT, int D, bool FP8, bool ALT, bool CAP>
-__global__ void __launch_bounds__(kTcLaunchThreads, 1) extend_tc_kernel(const ExtendParams p) {
+// WIDE (general kernel only): ONE thread per row -- 8 softmax warps (warp w: sub-tile w / 4, TMEM lane quarter w & 3)
+// on 208 registers each read the whole 128-column S row in one burst of four loads, so there is no row-max exchange
+// between warps, half as many warps have to arrive before P is published and only two softmax warps share a
+// sub-partition's MUFU / issue slots.  16 warps are launched (8 softmax, 4 loaders, MMA, 3 idle) with 128 registers
+// each; setmaxnreg turns that into 208 / 64 / 32 / 24 (2 x 208 + 64 + 32 = 512 on the fullest sub-partition).
+template <typename QT, int D, bool FP8, bool ALT, bool CAP, bool WIDE = false>
+__global__ void __launch_bounds__(WIDE ? kTcWideThreads : kTcLaunchThreads, 1) extend_tc_kernel(const ExtendParams p) {
+  static_assert(!(WIDE && ALT), "the small-q mode keeps two threads per row");
+  constexpr int kTcSoftmaxWarps = WIDE ? 8 : b200attn::kTcSoftmaxWarps;   // (shadow the two-threads-per-row constants)
+  constexpr int kTcLoaderWarp0 = kTcSoftmaxWarps;
+  constexpr int kTcMmaWarp = kTcLoaderWarp0 + 4;
+  constexpr int kTcSoftmaxRegs = WIDE ? 208 : b200attn::kTcSoftmaxRegs;
   static_assert(D == 128 || (D == 64 && !FP8), "head_dim 128, or 64 over a 16-bit pool");
   constexpr bool NARROW = FP8 || D == 64;  // a pool row (one head) is 128 bytes: 8 chunks, 8 rows per loader thread
   constexpr int OH = D / 2;                // O columns per thread (two threads per row)
@@ -234,7 +245,7 @@ __global__ void __launch_bounds__(kTcLaunchThreads, 1) extend_tc_kernel(const Ex
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int b = blockIdx.z, h = blockIdx.y;
 #ifdef B200ATTN_TC_TRACE
-  long long* tr = (blockIdx.x == 0 && blockIdx.y == 0 && blockIdx.z == 0 && ((threadIdx.x & 255) == 0 || threadIdx.x == kTcLoaderWarp0 * 32 || threadIdx.x == kTcMmaWarp * 32))
+  long long* tr = (blockIdx.x == 0 && blockIdx.y == 0 && blockIdx.z == 0 && (((threadIdx.x & (WIDE ? 127 : 255)) == 0 && warp < kTcSoftmaxWarps) || threadIdx.x == kTcLoaderWarp0 * 32 || threadIdx.x == kTcMmaWarp * 32))
                       ? reinterpret_cast<long long*>(p.lse) : nullptr;
 #endif
 
@@ -295,8 +306,8 @@ __global__ void __launch_bounds__(kTcLaunchThreads, 1) extend_tc_kernel(const Ex
     mbar_init(bar_q_full, 128);
     for (int i = 0; i < 2; ++i) {
       mbar_init(bar_s_full + 8 * i, 1);
-      mbar_init(bar_p_full + 8 * i, 256);
-      mbar_init(bar_p_half + 8 * i, 256);
+      mbar_init(bar_p_full + 8 * i, WIDE ? 128 : 256);
+      mbar_init(bar_p_half + 8 * i, WIDE ? 128 : 256);
     }
     mbar_init(bar_o_full, 1);
     fence_barrier_init();
@@ -316,6 +327,166 @@ __global__ void __launch_bounds__(kTcLaunchThreads, 1) extend_tc_kernel(const Ex
     // (registers: the launch gives every warp 80 -- one sub-partition holds 6 of the 21 warps -- the loaders and
     //  the MMA warp hand back what they do not need and the softmax warps take it: 4 x 96 + 64 + 32 = 480)
     setmaxnreg_inc<kTcSoftmaxRegs>();
+    if constexpr (WIDE) {
+    // ---------- one thread per row ----------
+    const int sub = warp >> 2;
+    if (sub < nsub) {
+      const int r = (warp & 3) * 32 + lane;
+      const int R = sub * kTcBM + r;
+      const int itok = tok0 + (R >> p.gp_shift);
+      const int hd = R & ((1 << p.gp_shift) - 1);
+      const bool rv = hd < p.group && itok < Le;
+      const int i_min_sub = tok0 + ((sub * kTcBM) >> p.gp_shift);
+      const uint32_t lane_off = static_cast<uint32_t>((warp & 3) * 32) << 16;
+      const uint32_t tS = tmem + lane_off + sub * kTcBN;                 // this row's 128 S columns
+      const uint32_t tO = tmem + lane_off + 2 * kTcBN + sub * kTcD;      // and its D O columns
+      constexpr bool cap = CAP;
+      const float c = cap ? kLog2e : p.scale_log2;
+      const float cap_pre = cap ? p.sm_scale / p.logit_cap : 0.f;
+      const int64_t mask_row_len = static_cast<int64_t>(Lp) + Le;
+      const uint8_t* mrow = nullptr;
+      if (use_mask) {
+        const int64_t ms = p.mask64 ? static_cast<const int64_t*>(p.mask_indptr)[b]
+                                    : static_cast<const int32_t*>(p.mask_indptr)[b];
+        mrow = p.custom_mask + ms + (rv ? itok : 0) * mask_row_len;
+      }
+      float m = -CUDART_INF_F, l = 0.f;
+      for (int n = 0; n < N; ++n) {
+        mbar_wait_wd(bar_s_full + 8 * sub, n & 1);
+        tc_fence_after();
+        TC_TR(sub * 3, n);
+        const int j0 = n * kTcBN, j_end = j0 + kTcBN;
+        const bool need_mask = j_end > Ltot || (p.window > 0 && j0 < Lp) ||
+                               (use_mask && (!p.skip_prefix_mask || j_end > Lp)) ||
+                               (!use_mask && p.causal && j_end - 1 - Lp > i_min_sub);
+        auto row_body = [&](auto masked_tag) {
+          constexpr bool MASKED = decltype(masked_tag)::value;
+          float s[128];
+          tmem_ld32<0>(tS, s);
+          tmem_ld32<32>(tS + 32, s);
+          tmem_ld32<64>(tS + 64, s);
+          tmem_ld32<96>(tS + 96, s);
+          tmem_wait_ld();
+          if constexpr (cap) {
+#pragma unroll
+            for (int j = 0; j < 128; ++j) s[j] = p.logit_cap * tanhf(s[j] * cap_pre);
+          }
+          if constexpr (MASKED) {
+            // one visible range [lo, lo + span) per row (window front, causal / tile end back) plus the custom-mask
+            // bytes from mask_from on: see the two-threads-per-row body below
+            const int hi = !rv ? 0 : ((p.causal && !use_mask) ? min(Ltot, Lp + itok + 1) : Ltot);
+            const int lo = p.window > 0 ? min(max(itok - p.window, 0), Lp) : 0;
+            const unsigned span = hi > lo ? static_cast<unsigned>(hi - lo) : 0u;
+            const int mask_from = !use_mask ? 0x7fffffff : (p.skip_prefix_mask ? Lp : 0);
+#pragma unroll
+            for (int jj = 0; jj < 128; ++jj)
+              s[jj] = static_cast<unsigned>(j0 + jj - lo) < span ? s[jj] : -CUDART_INF_F;
+            if (j0 + 128 > mask_from) {
+#pragma unroll
+              for (int jj = 0; jj < 128; ++jj) {
+                const int j = j0 + jj;
+                if (j >= mask_from && j < hi && mrow[j] == 0) s[jj] = -CUDART_INF_F;
+              }
+            }
+          }
+          float mx0 = -CUDART_INF_F, mx1 = -CUDART_INF_F, mx2 = -CUDART_INF_F, mx3 = -CUDART_INF_F;
+#pragma unroll
+          for (int j = 0; j < 128; j += 4) {
+            mx0 = fmaxf(mx0, s[j]);
+            mx1 = fmaxf(mx1, s[j + 1]);
+            mx2 = fmaxf(mx2, s[j + 2]);
+            mx3 = fmaxf(mx3, s[j + 3]);
+          }
+          TC_TR(sub * 3 + 1, n);
+          const float mx = fmaxf(fmaxf(mx0, mx1), fmaxf(mx2, mx3));
+          // lazy rescale: keep the stale max while the new one is within 2^8 of it (p stays <= 256)
+          const bool grow = mx > m && (m == -CUDART_INF_F || (mx - m) * c > kTcRescaleLog2);
+          if (__any_sync(0xffffffffu, grow)) {
+            float corr = 1.f;
+            if (grow) {
+              corr = fast_exp2((m - mx) * c);  // m = -inf -> 0
+              m = mx;
+              l *= corr;
+            }
+            if (n > 0) {
+              // this sub-tile's previous P.V has completed: its commit precedes the one that signalled s_full
+#pragma unroll
+              for (int cc = 0; cc < D; cc += 16) {   // 16 columns at a time: s[128] is live
+                float o[16];
+                tmem_ld16(tO + cc, o);
+                tmem_wait_ld();
+                uint32_t ou[16];
+#pragma unroll
+                for (int j = 0; j < 16; ++j) ou[j] = __float_as_uint(o[j] * corr);
+                tmem_st16(tO + cc, ou);
+              }
+            }
+          }
+          const float mc = (m == -CUDART_INF_F ? 0.f : m) * c;
+          float sum0 = 0.f, sum1 = 0.f;
+#pragma unroll
+          for (int cc = 0; cc < 128; cc += 32) {
+            uint32_t pk[16];
+#pragma unroll
+            for (int j = 0; j < 32; j += 2) {
+              const float p0 = fast_exp2(fmaf(s[cc + j], c, -mc));
+              const float p1 = fast_exp2(fmaf(s[cc + j + 1], c, -mc));
+              sum0 += p0;
+              sum1 += p1;
+              pk[j >> 1] = pack2<HALF>(p0, p1);
+            }
+            // packed P of tokens cc .. cc + 31 -> columns cc / 2 .. of the row's own S tile (already consumed)
+            tmem_st16(tS + (cc >> 1), pk);
+            if (cc == 32) {
+              // the first 64 tokens' P is in TMEM: the MMA warp runs their four P.V k-steps under the other 64 exps
+              tmem_wait_st();
+              tc_fence_before();
+              mbar_arrive(bar_p_half + 8 * sub);
+            }
+          }
+          l += sum0 + sum1;
+          tmem_wait_st();
+          tc_fence_before();
+          mbar_arrive(bar_p_full + 8 * sub);
+          TC_TR(sub * 3 + 2, n);
+        };
+        if (need_mask) row_body(std::true_type{});
+        else row_body(std::false_type{});
+      }
+      // ---- epilogue: the row's D columns of O / l -> global ----
+      const float mlog2 = (m == -CUDART_INF_F ? 0.f : m) * c;
+      mbar_wait_wd(bar_o_full, 0);
+      tc_fence_after();
+      TC_TR(13, 250);  // epilogue: O complete
+      const float inv = l > 0.f ? p.v_scale / l : 0.f;
+      QT* orow = reinterpret_cast<QT*>(p.o) + static_cast<int64_t>(q0 + (rv ? itok : 0)) * p.o_st +
+                 static_cast<int64_t>(h * p.group + (rv ? hd : 0)) * p.o_sh;
+#pragma unroll
+      for (int cc = 0; cc < D; cc += 32) {
+        float o[32];
+        tmem_ld32<0>(tO + cc, o);
+        tmem_wait_ld();
+        if (rv) {
+#pragma unroll
+          for (int j = 0; j < 32; j += 8) {
+            uint4 v;
+            v.x = pack2<OUT_HALF>(o[j] * inv, o[j + 1] * inv);
+            v.y = pack2<OUT_HALF>(o[j + 2] * inv, o[j + 3] * inv);
+            v.z = pack2<OUT_HALF>(o[j + 4] * inv, o[j + 5] * inv);
+            v.w = pack2<OUT_HALF>(o[j + 6] * inv, o[j + 7] * inv);
+            *reinterpret_cast<uint4*>(orow + cc + j) = v;
+          }
+        }
+      }
+#ifndef B200ATTN_TC_TRACE
+      if (rv && p.lse)
+        p.lse[static_cast<int64_t>(q0 + itok) * p.hq + h * p.group + hd] =
+            l > 0.f ? mlog2 * kLn2 + logf(l) : -CUDART_INF_F;
+#endif
+      TC_TR(13, 251);  // epilogue: outputs stored
+      tc_fence_before();
+    }
+    } else {
     // Two threads per row: warp w serves sub-tile w / 8, column half (w / 4) & 1, TMEM lane quarter w & 3
     // (a warp reaches only the 32 lanes of quarter warp_id % 4).  The halves exchange their row max
     // through shared memory (one named barrier per tile) and their row sum once at the end.
@@ -653,6 +824,7 @@ __global__ void __launch_bounds__(kTcLaunchThreads, 1) extend_tc_kernel(const Ex
       TC_TR(13, 251);  // epilogue: outputs stored
       tc_fence_before();
     }
+    }  // !WIDE
   } else {
   if (warp < kTcMmaWarp) {
     // =============================== loaders (4 warps) ===============================
@@ -843,8 +1015,9 @@ __global__ void __launch_bounds__(kTcLaunchThreads, 1) extend_tc_kernel(const Ex
         const uint32_t d = tmem + 2 * kTcBN + sub * kTcD, a = tmem + sub * kTcBN;
 #pragma unroll
         for (int i = 0; i < 4; ++i) {
-          const int k = (i >> 1) * 4 + which * 2 + (i & 1);
-          umma_ts(d, a + k * 8 + (k >= 4 ? 32 : 0), v0 + k * (2048 >> 4), IDESC_PV, (acc || i > 0) ? 1u : 0u);
+          // WIDE: a row's packed P is contiguous (token t -> column t / 2), its first half is k-steps 0..3
+          const int k = WIDE ? which * 4 + i : (i >> 1) * 4 + which * 2 + (i & 1);
+          umma_ts(d, a + k * 8 + ((!WIDE && k >= 4) ? 32 : 0), v0 + k * (2048 >> 4), IDESC_PV, (acc || i > 0) ? 1u : 0u);
         }
       };
       auto issue_pv_tile = [&](int sub, int slot, int n) {
