@@ -63,6 +63,11 @@ constexpr bool kTcEarlyP = false;
 #else
 constexpr bool kTcEarlyP = kTcSinglePass;   // (the two-pass body publishes P once per tile)
 #endif
+#ifdef B200ATTN_TC_LOADER_WIDENS
+constexpr bool kTcWidenWarps = false;   // A/B build: the loaders widen fp8 stages themselves
+#else
+constexpr bool kTcWidenWarps = true;
+#endif
 #ifndef B200ATTN_TC_REGS
 #define B200ATTN_TC_REGS 96, 64, 32
 #endif
@@ -215,6 +220,11 @@ __global__ void __launch_bounds__(WIDE ? kTcWideThreads : kTcLaunchThreads, 1) e
   constexpr int kTcLoaderWarp0 = kTcSoftmaxWarps;
   constexpr int kTcMmaWarp = kTcLoaderWarp0 + 4;
   constexpr int kTcSoftmaxRegs = WIDE ? 208 : b200attn::kTcSoftmaxRegs;
+  // fp8 pools, small-q mode: warps 21-23 widen a landed stage to f16 in place, so the loaders only issue copies --
+  // with the widening in the loader loop (LDS -> cvt -> STS between two stages' cp.async) the loaders bound every
+  // fp8 shape (the verify shape ran at 2.3 TB/s against 5.2 on a 16-bit pool)
+  constexpr bool WIDEN = FP8 && ALT && kTcWidenWarps;   // (the general kernel is tensor-bound: there the extra hop costs more than it frees, P2f 790 -> 741 TFLOP/s)
+  constexpr int kTcLoaderRegs = WIDEN ? 48 : b200attn::kTcLoaderRegs;
   static_assert(D == 128 || (D == 64 && !FP8), "head_dim 128, or 64 over a 16-bit pool");
   constexpr bool NARROW = FP8 || D == 64;  // a pool row (one head) is 128 bytes: 8 chunks, 8 rows per loader thread
   constexpr int OH = D / 2;                // O columns per thread (two threads per row)
@@ -235,7 +245,8 @@ __global__ void __launch_bounds__(WIDE ? kTcWideThreads : kTcLaunchThreads, 1) e
   const uint32_t bar_p_full = bar_s_full + 16;            // [2]
   const uint32_t bar_o_full = bar_p_full + 16;
   const uint32_t bar_p_half = bar_o_full + 8;             // [2] general kernel: P of every thread's first 32 tokens is in TMEM
-  const uint32_t tmem_slot = bar_p_half + 16;
+  const uint32_t bar_raw_full = bar_p_half + 16;          // [kTcSlots] fp8: a stage's raw bytes have landed (loaders -> widening warps)
+  const uint32_t tmem_slot = bar_raw_full + 8 * kTcSlots;
   // row max [parity][sub][half][row] and row sum [sub][half][row] exchanged between the two threads of a row
   float* xch = reinterpret_cast<float*>(smem_raw + (bars + 1024 - smem_u32(smem_raw)));
   float* lxch = xch + 2 * 2 * 2 * kTcBM;
@@ -300,8 +311,9 @@ __global__ void __launch_bounds__(WIDE ? kTcWideThreads : kTcLaunchThreads, 1) e
 
   if (threadIdx.x == 0) {
     for (int s = 0; s < kTcSlots; ++s) {
-      mbar_init(bar_kv_full + 8 * s, 128);
+      mbar_init(bar_kv_full + 8 * s, WIDEN ? 96 : 128);   // fp8: the three widening warps publish a stage
       mbar_init(bar_kv_empty + 8 * s, 1);
+      mbar_init(bar_raw_full + 8 * s, 128);
     }
     mbar_init(bar_q_full, 128);
     for (int i = 0; i < 2; ++i) {
@@ -870,6 +882,16 @@ __global__ void __launch_bounds__(WIDE ? kTcWideThreads : kTcLaunchThreads, 1) e
     const uint8_t* v_head = p.v_pool + static_cast<int64_t>(h) * D * (FP8 ? 1 : 2) + (NARROW ? chunk8 : chunk) * 16;
     // stage st is complete for this thread: (fp8: widen it in place) and hand it to the MMA warp
     auto publish = [&](int st) {
+      if constexpr (WIDEN) {
+        // this thread's raw bytes of stage st (and, the first time, its part of Q) are in shared memory
+        if (!q_pub) {
+          fence_proxy_async();
+          mbar_arrive(bar_q_full);
+          q_pub = true;
+        }
+        mbar_arrive(bar_raw_full + 8 * (st % kTcSlots));
+        return;
+      }
       if constexpr (FP8) {
         const uint32_t slot0 = kv_base + (st % kTcSlots) * kTcSlotBytes;
         uint4 raw[8];
@@ -1108,6 +1130,45 @@ __global__ void __launch_bounds__(WIDE ? kTcWideThreads : kTcLaunchThreads, 1) e
       umma_commit(bar_o_full);
       TC_TR(13, 253);  // last MMA committed
       tc_fence_before();
+    }
+  } else if constexpr (WIDEN) {
+    // =============================== fp8 widening warps (21-23) ===============================
+    // A stage holds 128 raw rows of 128 fp8 bytes in its upper slab; row r widens to 256 bytes = row r of both
+    // slabs, in the swizzled layout.  Thread (row group rb, chunk c) turns 16 bytes into two 16-byte f16 chunks.
+    // The outputs of a row's chunks 4-7 land on that row's own raw bytes and nowhere else, and the row's eight
+    // chunks sit in eight adjacent lanes: a __syncwarp between the loads and the stores is all the ordering needed.
+    setmaxnreg_dec<48>();
+    const int wt = threadIdx.x - (kTcMmaWarp + 1) * 32;  // 0..95
+    const int chunk8 = wt & 7, rb = wt >> 3;             // rows rb + 12 i
+    const int S = 2 * N;
+    for (int st = 0; st < S; ++st) {
+      const int slot = st % kTcSlots;
+      mbar_wait_wd(bar_raw_full + 8 * slot, static_cast<uint32_t>(st / kTcSlots) & 1u);
+      const uint32_t slot0 = kv_base + slot * kTcSlotBytes;
+      const uint32_t dslab = slot0 + static_cast<uint32_t>(chunk8 >> 2) * kTcSlab;
+#pragma unroll
+      for (int i0 = 0; i0 < 12; i0 += 4) {
+        uint4 raw[4];
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+          const int row = rb + 12 * (i0 + i);
+          raw[i] = row < kTcBN ? lds128(slot0 + kTcSlab + row * 128 + chunk8 * 16) : make_uint4(0u, 0u, 0u, 0u);
+        }
+        __syncwarp();
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+          const int row = rb + 12 * (i0 + i);
+          if (row < kTcBN) {
+            uint4 lo, hi;
+            e4m3x16_to_f16(raw[i], lo, hi, p.e5m2 != 0);
+            const uint32_t rowa = dslab + row * 128;
+            sts128(rowa + ((((2 * chunk8) & 7) ^ (row & 7)) << 4), lo);
+            sts128(rowa + ((((2 * chunk8 + 1) & 7) ^ (row & 7)) << 4), hi);
+          }
+        }
+      }
+      fence_proxy_async();
+      mbar_arrive(bar_kv_full + 8 * slot);
     }
   } else {
     setmaxnreg_dec<24>();   // warps 21-23 only lend their registers
