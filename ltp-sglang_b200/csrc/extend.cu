@@ -78,7 +78,7 @@ cudaError_t launch_extend_tc_smallq(const ExtendParams& p, int d, int items, cud
   cudaError_t e = cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, kSqSmemBytes);
   if (e != cudaSuccess) return e;
   const int sms = sm_count();
-  fn<<<items < sms ? items : sms, kTcThreads, kSqSmemBytes, stream>>>(p);
+  fn<<<items < sms ? items : sms, FP8 ? kTcLaunchThreads : kTcThreads, kSqSmemBytes, stream>>>(p);
   return cudaGetLastError();
 }
 
@@ -276,12 +276,11 @@ extern "C" __attribute__((visibility("default"))) int b200attn_extend(const b200
     // every request has at most 128 (token, head) rows -- decode-like and TARGET_VERIFY batches: the small-q
     // kernel splits each CTA's KV range over its two accumulators instead of leaving one idle
     const bool small_q = (static_cast<int64_t>(a->max_extend_len) << p.gp_shift) <= kTcBM;
-    // auto: with the host's mean KV length, at most 2048 tokens -> persistent (either pool type: the one-shot
-    // kernel's fp8 stages are widened by their own warps since round 2 and win from ~2k tokens on: 397 against
-    // 487 us at 4096, 377 / 514 at 16384, 498 / 420 at 512); without the hint: fp8 pools -> persistent
-    const bool sq_persistent =
-        smallq_mode() == 1 ||
-        (smallq_mode() == 0 && (a->avg_kv_len_hint > 0 ? a->avg_kv_len_hint <= 2048 : fp8));
+    // auto: fp8 pools (with the widening warps the persistent kernel is at or ahead of the one-shot one at every
+    // prefix length: 389 / 397 us at 4096, 391 / 377 at 16384, 371 / 498 at 512), and 16-bit pools whose mean KV
+    // length the host gave as at most 2048 tokens
+    const bool sq_persistent = smallq_mode() == 1 ||
+                               (smallq_mode() == 0 && (fp8 || (a->avg_kv_len_hint > 0 && a->avg_kv_len_hint <= 2048)));
     if (small_q && sq_persistent) {
       const int items = a->batch * a->num_kv_heads;
       if (fp8)

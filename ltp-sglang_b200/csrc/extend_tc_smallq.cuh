@@ -29,8 +29,11 @@ namespace b200attn {
 constexpr int kSqBarBytes = 11264;  // mbarriers + row max / row sum / merge exchange + 4 slot-id buffers
 constexpr int kSqSmemBytes = kTcQBytes + kTcSlots * kTcSlotBytes + kSqBarBytes + 1024;
 
+// fp8 pools: launched with three more warps (21-23) that widen every landed stage to f16 in place, as in the one-shot
+// kernel (extend_tc_kernel.cuh, WIDEN) -- the loaders only issue copies.
 template <typename QT, int D, bool FP8, bool CAP>
-__global__ void __launch_bounds__(kTcThreads, 1) extend_tc_smallq_kernel(const ExtendParams p) {
+__global__ void __launch_bounds__(FP8 ? kTcLaunchThreads : kTcThreads, 1) extend_tc_smallq_kernel(const ExtendParams p) {
+  constexpr bool WIDEN = FP8 && kTcWidenWarps;
   static_assert(D == 128 || (D == 64 && !FP8), "head_dim 128, or 64 over a 16-bit pool");
   constexpr bool NARROW = FP8 || D == 64;
   constexpr int OH = D / 2;
@@ -52,7 +55,8 @@ __global__ void __launch_bounds__(kTcThreads, 1) extend_tc_smallq_kernel(const E
   const uint32_t bar_p_full = bar_s_full + 16;        // [2]
   const uint32_t bar_o_full = bar_p_full + 16;
   const uint32_t bar_o_empty = bar_o_full + 8;
-  const uint32_t tmem_slot = bar_o_empty + 8;
+  const uint32_t bar_raw_full = bar_o_empty + 8;      // [kTcSlots] fp8: raw bytes landed (loaders -> widening warps)
+  const uint32_t tmem_slot = bar_raw_full + 8 * kTcSlots;
   float* xch = reinterpret_cast<float*>(smem_raw + (bars + 1024 - smem_u32(smem_raw)));  // [parity][sub][half][row]
   float* lxch = xch + 2 * 2 * 2 * kTcBM;                                                   // [sub][half][row]
   int32_t* sid = reinterpret_cast<int32_t*>(lxch + 2 * 2 * kTcBM);                         // [4][kTcBN]
@@ -94,8 +98,9 @@ __global__ void __launch_bounds__(kTcThreads, 1) extend_tc_smallq_kernel(const E
 
   if (threadIdx.x == 0) {
     for (int s = 0; s < kTcSlots; ++s) {
-      mbar_init(bar_kv_full + 8 * s, 128);
+      mbar_init(bar_kv_full + 8 * s, WIDEN ? 96 : 128);
       mbar_init(bar_kv_empty + 8 * s, 1);
+      mbar_init(bar_raw_full + 8 * s, 128);
     }
     for (int i = 0; i < 2; ++i) {
       mbar_init(bar_q_full + 8 * i, 128);
@@ -340,6 +345,14 @@ __global__ void __launch_bounds__(kTcThreads, 1) extend_tc_smallq_kernel(const E
     // stage st of this thread is complete: (fp8: widen it in place,) hand it to the MMA warp; code bit 1 = the
     // stage is an item's first (its group also carries the item's Q), bit 0 = that item's Q buffer
     auto publish = [&](int st, uint32_t code) {
+      if constexpr (WIDEN) {
+        if (code & 2u) {
+          fence_proxy_async();
+          mbar_arrive(bar_q_full + 8 * (code & 1u));
+        }
+        mbar_arrive(bar_raw_full + 8 * (st % kTcSlots));
+        return;
+      }
       if constexpr (FP8) {
         const uint32_t slot0 = kv_base + (st % kTcSlots) * kTcSlotBytes;
         uint4 raw[8];
@@ -506,7 +519,7 @@ __global__ void __launch_bounds__(kTcThreads, 1) extend_tc_smallq_kernel(const E
     // drain: the last min(gst, kTcLag) stages
     cp_async_wait<0>();
     for (int st = (gst > kTcLag ? gst - kTcLag : 0); st < gst; ++st) publish(st, (hist >> (2 * (gst - 1 - st))) & 3u);
-  } else {
+  } else if (warp == kTcMmaWarp) {
     // =============================== MMA issuer (warp 20) ===============================
     const uint64_t dq = umma_desc_sw128(q_base, 16, 1024);
     const uint64_t dk = umma_desc_sw128(kv_base, 16, 1024);
@@ -586,6 +599,45 @@ __global__ void __launch_bounds__(kTcThreads, 1) extend_tc_smallq_kernel(const E
       ++k;
     }
     tc_fence_before();
+  } else if constexpr (WIDEN) {
+    // =============================== fp8 widening warps (21-23) ===============================
+    // (same mapping as extend_tc_kernel's: thread = (row group, 16-byte chunk), a row's eight chunks in eight
+    //  adjacent lanes, __syncwarp between a row's loads and its stores)
+    const int wt = threadIdx.x - (kTcMmaWarp + 1) * 32;  // 0..95
+    const int chunk8 = wt & 7, rb = wt >> 3;
+    int gst = 0;
+    for (int w = blockIdx.x; w < items; w += gridDim.x) {
+      const Geo g = geo(w);
+      for (int s2 = 0; s2 < 2 * g.N; ++s2, ++gst) {
+        const int slot = gst % kTcSlots;
+        mbar_wait_wd(bar_raw_full + 8 * slot, static_cast<uint32_t>(gst / kTcSlots) & 1u);
+        const uint32_t slot0 = kv_base + slot * kTcSlotBytes;
+        const uint32_t dslab = slot0 + static_cast<uint32_t>(chunk8 >> 2) * kTcSlab;
+#pragma unroll
+        for (int i0 = 0; i0 < 12; i0 += 4) {
+          uint4 raw[4];
+#pragma unroll
+          for (int i = 0; i < 4; ++i) {
+            const int row = rb + 12 * (i0 + i);
+            raw[i] = row < kTcBN ? lds128(slot0 + kTcSlab + row * 128 + chunk8 * 16) : make_uint4(0u, 0u, 0u, 0u);
+          }
+          __syncwarp();
+#pragma unroll
+          for (int i = 0; i < 4; ++i) {
+            const int row = rb + 12 * (i0 + i);
+            if (row < kTcBN) {
+              uint4 lo, hi;
+              e4m3x16_to_f16(raw[i], lo, hi, p.e5m2 != 0);
+              const uint32_t rowa = dslab + row * 128;
+              sts128(rowa + ((((2 * chunk8) & 7) ^ (row & 7)) << 4), lo);
+              sts128(rowa + ((((2 * chunk8 + 1) & 7) ^ (row & 7)) << 4), hi);
+            }
+          }
+        }
+        fence_proxy_async();
+        mbar_arrive(bar_kv_full + 8 * slot);
+      }
+    }
   }
   __syncthreads();
   if (warp == kTcMmaWarp) {
