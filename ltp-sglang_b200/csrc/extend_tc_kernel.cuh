@@ -58,6 +58,11 @@ constexpr bool kTcSinglePass = false;   // A/B build: the general kernel keeps t
 #else
 constexpr bool kTcSinglePass = true;
 #endif
+#ifdef B200ATTN_TC_ALT_TWO_PASS
+constexpr bool kTcSinglePassAlt = false;   // A/B build: the small-q (ALT) instantiation keeps the two-pass body
+#else
+constexpr bool kTcSinglePassAlt = true;
+#endif
 #ifdef B200ATTN_TC_NO_EARLY_P
 constexpr bool kTcEarlyP = false;
 #else
@@ -539,7 +544,14 @@ __global__ void __launch_bounds__(WIDE ? kTcWideThreads : kTcLaunchThreads, 1) e
         tc_fence_after();
         TC_TR(sub * 3, n);
         if (dead) {
-          named_bar_sync(1 + sub, 256);  // a sync, not an arrive: the warp must not run ahead into the epilogue's use
+          // a sync, not an arrive: the warp must not run ahead into the epilogue's use of the barrier.  (Single-pass
+          // body: the row max is exchanged on the pair's own barrier, and both warps of a pair are dead together.)
+          if constexpr (kTcSinglePass && kTcSinglePassAlt) {
+            named_bar_sync(6 + sub * 4 + (warp & 3), 64);
+            mbar_arrive(bar_p_half + 8 * sub);
+          } else {
+            named_bar_sync(1 + sub, 256);
+          }
           mbar_arrive(bar_p_full + 8 * sub);
           continue;
         }
@@ -759,7 +771,7 @@ __global__ void __launch_bounds__(WIDE ? kTcWideThreads : kTcLaunchThreads, 1) e
 #endif
           TC_TR(sub * 3 + 2, n);
         };
-        if constexpr (ALT || !kTcSinglePass) {
+        if constexpr ((ALT && !kTcSinglePassAlt) || !kTcSinglePass) {
           if (need_mask) tile_body(std::true_type{});
           else tile_body(std::false_type{});
         } else {
