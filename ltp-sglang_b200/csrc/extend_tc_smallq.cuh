@@ -358,7 +358,7 @@ __global__ void __launch_bounds__(FP8 ? kTcLaunchThreads : kTcThreads, 1) extend
         uint4 raw[8];
 #pragma unroll
         for (int i = 0; i < 8; ++i) raw[i] = lds128(slot0 + kTcSlab + (rb8 + 16 * i) * 128 + chunk8 * 16);
-        named_bar_sync(4, 128);
+        __syncwarp();  // a row's eight raw chunks sit in eight adjacent lanes and its outputs only overwrite that row: no block barrier
         const uint32_t dslab = slot0 + static_cast<uint32_t>(chunk8 >> 2) * kTcSlab;
 #pragma unroll
         for (int i = 0; i < 8; ++i) {
