@@ -225,6 +225,10 @@ __global__ void __launch_bounds__(WIDE ? kTcWideThreads : kTcLaunchThreads, 1) e
   constexpr int kTcLoaderWarp0 = kTcSoftmaxWarps;
   constexpr int kTcMmaWarp = kTcLoaderWarp0 + 4;
   constexpr int kTcSoftmaxRegs = WIDE ? 208 : b200attn::kTcSoftmaxRegs;
+  // cp.async groups in flight per loader thread: the small-q mode over a 16-bit pool streams (HBM-bound) and wants three
+  // 32 KB stages in flight per SM (verify shape 407 -> 389 us, prefix 16384: 393 -> 360 us = 5.96 TB/s); the fp8 and the
+  // tensor-bound instantiations lose with three (P2f 797 -> 709 TFLOP/s: a stage is published one iteration later)
+  constexpr int kTcLag = (ALT && !FP8) ? 3 : b200attn::kTcLag;
   // fp8 pools, small-q mode: warps 21-23 widen a landed stage to f16 in place, so the loaders only issue copies --
   // with the widening in the loader loop (LDS -> cvt -> STS between two stages' cp.async) the loaders bound every
   // fp8 shape (the verify shape ran at 2.3 TB/s against 5.2 on a 16-bit pool)
