@@ -278,9 +278,10 @@ extern "C" __attribute__((visibility("default"))) int b200attn_extend(const b200
     const bool small_q = (static_cast<int64_t>(a->max_extend_len) << p.gp_shift) <= kTcBM;
     // auto: fp8 pools (with the widening warps the persistent kernel is at or ahead of the one-shot one at every
     // prefix length: 389 / 397 us at 4096, 391 / 377 at 16384, 371 / 498 at 512), and 16-bit pools whose mean KV
-    // length the host gave as at most 2048 tokens
+    // length the host gave as at most 768 tokens (the one-shot kernel of round 2's second pass wins from ~1k on:
+    // 277 / 282 / 345 us against 277 / 305 / 385 at 1024 / 1536 / 2048; 360 against 324 at 512)
     const bool sq_persistent = smallq_mode() == 1 ||
-                               (smallq_mode() == 0 && (fp8 || (a->avg_kv_len_hint > 0 && a->avg_kv_len_hint <= 2048)));
+                               (smallq_mode() == 0 && (fp8 || (a->avg_kv_len_hint > 0 && a->avg_kv_len_hint <= 768)));
     if (small_q && sq_persistent) {
       const int items = a->batch * a->num_kv_heads;
       if (fp8)
