@@ -138,6 +138,20 @@ def test_argument_errors_need_no_gpu():
     d = capi.DecodeArgs()
     d.batch = -1
     assert lib.b200attn_decode(C.byref(d), None) == capi.E_INVALID
+    # the allocation-free decode entry point: its own checks come before any CUDA call too
+    assert lib.b200attn_decode_static_ws(None, None) == capi.E_INVALID
+    s = capi.DecodeArgs()
+    s.batch, s.num_q_heads, s.num_kv_heads, s.head_dim, s.v_head_dim = 4096, 64, 8, 128, 128
+    s.q_dtype = s.kv_dtype = capi.BF16
+    assert lib.b200attn_workspace_bytes(4096, 64, 8, 128, 128, capi.BF16) > capi.STATIC_WS_BYTES
+    assert lib.b200attn_decode_static_ws(C.byref(s), None) == capi.E_STATIC_LIMIT   # beyond the static array
+    assert "static workspace" in capi.strerror(capi.E_STATIC_LIMIT)
+    s.batch = 0
+    assert lib.b200attn_decode_static_ws(C.byref(s), None) == capi.OK               # empty batch is a no-op
+    s.batch, s.ws_bytes = 8, 64
+    assert lib.b200attn_decode_static_ws(C.byref(s), None) == capi.E_INVALID        # the library owns the workspace
+    s.ws_bytes, s.head_dim, s.v_head_dim = 0, 72, 72
+    assert lib.b200attn_decode_static_ws(C.byref(s), None) == capi.E_UNSUPPORTED
     assert capi.launch_count() == n0
     assert lib.b200attn_plan_bytes(128) > 0 and lib.b200attn_plan_bytes(-1) == 0
     assert lib.b200attn_workspace_bytes(128, 32, 8, 128, 128, capi.BF16) > 0
